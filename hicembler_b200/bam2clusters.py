@@ -1,0 +1,387 @@
+"""Drop-ins for the hot-path functions of the reference's ``bam2clusters.py`` -- same names,
+argument order, return types and error behaviour; the work runs in sm_100a kernels through the
+C ABI (``_lib`` / ``ops``).  numpy at the surface like the reference; every function also accepts /
+offers device-resident torch tensors so N x N data never has to cross PCIe.
+
+Differences forced by the environment (documented in DESIGN.md):
+  * ``bam`` entries are BAM paths (decoded by ``pairs.read_bam``; no samtools needed), SAM text
+    paths, PAIR_DTYPE arrays, or dicts {records, names[, tlen, ref_span]} holding numpy arrays or
+    CUDA tensors -- instead of paths handed to a ``samtools view`` subprocess (:108-117).
+  * ``threads`` is ignored (it already is in the reference's bam2arrays, :128); CUDA contexts are not
+    fork-safe, so nothing here uses multiprocessing.
+"""
+from __future__ import annotations
+
+import gzip
+import os
+import pickle
+import resource
+import sys
+from datetime import datetime
+
+import numpy as np
+import torch
+
+from . import ops
+from .FastaIndex import FastaIndex
+from .fastcluster import linkage, linkage_square
+from .pairs import PAIR_DTYPE, SKIP_FLAG, load_alignments
+from .sinkhorn_knopp import SinkhornKnopp
+
+
+def logger(message, log=sys.stdout):
+    """bam2clusters.py:68-71"""
+    memory = resource.getrusage(resource.RUSAGE_SELF).ru_maxrss / 1024
+    log.write("[%s] %s    [memory: %6i Mb]\n" % (datetime.ctime(datetime.now()), message, memory))
+
+
+# ---------------------------------------------------------------------------------------------
+# alignments
+# ---------------------------------------------------------------------------------------------
+class Alignments:
+    """Decoded alignment records of one BAM, resident on the GPU."""
+
+    def __init__(self, records, names, tlen=None, ref_span=None):
+        self.records, self.names, self.tlen, self.ref_span = records, list(names), tlen, ref_span
+        self.name2id = {n: i for i, n in enumerate(self.names)}
+
+    @classmethod
+    def load(cls, src, names=None, device="cuda"):
+        if isinstance(src, Alignments):
+            return src
+        rec, tlen, span, nm = load_alignments(src) if not isinstance(src, torch.Tensor) else (src, None, None, None)
+        if isinstance(src, dict):
+            nm = src.get("names", nm)
+        nm = nm or names
+        if nm is None:
+            raise ValueError("contig names of the alignments are unknown: pass a BAM/SAM path or a "
+                             "dict with 'names'")
+        as_dev = lambda a: None if a is None else (a if isinstance(a, torch.Tensor)
+                                                   else torch.from_numpy(np.ascontiguousarray(a))).to(device)
+        return cls(ops.to_device_records(rec, device), nm, as_dev(tlen), as_dev(span))
+
+    def offsets(self, chr2window):
+        """chr2window (name -> first window) as an int32 table indexed by refID, -1 = absent."""
+        off = np.full(len(self.names), -1, dtype=np.int32)
+        for c, w in chr2window.items():
+            i = self.name2id.get(c)
+            if i is not None:
+                off[i] = w
+        return torch.from_numpy(off).to(self.records.device)
+
+    def region_mask(self, regions):
+        if not len(regions):
+            return None
+        m = np.zeros(len(self.names), dtype=np.uint8)
+        for r in regions:
+            if ":" in r:
+                raise NotImplementedError("bam2arrays supports whole-contig regions only")
+            i = self.name2id.get(r)
+            if i is not None:
+                m[i] = 1
+        return torch.from_numpy(m).to(self.records.device)
+
+
+# ---------------------------------------------------------------------------------------------
+# window arithmetic / tables (host side, tiny)
+# ---------------------------------------------------------------------------------------------
+def get_window(chrom, start, length, windowSize, chr2window):
+    """bam2clusters.py:119-126 (Python-2 integer division)."""
+    end = start + length
+    pos = int(start + round((end - start) // 2))
+    return pos // windowSize + chr2window[chrom]
+
+
+def contigs2windows(fasta, minSize=2000, verbose=0, genomeFrac=0.95, contigs=[]):
+    """bam2clusters.py:73-106: one window per contig >= max(minSize, N95)."""
+    contigs = set(contigs)
+    windows, skipped, chr2window = [], [], {}
+    faidx = fasta if isinstance(fasta, FastaIndex) else FastaIndex(fasta)
+    contig2size = {c: faidx.id2stats[c][0] for c in faidx}
+    n90 = faidx.get_N_and_L(genomeFrac)
+    if n90 > minSize:
+        minSize = n90
+        if verbose:
+            logger(" updated --minSize to N%s: %s" % (int(100 * genomeFrac), minSize))
+    for c in faidx:
+        size = contig2size[c]
+        if size < minSize:
+            skipped.append(size)
+            continue
+        elif contigs and c not in contigs:
+            continue
+        chr2window[c] = len(windows)
+        windows.append((c, 0, size))
+    if verbose:
+        logger(' %s bases in %s contigs divided in %s windows. ' % (faidx.genomeSize, len(faidx), len(windows)))
+        if skipped:
+            logger('  %s bases in %s contigs skipped.' % (sum(skipped), len(skipped)))
+    return minSize, windows, chr2window, contig2size
+
+
+# ---------------------------------------------------------------------------------------------
+# K1: binning
+# ---------------------------------------------------------------------------------------------
+def bam2counts(windows, windowSize, chr2window, bam, mapq, upto=0, regions=[], names=None):
+    """Device fast path of bam2arrays: list of u32 count matrices (CUDA int32 tensors, FULL
+    orientation: row = window of read 1) plus per-window-size stats.  ``ops.fold_counts`` turns
+    them into the reference's arrays or straight into the symmetrised matrix."""
+    nws = len(windowSize)
+    sizes = [len(w) for w in windows]
+    counts, stats = [None] * nws, [None] * nws
+    i = 1  # the reference's running line index (:132,139): shared by all BAMs
+    for _bam in bam:
+        al = Alignments.load(_bam, names)
+        rmask = al.region_mask(regions)
+        n_pairs = al.records.shape[0]
+        if upto:
+            # enumerate(proc.stdout, i) restarts at the last index used; a line with index > upto breaks
+            budget = max(0, upto - i + 1)
+            n_eff, lines = ops.upto_cutoff(al.records, mapq, budget, rmask) if budget else (0, 0)
+            more = n_eff < n_pairs and ops.upto_cutoff(al.records[n_eff:], mapq, 1, rmask)[1] > 0
+            if more:
+                i = max(i, upto + 1) if budget else i
+            elif lines:
+                i = i + lines - 1
+            n_pairs = n_eff
+        member = al.offsets(chr2window[0])
+        for ii in range(nws):
+            off = member if ii == 0 else al.offsets(chr2window[ii])
+            mode = 2 if counts[ii] is not None else 0
+            counts[ii], st = ops.bin_pairs(al.records, off, windowSize[ii], sizes[ii], mapq, member=member,
+                                           region_mask=rmask, n_pairs=n_pairs, out=counts[ii], mode=mode,
+                                           return_stats=True)
+            stats[ii] = st if stats[ii] is None else {k: (stats[ii][k] + v if isinstance(v, int) and not isinstance(v, bool) else v)
+                                                     for k, v in st.items()}
+    for ii in range(nws):
+        if counts[ii] is None:
+            counts[ii] = torch.zeros((sizes[ii], sizes[ii]), dtype=torch.int32, device="cuda")
+    return counts, stats
+
+
+def bam2arrays(windows, windowSize, chr2window, bam, mapq, upto=0, regions=[], verbose=1, threads=1,
+               device_out=False, names=None):
+    """Return contact matrices based on BAM -- bam2clusters.py:128-166.
+
+    One float32 (N_ii, N_ii) upper-triangular (incl. diagonal) array per window size.  Raises
+    IndexError / KeyError where the reference's loop would (:155,161)."""
+    counts, stats = bam2counts(windows, windowSize, chr2window, bam, mapq, upto, regions, names)
+    arrays = []
+    for cnt in counts:
+        a, _ = ops.fold_counts(cnt, "upper", inplace=True)
+        arrays.append(a if device_out else a.cpu().numpy())
+    if verbose:
+        logger(" %s alignments parsed" % (stats[0]["lines"] if stats and stats[0] else 0))
+    return arrays
+
+
+def bam2array(windows, contig2size, chr2window, bam, mapq=10, upto=0, regions=[], minSize=2000, threads=4,
+              verbose=1, nth=5, names=None, device_out=False):
+    """Return contig-level contact matrix and insert sizes -- bam2clusters.py:208-246.
+
+    Only alignments overlapping the sampled regions (s+1, s+minSize), s = 0, nth*minSize, ... of the
+    clustered contigs are used (:222); the result is the float64, transposed, size-normalised matrix
+    of :244 and ``c2dists`` = {contig: [abs(TLEN) or -1]} (:183-189).  ``upto`` only stops the
+    reference between (unordered) worker results (:239-240); it is not applied here."""
+    K = len(windows)
+    if not regions:
+        regions = list(chr2window.keys())
+    counts = None
+    c2dists = {}
+    lines = 0
+    region_set = set(regions)
+    for _bam in bam:
+        al = Alignments.load(_bam, names)
+        dev = al.records.device
+        member = al.offsets({c: w for c, w in chr2window.items()})
+        # samtools is queried for the regions of the worker's contigs only
+        rmember = al.offsets({c: chr2window[c] for c in chr2window if c in region_set})
+        csize = np.zeros(len(al.names), dtype=np.int32)
+        for c, s in contig2size.items():
+            if c in al.name2id:
+                csize[al.name2id[c]] = s
+        keep, dist = ops.contig_region_filter(al.records, al.tlen, al.ref_span, torch.from_numpy(csize).to(dev),
+                                              rmember, minSize, nth, mapq)
+        if int(keep.max().item() if keep.numel() else 0) > 1:
+            raise NotImplementedError("alignment spanning several sampled regions")
+        sel = keep.bool()
+        kept = al.records[sel].contiguous()
+        lines += kept.shape[0]
+        counts = ops.bin_pairs(kept, member, None, K, 0, member=member, skip_flag=0, out=counts,
+                               mode=2 if counts is not None else 0)
+        ref = al.records[sel][:, 0].cpu().numpy()
+        dv = dist[sel].cpu().numpy()
+        order = np.argsort(ref, kind="stable")
+        ref, dv = ref[order], dv[order]
+        cut = np.flatnonzero(np.diff(ref)) + 1
+        for r, chunk in zip(ref[np.r_[0, cut]] if len(ref) else [], np.split(dv, cut)):
+            c2dists.setdefault(al.names[r], [])
+            c2dists[al.names[r]] += chunk.tolist()
+    for c in regions:
+        c2dists.setdefault(c, [])
+    if verbose:
+        logger(" %s alignments parsed" % lines)
+    sizes = np.array([len(range(0, contig2size[c] + 1 - minSize, nth * minSize)) for c, s, e in windows],
+                     dtype=np.int32)
+    if counts is None:
+        counts = torch.zeros((K, K), dtype=torch.int32, device="cuda")
+    out = torch.empty((K, K), dtype=torch.float64, device=counts.device)
+    from . import _lib
+    _lib.check(_lib.lib().hc_contig_normalize(ops._ptr(counts), K, ops._ptr(torch.from_numpy(sizes).to(counts.device)),
+                                              ops._ptr(out), ops._stream()))
+    return (out if device_out else out.cpu().numpy()), c2dists
+
+
+# ---------------------------------------------------------------------------------------------
+# K2-K5: normalisation
+# ---------------------------------------------------------------------------------------------
+def normalize(d, max_iter=1000, epsilon=0.00001):
+    """Return fully balanced matrix -- bam2clusters.py:36-49.
+
+    Like the reference it symmetrises ``d`` and adds the pseudo-count IN PLACE (:42-43), and returns
+    a new float64 array D1.(d/vmax).D2."""
+    sk = SinkhornKnopp(max_iter=max_iter, epsilon=epsilon)
+    if isinstance(d, torch.Tensor):
+        _, vmax = ops.symmetrize_(d, add=1.0)
+        return sk.fit_device(d, float(vmax.item()))
+    X = torch.from_numpy(d).cuda() if d.flags.c_contiguous else torch.from_numpy(np.ascontiguousarray(d)).cuda()
+    _, vmax = ops.symmetrize_(X, add=1.0)
+    d[...] = X.cpu().numpy()
+    return sk.fit_device(X, float(vmax.item())).cpu().numpy()
+
+
+def distance_func(x, a, b, maxv=float('inf')):
+    """Distance from normalised contact frequency -- bam2clusters.py:248-251."""
+    if isinstance(x, torch.Tensor):
+        return ops.transform(x, ops.KIND_POWER_RAW, a, b)
+    if isinstance(x, np.ndarray) and x.ndim > 0:
+        xt = torch.from_numpy(np.ascontiguousarray(x if x.dtype in (np.float32, np.float64)
+                                                   else x.astype(np.float64))).cuda()
+        return ops.transform(xt, ops.KIND_POWER_RAW, a, b).cpu().numpy()
+    return (1. / (a * x)) ** (1. / b)
+
+
+def contact_func(x, a, b):
+    """bam2clusters.py:253-255"""
+    return 1. / (a * x ** b)
+
+
+# ---------------------------------------------------------------------------------------------
+# K6-K7: tree
+# ---------------------------------------------------------------------------------------------
+class HCTree:
+    """What array2tree returns when ete3 is not installed: the linkage array, leaf names and the
+    Newick string the reference builds with sch.to_tree + getNewick (bam2clusters.py:360-371,386)."""
+
+    def __init__(self, Z, names):
+        self.Z, self.names = Z, list(names)
+        self._newick = None
+
+    def write(self):
+        if self._newick is None:
+            self._newick = newick_from_linkage(self.Z, self.names)
+        return self._newick
+
+    def get_leaf_names(self):
+        import re
+        return [m for m in re.findall(r"[(,]([^(),:;]+):", self.write())]
+
+
+def newick_from_linkage(Z, leaf_names):
+    """Iterative equivalent of ``getNewick(sch.to_tree(Z), "", tree.dist, names)``
+    (bam2clusters.py:360-371): the reference recursion overflows Python's stack on deep trees."""
+    n = Z.shape[0] + 1
+    if n == 1:
+        return "%s:%.2f;" % (leaf_names[0], 0.0)
+    left = Z[:, 0].astype(np.int64)
+    right = Z[:, 1].astype(np.int64)
+    dist = np.concatenate([np.zeros(n), Z[:, 2]])
+    root = 2 * n - 2
+    out = []
+    # emit tokens left-to-right: "(" right-subtree "," left-subtree ")" [":%.2f"]
+    stack = [("node", root, None)]
+    while stack:
+        kind, node, pdist = stack.pop()
+        if kind == "text":
+            out.append(node)
+        elif node < n:
+            out.append("%s:%.2f" % (leaf_names[node], pdist - dist[node]))
+        else:
+            k = node - n
+            close = ");" if pdist is None else "):%.2f" % (pdist - dist[node])
+            stack.append(("text", close, None))
+            stack.append(("node", int(left[k]), dist[node]))
+            stack.append(("text", ",", None))
+            stack.append(("node", int(right[k]), dist[node]))
+            out.append("(")
+    return "".join(out)
+
+
+def array2Z(d, method="ward", transform=None, return_stats=False):
+    """Linkage array of ``d[np.triu_indices(n,1)]`` (bam2clusters.py:385) for a numpy or CUDA matrix.
+    ``transform`` = None, ("power", a, b) for distance_func(x+1, a, b) or ("logmax", vmax)."""
+    X = d if isinstance(d, torch.Tensor) else torch.from_numpy(np.ascontiguousarray(d)).cuda()
+    if X.dtype not in (torch.float32, torch.float64):
+        X = X.double()
+    kind, p0, p1 = ops.KIND_IDENTITY, 0.0, 1.0
+    if transform is not None:
+        if transform[0] == "power":
+            kind, p0, p1 = ops.KIND_POWER, transform[1], transform[2]
+        elif transform[0] == "logmax":
+            kind, p0 = ops.KIND_LOGMAX, transform[1]
+        else:
+            raise ValueError(transform)
+    if X.shape[0] < 2:
+        return (np.empty((0, 4)), {}) if return_stats else np.empty((0, 4))
+    return linkage_square(X.contiguous(), method, kind, p0, p1, return_stats=return_stats)
+
+
+def array2tree(d, names, outbase="", method="ward"):
+    """Return tree representation for array -- bam2clusters.py:382-399 (PDF rendering left out:
+    no graphics stack)."""
+    Z = array2Z(d, method)
+    t = HCTree(Z, names)
+    try:
+        import ete3
+        t = ete3.Tree(t.write())
+    except ImportError:
+        pass
+    if outbase:
+        with open(outbase + ".nw", "w") as out:
+            out.write(t.write())
+    return t
+
+
+def cluster_contigs(outbase, d, bin_chr, bin_position, threads=4, frac=0.66, iterations=30, maxnumchr=500,
+                    seed=0, dpi=100, minchr=3, nchr=0, selections=None, return_details=False):
+    """Estimate number of chromosomes and assign contigs to chromosomes -- bam2clusters.py:406-457.
+
+    Like the reference, ``seed`` and ``threads`` are ignored and the sub-samples come from the global
+    ``np.random`` (:410,429) unless ``selections`` (list of index arrays) injects them.  The 1 + 30
+    ward linkages run on the GPU, the bootstrap ones overlapped on separate streams."""
+    import scipy.cluster.hierarchy as sch
+    prng = np.random
+    D = d if isinstance(d, torch.Tensor) else torch.from_numpy(np.ascontiguousarray(d, dtype=np.float64)).cuda()
+    Z = linkage_square(D, "ward")
+    mean_step_len = None
+    if not nchr:
+        n = D.shape[0]
+        subset = int(round(n * frac))
+        if subset < maxnumchr:
+            maxnumchr = subset - 1
+        Ws = []
+        for i in range(iterations):
+            selection = selections[i] if selections is not None else prng.permutation(n)[:subset]
+            sel = torch.as_tensor(np.asarray(selection), dtype=torch.long, device=D.device)
+            sub = D.index_select(0, sel).index_select(1, sel).contiguous()
+            Ws.append(ops.transform_to_working(sub, ops.KIND_IDENTITY, square=True)[0])
+        dZ = [np.diff(iZ[:, 2]) for iZ in ops.linkage_batch(Ws, "ward")]
+        mean_step_len = np.mean(np.array(dZ), 0)
+        nchr = int(np.argmax(mean_step_len[-minchr + 1::-1][:maxnumchr]) + minchr)
+    clusters = [[] for _ in range(nchr)]
+    assignments = sch.fcluster(Z, t=nchr, criterion='maxclust')
+    for i, c in zip(assignments - 1, bin_chr):
+        clusters[i].append(c)
+    if return_details:
+        return clusters, nchr, Z, mean_step_len
+    return clusters

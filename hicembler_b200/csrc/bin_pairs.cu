@@ -1,0 +1,599 @@
+// K1: read pair -> window binning (scatter-add into the dense contact matrix).
+//
+// Replaces the Python per-line loop of bam2arrays (reference bam2clusters.py:128-166), with the
+// window arithmetic of get_window (:119-126) and the record filter of `samtools view -q -F`
+// (:108-117).  Semantics per record: SURVEY.md appendix C.
+//
+// B200 design.  The matrix row a record lands in is the window of READ 1, and a coordinate-sorted
+// BAM delivers read-1 records in (nearly) ascending window order.  So instead of scattering
+// 64-byte read-modify-writes over a 10 GB matrix, a CTA owns a tile of R complete matrix rows in
+// its 200+ KB of shared memory (one 50 000-column u32 row = 200 KB fits an sm_100 SM), streams
+// exactly the slice of the pair stream that falls in those rows, accumulates with shared-memory
+// atomics and writes every row ONCE with plain coalesced stores (no memset, no global atomics).
+// HBM traffic = 24 B/pair + 4 B/cell = the algorithmic minimum.
+//
+// The slice of the stream belonging to a row tile is found from one sampled key per 256-record
+// chunk (prefix-max repaired, so ANY input order stays correct): records that fall outside the
+// rows their chunk advertises are "stragglers", appended to an overflow list and applied with
+// global atomics afterwards; if the list overflows (input not sorted at all) the whole call is
+// redone by the plain global-atomic kernel.
+#include <limits.h>
+
+#include "common.cuh"
+
+namespace {
+
+constexpr int CHUNK_LOG = 8;
+constexpr int CHUNK = 1 << CHUNK_LOG;  // records per chunk
+constexpr int SCAN_BLOCK = 4096;       // chunks per scan block
+
+struct BinArgs {
+    const uint2 *pairs;
+    long long n_pairs;
+    const int32_t *offsets, *member;
+    const uint8_t *region_mask;
+    int32_t n_contigs;
+    uint32_t window_bp;
+    int32_t n_windows, mapq_min;
+    uint32_t skip_flag;
+    int32_t row0, row1;
+    uint32_t *counts;
+    int accumulate;  // add to the existing matrix instead of overwriting it
+    // tiling
+    int32_t R, W, n_groups, n_segs;
+    long long n_chunks;
+    const int32_t *chunk_lo, *chunk_hi;  // group-aligned row bounds advertised by each chunk
+    const long long *tile_clo, *tile_chi;  // chunk range per row group
+    uint2 *overflow;
+    unsigned long long *overflow_count;
+    long long overflow_cap;
+    unsigned long long *stats;
+};
+
+enum { ST_FILTERED = 0, ST_OK = 1, ST_ABSENT = 2, ST_RANGE = 3, ST_KEY = 4 };
+
+__device__ __forceinline__ int decode(const BinArgs &a, uint2 q0, uint2 q1, uint2 q2, int32_t &row,
+                                      int32_t &col) {
+    const int32_t ref = (int32_t)q0.x, pos = (int32_t)q0.y;
+    const int32_t nref = (int32_t)q1.x, npos = (int32_t)q1.y;
+    const int32_t lseq = (int32_t)q2.x;
+    const uint32_t flag = q2.y & 0xffffu, mapq = (q2.y >> 16) & 0xffu;
+    if ((flag & a.skip_flag) || (int32_t)mapq < a.mapq_min) return ST_FILTERED;
+    const bool ref_ok = (uint32_t)ref < (uint32_t)a.n_contigs;
+    if (a.region_mask && !(ref_ok && a.region_mask[ref])) return ST_FILTERED;
+    const bool nref_ok = (uint32_t)nref < (uint32_t)a.n_contigs;
+    if (!ref_ok || !nref_ok) return ST_ABSENT;
+    if (__ldg(a.member + ref) < 0 || __ldg(a.member + nref) < 0) return ST_ABSENT;
+    const int32_t o1 = __ldg(a.offsets + ref), o2 = __ldg(a.offsets + nref);
+    if (o1 < 0 || o2 < 0) return ST_KEY;
+    const int32_t half = (lseq > 1 ? lseq : 1) >> 1;  // len("*") == 1; Py2 integer division
+    const long long p1 = (long long)pos + 1 + half, p2 = (long long)npos + 1 + half;
+    if (p1 < 0 || p2 < 0) return ST_RANGE;
+    const long long w1 = (long long)((uint32_t)p1 / a.window_bp) + o1;
+    const long long w2 = (long long)((uint32_t)p2 / a.window_bp) + o2;
+    if (w1 >= a.n_windows || w2 >= a.n_windows) return ST_RANGE;
+    row = (int32_t)w1;
+    col = (int32_t)w2;
+    return ST_OK;
+}
+
+// sampled key of a chunk: window of read 1 of the chunk's first record, -1 if it has none
+__global__ void k_lead(BinArgs a, int32_t *lead) {
+    long long c = blockIdx.x * (long long)blockDim.x + threadIdx.x;
+    if (c >= a.n_chunks) return;
+    const uint2 *p = a.pairs + 3 * (c << CHUNK_LOG);
+    uint2 q0 = __ldg(p), q2 = __ldg(p + 2);
+    int32_t ref = (int32_t)q0.x, key = -1;
+    if ((uint32_t)ref < (uint32_t)a.n_contigs) {
+        int32_t o = __ldg(a.offsets + ref);
+        int32_t lseq = (int32_t)q2.x;
+        long long p1 = (long long)(int32_t)q0.y + 1 + ((lseq > 1 ? lseq : 1) >> 1);
+        if (o >= 0 && p1 >= 0) {
+            long long w = (long long)((uint32_t)p1 / a.window_bp) + o;
+            key = (int32_t)(w < a.n_windows ? w : a.n_windows - 1);
+        }
+    }
+    lead[c] = key;
+}
+
+__device__ __forceinline__ int32_t block_max(int32_t v, int32_t *sh) {
+    for (int o = 16; o; o >>= 1) v = max(v, __shfl_xor_sync(0xffffffffu, v, o));
+    if ((threadIdx.x & 31) == 0) sh[threadIdx.x >> 5] = v;
+    __syncthreads();
+    if (threadIdx.x < 32) {
+        int32_t w = threadIdx.x < (blockDim.x >> 5) ? sh[threadIdx.x] : INT_MIN;
+        for (int o = 16; o; o >>= 1) w = max(w, __shfl_xor_sync(0xffffffffu, w, o));
+        if (threadIdx.x == 0) sh[0] = w;
+    }
+    __syncthreads();
+    int32_t r = sh[0];
+    __syncthreads();
+    return r;
+}
+
+__global__ void k_scan_blockmax(const int32_t *lead, long long n, int32_t *bmax) {
+    __shared__ int32_t sh[32];
+    long long base = (long long)blockIdx.x * SCAN_BLOCK;
+    int32_t v = INT_MIN;
+    for (int i = threadIdx.x; i < SCAN_BLOCK && base + i < n; i += blockDim.x) v = max(v, lead[base + i]);
+    v = block_max(v, sh);
+    if (threadIdx.x == 0) bmax[blockIdx.x] = v;
+}
+
+// exclusive prefix max over the (few) block maxima, single thread block
+__global__ void k_scan_carry(int32_t *bmax, int nb) {
+    if (threadIdx.x == 0) {
+        int32_t run = -1;
+        for (int b = 0; b < nb; ++b) {
+            int32_t v = bmax[b];
+            bmax[b] = run;
+            run = max(run, v);
+        }
+    }
+}
+
+// inclusive prefix max inside each scan block (1024 threads x 4 elements), then the
+// group-aligned row bounds every chunk advertises
+__global__ void k_scan_apply(int32_t *lead, long long n, const int32_t *bmax) {
+    __shared__ int32_t sh[1024];
+    long long base = (long long)blockIdx.x * SCAN_BLOCK + threadIdx.x * 4;
+    int32_t v[4];
+#pragma unroll
+    for (int k = 0; k < 4; ++k) v[k] = (base + k < n) ? lead[base + k] : INT_MIN;
+    v[1] = max(v[1], v[0]);
+    v[2] = max(v[2], v[1]);
+    v[3] = max(v[3], v[2]);
+    sh[threadIdx.x] = v[3];
+    __syncthreads();
+    for (int o = 1; o < 1024; o <<= 1) {
+        int32_t t = threadIdx.x >= o ? sh[threadIdx.x - o] : INT_MIN;
+        __syncthreads();
+        sh[threadIdx.x] = max(sh[threadIdx.x], t);
+        __syncthreads();
+    }
+    int32_t carry = max(bmax[blockIdx.x], threadIdx.x ? sh[threadIdx.x - 1] : INT_MIN);
+#pragma unroll
+    for (int k = 0; k < 4; ++k)
+        if (base + k < n) lead[base + k] = max(v[k], carry);
+}
+
+__global__ void k_chunk_bounds(BinArgs a, const int32_t *leadm, int32_t *chunk_lo, int32_t *chunk_hi) {
+    long long c = blockIdx.x * (long long)blockDim.x + threadIdx.x;
+    if (c >= a.n_chunks) return;
+    int32_t lo = leadm[c], hi = (c + 1 < a.n_chunks) ? leadm[c + 1] : INT_MAX;
+    lo = min(max(lo, a.row0), a.row1 - 1);
+    hi = min(max(hi, a.row0), a.row1 - 1);
+    chunk_lo[c] = a.row0 + (lo - a.row0) / a.R * a.R;
+    chunk_hi[c] = a.row0 + ((hi - a.row0) / a.R + 1) * a.R;
+}
+
+// chunk range [clo, chi) intersecting each row group: chunk_lo[c] <= r0 < chunk_hi[c]
+__global__ void k_tile_ranges(BinArgs a, long long *tile_clo, long long *tile_chi) {
+    int g = blockIdx.x * blockDim.x + threadIdx.x;
+    if (g >= a.n_groups) return;
+    int32_t r0 = a.row0 + g * a.R;
+    long long lo = 0, hi = a.n_chunks;
+    while (lo < hi) {  // first c with chunk_hi[c] > r0
+        long long m = (lo + hi) >> 1;
+        if (a.chunk_hi[m] > r0) hi = m; else lo = m + 1;
+    }
+    tile_clo[g] = lo;
+    lo = 0, hi = a.n_chunks;
+    while (lo < hi) {  // first c with chunk_lo[c] > r0
+        long long m = (lo + hi) >> 1;
+        if (a.chunk_lo[m] > r0) hi = m; else lo = m + 1;
+    }
+    tile_chi[g] = lo;
+}
+
+// Main kernel: one CTA per (row group, column segment) tile.
+template <int UNROLL>
+__global__ void __launch_bounds__(1024, 1) k_bin_tiles(BinArgs a) {
+    extern __shared__ uint32_t tile[];
+    const int g = blockIdx.x / a.n_segs, s = blockIdx.x - g * a.n_segs;
+    const int32_t r0 = a.row0 + g * a.R, r1 = min(r0 + a.R, a.row1);
+    const int32_t c0 = s * a.W, c1 = min(c0 + a.W, a.n_windows);
+    const int W = c1 - c0;
+    const int cells = (r1 - r0) * W;
+    for (int i = threadIdx.x; i < cells; i += blockDim.x) tile[i] = 0;
+    __syncthreads();
+
+    unsigned long long n_lines = 0, n_ok = 0, n_absent = 0, n_range = 0, n_key = 0, n_over = 0;
+    const long long clo = a.tile_clo[g], chi = a.tile_chi[g];
+    const long long beg = clo << CHUNK_LOG;
+    const long long end = min(chi << CHUNK_LOG, a.n_pairs);
+    const int T = blockDim.x, lane_id = threadIdx.x & 31;
+    // warp-uniform trip count (the straggler ballot below needs the whole warp)
+    for (long long wbase = beg + (threadIdx.x - lane_id); wbase < end; wbase += (long long)T * UNROLL) {
+        const long long base = wbase + lane_id;
+        uint2 q[UNROLL][3];
+#pragma unroll
+        for (int u = 0; u < UNROLL; ++u) {
+            long long idx = base + (long long)u * T;
+            if (idx < end) {
+                const uint2 *p = a.pairs + 3 * idx;
+                q[u][0] = __ldg(p);
+                q[u][1] = __ldg(p + 1);
+                q[u][2] = __ldg(p + 2);
+            } else {
+                q[u][2].y = 0xffffu;  // every flag bit set -> filtered
+                q[u][0] = q[u][1] = make_uint2(0, 0);
+                q[u][2].x = 0;
+            }
+        }
+#pragma unroll
+        for (int u = 0; u < UNROLL; ++u) {
+            long long idx = base + (long long)u * T;
+            bool live = idx < end;
+            long long c = (live ? idx : beg) >> CHUNK_LOG;
+            int32_t row = 0, col = 0;
+            int st = live ? decode(a, q[u][0], q[u][1], q[u][2], row, col) : ST_FILTERED;
+            int32_t lo = __ldg(a.chunk_lo + c), hi = __ldg(a.chunk_hi + c);
+            bool owner = live && (lo == r0) && (s == 0);  // this CTA accounts for the record
+            if (owner) {
+                n_lines += st != ST_FILTERED;
+                n_ok += st == ST_OK;
+                n_absent += st == ST_ABSENT;
+                n_range += st == ST_RANGE;
+                n_key += st == ST_KEY;
+            }
+            bool ok = st == ST_OK;
+            if (ok && row >= r0 && row < r1 && col >= c0 && col < c1)
+                atomicAdd(&tile[(row - r0) * W + (col - c0)], 1u);
+            // straggler: row not advertised by its chunk -> nobody's tile sees it
+            bool strag = owner && ok && (row < lo || row >= hi) && row >= a.row0 && row < a.row1;
+            unsigned m = __ballot_sync(0xffffffffu, strag);
+            if (m) {
+                int lane = threadIdx.x & 31, leader = __ffs(m) - 1;
+                unsigned long long slot = 0;
+                if (lane == leader) slot = atomicAdd(a.overflow_count, (unsigned long long)__popc(m));
+                slot = __shfl_sync(0xffffffffu, slot, leader);
+                if (strag) {
+                    slot += __popc(m & ((1u << lane) - 1));
+                    if ((long long)slot < a.overflow_cap) a.overflow[slot] = make_uint2(row, col);
+                    n_over++;
+                }
+            }
+        }
+    }
+    __syncthreads();
+    // every tile row is written exactly once, coalesced
+    for (int rr = 0; rr < r1 - r0; ++rr) {
+        uint32_t *dst = a.counts + (size_t)(r0 - a.row0 + rr) * a.n_windows + c0;
+        const uint32_t *src = tile + rr * W;
+        if (a.accumulate) for (int i = threadIdx.x; i < W; i += blockDim.x) dst[i] += src[i];
+        else for (int i = threadIdx.x; i < W; i += blockDim.x) dst[i] = src[i];
+    }
+    unsigned long long v[6] = {n_lines, n_ok, n_absent, n_range, n_key, n_over};
+#pragma unroll
+    for (int k = 0; k < 6; ++k) {
+        unsigned long long t = hc::warp_sum_u64(v[k]);
+        if ((threadIdx.x & 31) == 0 && t) atomicAdd(a.stats + k, t);
+    }
+}
+
+__global__ void k_apply_overflow(BinArgs a) {
+    long long n = min((long long)*a.overflow_count, a.overflow_cap);
+    for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n;
+         i += (long long)gridDim.x * blockDim.x) {
+        uint2 e = a.overflow[i];
+        atomicAdd(a.counts + (size_t)((int32_t)e.x - a.row0) * a.n_windows + e.y, 1u);
+    }
+}
+
+// Fallback: plain global atomics on a zeroed matrix, any input order.
+__global__ void __launch_bounds__(256) k_bin_atomic(BinArgs a) {
+    unsigned long long n_lines = 0, n_ok = 0, n_absent = 0, n_range = 0, n_key = 0;
+    for (long long idx = blockIdx.x * (long long)blockDim.x + threadIdx.x; idx < a.n_pairs;
+         idx += (long long)gridDim.x * blockDim.x) {
+        const uint2 *p = a.pairs + 3 * idx;
+        int32_t row, col;
+        int st = decode(a, __ldg(p), __ldg(p + 1), __ldg(p + 2), row, col);
+        n_lines += st != ST_FILTERED;
+        n_ok += st == ST_OK;
+        n_absent += st == ST_ABSENT;
+        n_range += st == ST_RANGE;
+        n_key += st == ST_KEY;
+        if (st == ST_OK && row >= a.row0 && row < a.row1)
+            atomicAdd(a.counts + (size_t)(row - a.row0) * a.n_windows + col, 1u);
+    }
+    unsigned long long v[5] = {n_lines, n_ok, n_absent, n_range, n_key};
+#pragma unroll
+    for (int k = 0; k < 5; ++k) {
+        unsigned long long t = hc::warp_sum_u64(v[k]);
+        if ((threadIdx.x & 31) == 0 && t) atomicAdd(a.stats + k, t);
+    }
+}
+
+// ---- upto -------------------------------------------------------------------------------
+__device__ __forceinline__ bool is_line(const uint2 *pairs, long long idx, const uint8_t *region_mask,
+                                        int32_t n_contigs, int32_t mapq_min, uint32_t skip_flag) {
+    uint2 q2 = __ldg(pairs + 3 * idx + 2);
+    uint32_t flag = q2.y & 0xffffu, mapq = (q2.y >> 16) & 0xffu;
+    if ((flag & skip_flag) || (int32_t)mapq < mapq_min) return false;
+    if (region_mask) {
+        int32_t ref = (int32_t)__ldg(pairs + 3 * idx).x;
+        if (!((uint32_t)ref < (uint32_t)n_contigs && region_mask[ref])) return false;
+    }
+    return true;
+}
+
+__global__ void k_count_lines(const uint2 *pairs, long long n, const uint8_t *region_mask,
+                              int32_t n_contigs, int32_t mapq_min, uint32_t skip_flag,
+                              unsigned long long *block_lines) {
+    __shared__ unsigned long long sh[32];
+    long long base = (long long)blockIdx.x * 4096;
+    unsigned long long cnt = 0;
+    for (int i = threadIdx.x; i < 4096 && base + i < n; i += blockDim.x)
+        cnt += is_line(pairs, base + i, region_mask, n_contigs, mapq_min, skip_flag);
+    cnt = hc::warp_sum_u64(cnt);
+    if ((threadIdx.x & 31) == 0) sh[threadIdx.x >> 5] = cnt;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        unsigned long long t = 0;
+        for (int w = 0; w < (blockDim.x >> 5); ++w) t += sh[w];
+        block_lines[blockIdx.x] = t;
+    }
+}
+
+// single block: locate the block holding the upto-th line, then the record inside it
+__global__ void k_find_cutoff(const uint2 *pairs, long long n, const uint8_t *region_mask,
+                              int32_t n_contigs, int32_t mapq_min, uint32_t skip_flag,
+                              const unsigned long long *block_lines, long long n_blocks,
+                              long long upto, long long *result) {
+    __shared__ long long s_block, s_before;
+    __shared__ int s_warp_cnt[32];
+    if (threadIdx.x == 0) {
+        unsigned long long run = 0;
+        long long b = 0;
+        for (; b < n_blocks; ++b) {
+            if (run + block_lines[b] >= (unsigned long long)upto) break;
+            run += block_lines[b];
+        }
+        s_block = b;
+        s_before = (long long)run;
+    }
+    __syncthreads();
+    if (s_block >= n_blocks) {  // fewer than upto lines in total
+        if (threadIdx.x == 0) { result[0] = n; result[1] = s_before; }
+        return;
+    }
+    long long base = s_block * 4096, need = upto - s_before;  // need >= 1
+    // 1024 threads x 4 consecutive records, ordered scan
+    int flags[4], mine = 0;
+    for (int k = 0; k < 4; ++k) {
+        long long idx = base + threadIdx.x * 4 + k;
+        flags[k] = idx < n && is_line(pairs, idx, region_mask, n_contigs, mapq_min, skip_flag);
+        mine += flags[k];
+    }
+    int incl = mine;
+    for (int o = 1; o < 32; o <<= 1) {
+        int t = __shfl_up_sync(0xffffffffu, incl, o);
+        if ((threadIdx.x & 31) >= o) incl += t;
+    }
+    if ((threadIdx.x & 31) == 31) s_warp_cnt[threadIdx.x >> 5] = incl;
+    __syncthreads();
+    int before = incl - mine;
+    for (int w = 0; w < (threadIdx.x >> 5); ++w) before += s_warp_cnt[w];
+    for (int k = 0; k < 4; ++k) {
+        if (flags[k]) {
+            before++;
+            if (before == need) { result[0] = base + threadIdx.x * 4 + k + 1; result[1] = upto; }
+        }
+    }
+}
+
+__global__ void k_region_filter(const uint2 *pairs, long long n, const int32_t *tlen,
+                                const int32_t *ref_span, const int32_t *contig_size,
+                                const int32_t *member, int32_t n_contigs, int32_t min_size,
+                                int32_t nth, int32_t mapq_min, uint32_t skip_flag, uint8_t *keep,
+                                int32_t *dist) {
+    for (long long k = blockIdx.x * (long long)blockDim.x + threadIdx.x; k < n;
+         k += (long long)gridDim.x * blockDim.x) {
+        uint2 q0 = __ldg(pairs + 3 * k), q1 = __ldg(pairs + 3 * k + 1), q2 = __ldg(pairs + 3 * k + 2);
+        int32_t ref = (int32_t)q0.x, pos = (int32_t)q0.y, nref = (int32_t)q1.x;
+        uint32_t flag = q2.y & 0xffffu, mapq = (q2.y >> 16) & 0xffu;
+        uint8_t kp = 0;
+        int32_t d = -1;
+        if (!(flag & skip_flag) && (int32_t)mapq >= mapq_min && (uint32_t)ref < (uint32_t)n_contigs &&
+            member[ref] >= 0 && pos >= 0) {
+            // regions (s+1, s+minSize), s = 0, step, 2*step..., s <= size - minSize (1-based, inclusive)
+            long long step = (long long)nth * min_size;
+            long long first = (long long)pos + 1, last = (long long)pos + max(ref_span ? ref_span[k] : 1, 1);
+            long long smax = (long long)contig_size[ref] - min_size;  // largest admissible s
+            if (smax >= 0) {
+                // region index range overlapping [first, last]: s+1 <= last and s+minSize >= first
+                long long i_hi = (last - 1) / step;                   // s <= last-1
+                long long lo_s = first - min_size;                   // s >= first - minSize
+                long long i_lo = lo_s <= 0 ? 0 : (lo_s + step - 1) / step;
+                long long i_max = smax / step;
+                if (i_hi > i_max) i_hi = i_max;
+                if (i_lo <= i_hi) {
+                    kp = (uint8_t)min((long long)255, i_hi - i_lo + 1);  // printed once per region hit
+                    if (nref == ref) {
+                        int32_t t = tlen ? tlen[k] : 0;
+                        d = t < 0 ? -t : t;
+                    }
+                }
+            }
+        }
+        keep[k] = kp;
+        dist[k] = d;
+    }
+}
+
+}  // namespace
+
+extern "C" size_t hc_bin_pairs_workspace_bytes(int64_t n_pairs, int64_t n_rows) {
+    size_t n_chunks = (size_t)((n_pairs + CHUNK - 1) / CHUNK) + 1;
+    size_t nb = (n_chunks + SCAN_BLOCK - 1) / SCAN_BLOCK + 1;
+    size_t bytes = 4096;
+    bytes += hc::align_up(n_chunks * 4, 256) * 3;        // lead/chunk_lo/chunk_hi
+    bytes += hc::align_up(nb * 4, 256);                  // block maxima
+    bytes += hc::align_up((size_t)n_rows * 8, 256) * 2;  // tile ranges (<= one group per row)
+    bytes += hc::align_up((size_t)(n_pairs / 16 + 65536) * 8, 256);  // overflow list
+    return bytes;
+}
+
+extern "C" int hc_bin_pairs(const hc_pair_t *pairs, int64_t n_pairs, const int32_t *offsets,
+                            const int32_t *member, const uint8_t *region_mask, int32_t n_contigs,
+                            uint32_t window_bp, int32_t n_windows, int32_t mapq_min,
+                            uint32_t skip_flag, int32_t row0, int32_t row1, uint32_t *counts,
+                            void *workspace, size_t workspace_bytes, int mode, int64_t *h_stats,
+                            void *stream_) {
+    cudaStream_t stream = (cudaStream_t)stream_;
+    HC_REQUIRE(n_pairs >= 0 && n_windows > 0 && window_bp > 0, "bad sizes");
+    HC_REQUIRE(row0 >= 0 && row0 < row1 && row1 <= n_windows, "bad row block");
+    HC_REQUIRE(offsets && counts && h_stats && workspace, "null pointer");
+    HC_REQUIRE(((uintptr_t)pairs & 7) == 0, "pairs must be 8-byte aligned");
+    if (workspace_bytes < hc_bin_pairs_workspace_bytes(n_pairs, row1 - row0)) {
+        hc::set_error("hc_bin_pairs: workspace too small");
+        return HC_EWORKSPACE;
+    }
+    const int32_t rows = row1 - row0;
+    BinArgs a;
+    memset(&a, 0, sizeof a);
+    a.pairs = (const uint2 *)pairs;
+    a.n_pairs = n_pairs;
+    a.offsets = offsets;
+    a.member = member ? member : offsets;
+    a.region_mask = region_mask;
+    a.n_contigs = n_contigs;
+    a.window_bp = window_bp;
+    a.n_windows = n_windows;
+    a.mapq_min = mapq_min;
+    a.skip_flag = skip_flag;
+    a.row0 = row0;
+    a.row1 = row1;
+    a.counts = counts;
+    a.n_chunks = (n_pairs + CHUNK - 1) / CHUNK;
+
+    // tile shape: R rows x W columns of u32 in shared memory
+    int dev = 0, smem_max = 0;
+    HC_CUDA_OK(cudaGetDevice(&dev));
+    HC_CUDA_OK(cudaDeviceGetAttribute(&smem_max, cudaDevAttrMaxSharedMemoryPerBlockOptin, dev));
+    const int sms = hc::sm_count();
+    long long max_cells = (smem_max - 1024) / 4;
+    if (const char *e = getenv("HC_BIN_MAX_CELLS")) max_cells = atoll(e);
+    a.n_segs = (int)((n_windows + max_cells - 1) / max_cells);
+    a.W = (n_windows + a.n_segs - 1) / a.n_segs;
+    int Rmax = (int)(max_cells / a.W);
+    if (Rmax < 1) Rmax = 1;
+    int Rwant = (rows + 4 * sms - 1) / (4 * sms);  // aim for >= 4 tiles per SM
+    a.R = Rwant < 1 ? 1 : (Rwant > Rmax ? Rmax : Rwant);
+    if (const char *e = getenv("HC_BIN_ROWS")) a.R = atoi(e) < 1 ? 1 : (atoi(e) > Rmax ? Rmax : atoi(e));
+    a.n_groups = (rows + a.R - 1) / a.R;
+
+    hc::Carver ws(workspace, workspace_bytes);
+    unsigned long long *stats = ws.take<unsigned long long>(16);
+    int32_t *lead = ws.take<int32_t>(a.n_chunks + 1);
+    int32_t *chunk_lo = ws.take<int32_t>(a.n_chunks + 1);
+    int32_t *chunk_hi = ws.take<int32_t>(a.n_chunks + 1);
+    long long nb = (a.n_chunks + SCAN_BLOCK - 1) / SCAN_BLOCK;
+    int32_t *bmax = ws.take<int32_t>(nb + 1);
+    long long *tile_clo = ws.take<long long>(a.n_groups);
+    long long *tile_chi = ws.take<long long>(a.n_groups);
+    a.overflow_cap = n_pairs / 16 + 65536;
+    a.overflow = ws.take<uint2>(a.overflow_cap);
+    if (!ws.ok()) {
+        hc::set_error("hc_bin_pairs: workspace carve overflow");
+        return HC_EWORKSPACE;
+    }
+    a.stats = stats;
+    a.overflow_count = stats + 8;
+    a.chunk_lo = chunk_lo;
+    a.chunk_hi = chunk_hi;
+    a.tile_clo = tile_clo;
+    a.tile_chi = tile_chi;
+
+    unsigned long long h[16];
+    a.accumulate = (mode & 2) != 0;
+    bool fast = ((mode & 1) == 0) && n_pairs > 0;
+    if (fast) {
+        HC_CUDA_OK(cudaMemsetAsync(stats, 0, 16 * sizeof(unsigned long long), stream));
+        int cb = (int)((a.n_chunks + 255) / 256);
+        k_lead<<<cb, 256, 0, stream>>>(a, lead);
+        k_scan_blockmax<<<(int)nb, 256, 0, stream>>>(lead, a.n_chunks, bmax);
+        k_scan_carry<<<1, 32, 0, stream>>>(bmax, (int)nb);
+        k_scan_apply<<<(int)nb, 1024, 0, stream>>>(lead, a.n_chunks, bmax);
+        k_chunk_bounds<<<cb, 256, 0, stream>>>(a, lead, chunk_lo, chunk_hi);
+        k_tile_ranges<<<(a.n_groups + 127) / 128, 128, 0, stream>>>(a, tile_clo, tile_chi);
+        size_t smem = (size_t)a.R * a.W * 4;
+        int threads = smem > 96 * 1024 ? 1024 : (smem > 32 * 1024 ? 512 : 256);
+        if (const char *e = getenv("HC_BIN_THREADS")) threads = atoi(e);
+        HC_CUDA_OK(cudaFuncSetAttribute(k_bin_tiles<4>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                        smem_max));
+        k_bin_tiles<4><<<a.n_groups * a.n_segs, threads, smem, stream>>>(a);
+        HC_CHECK_LAUNCH();
+        k_apply_overflow<<<4 * sms, 256, 0, stream>>>(a);
+        HC_CHECK_LAUNCH();
+        HC_CUDA_OK(cudaMemcpyAsync(h, stats, sizeof h, cudaMemcpyDeviceToHost, stream));
+        HC_CUDA_OK(cudaStreamSynchronize(stream));
+        if ((long long)h[8] > a.overflow_cap) fast = false;  // unsorted input: redo with atomics
+    }
+    if (!fast) {
+        HC_CUDA_OK(cudaMemsetAsync(stats, 0, 16 * sizeof(unsigned long long), stream));
+        if (!a.accumulate) HC_CUDA_OK(cudaMemsetAsync(counts, 0, (size_t)rows * n_windows * 4, stream));
+        if (n_pairs > 0) {
+            k_bin_atomic<<<16 * sms, 256, 0, stream>>>(a);
+            HC_CHECK_LAUNCH();
+        }
+        HC_CUDA_OK(cudaMemcpyAsync(h, stats, sizeof h, cudaMemcpyDeviceToHost, stream));
+        HC_CUDA_OK(cudaStreamSynchronize(stream));
+        h[5] = 0;
+    }
+    for (int k = 0; k < 6; ++k) h_stats[k] = (int64_t)h[k];
+    h_stats[6] = fast ? 1 : 0;
+    h_stats[7] = ((int64_t)a.R << 32) | (uint32_t)a.n_segs;
+    if (h[4]) {
+        hc::set_error("contig present in chr2window[0] but absent for this window size (%llu records)", h[4]);
+        return HC_EKEY;
+    }
+    if (h[3]) {
+        hc::set_error("window index out of range for %llu records", h[3]);
+        return HC_ERANGE;
+    }
+    return HC_OK;
+}
+
+extern "C" int hc_upto_cutoff(const hc_pair_t *pairs, int64_t n_pairs, const uint8_t *region_mask,
+                              int32_t n_contigs, int32_t mapq_min, uint32_t skip_flag, int64_t upto,
+                              void *workspace, size_t workspace_bytes, int64_t *h_n_effective,
+                              int64_t *h_lines, void *stream_) {
+    cudaStream_t stream = (cudaStream_t)stream_;
+    HC_REQUIRE(h_n_effective && h_lines && upto > 0, "bad arguments");
+    long long nb = (n_pairs + 4095) / 4096;
+    if (workspace_bytes < (size_t)(nb + 2) * 8 + 256) {
+        hc::set_error("hc_upto_cutoff: workspace too small");
+        return HC_EWORKSPACE;
+    }
+    if (n_pairs == 0) { *h_n_effective = 0; *h_lines = 0; return HC_OK; }
+    long long *result = (long long *)workspace;
+    unsigned long long *block_lines = (unsigned long long *)((char *)workspace + 256);
+    k_count_lines<<<(int)nb, 256, 0, stream>>>((const uint2 *)pairs, n_pairs, region_mask, n_contigs,
+                                               mapq_min, skip_flag, block_lines);
+    k_find_cutoff<<<1, 1024, 0, stream>>>((const uint2 *)pairs, n_pairs, region_mask, n_contigs, mapq_min,
+                                          skip_flag, block_lines, nb, upto, result);
+    HC_CHECK_LAUNCH();
+    long long h[2];
+    HC_CUDA_OK(cudaMemcpyAsync(h, result, sizeof h, cudaMemcpyDeviceToHost, stream));
+    HC_CUDA_OK(cudaStreamSynchronize(stream));
+    *h_n_effective = h[0];
+    *h_lines = h[1];
+    return HC_OK;
+}
+
+extern "C" int hc_contig_region_filter(const hc_pair_t *pairs, int64_t n_pairs, const int32_t *tlen,
+                                       const int32_t *ref_span, const int32_t *contig_size,
+                                       const int32_t *member, int32_t n_contigs, int32_t min_size,
+                                       int32_t nth, int32_t mapq_min, uint32_t skip_flag,
+                                       uint8_t *keep, int32_t *dist, void *stream_) {
+    cudaStream_t stream = (cudaStream_t)stream_;
+    HC_REQUIRE(min_size > 0 && nth > 0 && keep && dist && contig_size && member, "bad arguments");
+    if (n_pairs == 0) return HC_OK;
+    k_region_filter<<<8 * hc::sm_count(), 256, 0, stream>>>((const uint2 *)pairs, n_pairs, tlen, ref_span,
+                                                            contig_size, member, n_contigs, min_size, nth,
+                                                            mapq_min, skip_flag, keep, dist);
+    HC_CHECK_LAUNCH();
+    return HC_OK;
+}

@@ -1,0 +1,421 @@
+// K2 (fold / symmetrise), K6 (contacts -> distances into the linkage working matrix),
+// condensed <-> square conversions and K8 block reductions.
+//
+// All N x N passes here are tile-PAIR kernels: one CTA owns tiles (I,J) and (J,I), I <= J, stages
+// both through shared memory and writes both.  That makes "d += d.T - diag(d)" (reference
+// bam2clusters.py:42,511) a single read + single write of the matrix (8 N^2 bytes for float32 =
+// the algorithmic minimum), lets it run in place, and lets the transform read only the upper
+// triangle that d[np.triu_indices(n,1)] (bam2clusters.py:385) selects.
+#include <math.h>
+
+#include "common.cuh"
+
+namespace {
+
+constexpr int TS = 32;  // tile side; blocks are (32, 8)
+
+__device__ __forceinline__ void atomic_max_nonneg(float *addr, float v) {
+    atomicMax((int *)addr, __float_as_int(v));
+}
+__device__ __forceinline__ void atomic_max_nonneg(double *addr, double v) {
+    atomicMax((long long *)addr, __double_as_longlong(v));
+}
+
+template <typename T>
+__device__ __forceinline__ T block_max_2d(T v, T *sh) {
+    for (int o = 16; o; o >>= 1) v = fmax(v, __shfl_xor_sync(0xffffffffu, v, o));
+    if (threadIdx.x == 0) sh[threadIdx.y] = v;
+    __syncthreads();
+    T r = sh[0];
+    for (int k = 1; k < blockDim.y; ++k) r = fmax(r, sh[k]);
+    return r;
+}
+
+// counts (u32, full orientation) -> float32 upper-triangular (mode 0) or symmetrised (mode 1)
+__global__ void __launch_bounds__(256) k_fold_counts(const uint32_t *C, int n, int mode, float add,
+                                                      float *out, float *vmax) {
+    const int I = blockIdx.y, J = blockIdx.x;
+    if (I > J) return;
+    __shared__ uint32_t A[TS][TS + 1], B[TS][TS + 1];
+    __shared__ float shm[8];
+    const int tx = threadIdx.x;
+    for (int r = threadIdx.y; r < TS; r += 8) {
+        int i = I * TS + r, j = J * TS + tx;
+        A[r][tx] = (i < n && j < n) ? C[(size_t)i * n + j] : 0u;
+        int i2 = J * TS + r, j2 = I * TS + tx;
+        B[r][tx] = (i2 < n && j2 < n) ? C[(size_t)i2 * n + j2] : 0u;
+    }
+    __syncthreads();
+    float m = 0.f;
+    for (int r = threadIdx.y; r < TS; r += 8) {
+        int i = I * TS + r, j = J * TS + tx;
+        if (i < n && j < n) {
+            uint32_t s = (i == j) ? A[r][tx] : A[r][tx] + B[tx][r];
+            float v;
+            if (mode == 0) v = (i <= j) ? (float)s : 0.f;
+            else v = (float)s + add;
+            out[(size_t)i * n + j] = v;
+            m = fmaxf(m, v);
+        }
+        if (I != J) {
+            int i2 = J * TS + r, j2 = I * TS + tx;
+            if (i2 < n && j2 < n) {
+                float v = (mode == 0) ? 0.f : (float)(B[r][tx] + A[tx][r]) + add;
+                out[(size_t)i2 * n + j2] = v;
+                m = fmaxf(m, v);
+            }
+        }
+    }
+    if (vmax) {
+        m = block_max_2d(m, shm);
+        if (threadIdx.x == 0 && threadIdx.y == 0) atomic_max_nonneg(vmax, m);
+    }
+}
+
+// in place  d += d.T - diag(d.diagonal())  (+ add)
+template <typename T>
+__global__ void __launch_bounds__(256) k_symmetrize(T *d, int n, T add, T *vmax) {
+    const int I = blockIdx.y, J = blockIdx.x;
+    if (I > J) return;
+    __shared__ T A[TS][TS + 1], B[TS][TS + 1];
+    __shared__ T shm[8];
+    const int tx = threadIdx.x;
+    for (int r = threadIdx.y; r < TS; r += 8) {
+        int i = I * TS + r, j = J * TS + tx;
+        A[r][tx] = (i < n && j < n) ? d[(size_t)i * n + j] : (T)0;
+        int i2 = J * TS + r, j2 = I * TS + tx;
+        B[r][tx] = (i2 < n && j2 < n) ? d[(size_t)i2 * n + j2] : (T)0;
+    }
+    __syncthreads();
+    T m = 0;
+    for (int r = threadIdx.y; r < TS; r += 8) {
+        int i = I * TS + r, j = J * TS + tx;
+        if (i < n && j < n) {
+            T v = ((i == j) ? A[r][tx] : A[r][tx] + B[tx][r]) + add;
+            d[(size_t)i * n + j] = v;
+            m = fmax(m, v);
+        }
+        if (I != J) {
+            int i2 = J * TS + r, j2 = I * TS + tx;
+            if (i2 < n && j2 < n) {
+                T v = (B[r][tx] + A[tx][r]) + add;
+                d[(size_t)i2 * n + j2] = v;
+                m = fmax(m, v);
+            }
+        }
+    }
+    if (vmax) {
+        m = block_max_2d(m, shm);
+        if (threadIdx.x == 0 && threadIdx.y == 0) atomic_max_nonneg(vmax, m);
+    }
+}
+
+struct Xform {
+    int kind;
+    double p0, p1;
+    const double *r, *c;
+    double vmax;
+    int square;
+};
+
+// value of the distance for upper-triangle entry (i,j), i<j, given raw X[i][j]
+template <typename T>
+__device__ __forceinline__ double xform(const Xform &t, T raw, int i, int j) {
+    double v;
+    if (t.r) {
+        T p = raw / (T)t.vmax;                       // d/vmax in the matrix dtype (bam2clusters.py:46)
+        v = __dmul_rn(__dmul_rn(t.r[i], (double)p), t.c[j]);  // (D1.P).D2  (sinkhorn_knopp.py:161)
+        if (t.kind == 1) v = v + 1.0;
+    } else if (t.kind == 1 || t.kind == 2) {
+        v = (double)(T)(raw + (T)1);                 // x+1 in the matrix dtype
+    } else {
+        v = (double)raw;
+    }
+    double out;
+    if (t.kind == 1 || t.kind == 3) out = pow(1.0 / (t.p0 * v), 1.0 / t.p1);
+    else if (t.kind == 2) {
+        if (sizeof(T) == 4 && !t.r) out = (double)(logf((float)t.p0) - logf((float)v));
+        else out = log(t.p0) - log(t.r ? v + 1.0 : v);
+    } else out = v;
+    return t.square ? __dmul_rn(out, out) : out;
+}
+
+template <typename T>
+__global__ void __launch_bounds__(256) k_transform_working(const T *X, int n, Xform t, double *W,
+                                                            int32_t *flags) {
+    const int I = blockIdx.y, J = blockIdx.x;
+    if (I > J) return;
+    __shared__ double A[TS][TS + 1];
+    const int tx = threadIdx.x;
+    bool bad = false;
+    for (int r = threadIdx.y; r < TS; r += 8) {
+        int i = I * TS + r, j = J * TS + tx;
+        double v = 0;
+        if (i < n && j < n && i < j) {
+            v = xform<T>(t, X[(size_t)i * n + j], i, j);
+            bad |= isnan(v);
+        }
+        A[r][tx] = v;
+    }
+    __syncthreads();
+    const double inf = __longlong_as_double(0x7ff0000000000000LL);
+    for (int r = threadIdx.y; r < TS; r += 8) {
+        int i = I * TS + r, j = J * TS + tx;
+        if (i < n && j < n) {
+            double v = (i < j) ? A[r][tx] : (i == j ? inf : A[tx][r]);
+            W[(size_t)i * n + j] = v;
+        }
+        if (I != J) {
+            int i2 = J * TS + r, j2 = I * TS + tx;  // lower tile: W[i2][j2] = f(X[j2][i2])
+            if (i2 < n && j2 < n) W[(size_t)i2 * n + j2] = A[tx][r];
+        }
+    }
+    if (bad) atomicOr(flags, 1);
+}
+
+template <typename TI, typename TO>
+__global__ void k_transform_flat(const TI *X, long long count, Xform t, TO *out) {
+    for (long long k = blockIdx.x * (long long)blockDim.x + threadIdx.x; k < count;
+         k += (long long)gridDim.x * blockDim.x)
+        out[k] = (TO)xform<TI>(t, X[k], 0, 0);
+}
+
+__device__ __forceinline__ long long condensed_row_offset(long long i, long long n) {
+    return i * (2 * n - i - 1) / 2;  // index of (i, i+1)
+}
+
+template <typename T>
+__global__ void k_condense(const T *X, int n, double *y) {
+    int i = blockIdx.x;
+    long long off = condensed_row_offset(i, n);
+    for (int j = i + 1 + threadIdx.x; j < n; j += blockDim.x) y[off + (j - i - 1)] = (double)X[(size_t)i * n + j];
+}
+
+__global__ void __launch_bounds__(256) k_expand_condensed(const double *y, int n, int square, double *W,
+                                                           int32_t *flags) {
+    const int I = blockIdx.y, J = blockIdx.x;
+    if (I > J) return;
+    __shared__ double A[TS][TS + 1];
+    const int tx = threadIdx.x;
+    bool bad = false;
+    for (int r = threadIdx.y; r < TS; r += 8) {
+        int i = I * TS + r, j = J * TS + tx;
+        double v = 0;
+        if (i < n && j < n && i < j) {
+            v = y[condensed_row_offset(i, n) + (j - i - 1)];
+            bad |= isnan(v);
+            if (square) v = __dmul_rn(v, v);
+        }
+        A[r][tx] = v;
+    }
+    __syncthreads();
+    const double inf = __longlong_as_double(0x7ff0000000000000LL);
+    for (int r = threadIdx.y; r < TS; r += 8) {
+        int i = I * TS + r, j = J * TS + tx;
+        if (i < n && j < n) W[(size_t)i * n + j] = (i < j) ? A[r][tx] : (i == j ? inf : A[tx][r]);
+        if (I != J) {
+            int i2 = J * TS + r, j2 = I * TS + tx;
+            if (i2 < n && j2 < n) W[(size_t)i2 * n + j2] = A[tx][r];
+        }
+    }
+    if (bad) atomicOr(flags, 1);
+}
+
+// ---- K8 ----------------------------------------------------------------------------------
+// stage 1: tmp[k][j] = mean over rows of segment k (sequential float32 adds in row order, the
+// order np.mean(A[indices], axis=0) uses for a C-contiguous selection), bam2scaffolds.py:63
+__global__ void k_segmean_rows(const float *A, int n, const int32_t *seg_begin, const int32_t *seg_end,
+                               int n_seg, float *tmp) {
+    int k = blockIdx.y;
+    int j = blockIdx.x * blockDim.x + threadIdx.x;
+    if (j >= n) return;
+    int b = seg_begin[k], e = seg_end[k];
+    float s = 0.f;
+    for (int i = b; i < e; ++i) s = __fadd_rn(s, A[(size_t)i * n + j]);
+    tmp[(size_t)k * n + j] = __fdiv_rn(s, (float)(e - b));
+}
+// stage 2: out[k1][k2] = mean over j in segment k2 of tmp[k1][j]
+__global__ void k_segmean_cols(const float *tmp, int n, const int32_t *seg_begin, const int32_t *seg_end,
+                               int n_seg, float *out) {
+    int k2 = blockIdx.x * blockDim.x + threadIdx.x, k1 = blockIdx.y;
+    if (k2 >= n_seg) return;
+    int b = seg_begin[k2], e = seg_end[k2];
+    float s = 0.f;
+    for (int j = b; j < e; ++j) s = __fadd_rn(s, tmp[(size_t)k1 * n + j]);
+    out[(size_t)k1 * n_seg + k2] = __fdiv_rn(s, (float)(e - b));
+}
+
+// normalize_rows (array2scaffolds.py:33-41): column sums, row sums and row maxima in one read
+__global__ void k_rowcol_sums(const float *A, int n, double *colsum, double *rowsum, float *rowmax) {
+    // block (256): rows [blockIdx.y*64, +64), columns blockIdx.x*256 + tx
+    int j = blockIdx.x * 256 + threadIdx.x;
+    int i0 = blockIdx.y * 64, i1 = min(i0 + 64, n);
+    double cs = 0;
+    for (int i = i0; i < i1; ++i) {
+        float v = (j < n) ? A[(size_t)i * n + j] : 0.f;
+        cs += v;
+        float mx = v;
+        double rs = hc::warp_sum_f64((double)v);
+        for (int o = 16; o; o >>= 1) mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, o));
+        if ((threadIdx.x & 31) == 0) {
+            atomicAdd(rowsum + i, rs);
+            atomicMax((int *)(rowmax + i), __float_as_int(mx));
+        }
+    }
+    if (j < n) atomicAdd(colsum + j, cs);
+}
+__global__ void k_colsum_max(const double *colsum, int n, float *maxv) {
+    __shared__ float sh[8];
+    float m = 0.f;
+    for (int j = threadIdx.x; j < n; j += blockDim.x) m = fmaxf(m, (float)colsum[j]);
+    for (int o = 16; o; o >>= 1) m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, o));
+    if ((threadIdx.x & 31) == 0) sh[threadIdx.x >> 5] = m;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        for (int k = 1; k < 8; ++k) m = fmaxf(m, sh[k]);
+        *maxv = fmaxf(m, sh[0]);
+    }
+}
+__global__ void k_scale_rows(float *A, int n, const double *rowsum, const float *rowmax, const float *maxv) {
+    int i = blockIdx.y;
+    if (rowmax[i] == 0.f) return;  // "only if any signal"
+    float f = __fdiv_rn(*maxv, (float)rowsum[i]);  // 1.*maxv/a[i].sum() in float32 (NEP 50)
+    for (int j = blockIdx.x * blockDim.x + threadIdx.x; j < n; j += gridDim.x * blockDim.x)
+        A[(size_t)i * n + j] = __fmul_rn(A[(size_t)i * n + j], f);
+}
+
+// bam2array's tail (bam2clusters.py:244): array = (array / sizes).T / sizes on the float32
+// upper-triangular count matrix -> float64, transposed (lower triangular)
+__global__ void k_contig_normalize(const uint32_t *C, int n, const int32_t *sizes, double *out) {
+    int j = blockIdx.x * blockDim.x + threadIdx.x, i = blockIdx.y;
+    if (j >= n) return;
+    double v = 0.0;
+    if (i >= j) {
+        uint32_t u = (i == j) ? C[(size_t)i * n + i] : C[(size_t)j * n + i] + C[(size_t)i * n + j];
+        v = __ddiv_rn(__ddiv_rn((double)(float)u, (double)sizes[i]), (double)sizes[j]);
+    }
+    out[(size_t)i * n + j] = v;
+}
+
+}  // namespace
+
+extern "C" int hc_fold_counts(const uint32_t *counts, int32_t n, int mode, float add, float *out,
+                              float *d_vmax, void *stream_) {
+    cudaStream_t stream = (cudaStream_t)stream_;
+    HC_REQUIRE(counts && out && n > 0 && (mode == 0 || mode == 1), "bad arguments");
+    if (d_vmax) HC_CUDA_OK(cudaMemsetAsync(d_vmax, 0, sizeof(float), stream));
+    int T = (n + TS - 1) / TS;
+    k_fold_counts<<<dim3(T, T), dim3(TS, 8), 0, stream>>>(counts, n, mode, add, out, d_vmax);
+    HC_CHECK_LAUNCH();
+    return HC_OK;
+}
+
+extern "C" int hc_symmetrize(void *d, int32_t n, int dtype, double add, void *d_vmax, void *stream_) {
+    cudaStream_t stream = (cudaStream_t)stream_;
+    HC_REQUIRE(d && n > 0 && (dtype == 0 || dtype == 1), "bad arguments");
+    int T = (n + TS - 1) / TS;
+    if (d_vmax) HC_CUDA_OK(cudaMemsetAsync(d_vmax, 0, dtype ? 8 : 4, stream));
+    if (dtype == 0)
+        k_symmetrize<float><<<dim3(T, T), dim3(TS, 8), 0, stream>>>((float *)d, n, (float)add, (float *)d_vmax);
+    else
+        k_symmetrize<double><<<dim3(T, T), dim3(TS, 8), 0, stream>>>((double *)d, n, add, (double *)d_vmax);
+    HC_CHECK_LAUNCH();
+    return HC_OK;
+}
+
+extern "C" int hc_transform_to_working(const void *X, int dtype, int32_t n, int kind, double p0, double p1,
+                                       const double *r, const double *c, double vmax, int square,
+                                       double *W, int32_t *d_flags, void *stream_) {
+    cudaStream_t stream = (cudaStream_t)stream_;
+    HC_REQUIRE(X && W && d_flags && n > 0 && kind >= 0 && kind <= 3 && (dtype == 0 || dtype == 1), "bad arguments");
+    HC_REQUIRE((r == nullptr) == (c == nullptr), "r and c must be given together");
+    Xform t{kind, p0, p1, r, c, vmax, square};
+    int T = (n + TS - 1) / TS;
+    HC_CUDA_OK(cudaMemsetAsync(d_flags, 0, sizeof(int32_t), stream));
+    if (dtype == 0)
+        k_transform_working<float><<<dim3(T, T), dim3(TS, 8), 0, stream>>>((const float *)X, n, t, W, d_flags);
+    else
+        k_transform_working<double><<<dim3(T, T), dim3(TS, 8), 0, stream>>>((const double *)X, n, t, W, d_flags);
+    HC_CHECK_LAUNCH();
+    return HC_OK;
+}
+
+extern "C" int hc_transform(const void *X, int dtype, int64_t count, int kind, double p0, double p1, void *out,
+                            int out_dtype, void *stream_) {
+    cudaStream_t stream = (cudaStream_t)stream_;
+    HC_REQUIRE(X && out && count >= 0 && kind >= 0 && kind <= 3, "bad arguments");
+    Xform t{kind, p0, p1, nullptr, nullptr, 1.0, 0};
+    if (count == 0) return HC_OK;
+    int blocks = 8 * hc::sm_count();
+    if (dtype == 0 && out_dtype == 0)
+        k_transform_flat<float, float><<<blocks, 256, 0, stream>>>((const float *)X, count, t, (float *)out);
+    else if (dtype == 0 && out_dtype == 1)
+        k_transform_flat<float, double><<<blocks, 256, 0, stream>>>((const float *)X, count, t, (double *)out);
+    else if (dtype == 1 && out_dtype == 1)
+        k_transform_flat<double, double><<<blocks, 256, 0, stream>>>((const double *)X, count, t, (double *)out);
+    else {
+        hc::set_error("hc_transform: unsupported dtype combination");
+        return HC_EINVAL;
+    }
+    HC_CHECK_LAUNCH();
+    return HC_OK;
+}
+
+extern "C" int hc_condense(const void *X, int dtype, int32_t n, double *y, void *stream_) {
+    cudaStream_t stream = (cudaStream_t)stream_;
+    HC_REQUIRE(X && y && n > 0, "bad arguments");
+    if (n < 2) return HC_OK;
+    if (dtype == 0) k_condense<float><<<n - 1, 256, 0, stream>>>((const float *)X, n, y);
+    else k_condense<double><<<n - 1, 256, 0, stream>>>((const double *)X, n, y);
+    HC_CHECK_LAUNCH();
+    return HC_OK;
+}
+
+extern "C" int hc_expand_condensed(const double *y, int32_t n, int square, double *W, int32_t *d_flags,
+                                   void *stream_) {
+    cudaStream_t stream = (cudaStream_t)stream_;
+    HC_REQUIRE(y && W && d_flags && n > 0, "bad arguments");
+    int T = (n + TS - 1) / TS;
+    HC_CUDA_OK(cudaMemsetAsync(d_flags, 0, sizeof(int32_t), stream));
+    k_expand_condensed<<<dim3(T, T), dim3(TS, 8), 0, stream>>>(y, n, square, W, d_flags);
+    HC_CHECK_LAUNCH();
+    return HC_OK;
+}
+
+extern "C" int hc_segment_mean_2d(const float *A, int32_t n, const int32_t *seg_begin, const int32_t *seg_end,
+                                  int32_t n_seg, float *tmp, float *out, void *stream_) {
+    cudaStream_t stream = (cudaStream_t)stream_;
+    HC_REQUIRE(A && seg_begin && seg_end && tmp && out && n > 0 && n_seg > 0, "bad arguments");
+    k_segmean_rows<<<dim3((n + 255) / 256, n_seg), 256, 0, stream>>>(A, n, seg_begin, seg_end, n_seg, tmp);
+    k_segmean_cols<<<dim3((n_seg + 127) / 128, n_seg), 128, 0, stream>>>(tmp, n, seg_begin, seg_end, n_seg, out);
+    HC_CHECK_LAUNCH();
+    return HC_OK;
+}
+
+extern "C" int hc_normalize_rows(float *A, int32_t n, void *workspace, size_t workspace_bytes, void *stream_) {
+    cudaStream_t stream = (cudaStream_t)stream_;
+    HC_REQUIRE(A && workspace && n > 0, "bad arguments");
+    size_t need = (size_t)n * 8 * 2 + (size_t)n * 4 + 1024;
+    if (workspace_bytes < need) {
+        hc::set_error("hc_normalize_rows: workspace too small");
+        return HC_EWORKSPACE;
+    }
+    hc::Carver ws(workspace, workspace_bytes);
+    double *colsum = ws.take<double>(n), *rowsum = ws.take<double>(n);
+    float *rowmax = ws.take<float>(n), *maxv = ws.take<float>(1);
+    HC_CUDA_OK(cudaMemsetAsync(workspace, 0, ws.off, stream));
+    k_rowcol_sums<<<dim3((n + 255) / 256, (n + 63) / 64), 256, 0, stream>>>(A, n, colsum, rowsum, rowmax);
+    k_colsum_max<<<1, 256, 0, stream>>>(colsum, n, maxv);
+    k_scale_rows<<<dim3(min((n + 255) / 256, 64), n), 256, 0, stream>>>(A, n, rowsum, rowmax, maxv);
+    HC_CHECK_LAUNCH();
+    return HC_OK;
+}
+
+extern "C" int hc_contig_normalize(const uint32_t *counts, int32_t n, const int32_t *sizes, double *out,
+                                   void *stream_) {
+    cudaStream_t stream = (cudaStream_t)stream_;
+    HC_REQUIRE(counts && sizes && out && n > 0, "bad arguments");
+    k_contig_normalize<<<dim3((n + 255) / 256, n), 256, 0, stream>>>(counts, n, sizes, out);
+    HC_CHECK_LAUNCH();
+    return HC_OK;
+}

@@ -1,0 +1,353 @@
+"""Device-resident operators: torch CUDA tensors in, torch CUDA tensors out.
+
+torch is used for device memory and streams only; every computation is a call into
+libhicembler_b200.so (hand-written sm_100a kernels).  These are the building blocks the
+reference-named drop-ins in ``bam2clusters.py`` / ``bam2scaffolds.py`` / ``array2scaffolds.py`` /
+``sinkhorn_knopp.py`` / ``fastcluster.py`` are made of, and the "fast path" that keeps N x N data in
+HBM from pair records to the linkage array.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import warnings
+
+import numpy as np
+import torch
+
+from . import _lib
+from .pairs import PAIR_DTYPE, SKIP_FLAG
+
+METHODS = {"single": 0, "complete": 1, "average": 2, "weighted": 3, "ward": 4}
+KIND_IDENTITY, KIND_POWER, KIND_LOGMAX, KIND_POWER_RAW = 0, 1, 2, 3
+_UINT32_MAX = 0xFFFFFFFF
+
+
+def _stream():
+    return C.c_void_p(torch.cuda.current_stream().cuda_stream)
+
+
+def _dev(t: torch.Tensor):
+    if not t.is_cuda:
+        raise RuntimeError("hicembler_b200 operators need CUDA tensors (there is no CPU fallback)")
+    _lib.check(_lib.lib().hc_set_device(t.device.index))
+
+
+def _ptr(t):
+    return C.c_void_p(0 if t is None else t.data_ptr())
+
+
+def _dtype_code(t):
+    if t.dtype == torch.float32:
+        return 0
+    if t.dtype == torch.float64:
+        return 1
+    raise TypeError("matrix must be float32 or float64, got %s" % t.dtype)
+
+
+def device_info():
+    sm, mem, major, minor = C.c_int(), C.c_size_t(), C.c_int(), C.c_int()
+    _lib.check(_lib.lib().hc_device_info(C.byref(sm), C.byref(mem), C.byref(major), C.byref(minor)))
+    return dict(sm_count=sm.value, total_mem=mem.value, cc=(major.value, minor.value))
+
+
+def to_device_records(rec, device="cuda"):
+    """numpy PAIR_DTYPE array / int32 [n,6] tensor -> int32 [n,6] CUDA tensor (24-byte records)."""
+    if isinstance(rec, torch.Tensor):
+        t = rec
+    else:
+        rec = np.ascontiguousarray(rec)
+        if rec.dtype != PAIR_DTYPE:
+            raise TypeError("records must have pairs.PAIR_DTYPE")
+        t = torch.from_numpy(rec.view(np.int32).reshape(-1, 6))
+    if t.dtype != torch.int32 or t.dim() != 2 or t.shape[1] != 6:
+        raise TypeError("record tensor must be int32 [n, 6]")
+    return t.to(device, non_blocking=True).contiguous()
+
+
+# ---------------------------------------------------------------------------------------------
+# K1
+# ---------------------------------------------------------------------------------------------
+def upto_cutoff(records, mapq, upto, region_mask=None, skip_flag=SKIP_FLAG):
+    """(n_effective, lines): leading records containing ``upto`` lines that survive -q/-F."""
+    _dev(records)
+    n = records.shape[0]
+    ws = torch.empty(8 * (n // 4096 + 2) + 512, dtype=torch.uint8, device=records.device)
+    n_eff, lines = C.c_int64(), C.c_int64()
+    n_contigs = 0 if region_mask is None else region_mask.numel()
+    _lib.check(_lib.lib().hc_upto_cutoff(_ptr(records), n, _ptr(region_mask), n_contigs, int(mapq),
+                                         skip_flag, int(upto), _ptr(ws), ws.numel(),
+                                         C.byref(n_eff), C.byref(lines), _stream()))
+    return n_eff.value, lines.value
+
+
+def bin_pairs(records, offsets, window_bp, n_windows, mapq, member=None, region_mask=None,
+              n_pairs=None, rows=None, skip_flag=SKIP_FLAG, mode=0, out=None, workspace=None,
+              return_stats=False):
+    """Scatter-add read pairs into the full-orientation u32 count matrix (K1).
+
+    offsets/member: int32 CUDA tensors indexed by refID (-1 = absent).  ``window_bp=None`` bins
+    one window per contig (contig-level matrix).  Returns int32-typed tensor holding u32 counts of
+    shape (rows, n_windows)."""
+    _dev(records)
+    dev = records.device
+    n = records.shape[0] if n_pairs is None else int(n_pairs)
+    row0, row1 = (0, n_windows) if rows is None else rows
+    if out is None:
+        out = torch.empty((row1 - row0, n_windows), dtype=torch.int32, device=dev)
+    need = _lib.lib().hc_bin_pairs_workspace_bytes(n, row1 - row0)
+    if workspace is None or workspace.numel() < need:
+        workspace = torch.empty(need, dtype=torch.uint8, device=dev)
+    stats = (C.c_int64 * 8)()
+    wbp = _UINT32_MAX if window_bp is None else int(window_bp)
+    rc = _lib.lib().hc_bin_pairs(_ptr(records), n, _ptr(offsets), _ptr(member), _ptr(region_mask),
+                                 offsets.numel(), wbp, int(n_windows), int(mapq), skip_flag,
+                                 row0, row1, _ptr(out), _ptr(workspace), workspace.numel(), mode,
+                                 stats, _stream())
+    _lib.check(rc)
+    st = dict(lines=stats[0], binned=stats[1], skipped_absent=stats[2], out_of_range=stats[3],
+              key_errors=stats[4], overflow=stats[5], fast_path=bool(stats[6]),
+              tile_rows=stats[7] >> 32, col_segments=stats[7] & 0xFFFFFFFF)
+    return (out, st) if return_stats else out
+
+
+def contig_region_filter(records, tlen, ref_span, contig_size, member, min_size, nth, mapq,
+                         skip_flag=SKIP_FLAG):
+    _dev(records)
+    n = records.shape[0]
+    keep = torch.empty(n, dtype=torch.uint8, device=records.device)
+    dist = torch.empty(n, dtype=torch.int32, device=records.device)
+    _lib.check(_lib.lib().hc_contig_region_filter(
+        _ptr(records), n, _ptr(tlen), _ptr(ref_span), _ptr(contig_size), _ptr(member),
+        contig_size.numel(), int(min_size), int(nth), int(mapq), skip_flag, _ptr(keep), _ptr(dist),
+        _stream()))
+    return keep, dist
+
+
+# ---------------------------------------------------------------------------------------------
+# K2
+# ---------------------------------------------------------------------------------------------
+def fold_counts(counts, mode="upper", add=0.0, inplace=False):
+    """counts (u32 full orientation) -> float32: 'upper' (what bam2arrays returns) or 'sym'
+    (after d += d.T - diag(d), plus ``add``).  Returns (matrix, vmax tensor or None)."""
+    _dev(counts)
+    n = counts.shape[0]
+    assert counts.shape == (n, n) and counts.dtype == torch.int32
+    out = counts.view(torch.float32) if inplace else torch.empty((n, n), dtype=torch.float32,
+                                                                 device=counts.device)
+    vmax = torch.zeros(1, dtype=torch.float32, device=counts.device)
+    _lib.check(_lib.lib().hc_fold_counts(_ptr(counts), n, 0 if mode == "upper" else 1, float(add),
+                                         _ptr(out), _ptr(vmax), _stream()))
+    return out, vmax
+
+
+def symmetrize_(d, add=0.0):
+    """In place ``d += d.T - np.diag(d.diagonal())`` (+ add).  Returns (d, max tensor)."""
+    _dev(d)
+    n = d.shape[0]
+    assert d.shape == (n, n) and d.is_contiguous()
+    vmax = torch.zeros(1, dtype=d.dtype, device=d.device)
+    _lib.check(_lib.lib().hc_symmetrize(_ptr(d), n, _dtype_code(d), float(add), _ptr(vmax), _stream()))
+    return d, vmax
+
+
+# ---------------------------------------------------------------------------------------------
+# K3-K5
+# ---------------------------------------------------------------------------------------------
+class SinkhornResult:
+    __slots__ = ("r", "c", "iterations", "stopping_condition", "warned")
+
+
+def sinkhorn_fit(X, vmax=1.0, max_iter=1000, epsilon=1e-3, iterations0=0, allreduce=None):
+    """Sinkhorn-Knopp scaling vectors for P = X / vmax (sinkhorn_knopp.py:93-163).
+
+    X: (nrows, n) CUDA float32/float64 row block (the whole matrix when not sharded).
+    ``allreduce(y)`` sums the float64 column vector over ranks in place (row-sharded use).
+    ``iterations0`` is SinkhornKnopp._iterations carried over from earlier fits (:150-152).
+    """
+    _dev(X)
+    L = _lib.lib()
+    nrows, n = X.shape
+    dt = _dtype_code(X)
+    dev = X.device
+    f64 = dict(dtype=torch.float64, device=dev)
+    nchunks = L.hc_sk_num_row_chunks(nrows)
+    ypart = torch.empty((nchunks, n), **f64)
+    y, c, c_new = torch.empty(n, **f64), torch.empty(n, **f64), torch.empty(n, **f64)
+    x, r = torch.empty(nrows, **f64), torch.empty(nrows, **f64)
+    flags = torch.zeros(8, dtype=torch.int32, device=dev)
+    s = _stream()
+    vmax = float(vmax)
+
+    def colpass(rvec, check):
+        _lib.check(L.hc_sk_colpass(_ptr(X), dt, nrows, n, vmax, _ptr(rvec), _ptr(ypart),
+                                   _ptr(flags) if check else None, s))
+        _lib.check(L.hc_sk_colfinish(_ptr(ypart), nchunks, n, _ptr(y), s))
+        if allreduce is not None:
+            allreduce(y)
+
+    res = SinkhornResult()
+    res.warned = False
+    # r = ones; pdotr = P.T.dot(r); c = 1/pdotr                                  (:120-129)
+    colpass(None, True)
+    _lib.check(L.hc_sk_update_c(_ptr(y), None, n, epsilon, _ptr(c), _ptr(flags), s))
+    # raw row sums for the first evaluation of the while test on P_eps = P      (:137-141)
+    _lib.check(L.hc_sk_rowpass(_ptr(X), dt, nrows, n, vmax, None, _ptr(x), None, _ptr(flags), s))
+    outside = torch.zeros(1, dtype=torch.int32, device=dev)
+    _lib.check(L.hc_sk_outside(_ptr(x), nrows, epsilon, _ptr(outside), s))
+    _lib.check(L.hc_sk_outside(_ptr(y), n, epsilon, _ptr(outside), s))
+    flags[4] = 0
+    # pdotc = P.dot(c); r = 1/pdotc                                             (:130-134)
+    _lib.check(L.hc_sk_rowpass(_ptr(X), dt, nrows, n, vmax, _ptr(c), _ptr(x), _ptr(r), _ptr(flags), s))
+    if allreduce is not None:
+        allreduce(outside)
+    h = flags.tolist()
+    if h[0]:
+        raise AssertionError("P must be non-negative (sinkhorn_knopp.py:110)")
+    if h[2]:
+        warnings.warn("Matrix P must have total support. See documentation", UserWarning)
+        res.warned = True
+    if h[4]:
+        warnings.warn("Matrix P must have total support. See documentation", UserWarning)
+        res.warned = True
+    cond = bool(outside.item())
+    iterations = int(iterations0)
+    stop = None
+    if cond:
+        colpass(r, False)  # y = P^T r0
+    while cond:
+        # c = 1/(P^T r); r = 1/(P c)                                            (:143-144)
+        _lib.check(L.hc_sk_update_c(_ptr(y), None, n, epsilon, _ptr(c), _ptr(flags), s))
+        _lib.check(L.hc_sk_rowpass(_ptr(X), dt, nrows, n, vmax, _ptr(c), _ptr(x), _ptr(r), _ptr(flags), s))
+        iterations += 1
+        if iterations >= max_iter:
+            stop = "max_iter"
+            break
+        # column sums of D1.P.D2 = c * (P^T r): the next column pass doubles as the test (:138-141)
+        colpass(r, False)
+        flags[3] = 0
+        _lib.check(L.hc_sk_update_c(_ptr(y), _ptr(c), n, epsilon, _ptr(c_new), _ptr(flags), s))
+        cond = bool(flags[3].item())
+    res.r, res.c = r, c
+    res.iterations = iterations
+    res.stopping_condition = stop or "epsilon"
+    return res
+
+
+def sinkhorn_apply(X, r, c, vmax=1.0, out_dtype=torch.float64, out=None):
+    """P_eps = D1.dot(P).dot(D2) (:159-161) as an elementwise scaling."""
+    _dev(X)
+    nrows, n = X.shape
+    if out is None:
+        out = torch.empty((nrows, n), dtype=out_dtype, device=X.device)
+    _lib.check(_lib.lib().hc_sk_apply(_ptr(X), _dtype_code(X), nrows, n, float(vmax), _ptr(r), _ptr(c),
+                                      _ptr(out), _dtype_code(out), _stream()))
+    return out
+
+
+# ---------------------------------------------------------------------------------------------
+# K6 / K7
+# ---------------------------------------------------------------------------------------------
+def transform_to_working(X, kind=KIND_IDENTITY, p0=0.0, p1=1.0, r=None, c=None, vmax=1.0,
+                         square=False, out=None):
+    """Upper triangle of X -> full symmetric float64 linkage working matrix (K6)."""
+    _dev(X)
+    n = X.shape[0]
+    assert X.shape == (n, n) and X.is_contiguous()
+    if out is None:
+        out = torch.empty((n, n), dtype=torch.float64, device=X.device)
+    flags = torch.zeros(2, dtype=torch.int32, device=X.device)
+    _lib.check(_lib.lib().hc_transform_to_working(_ptr(X), _dtype_code(X), n, kind, float(p0), float(p1),
+                                                  _ptr(r), _ptr(c), float(vmax), int(bool(square)),
+                                                  _ptr(out), _ptr(flags), _stream()))
+    return out, flags
+
+
+def transform(X, kind, p0=0.0, p1=1.0, out_dtype=None):
+    _dev(X)
+    X = X.contiguous()
+    if out_dtype is None:
+        out_dtype = X.dtype if kind == KIND_LOGMAX else torch.float64
+    out = torch.empty(X.shape, dtype=out_dtype, device=X.device)
+    _lib.check(_lib.lib().hc_transform(_ptr(X), _dtype_code(X), X.numel(), kind, float(p0), float(p1),
+                                       _ptr(out), _dtype_code(out), _stream()))
+    return out
+
+
+def condense(X):
+    _dev(X)
+    n = X.shape[0]
+    y = torch.empty(n * (n - 1) // 2, dtype=torch.float64, device=X.device)
+    _lib.check(_lib.lib().hc_condense(_ptr(X.contiguous()), _dtype_code(X), n, _ptr(y), _stream()))
+    return y
+
+
+def expand_condensed(y, n, square=False):
+    _dev(y)
+    W = torch.empty((n, n), dtype=torch.float64, device=y.device)
+    flags = torch.zeros(2, dtype=torch.int32, device=y.device)
+    _lib.check(_lib.lib().hc_expand_condensed(_ptr(y), n, int(bool(square)), _ptr(W), _ptr(flags), _stream()))
+    return W, flags
+
+
+def linkage_working(W, method="ward", nan_flags=None, return_stats=False):
+    """NN-chain linkage of a working matrix (destroyed).  Returns Z (numpy (n-1, 4) float64)."""
+    _dev(W)
+    n = W.shape[0]
+    if nan_flags is not None and int(nan_flags[0].item()):
+        raise FloatingPointError("NaN dissimilarity value.")
+    L = _lib.lib()
+    ws = torch.empty(L.hc_linkage_workspace_bytes(n), dtype=torch.uint8, device=W.device)
+    Z = np.empty((max(n - 1, 0), 4), dtype=np.float64)
+    stats = (C.c_int64 * 4)()
+    _lib.check(L.hc_linkage(_ptr(W), n, METHODS[method], _ptr(ws), ws.numel(),
+                            Z.ctypes.data_as(C.c_void_p), stats, _stream()))
+    if return_stats:
+        return Z, dict(scans=stats[0], scan_active=stats[1], merges=stats[2], update_active=stats[3])
+    return Z
+
+
+def linkage_batch(Ws, method="ward"):
+    """Independent linkages overlapped on separate streams (each is one thread-block cluster)."""
+    if not Ws:
+        return []
+    _dev(Ws[0])
+    L = _lib.lib()
+    cur = torch.cuda.current_stream()
+    streams = [torch.cuda.Stream() for _ in range(min(len(Ws), 8))]
+    jobs = []
+    for k, W in enumerate(Ws):
+        n = W.shape[0]
+        st = streams[k % len(streams)]
+        st.wait_stream(cur)
+        ws = torch.empty(L.hc_linkage_workspace_bytes(n), dtype=torch.uint8, device=W.device)
+        _lib.check(L.hc_linkage_launch(_ptr(W), n, METHODS[method], _ptr(ws), ws.numel(),
+                                       C.c_void_p(st.cuda_stream)))
+        jobs.append((n, ws, st))
+    out = []
+    for n, ws, st in jobs:
+        Z = np.empty((max(n - 1, 0), 4), dtype=np.float64)
+        _lib.check(L.hc_linkage_finish(n, METHODS[method], _ptr(ws), ws.numel(),
+                                       Z.ctypes.data_as(C.c_void_p), None, C.c_void_p(st.cuda_stream)))
+        out.append(Z)
+    return out
+
+
+# ---------------------------------------------------------------------------------------------
+# K8
+# ---------------------------------------------------------------------------------------------
+def segment_mean_2d(A, seg_begin, seg_end):
+    _dev(A)
+    n, k = A.shape[0], seg_begin.numel()
+    tmp = torch.empty((k, n), dtype=torch.float32, device=A.device)
+    out = torch.empty((k, k), dtype=torch.float32, device=A.device)
+    _lib.check(_lib.lib().hc_segment_mean_2d(_ptr(A), n, _ptr(seg_begin), _ptr(seg_end), k, _ptr(tmp),
+                                             _ptr(out), _stream()))
+    return out
+
+
+def normalize_rows_(A):
+    _dev(A)
+    n = A.shape[0]
+    ws = torch.empty(20 * n + 4096, dtype=torch.uint8, device=A.device)
+    _lib.check(_lib.lib().hc_normalize_rows(_ptr(A), n, _ptr(ws), ws.numel(), _stream()))
+    return A

@@ -1,0 +1,198 @@
+/* hicembler_b200 -- C ABI of the B200 (sm_100a) hot path of HiCembler.
+ *
+ * Every entry point takes plain pointers and sizes.  Pointers are DEVICE pointers unless the
+ * parameter name starts with ``h_`` (host).  ``stream`` is a cudaStream_t passed as void*
+ * (NULL = default stream).  Nothing here allocates caller-visible memory: outputs and
+ * workspaces are caller-allocated (the Python layer uses torch tensors as buffers).
+ * All functions return 0 on success or a negative hc_status; hc_last_error() gives the text.
+ *
+ * The reference (lpryszcz/HiCembler) has no FFI of its own: the boundary it exposes is a set of
+ * Python callables plus two library calls (fastcluster.linkage, SinkhornKnopp.fit).  Each entry
+ * point below cites the reference lines it replaces; INTEGRATION.md shows the ctypes binding a
+ * maintainer adds on the reference side.
+ */
+#ifndef HICEMBLER_B200_H
+#define HICEMBLER_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define HC_VERSION 100
+
+typedef enum {
+    HC_OK = 0,
+    HC_EINVAL = -1,   /* bad argument */
+    HC_ERANGE = -2,   /* window index outside the matrix: reference raises IndexError (bam2clusters.py:161) */
+    HC_EKEY = -3,     /* contig in chr2window[0] but not in chr2window[ii]: reference raises KeyError (:151,155) */
+    HC_ENAN = -4,     /* NaN dissimilarity: fastcluster raises */
+    HC_ENEG = -5,     /* negative entry in P: SinkhornKnopp.fit asserts (sinkhorn_knopp.py:110) */
+    HC_ECUDA = -6,    /* CUDA runtime error */
+    HC_EWORKSPACE = -7, /* workspace too small */
+    HC_ENOTRI = -8    /* condensed length is not n*(n-1)/2: fastcluster raises ValueError */
+} hc_status;
+
+/* One alignment record, 24 bytes, little endian (BAM core fields of
+ * bin/snap/SNAPLib/Bam.h:91-105 consumed at bam2clusters.py:145-146). pos/next_pos are 0-based. */
+typedef struct {
+    int32_t refID, pos, next_refID, next_pos, l_seq;
+    uint16_t flag;
+    uint8_t mapq, pad;
+} hc_pair_t;
+
+int hc_version(void);
+int hc_last_error(char *h_buf, size_t n);
+/* number of SMs / bytes of HBM of the current device (for grid sizing by the caller) */
+int hc_set_device(int device);
+int hc_device_info(int *h_sm_count, size_t *h_total_mem, int *h_cc_major, int *h_cc_minor);
+
+/* ---------------------------------------------------------------------------------------
+ * K1  read pair -> window binning.   Replaces the per-line loop of bam2arrays
+ * (bam2clusters.py:128-166, get_window :119-126, samtools filter :108-117) and, with
+ * window_bp = UINT32_MAX (one window per contig), the Counter loop of _bam2array (:197-202).
+ *
+ * counts is the FULL (not triangular) u32 matrix block rows [row0,row1) x n_windows with
+ * row = window of read 1, column = window of the mate; hc_fold_counts() turns it into the
+ * reference's upper-triangular float32 array or into the symmetrised matrix.
+ *
+ * offsets[c]  = chr2window[ii][contig c]  (first window of contig c, -1 = absent)
+ * member[c]   = chr2window[0][contig c]   (membership test of :151; NULL = same as offsets)
+ * region_mask = per-contig 0/1 for ``samtools view bam <contig>...`` (NULL = no regions)
+ * n_pairs     = records to read (apply hc_upto_cutoff first for ``upto``)
+ * h_stats[8]  = {lines kept by -q/-F/regions, pairs binned, skipped (contig absent),
+ *               out-of-range, key errors, records routed through the overflow list,
+ *               fast path used (1) or atomic fallback (0), reserved}
+ * mode: bit 0 clear = auto (row-privatised shared-memory tiles; falls back to global atomics when
+ *       the input is not sorted), bit 0 set = force the global-atomic kernel;
+ *       bit 1 set = accumulate into counts (several BAM files, bam2clusters.py:133) instead of
+ *       overwriting it.
+ */
+size_t hc_bin_pairs_workspace_bytes(int64_t n_pairs, int64_t n_rows);
+int hc_bin_pairs(const hc_pair_t *pairs, int64_t n_pairs,
+                 const int32_t *offsets, const int32_t *member, const uint8_t *region_mask,
+                 int32_t n_contigs, uint32_t window_bp, int32_t n_windows,
+                 int32_t mapq_min, uint32_t skip_flag, int32_t row0, int32_t row1,
+                 uint32_t *counts, void *workspace, size_t workspace_bytes,
+                 int mode, int64_t *h_stats, void *stream);
+
+/* ``upto`` of bam2arrays (:139-141): number of leading records that contain exactly ``upto``
+ * lines surviving -q/-F/regions (n_pairs if fewer survive).  workspace >= 8*(n_pairs/4096+2). */
+int hc_upto_cutoff(const hc_pair_t *pairs, int64_t n_pairs, const uint8_t *region_mask,
+                   int32_t n_contigs, int32_t mapq_min, uint32_t skip_flag, int64_t upto,
+                   void *workspace, size_t workspace_bytes, int64_t *h_n_effective,
+                   int64_t *h_lines, void *stream);
+
+/* Contig-level side outputs of _bam2array (:183-189, region queries :179,222): for every record
+ * kept by -q/-F whose alignment [pos, pos+ref_span) overlaps a sampled region
+ * (s+1, s+minSize), s = 0, nth*minSize, ... of its contig, write keep[k]=1 and
+ * dist[k] = |tlen| (same contig) or -1 (other contig); else keep[k]=0. */
+int hc_contig_region_filter(const hc_pair_t *pairs, int64_t n_pairs, const int32_t *tlen,
+                            const int32_t *ref_span, const int32_t *contig_size,
+                            const int32_t *member, int32_t n_contigs, int32_t min_size,
+                            int32_t nth, int32_t mapq_min, uint32_t skip_flag, uint8_t *keep,
+                            int32_t *dist, void *stream);
+
+/* ---------------------------------------------------------------------------------------
+ * K2  fold / symmetrise.
+ * hc_fold_counts: counts (u32, n x n, full orientation) -> float32 n x n
+ *   mode 0: reference layout of bam2arrays: upper triangle incl. diagonal, zeros below
+ *   mode 1: symmetrised  d += d.T - diag(d)  (bam2clusters.py:42,511; bam2scaffolds.py:262),
+ *           plus ``add`` (the +1 pseudo-count of normalize(), :43); d_vmax receives max(out)
+ * out may alias counts (in place).  d_vmax: device float (may be NULL for mode 0). */
+int hc_fold_counts(const uint32_t *counts, int32_t n, int mode, float add, float *out,
+                   float *d_vmax, void *stream);
+/* in-place ``d += d.T - np.diag(d.diagonal())`` (+add) for float32 (dtype 0) / float64 (1);
+ * d_vmax (same dtype) receives max. Equivalent to array2scaffolds.py:117-118. */
+int hc_symmetrize(void *d, int32_t n, int dtype, double add, void *d_vmax, void *stream);
+/* tail of bam2array (bam2clusters.py:244): (array / sizes).T / sizes on the contig-level counts
+ * (u32, full orientation) -> float64 n x n, transposed (lower triangular) like the reference */
+int hc_contig_normalize(const uint32_t *counts, int32_t n, const int32_t *sizes, double *out,
+                        void *stream);
+
+/* ---------------------------------------------------------------------------------------
+ * K3-K5  Sinkhorn-Knopp (bin/sinkhorn_knopp/sinkhorn_knopp/sinkhorn_knopp.py:93-163 as called
+ * by normalize(), bam2clusters.py:36-49).  X is the row block [row0,row0+nrows) x n of the
+ * matrix, dtype 0 = float32 / 1 = float64; P = X / vmax elementwise in X's dtype (vmax = 1 for a
+ * plain fit).  r (nrows) and c (n) are float64.
+ *   hc_sk_colpass : ypart[b][j] = sum over rows of row-chunk b of P[i][j] * r[i]   (r NULL = ones)
+ *                   also flags negative / NaN entries on the first call (d_flags[0]/[1])
+ *   hc_sk_colfinish: y[j] = sum_b ypart[b][j]  (fixed order => deterministic)
+ *   hc_sk_update_c : c = 1/y ; d_flags[2] |= any(y == 0); if c_prev != NULL also evaluates the
+ *                   stopping test of :138-141 on column sums c_prev[j]*y[j] -> d_flags[3] = 1
+ *                   when some column is outside 1 +- eps
+ *   hc_sk_rowpass : x[i] = sum_j P[i][j]*c[j]  (c NULL = ones); r[i] = 1/x[i] if r != NULL
+ *   hc_sk_apply   : out[i][j] = (r[i]*P[i][j])*c[j]   (out dtype 0 = f32, 1 = f64)
+ * Row-sharded use: every rank runs colpass+colfinish on its block, all-reduces y (NCCL sum), then
+ * update_c / rowpass locally. */
+int32_t hc_sk_num_row_chunks(int32_t nrows);
+int hc_sk_colpass(const void *X, int dtype, int32_t nrows, int32_t n, double vmax,
+                  const double *r, double *ypart, int32_t *d_flags, void *stream);
+int hc_sk_colfinish(const double *ypart, int32_t n_chunks, int32_t n, double *y, void *stream);
+int hc_sk_update_c(const double *y, const double *c_prev, int32_t n, double eps, double *c,
+                   int32_t *d_flags, void *stream);
+int hc_sk_rowpass(const void *X, int dtype, int32_t nrows, int32_t n, double vmax,
+                  const double *c, double *x, double *r, int32_t *d_flags, void *stream);
+/* *d_flag |= any(v outside 1 +- eps): the first evaluation of the while test (:138-141) on raw P */
+int hc_sk_outside(const double *v, int32_t n, double eps, int32_t *d_flag, void *stream);
+int hc_sk_apply(const void *X, int dtype, int32_t nrows, int32_t n, double vmax, const double *r,
+                const double *c, void *out, int out_dtype, void *stream);
+
+/* ---------------------------------------------------------------------------------------
+ * K6  contacts -> distances, written straight into the linkage working matrix.
+ * Reads the UPPER triangle of X (n x n, dtype 0/1) -- the part d[np.triu_indices(n,1)]
+ * selects (bam2clusters.py:385,411; array2scaffolds.py:163) -- and writes the full symmetric
+ * float64 matrix W (n x n).  v = X[i][j], optionally balanced on the fly as
+ * (r[i]*(v/vmax))*c[j] when r != NULL.
+ *   kind 0: identity                       kind 1: (1/(a*(v+1)))**(1/b)   (bam2clusters.py:248-251,516)
+ *   kind 2: log(vmax2) - log(v+1) computed in X's dtype (array2scaffolds.py:31), p0 = vmax2
+ *   kind 3: (1/(a*v))**(1/b)  -- distance_func itself, no pseudo-count (bam2clusters.py:248-251)
+ * square != 0 stores the squared distance (fastcluster works on squares for ward).
+ * d_flags[0] is set if a NaN is produced. */
+int hc_transform_to_working(const void *X, int dtype, int32_t n, int kind, double p0, double p1,
+                            const double *r, const double *c, double vmax, int square, double *W,
+                            int32_t *d_flags, void *stream);
+/* elementwise transform of a full matrix (same kinds), out dtype = in dtype (kind 2) or f64 */
+int hc_transform(const void *X, int dtype, int64_t count, int kind, double p0, double p1,
+                 void *out, int out_dtype, void *stream);
+/* y = d[np.triu_indices(n,1)] as float64 (condensed) and the inverse expansion */
+int hc_condense(const void *X, int dtype, int32_t n, double *y, void *stream);
+int hc_expand_condensed(const double *y, int32_t n, int square, double *W, int32_t *d_flags,
+                        void *stream);
+
+/* ---------------------------------------------------------------------------------------
+ * K7  agglomerative clustering: GPU nearest-neighbour chain + Lance-Williams updates.
+ * Replaces fastcluster.linkage(y, method) (bam2clusters.py:385,403,411,430) and
+ * sch.linkage (array2scaffolds.py:163).  W is the full symmetric float64 working matrix from
+ * hc_transform_to_working / hc_expand_condensed (squared for ward) and is destroyed.
+ * method: 0 single, 1 complete, 2 average, 3 weighted, 4 ward.
+ * h_Z receives the scipy linkage array (n-1) x 4 float64 (host).  h_stats[4] = {NN scans,
+ * sum of active sizes over scans, merges, sum of active sizes over updates}. */
+size_t hc_linkage_workspace_bytes(int32_t n);
+int hc_linkage(double *W, int32_t n, int method, void *workspace, size_t workspace_bytes,
+               double *h_Z, int64_t *h_stats, void *stream);
+/* the same in two halves, so that independent linkages (the 30 bootstrap runs of cluster_contigs,
+ * bam2clusters.py:427-431, or the per-cluster trees of bam2scaffolds.py:294-298) overlap on
+ * different streams: launch is asynchronous, finish waits on the stream and labels the tree. */
+int hc_linkage_launch(double *W, int32_t n, int method, void *workspace, size_t workspace_bytes,
+                      void *stream);
+int hc_linkage_finish(int32_t n, int method, void *workspace, size_t workspace_bytes, double *h_Z,
+                      int64_t *h_stats, void *stream);
+
+/* ---------------------------------------------------------------------------------------
+ * K8  block reductions on the resident matrix.
+ * hc_segment_mean_2d: _average_reduce_2d (bam2scaffolds.py:53-71) for window->contig keys whose
+ *   windows form one contiguous run each: group k (in np.unique(keys) order) covers windows
+ *   [seg_begin[k], seg_end[k]); float32 in, float32 out (n_seg x n_seg); tmp = n_seg x n floats.
+ * hc_normalize_rows: normalize_rows (array2scaffolds.py:33-41), float32 in place;
+ *   workspace >= 20*n + 1024 bytes. */
+int hc_segment_mean_2d(const float *A, int32_t n, const int32_t *seg_begin, const int32_t *seg_end,
+                       int32_t n_seg, float *tmp, float *out, void *stream);
+int hc_normalize_rows(float *A, int32_t n, void *workspace, size_t workspace_bytes, void *stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* HICEMBLER_B200_H */

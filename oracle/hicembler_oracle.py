@@ -1,0 +1,634 @@
+"""CPU oracle for the HiCembler hot path -- TEST INFRASTRUCTURE, NOT PRODUCT CODE.
+
+Only ``tests/``, ``__graft_entry__.smoke()`` and ``bench.py``'s ``cpu_baseline`` /
+``--impl reference`` legs may import this module.  The product package
+(``hicembler_b200``) never imports anything under ``oracle/``.
+
+Every function is a literal Python-3 / numpy restatement of the reference lines it cites
+(paths relative to the reference checkout).  Python-2 traps that were resolved while
+restating: integer ``/`` is ``//``; ``round()`` of an already-floored integer is the
+identity; dict iteration order is replaced by an explicit ordered contig list.
+
+Parity pinning:
+  * Sinkhorn-Knopp: pinned.  ``SinkhornKnopp`` below is checked against the vendored
+    ``bin/sinkhorn_knopp`` (imported with a one-line py3 shim, see
+    ``oracle/make_golden.py``), against its docstring known answer
+    (``sinkhorn_knopp.py:61-69``) and its six unit tests (restated in
+    ``tests/test_oracle_sinkhorn.py``).
+  * linkage: pinned against ``scipy.cluster.hierarchy.linkage`` (the reference's own call at
+    ``array2scaffolds.py:163``) and scipy's known-answer vectors; the fastcluster NN-chain
+    restatement (``oracle/nnchain.c``) is pinned only through those (fastcluster itself is a
+    PyPI dependency absent from the reference tree and from this image) -> under exact ties
+    its merge ORDER is "parity unpinned".
+  * binning / transform / block mean: the reference holds no test or golden vector for them
+    -> "parity unpinned"; the restatement follows the cited lines literally.
+"""
+from __future__ import annotations
+
+import ctypes
+import os
+import warnings
+from collections import Counter
+
+import numpy as np
+
+# --------------------------------------------------------------------------------------
+# SAM filtering and window arithmetic
+# --------------------------------------------------------------------------------------
+SKIP_FLAG = 3980  # bam2clusters.py:108  (4+8+128+256+512+1024+2048)
+
+
+def samtools_view(lines, mapq=0, skipFlag=SKIP_FLAG):
+    """Restates ``samtools view -q mapq -F skipFlag`` (bam2clusters.py:108-117).
+
+    Yields the SAM text lines samtools would print: header lines dropped, records kept when
+    ``MAPQ >= mapq`` and ``(FLAG & skipFlag) == 0``.
+    """
+    for line in lines:
+        if line.startswith("@"):
+            continue
+        f = line.split("\t", 5)
+        if int(f[1]) & skipFlag:
+            continue
+        if int(f[4]) < mapq:
+            continue
+        yield line
+
+
+def get_window(chrom, start, length, windowSize, chr2window):
+    """bam2clusters.py:119-126 (copies: fastq2array.py:146-153, bam2plot.py:96-103).
+
+    Py2: ``pos = int(start+round((end-start)/2))`` with integer ``/``.
+    """
+    end = start + length
+    pos = int(start + round((end - start) // 2))
+    window = pos // windowSize + chr2window[chrom]
+    return window
+
+
+def bam2arrays(windows, windowSize, chr2window, sam, mapq, upto=0, regions=(), verbose=0):
+    """bam2clusters.py:128-166.  ``sam`` is a list of iterables of SAM text lines (one per
+    BAM); each stands for the ``samtools view`` pipe of that BAM *before* -q/-F filtering.
+
+    ``regions`` restates ``samtools view bam <contig>...``: only records whose RNAME is one of
+    the region contigs are printed (whole-contig regions, the only form the live pipeline
+    passes to this function, bam2scaffolds.py:244).
+    """
+    arrays = [np.zeros((len(w), len(w)), dtype="float32") for w in windows]
+    i = 1
+    regions = set(regions)
+    for _sam in sam:
+        stream = samtools_view(_sam, mapq)
+        if regions:
+            stream = (l for l in stream if l.split("\t", 3)[2] in regions)
+        for i, line in enumerate(stream, i):
+            if upto and i > upto:
+                break
+            ref1, start1, _mapq, cigar, ref2, start2, insertSize, seq = line.split("\t")[2:10]
+            start1, start2, seqlen = int(start1), int(start2), len(seq)
+            if ref2 == "=":
+                ref2 = ref1
+            if ref1 not in chr2window[0] or ref2 not in chr2window[0]:
+                continue
+            for ii in range(len(windowSize)):
+                w1 = get_window(ref1, start1, seqlen, windowSize[ii], chr2window[ii])
+                w2 = get_window(ref2, start2, seqlen, windowSize[ii], chr2window[ii])
+                if w2 < w1:
+                    w1, w2 = w2, w1
+                arrays[ii][w1][w2] += 1
+    return arrays
+
+
+def bin_records(rec, window_bp, offsets, n_windows, mapq, skip_flag=SKIP_FLAG, upto=0,
+                member=None, region_mask=None):
+    """Vectorised numpy form of the same arithmetic over decoded pair records
+     -- used where the literal per-line loop is too slow.
+
+    rec: structured array with refID,pos,next_refID,next_pos,l_seq,flag,mapq (0-based pos).
+    offsets: int64[n_contigs], -1 = contig absent from chr2window.
+    Returns float32 upper-triangular (n_windows, n_windows), as bam2arrays does.
+    """
+    keep = ((rec["flag"].astype(np.int64) & skip_flag) == 0) & (rec["mapq"] >= mapq)
+    if region_mask is not None:
+        keep &= region_mask[rec["refID"]].astype(bool)
+    if upto:
+        keep &= np.cumsum(keep) <= upto
+    member = offsets if member is None else member
+    r = rec[keep]
+    ok = (member[r["refID"]] >= 0) & (member[r["next_refID"]] >= 0)
+    r = r[ok]
+    L = np.maximum(r["l_seq"].astype(np.int64), 1)
+    p1 = r["pos"].astype(np.int64) + 1 + L // 2
+    p2 = r["next_pos"].astype(np.int64) + 1 + L // 2
+    o1, o2 = offsets[r["refID"]], offsets[r["next_refID"]]
+    if np.any(o1 < 0) or np.any(o2 < 0):
+        raise KeyError("contig present in chr2window[0] but absent for this window size")
+    w1 = p1 // window_bp + o1
+    w2 = p2 // window_bp + o2
+    lo, hi = np.minimum(w1, w2), np.maximum(w1, w2)
+    if len(hi) and hi.max() >= n_windows:
+        raise IndexError("window index out of range")
+    flat = np.bincount(lo * n_windows + hi, minlength=n_windows * n_windows)
+    # the reference accumulates float32 += 1, which is exact below 2**24 per cell
+    assert flat.max(initial=0) < (1 << 24)
+    return flat.reshape(n_windows, n_windows).astype(np.float32)
+
+
+# --------------------------------------------------------------------------------------
+# contig-level matrix (bam2clusters.py:168-246)
+# --------------------------------------------------------------------------------------
+def contig_regions(contig2size, chr2window, minSize, nth=5):
+    """bam2clusters.py:222 -- sampled regions (s+1, s+minSize) every nth*minSize bp."""
+    return {c: np.array([(s + 1, s + minSize)
+                         for s in range(0, contig2size[c] + 1 - minSize, nth * minSize)])
+            for c in chr2window}
+
+
+def samtools_region_lines(lines, regions_of):
+    """Restates ``samtools view bam c:s-e ...`` on a coordinate-sorted BAM: a record is
+    printed once per region its alignment [POS, POS+reflen-1] overlaps (regions here are
+    disjoint).  reflen is taken from the CIGAR (M/D/N/=/X consume the reference)."""
+    import re
+    cig = re.compile(r"(\d+)([MIDNSHP=X])")
+    for line in lines:
+        f = line.split("\t", 7)
+        reg = regions_of.get(f[2])
+        if reg is None or not len(reg):
+            continue
+        pos = int(f[3])
+        reflen = sum(int(n) for n, op in cig.findall(f[5]) if op in "MDN=X") or 1
+        end = pos + reflen - 1
+        hits = int(np.sum((reg[:, 0] <= end) & (reg[:, 1] >= pos)))
+        for _ in range(hits):
+            yield line
+
+
+def _bam2array(sam, contigs, mapq, contig2size, chr2window, c2regions):
+    """bam2clusters.py:168-206 (one worker)."""
+    data = Counter()
+    c2dists = {c: [] for c in contigs}
+    i = 0
+    stream = samtools_region_lines(samtools_view(sam, mapq), {c: c2regions[c] for c in contigs})
+    for i, line in enumerate(stream, 1):
+        ref1, start1, _mapq, cigar, ref2, start2, isize, seq = line.split("\t")[2:10]
+        start1, start2, seqlen, isize = int(start1), int(start2), len(seq), abs(int(isize))
+        if ref2 == "=":
+            ref2 = ref1
+        else:
+            isize = -1
+        c2dists[ref1].append(isize)
+        start2 += seqlen // 2
+        if ref2 in chr2window and np.any([c2regions[ref2][:, 0] <= start2,
+                                          c2regions[ref2][:, 1] >= start2]):
+            w1, w2 = chr2window[ref1], chr2window[ref2]
+            if w2 < w1:
+                w1, w2 = w2, w1
+            data[(w1, w2)] += 1
+    return data, i, c2dists
+
+
+def bam2array(windows, contig2size, chr2window, sam, mapq=10, upto=0, regions=(),
+              minSize=2000, threads=4, nth=5):
+    """bam2clusters.py:208-246 with the Pool replaced by a serial loop over the same
+    strided contig subsets (the result is a sum of Counters, order-independent)."""
+    array = np.zeros((len(windows), len(windows)), dtype="float32")
+    regions = list(regions) if len(regions) else list(chr2window.keys())
+    threads = min(threads, len(regions))
+    i = 0
+    c2dists = {}
+    c2regions = contig_regions(contig2size, chr2window, minSize, nth)
+    sizes = [len(c2regions[c]) for c, s, e in windows]
+    for _sam in sam:
+        _sam = list(_sam)
+        for ii in range(threads):
+            wdata, algs, _c2dists = _bam2array(_sam, regions[ii::threads], mapq, contig2size,
+                                               chr2window, c2regions)
+            i += algs
+            for (w1, w2), c in wdata.items():
+                array[w1][w2] += c
+            for c in _c2dists:
+                c2dists.setdefault(c, [])
+                c2dists[c] += _c2dists[c]
+    array = (array / sizes).T / sizes
+    return array, c2dists
+
+
+# --------------------------------------------------------------------------------------
+# window tables
+# --------------------------------------------------------------------------------------
+def get_N_and_L(sizes, genomeFrac=0.5):
+    """bin/FastaIndex/FastaIndex.py:304-325 (N only)."""
+    genomeSize = sum(sizes)
+    totsize = 0
+    size = 0
+    for size in sorted(sizes, reverse=True):
+        totsize += size
+        if totsize >= genomeFrac * genomeSize:
+            break
+    return size
+
+
+def contigs2windows(contig_sizes, minSize=2000, genomeFrac=0.95, contigs=()):
+    """bam2clusters.py:73-106.  ``contig_sizes`` is an ORDERED list of (name, size) standing
+    for FastaIndex iteration order (explicit)."""
+    contigs = set(contigs)
+    windows, chr2window = [], {}
+    contig2size = dict(contig_sizes)
+    n90 = get_N_and_L([s for _, s in contig_sizes], genomeFrac)
+    if n90 > minSize:
+        minSize = n90
+    for c, size in contig_sizes:
+        if size < minSize:
+            continue
+        elif contigs and c not in contigs:
+            continue
+        chr2window[c] = len(windows)
+        windows.append((c, 0, size))
+    return minSize, windows, chr2window, contig2size
+
+
+def fasta2windows(contig_sizes, windowSize, skipShorter=1, minSize=2000, contigs=(),
+                  filterwindows=1):
+    """bam2scaffolds.py:73-124; windowSize in kb.  Returns (windowSize_bp, windows,
+    chr2window, base2chr, genomeSize)."""
+    sizes = [s for _, s in contig_sizes]
+    genome_total = sum(sizes)
+    windowSize = list(windowSize)
+    if filterwindows:
+        maxchrlen = max(sizes)
+        windowSize = [x for x in windowSize if 1000 * x < maxchrlen
+                      and 1000 * x < 0.01 * genome_total and 1000 * x > 0.000001 * genome_total]
+    windowSize = [w * 1000 for w in windowSize]
+    windows, chr2window = [[] for w in windowSize], [{} for w in windowSize]
+    genomeSize = 0
+    base2chr = {}
+    contigs = set(contigs)
+    for c, size in contig_sizes:
+        if contigs and c not in contigs:
+            continue
+        if skipShorter and size < min(windowSize) or size < minSize:
+            continue
+        for ii in range(len(windowSize)):
+            if skipShorter and size < windowSize[ii]:
+                continue
+            chr2window[ii][c] = len(windows[ii])
+            start = 0
+            for start in range(0, size, windowSize[ii]):
+                windows[ii].append((c, start, start + windowSize[ii]))
+            if not skipShorter:
+                windows[ii][-1] = (c, start, size)
+        base2chr[genomeSize + size // 2] = c
+        genomeSize += size
+    return windowSize, windows, chr2window, base2chr, genome_total
+
+
+# --------------------------------------------------------------------------------------
+# symmetrise / normalise / transform
+# --------------------------------------------------------------------------------------
+def symmetrize(d):
+    """bam2clusters.py:42,274,511; bam2scaffolds.py:262 (in place)."""
+    d += d.T - np.diag(d.diagonal())
+    return d
+
+
+def symmetrize_halfdiag(d):
+    """array2scaffolds.py:117-118, bam2scaffolds.py:32-33 (in place)."""
+    d += d.T
+    d -= np.diag(d.diagonal() / 2)
+    return d
+
+
+class SinkhornKnopp:
+    """Literal restatement of bin/sinkhorn_knopp/sinkhorn_knopp/sinkhorn_knopp.py:73-163
+    (``IntType, FloatType`` -> ``int, float``)."""
+
+    def __init__(self, max_iter=1000, epsilon=1e-3):
+        assert type(max_iter) is int or type(max_iter) is float, \
+            "max_iter is not of type int or float: %r" % max_iter
+        assert max_iter > 0, "max_iter must be greater than 0: %r" % max_iter
+        self._max_iter = int(max_iter)
+        assert type(epsilon) is float or type(epsilon) is int, \
+            "epsilon is not of type float or int: %r" % epsilon
+        assert epsilon > 0 and epsilon < 1, \
+            "epsilon must be between 0 and 1 exclusive: %r" % epsilon
+        self._epsilon = epsilon
+        self._stopping_condition = None
+        self._iterations = 0
+        self._D1 = np.ones(1)
+        self._D2 = np.ones(1)
+
+    def fit(self, P, materialize=True):
+        """``materialize=False`` skips the dense diag GEMMs (O(N^3)) and builds the same
+        P_eps by broadcasting -- identical products, used only for large-N oracle runs."""
+        P = np.asarray(P)
+        assert np.all(P >= 0)
+        assert P.ndim == 2
+        assert P.shape[0] == P.shape[1]
+        N = P.shape[0]
+        max_thresh = 1 + self._epsilon
+        min_thresh = 1 - self._epsilon
+        r = np.ones((N, 1))
+        pdotr = P.T.dot(r)
+        msg = "Matrix P must have total support. See documentation"
+        if not np.all(pdotr != 0):
+            warnings.warn(msg, UserWarning)
+        with np.errstate(divide="ignore", invalid="ignore"):
+            c = 1 / pdotr
+            pdotc = P.dot(c)
+            if not np.all(pdotc != 0):
+                warnings.warn(msg, UserWarning)
+            r = 1 / pdotc
+            del pdotr, pdotc
+
+            def scaled(r, c):
+                if materialize:
+                    self._D1 = np.diag(np.squeeze(r))
+                    self._D2 = np.diag(np.squeeze(c))
+                    return self._D1.dot(P).dot(self._D2)
+                self._D1, self._D2 = np.squeeze(r), np.squeeze(c)
+                return (r * P) * c.T
+
+            P_eps = np.copy(P)
+            while np.any(np.sum(P_eps, axis=1) < min_thresh) \
+                    or np.any(np.sum(P_eps, axis=1) > max_thresh) \
+                    or np.any(np.sum(P_eps, axis=0) < min_thresh) \
+                    or np.any(np.sum(P_eps, axis=0) > max_thresh):
+                c = 1 / P.T.dot(r)
+                r = 1 / P.dot(c)
+                P_eps = scaled(r, c)
+                self._iterations += 1
+                if self._iterations >= self._max_iter:
+                    self._stopping_condition = "max_iter"
+                    break
+            if not self._stopping_condition:
+                self._stopping_condition = "epsilon"
+            P_eps = scaled(r, c)
+        self._r, self._c = np.squeeze(r), np.squeeze(c)
+        return P_eps
+
+
+def normalize(d, max_iter=1000, epsilon=0.00001, materialize=True, sk=None):
+    """bam2clusters.py:36-49 (mutates ``d`` in place, returns a new float64 array)."""
+    sk = sk or SinkhornKnopp(max_iter=max_iter, epsilon=epsilon)
+    d += d.T - np.diag(d.diagonal())
+    d += 1
+    vmax = d.max()
+    d = sk.fit(d / vmax, materialize=materialize)
+    return d
+
+
+def distance_func(x, a, b, maxv=float("inf")):
+    """bam2clusters.py:248-251."""
+    return (1. / (a * x)) ** (1. / b)
+
+
+def contact_func(x, a, b):
+    """bam2clusters.py:253-255."""
+    return 1. / (a * x ** b)
+
+
+def transform_distance(d, a, b):
+    """bam2clusters.py:516, bam2scaffolds.py:265: ``distance_func(x+1, *params)``."""
+    return distance_func(d + 1, a, b)
+
+
+def transform_logmax(x):
+    """array2scaffolds.py:31."""
+    return np.log(np.max(x + 1)) - np.log(x + 1)
+
+
+def normalize_rows(a):
+    """array2scaffolds.py:33-41 / bam2scaffolds.py:43-51 (in place)."""
+    rows, cols = a.shape
+    maxv = a.sum(axis=0).max()
+    for i in range(rows):
+        if a[i].max():
+            a[i] *= 1. * maxv / a[i].sum()
+    return a
+
+
+def normalize_diagional(d, bin_chr, bin_position):
+    """bam2clusters.py:51-66."""
+    indices = d.diagonal() != 0
+    d = d[indices, :]
+    d = d[:, indices]
+    bin_chr = bin_chr[indices]
+    bin_position = bin_position[indices, :]
+    d += d.T
+    d -= np.diag(d.diagonal() / 2)
+    n2 = np.mean(d.diagonal()) / d.diagonal()
+    d *= (d * n2).T * n2
+    return d, bin_chr, bin_position
+
+
+def _func_reduce(A, keys, func, allkeys=None):
+    """bam2scaffolds.py:53-65."""
+    unique_keys = np.unique(keys)
+    if allkeys is None:
+        allkeys = unique_keys
+    newshape = (len(allkeys),) + A.shape[1:]
+    newA = np.zeros(newshape, dtype=A.dtype)
+    for i, k in enumerate(allkeys):
+        indices = (keys == k)
+        newA[i] = func(A[indices], axis=0)
+    return newA
+
+
+def _average_reduce(A, keys):
+    return _func_reduce(A, keys, func=np.mean)
+
+
+def _average_reduce_2d(A, keys):
+    """bam2scaffolds.py:70-71."""
+    return _average_reduce(_average_reduce(A, keys).T, keys).T
+
+
+def condense(d):
+    """``d[np.triu_indices(n, 1)]`` -- bam2clusters.py:385,403,411,430; array2scaffolds.py:163."""
+    return d[np.triu_indices(d.shape[0], 1)]
+
+
+# --------------------------------------------------------------------------------------
+# linkage
+# --------------------------------------------------------------------------------------
+METHODS = {"single": 0, "complete": 1, "average": 2, "weighted": 3, "ward": 4}
+_HERE = os.path.dirname(os.path.abspath(__file__))
+_nn = None
+
+
+def _nnchain_lib():
+    global _nn
+    if _nn is None:
+        path = os.path.join(_HERE, "libnnchain.so")
+        if not os.path.exists(path):
+            import subprocess
+            subprocess.check_call(["make", "-s", "-C", _HERE, "libnnchain.so"])
+        _nn = ctypes.CDLL(path)
+        _nn.fc_linkage.restype = ctypes.c_int
+        _nn.fc_linkage.argtypes = [ctypes.c_int64, ctypes.c_void_p, ctypes.c_int,
+                                   ctypes.c_void_p, ctypes.c_void_p]
+    return _nn
+
+
+def linkage_fastcluster(y, method="ward", return_stats=False):
+    """``fastcluster.linkage(y, method)`` (call sites bam2clusters.py:385,403,411,430) through
+    the C restatement of its NN-chain (oracle/nnchain.c; fastcluster is a PyPI dependency,
+    1.1.x, not vendored in the reference)."""
+    y = np.array(y, dtype=np.float64, order="C", copy=True)
+    NN = len(y)
+    N = int(np.ceil(np.sqrt(NN * 2)))
+    if (N * (N - 1) // 2) != NN:
+        raise ValueError("The length of the condensed distance matrix must be (k \\choose 2) "
+                         "for k data points!")
+    Z = np.empty((max(N - 1, 0), 4))
+    stats = np.zeros(4, dtype=np.int64)
+    if N > 1:
+        rc = _nnchain_lib().fc_linkage(N, y.ctypes.data, METHODS[method], Z.ctypes.data,
+                                       stats.ctypes.data)
+        if rc == -1:
+            raise FloatingPointError("NaN dissimilarity value.")
+        if rc:
+            raise RuntimeError("nnchain oracle failed: %d" % rc)
+    return (Z, stats) if return_stats else Z
+
+
+def linkage_fastcluster_py(y, method="ward"):
+    """Pure-Python restatement of the same algorithm for small N;
+    cross-checks the C restatement."""
+    y = np.array(y, dtype=np.float64)
+    NN = len(y)
+    N = int(np.ceil(np.sqrt(NN * 2)))
+    assert N * (N - 1) // 2 == NN
+    if np.isnan(y).any():
+        raise FloatingPointError("NaN dissimilarity value.")
+    D = np.zeros((N, N))
+    D[np.triu_indices(N, 1)] = y
+    if method == "ward":
+        D = D * D
+
+    def g(i, j):
+        return D[i, j] if i < j else D[j, i]
+
+    def s(i, j, v):
+        if i < j:
+            D[i, j] = v
+        else:
+            D[j, i] = v
+
+    members = [1] * N
+    active = list(range(N))
+    chain = [0] * N
+    tip = 0
+    rec = []
+    for _ in range(N - 1):
+        if tip <= 3:
+            a = active[0]
+            chain[0] = a
+            tip = 1
+            b = active[1]
+            m = g(a, b)
+            for i in active[2:]:
+                if g(a, i) < m:
+                    m = g(a, i)
+                    b = i
+        else:
+            tip -= 3
+            a = chain[tip - 1]
+            b = chain[tip]
+            m = g(a, b)
+        while True:
+            chain[tip] = b
+            for i in active:
+                if i != b and g(i, b) < m:
+                    m = g(i, b)
+                    a = i
+            b = a
+            a = chain[tip]
+            tip += 1
+            if b == chain[tip - 2]:
+                break
+        rec.append((a, b, m))
+        i1, i2 = (a, b) if a < b else (b, a)
+        n1, n2 = float(members[i1]), float(members[i2])
+        members[i2] += members[i1]
+        active.remove(i1)
+        for k in active:
+            if k == i2:
+                continue
+            if method == "average":
+                sa, t = n1 / (n1 + n2), n2 / (n1 + n2)
+                s(k, i2, sa * g(k, i1) + t * g(k, i2))
+            elif method == "ward":
+                v = float(members[k])
+                s(k, i2, ((v + n1) * g(k, i1) - v * m + (v + n2) * g(k, i2)) / (n1 + n2 + v))
+            elif method == "complete":
+                s(k, i2, max(g(k, i1), g(k, i2)))
+            elif method == "single":
+                s(k, i2, min(g(k, i1), g(k, i2)))
+            elif method == "weighted":
+                s(k, i2, (g(k, i1) + g(k, i2)) * .5)
+    h = np.array([r[2] for r in rec])
+    if method == "ward":
+        h = np.sqrt(h)
+    order = np.argsort(h, kind="stable")
+    parent = list(range(2 * N - 1))
+    size = [1] * (2 * N - 1)
+
+    def find(x):
+        root = x
+        while parent[root] != root:
+            root = parent[root]
+        while parent[x] != root:
+            parent[x], x = root, parent[x]
+        return root
+
+    Z = np.empty((N - 1, 4))
+    nxt = N
+    for row, k in enumerate(order):
+        a, b = find(rec[k][0]), find(rec[k][1])
+        parent[a] = parent[b] = nxt
+        size[nxt] = size[a] + size[b]
+        Z[row] = (min(a, b), max(a, b), h[k], size[nxt])
+        nxt += 1
+    return Z
+
+
+def linkage_scipy(y, method="ward"):
+    """``sch.linkage(y, method)`` -- array2scaffolds.py:163 (the real library, importable)."""
+    import scipy.cluster.hierarchy as sch
+    return sch.linkage(y, method=method)
+
+
+def array2Z(d, method="ward", lib="fastcluster"):
+    """Linkage part of array2tree: bam2clusters.py:385 (fastcluster) /
+    array2scaffolds.py:163 (scipy)."""
+    y = condense(d)
+    return linkage_fastcluster(y, method) if lib == "fastcluster" else linkage_scipy(y, method)
+
+
+def cluster_contigs(d, bin_chr, frac=0.66, iterations=30, maxnumchr=500, minchr=3, nchr=0,
+                    selections=None, prng=None):
+    """bam2clusters.py:406-457 without the plots.  The reference draws from the global
+    unseeded ``np.random`` (:410,429); ``selections`` (list of index arrays) or ``prng``
+    make the draw injectable.  Returns (clusters, nchr, Z, mean_step_len)."""
+    import scipy.cluster.hierarchy as sch
+    prng = prng or np.random
+    Z = linkage_fastcluster(condense(d), "ward")
+    mean_step_len = None
+    if not nchr:
+        dZ = []
+        n = d.shape[0]
+        subset = int(round(n * frac))
+        if subset < maxnumchr:
+            maxnumchr = subset - 1
+        for i in range(iterations):
+            selection = selections[i] if selections is not None else prng.permutation(n)[:subset]
+            iZ = linkage_fastcluster(condense(d[selection, :][:, selection]), "ward")
+            dZ.append(np.diff(iZ[:, 2]))
+        mean_step_len = np.mean(np.array(dZ), 0)
+        nchr = int(np.argmax(mean_step_len[-minchr + 1::-1][:maxnumchr]) + minchr)
+    clusters = [[] for n in range(nchr)]
+    assignments = sch.fcluster(Z, t=nchr, criterion="maxclust")
+    for i, c in zip(assignments - 1, bin_chr):
+        clusters[i].append(c)
+    return clusters, nchr, Z, mean_step_len
