@@ -157,79 +157,81 @@ class SinkhornResult:
     __slots__ = ("r", "c", "iterations", "stopping_condition", "warned")
 
 
+class _CudaSinkhornPasses:
+    """The per-rank kernels behind sk_driver.sinkhorn_driver: one row block of P = X / vmax."""
+
+    def __init__(self, X, vmax, epsilon):
+        _dev(X)
+        self.L = _lib.lib()
+        self.X, self.vmax, self.eps = X, float(vmax), float(epsilon)
+        self.nrows, self.n = X.shape
+        self.dt = _dtype_code(X)
+        f64 = dict(dtype=torch.float64, device=X.device)
+        self.nchunks = self.L.hc_sk_num_row_chunks(self.nrows)
+        self.ypart = torch.empty((self.nchunks, self.n), **f64)
+        self.y, self.c, self.c_new = (torch.empty(self.n, **f64) for _ in range(3))
+        self.x, self.r = torch.empty(self.nrows, **f64), torch.empty(self.nrows, **f64)
+        self.flags = torch.zeros(8, dtype=torch.int32, device=X.device)
+        self.outside = torch.zeros(1, dtype=torch.int32, device=X.device)
+        self.s = _stream()
+
+    def colpass(self, use_r, check=False):
+        """y_local = P_block^T r (r = ones when use_r is False); returns the tensor to all-reduce"""
+        L = self.L
+        _lib.check(L.hc_sk_colpass(_ptr(self.X), self.dt, self.nrows, self.n, self.vmax,
+                                   _ptr(self.r) if use_r else None, _ptr(self.ypart),
+                                   _ptr(self.flags) if check else None, self.s))
+        _lib.check(L.hc_sk_colfinish(_ptr(self.ypart), self.nchunks, self.n, _ptr(self.y), self.s))
+        return self.y
+
+    def update_c(self, test):
+        """c = 1/y; with test=True first evaluates the column-sum test on c*y -> True if outside"""
+        if test:
+            self.flags[3] = 0
+            _lib.check(self.L.hc_sk_update_c(_ptr(self.y), _ptr(self.c), self.n, self.eps, _ptr(self.c_new),
+                                             _ptr(self.flags), self.s))
+            if not bool(self.flags[3].item()):
+                return False
+            self.c, self.c_new = self.c_new, self.c
+            return True
+        _lib.check(self.L.hc_sk_update_c(_ptr(self.y), None, self.n, self.eps, _ptr(self.c), _ptr(self.flags), self.s))
+        return True
+
+    def raw_outside(self):
+        """first evaluation of the while test on P itself (row sums, column sums); local flag tensor"""
+        L = self.L
+        _lib.check(L.hc_sk_rowpass(_ptr(self.X), self.dt, self.nrows, self.n, self.vmax, None, _ptr(self.x), None,
+                                   _ptr(self.flags), self.s))
+        self.flags[4] = 0
+        _lib.check(L.hc_sk_outside(_ptr(self.x), self.nrows, self.eps, _ptr(self.outside), self.s))
+        _lib.check(L.hc_sk_outside(_ptr(self.y), self.n, self.eps, _ptr(self.outside), self.s))
+        return self.outside
+
+    def rowpass(self):
+        """r = 1/(P_block c)"""
+        _lib.check(self.L.hc_sk_rowpass(_ptr(self.X), self.dt, self.nrows, self.n, self.vmax, _ptr(self.c),
+                                        _ptr(self.x), _ptr(self.r), _ptr(self.flags), self.s))
+
+    def read_flags(self):
+        h = self.flags.tolist()
+        return dict(negative=bool(h[0]), zero_col=bool(h[2]), zero_row=bool(h[4]))
+
+    def flag_value(self, t):
+        return bool(t.item())
+
+
 def sinkhorn_fit(X, vmax=1.0, max_iter=1000, epsilon=1e-3, iterations0=0, allreduce=None):
     """Sinkhorn-Knopp scaling vectors for P = X / vmax (sinkhorn_knopp.py:93-163).
 
     X: (nrows, n) CUDA float32/float64 row block (the whole matrix when not sharded).
-    ``allreduce(y)`` sums the float64 column vector over ranks in place (row-sharded use).
-    ``iterations0`` is SinkhornKnopp._iterations carried over from earlier fits (:150-152).
-    """
-    _dev(X)
-    L = _lib.lib()
-    nrows, n = X.shape
-    dt = _dtype_code(X)
-    dev = X.device
-    f64 = dict(dtype=torch.float64, device=dev)
-    nchunks = L.hc_sk_num_row_chunks(nrows)
-    ypart = torch.empty((nchunks, n), **f64)
-    y, c, c_new = torch.empty(n, **f64), torch.empty(n, **f64), torch.empty(n, **f64)
-    x, r = torch.empty(nrows, **f64), torch.empty(nrows, **f64)
-    flags = torch.zeros(8, dtype=torch.int32, device=dev)
-    s = _stream()
-    vmax = float(vmax)
-
-    def colpass(rvec, check):
-        _lib.check(L.hc_sk_colpass(_ptr(X), dt, nrows, n, vmax, _ptr(rvec), _ptr(ypart),
-                                   _ptr(flags) if check else None, s))
-        _lib.check(L.hc_sk_colfinish(_ptr(ypart), nchunks, n, _ptr(y), s))
-        if allreduce is not None:
-            allreduce(y)
-
+    ``allreduce(t)`` sums a tensor over ranks in place (row-sharded use: the float64 column-sum
+    vector once per column pass).  ``iterations0`` is SinkhornKnopp._iterations carried over from
+    earlier fits (:150-152)."""
+    from .sk_driver import sinkhorn_driver
+    passes = _CudaSinkhornPasses(X, vmax, epsilon)
+    iterations, stop, warned = sinkhorn_driver(passes, max_iter, iterations0, allreduce)
     res = SinkhornResult()
-    res.warned = False
-    # r = ones; pdotr = P.T.dot(r); c = 1/pdotr                                  (:120-129)
-    colpass(None, True)
-    _lib.check(L.hc_sk_update_c(_ptr(y), None, n, epsilon, _ptr(c), _ptr(flags), s))
-    # raw row sums for the first evaluation of the while test on P_eps = P      (:137-141)
-    _lib.check(L.hc_sk_rowpass(_ptr(X), dt, nrows, n, vmax, None, _ptr(x), None, _ptr(flags), s))
-    outside = torch.zeros(1, dtype=torch.int32, device=dev)
-    _lib.check(L.hc_sk_outside(_ptr(x), nrows, epsilon, _ptr(outside), s))
-    _lib.check(L.hc_sk_outside(_ptr(y), n, epsilon, _ptr(outside), s))
-    flags[4] = 0
-    # pdotc = P.dot(c); r = 1/pdotc                                             (:130-134)
-    _lib.check(L.hc_sk_rowpass(_ptr(X), dt, nrows, n, vmax, _ptr(c), _ptr(x), _ptr(r), _ptr(flags), s))
-    if allreduce is not None:
-        allreduce(outside)
-    h = flags.tolist()
-    if h[0]:
-        raise AssertionError("P must be non-negative (sinkhorn_knopp.py:110)")
-    if h[2]:
-        warnings.warn("Matrix P must have total support. See documentation", UserWarning)
-        res.warned = True
-    if h[4]:
-        warnings.warn("Matrix P must have total support. See documentation", UserWarning)
-        res.warned = True
-    cond = bool(outside.item())
-    iterations = int(iterations0)
-    stop = None
-    if cond:
-        colpass(r, False)  # y = P^T r0
-    while cond:
-        # c = 1/(P^T r); r = 1/(P c)                                            (:143-144)
-        _lib.check(L.hc_sk_update_c(_ptr(y), None, n, epsilon, _ptr(c), _ptr(flags), s))
-        _lib.check(L.hc_sk_rowpass(_ptr(X), dt, nrows, n, vmax, _ptr(c), _ptr(x), _ptr(r), _ptr(flags), s))
-        iterations += 1
-        if iterations >= max_iter:
-            stop = "max_iter"
-            break
-        # column sums of D1.P.D2 = c * (P^T r): the next column pass doubles as the test (:138-141)
-        colpass(r, False)
-        flags[3] = 0
-        _lib.check(L.hc_sk_update_c(_ptr(y), _ptr(c), n, epsilon, _ptr(c_new), _ptr(flags), s))
-        cond = bool(flags[3].item())
-    res.r, res.c = r, c
-    res.iterations = iterations
-    res.stopping_condition = stop or "epsilon"
+    res.r, res.c, res.iterations, res.stopping_condition, res.warned = passes.r, passes.c, iterations, stop, warned
     return res
 
 

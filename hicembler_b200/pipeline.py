@@ -1,0 +1,70 @@
+"""Device-resident hot path: pair records -> windowed contact matrix -> (Sinkhorn-Knopp) ->
+distances -> linkage array, the sequence bam2clusters() / contigs2scaffold() run in the reference
+(bam2clusters.py:493-522, bam2scaffolds.py:243-266) with all N x N data staying in HBM."""
+from __future__ import annotations
+
+import torch
+
+from . import ops
+
+
+class StageTimer:
+    """CUDA-event timer per stage (events on the current stream)."""
+
+    def __init__(self, enabled=True):
+        self.enabled, self.marks = enabled, []
+
+    def mark(self, name):
+        if self.enabled:
+            e = torch.cuda.Event(enable_timing=True)
+            e.record()
+            self.marks.append((name, e))
+
+    def result_ms(self):
+        if not self.marks:
+            return {}
+        self.marks[-1][1].synchronize()
+        out = {}
+        for (n0, e0), (n1, e1) in zip(self.marks[:-1], self.marks[1:]):
+            out[n1] = out.get(n1, 0.0) + e0.elapsed_time(e1)
+        return out
+
+
+def pairs_to_dendrogram(records, offsets, window_bp, n_windows, mapq=10, params=(0.5, 1.1), method="ward",
+                        balance=False, max_iter=1000, epsilon=0.00001, keep=False, timer=None,
+                        member=None, region_mask=None, workspace=None):
+    """records: int32 [P,6] CUDA tensor; offsets: int32 CUDA table refID -> first window.
+
+    balance=False is the reference at HEAD (normalize() commented out, bam2clusters.py:512);
+    balance=True applies normalize() (:36-49) before distance_func(x+1, a, b) (:516).
+    Returns dict(Z, stats, [r, c, sk_iterations, sk_stop, working, sym])."""
+    t = timer or StageTimer(False)
+    t.mark("start")
+    counts, st = ops.bin_pairs(records, offsets, window_bp, n_windows, mapq, member=member,
+                               region_mask=region_mask, workspace=workspace, return_stats=True)
+    t.mark("bin_pairs")
+    out = {"stats": st}
+    a, b = params
+    if balance:
+        S1, vmax = ops.fold_counts(counts, "sym", add=1.0, inplace=True)
+        t.mark("fold")
+        vm = float(vmax.item())
+        res = ops.sinkhorn_fit(S1, vm, max_iter, epsilon)
+        t.mark("sinkhorn")
+        out.update(r=res.r, c=res.c, sk_iterations=res.iterations, sk_stop=res.stopping_condition, vmax=vm)
+        W, flags = ops.transform_to_working(S1, ops.KIND_POWER, a, b, res.r, res.c, vm, square=(method == "ward"))
+        sym = S1
+    else:
+        S, vmax = ops.fold_counts(counts, "sym", inplace=True)
+        t.mark("fold")
+        W, flags = ops.transform_to_working(S, ops.KIND_POWER, a, b, square=(method == "ward"))
+        sym = S
+    t.mark("transform")
+    if keep:
+        out["working"] = W.clone()
+        out["sym"] = sym
+    Z, lst = ops.linkage_working(W, method, nan_flags=flags, return_stats=True)
+    t.mark("linkage")
+    out["Z"] = Z
+    out["linkage_stats"] = lst
+    return out

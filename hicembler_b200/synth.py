@@ -149,3 +149,9 @@ CONFIGS = {
     "C3": dict(n_contigs=10_000, n_windows=50_000, window_bp=60_000, n_chrom=23,
                n_pairs=500_000_000, method="ward"),
 }
+
+CONFIG_DESCRIPTIONS = {
+    "C1": "synthetic 200-contig 20 Mb genome, 1M pairs, 10 kb windows (N=2000), ward",
+    "C2": "synthetic 2k-contig 500 Mb assembly, 50M pairs, 50 kb windows (N=10000), average linkage",
+    "C3": "synthetic 10k-contig 3 Gb human-like assembly, 500M pairs, 60 kb windows (N=50000), ward",
+}

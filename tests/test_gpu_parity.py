@@ -1,0 +1,504 @@
+"""Parity of the CUDA path (through the C ABI) against the CPU oracle on the same seeded inputs.
+
+Bars (BASELINE.json north_star): contact counts bit-exact; balanced matrix <= 1e-5 relative with
+identical iteration count / stopping condition; identical linkage merge order (Z[:, :2], Z[:, 3])
+with heights <= 1e-5 relative (we hold them to 1e-12)."""
+import os
+import warnings
+
+import numpy as np
+import pytest
+
+import hicembler_oracle as O
+from util import hic_like_counts, sam_lines, small_case
+
+pytestmark = pytest.mark.gpu
+
+torch = pytest.importorskip("torch")
+
+
+@pytest.fixture(scope="module", autouse=True)
+def _need_cuda(cuda):
+    # the product path must be the CUDA library: fail loudly if it is missing
+    from hicembler_b200 import _lib
+    assert os.path.exists(_lib.LIB_PATH), "libhicembler_b200.so not built"
+    _lib.lib()
+
+
+def _tables(g, ws_kb=(5,), **kw):
+    return O.fasta2windows(g.contig_sizes, list(ws_kb), minSize=2000, filterwindows=0, **kw)
+
+
+def _bam(g, rec):
+    return {"records": rec, "names": g.names}
+
+
+# ------------------------------------------------------------------------------------------
+# K1 binning
+# ------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("kw", [dict(), dict(with_mates=True, bad_flag_frac=0.02, vary_len=True),
+                                dict(sort=False)])
+def test_bam2arrays_multi_window_bit_exact(kw):
+    from hicembler_b200.bam2clusters import bam2arrays
+    g, rec = small_case(n_pairs=20000, **kw)
+    wsz, windows, chr2window, _, _ = _tables(g, (5, 10, 2))
+    want = O.bam2arrays(windows, wsz, chr2window, [sam_lines(g, rec)], 10)
+    got = bam2arrays(windows, wsz, chr2window, [_bam(g, rec)], 10, verbose=0)
+    assert len(got) == 3
+    for a, b in zip(got, want):
+        assert a.dtype == np.float32 and np.array_equal(a, b)
+
+
+@pytest.mark.parametrize("mode", [0, 1])
+@pytest.mark.parametrize("env", [dict(), dict(HC_BIN_MAX_CELLS="700", HC_BIN_ROWS="3")])
+def test_bin_pairs_paths_agree(mode, env, monkeypatch):
+    """shared-memory tile path (also with several column segments / odd tile heights) and the
+    global-atomic path give the same full-orientation counts"""
+    from hicembler_b200 import ops
+    for k, v in env.items():
+        monkeypatch.setenv(k, v)
+    g, rec = small_case(n_contigs=40, n_windows=1000, window_bp=5000, n_chrom=4, n_pairs=300000, seed=9)
+    off = torch.from_numpy(g.window_offsets().astype(np.int32)).cuda()
+    cnt, st = ops.bin_pairs(ops.to_device_records(rec), off, g.window_bp, 1000, 10, mode=mode, return_stats=True)
+    full = cnt.cpu().numpy().astype(np.int64)
+    want = O.bin_records(rec, g.window_bp, g.window_offsets(), 1000, 10)
+    got = np.triu(full + full.T - np.diag(full.diagonal()))
+    assert np.array_equal(got, want.astype(np.int64))
+    assert st["binned"] == int(want.sum()) and st["fast_path"] == (mode == 0)
+    kept = ((rec["flag"] & 3980) == 0) & (rec["mapq"] >= 10)
+    assert st["lines"] == int(kept.sum())
+    up, _ = ops.fold_counts(cnt, "upper")
+    assert np.array_equal(up.cpu().numpy(), want)
+
+
+def test_unsorted_input_falls_back_and_stays_exact():
+    from hicembler_b200 import ops
+    g, rec = small_case(n_contigs=40, n_windows=1000, window_bp=5000, n_chrom=4, n_pairs=400000, seed=3, sort=False)
+    off = torch.from_numpy(g.window_offsets().astype(np.int32)).cuda()
+    cnt, st = ops.bin_pairs(ops.to_device_records(rec), off, g.window_bp, 1000, 10, return_stats=True)
+    up, _ = ops.fold_counts(cnt, "upper")
+    assert np.array_equal(up.cpu().numpy(), O.bin_records(rec, g.window_bp, g.window_offsets(), 1000, 10))
+
+
+def test_nearly_sorted_input_uses_overflow_list():
+    from hicembler_b200 import ops
+    g, rec = small_case(n_contigs=40, n_windows=1000, window_bp=5000, n_chrom=4, n_pairs=300000, seed=4)
+    rec = rec.copy()
+    rng = np.random.default_rng(0)
+    idx = rng.choice(len(rec), 500, replace=False)
+    rec[idx] = rec[rng.permutation(idx)]       # 500 records out of place
+    off = torch.from_numpy(g.window_offsets().astype(np.int32)).cuda()
+    cnt, st = ops.bin_pairs(ops.to_device_records(rec), off, g.window_bp, 1000, 10, return_stats=True)
+    assert st["fast_path"] and st["overflow"] > 0
+    up, _ = ops.fold_counts(cnt, "upper")
+    assert np.array_equal(up.cpu().numpy(), O.bin_records(rec, g.window_bp, g.window_offsets(), 1000, 10))
+
+
+def test_upto_regions_absent_contigs_two_bams():
+    from hicembler_b200.bam2clusters import bam2arrays
+    g, rec = small_case(n_pairs=3000)
+    sub = g.names[2:9]
+    wsz, windows, chr2window, _, _ = _tables(g, (5,), contigs=sub)
+    lines = sam_lines(g, rec)
+    for upto in (0, 1, 700, 10 ** 6):
+        want = O.bam2arrays(windows, wsz, chr2window, [lines, lines], 10, upto=upto, regions=sub)[0]
+        got = bam2arrays(windows, wsz, chr2window, [_bam(g, rec), _bam(g, rec)], 10, upto=upto, regions=sub, verbose=0)[0]
+        assert np.array_equal(got, want), upto
+
+
+def test_empty_input():
+    from hicembler_b200.bam2clusters import bam2arrays
+    g, rec = small_case(n_pairs=100)
+    wsz, windows, chr2window, _, _ = _tables(g, (5,))
+    got = bam2arrays(windows, wsz, chr2window, [_bam(g, rec[:0])], 10, verbose=0)[0]
+    assert got.shape == (len(windows[0]),) * 2 and not got.any()
+
+
+def test_index_and_key_errors():
+    from hicembler_b200.bam2clusters import bam2arrays
+    g, rec = small_case(n_pairs=200)
+    wsz, windows, chr2window, _, _ = _tables(g, (5,))
+    bad = rec.copy()
+    last = len(g.names) - 1
+    bad["refID"][:] = last
+    bad["next_refID"][:] = last
+    bad["pos"][:] = g.sizes[last] + 10000
+    bad["mapq"][:] = 60
+    bad["flag"][:] = 99
+    with pytest.raises(IndexError):
+        bam2arrays(windows, wsz, chr2window, [_bam(g, bad)], 10, verbose=0)
+    # contig in chr2window[0] but not in chr2window[1] -> KeyError like bam2clusters.py:155
+    wsz2, windows2, chr2window2, _, _ = _tables(g, (5, 10))
+    victim = g.names[int(rec["refID"][0])]
+    c2w = [dict(chr2window2[0]), {k: v for k, v in chr2window2[1].items() if k != victim}]
+    ok = rec.copy()
+    ok["mapq"][:] = 60
+    ok["flag"][:] = 99
+    with pytest.raises(KeyError):
+        bam2arrays(windows2, wsz2, c2w, [_bam(g, ok)], 10, verbose=0)
+
+
+def test_golden_binning(golden_dir):
+    from hicembler_b200 import ops, pairs
+    gld = np.load(os.path.join(golden_dir, "binning.npz"))
+    rec = np.ascontiguousarray(gld["records"]).view(pairs.PAIR_DTYPE).reshape(-1)
+    dev = ops.to_device_records(rec)
+    member = torch.from_numpy(gld["offsets0"]).cuda()
+    for ii, ws in enumerate(gld["window_bp"]):
+        a = gld["array%d" % ii]
+        off = torch.from_numpy(gld["offsets%d" % ii]).cuda()
+        cnt = ops.bin_pairs(dev, off, int(ws), a.shape[0], 10, member=member)
+        assert np.array_equal(ops.fold_counts(cnt, "upper")[0].cpu().numpy(), a)
+    n_eff, lines = ops.upto_cutoff(dev, 10, 1500)
+    a = gld["array0_upto1500"]
+    cnt = ops.bin_pairs(dev, member, int(gld["window_bp"][0]), a.shape[0], 10, n_pairs=n_eff)
+    assert lines == 1500 and np.array_equal(ops.fold_counts(cnt, "upper")[0].cpu().numpy(), a)
+
+
+def test_c1_config_counts_bit_exact():
+    """BASELINE.json configs[0]: 200 contigs, 20 Mb, 1 M pairs, 10 kb windows"""
+    from hicembler_b200 import ops, synth
+    cfg = synth.CONFIGS["C1"]
+    g = synth.make_genome(cfg["n_contigs"], cfg["n_windows"], cfg["window_bp"], cfg["n_chrom"], seed=1)
+    rec_t = synth.make_pairs(g, cfg["n_pairs"], seed=1, device="cuda")
+    rec = synth.records_numpy(rec_t)
+    off = torch.from_numpy(g.window_offsets().astype(np.int32)).cuda()
+    cnt, st = ops.bin_pairs(rec_t, off, g.window_bp, cfg["n_windows"], 10, return_stats=True)
+    want = O.bin_records(rec, g.window_bp, g.window_offsets(), cfg["n_windows"], 10)
+    assert st["fast_path"]
+    assert np.array_equal(ops.fold_counts(cnt, "upper")[0].cpu().numpy(), want)
+
+
+def test_contig_level_bam2array():
+    from hicembler_b200.bam2clusters import bam2array
+    from hicembler_b200 import pairs
+    g, rec = small_case(n_contigs=10, n_windows=80, window_bp=5000, n_pairs=6000)
+    minSize, windows, chr2window, contig2size = O.contigs2windows(g.contig_sizes, minSize=2000)
+    lines = sam_lines(g, rec)
+    want, want_d = O.bam2array(windows, contig2size, chr2window, [lines], mapq=10, minSize=minSize, threads=3)
+    _, tlen, span = pairs.sam_to_records(lines, {n: i for i, n in enumerate(g.names)})
+    got, got_d = bam2array(windows, contig2size, chr2window, [dict(records=rec, names=g.names, tlen=tlen, ref_span=span)],
+                           mapq=10, minSize=minSize, verbose=0)
+    assert got.dtype == np.float64 and np.array_equal(got, want)
+    assert set(got_d) == set(want_d)
+    for c in want_d:
+        assert sorted(got_d[c]) == sorted(want_d[c])
+
+
+# ------------------------------------------------------------------------------------------
+# K2 symmetrise
+# ------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("n", [1, 31, 64, 257])
+@pytest.mark.parametrize("dt", [np.float32, np.float64])
+def test_symmetrize_in_place(n, dt):
+    from hicembler_b200 import ops
+    d = np.random.default_rng(n).random((n, n)).astype(dt)
+    want = O.symmetrize(d.copy())
+    X = torch.from_numpy(d.copy()).cuda()
+    _, vmax = ops.symmetrize_(X)
+    assert np.array_equal(X.cpu().numpy(), want) and vmax.item() == want.max()
+    half = O.symmetrize_halfdiag(np.triu(d).copy())
+    Y = torch.from_numpy(np.triu(d).copy()).cuda()
+    ops.symmetrize_(Y)
+    assert np.array_equal(Y.cpu().numpy(), half)
+
+
+def test_fold_counts_sym_plus_one():
+    from hicembler_b200 import ops
+    rng = np.random.default_rng(2)
+    C = rng.integers(0, 50, (130, 130)).astype(np.int32)
+    X = torch.from_numpy(C).cuda()
+    up = np.triu(C + C.T - np.diag(C.diagonal())).astype(np.float32)
+    want = O.symmetrize(up.copy()) + 1
+    got, vmax = ops.fold_counts(X, "sym", add=1.0)
+    assert np.array_equal(got.cpu().numpy(), want) and vmax.item() == want.max()
+    got2, _ = ops.fold_counts(X.clone(), "sym", add=1.0, inplace=True)
+    assert np.array_equal(got2.cpu().numpy(), want)
+
+
+# ------------------------------------------------------------------------------------------
+# K3-K5 Sinkhorn-Knopp
+# ------------------------------------------------------------------------------------------
+def test_sinkhorn_reference_unit_tests():
+    """bin/sinkhorn_knopp/tests/test_sinkhorn_knopp.py:9-99 against the CUDA implementation"""
+    from hicembler_b200.sinkhorn_knopp import SinkhornKnopp
+    sk = SinkhornKnopp()
+    assert sk._max_iter == 1000 and sk._epsilon == 1e-3
+    for kw in (dict(max_iter='1'), dict(epsilon='1'), dict(max_iter=-1), dict(epsilon=1), dict(epsilon=0)):
+        with pytest.raises(AssertionError):
+            SinkhornKnopp(**kw)
+    for bad in (1, [[1, 2], [1, 2], [1, 2]], [[1, 2], [1, -1]]):
+        with pytest.raises(AssertionError):
+            SinkhornKnopp().fit(bad)
+    sk = SinkhornKnopp(max_iter=5)
+    assert sk._stopping_condition is None
+    sk.fit(np.eye(2))
+    assert sk._stopping_condition == 'epsilon'
+    sk.fit(np.array([[.011, .15], [1.71, .1]]))
+    assert sk._stopping_condition == 'max_iter' and sk._iterations == 5
+    with warnings.catch_warnings(record=True) as w:
+        warnings.simplefilter("always")
+        SinkhornKnopp().fit(np.array([[0., 0.], [1., 0.]]))
+        assert w[0].category is UserWarning
+    for P, eps in (([[1, 2], [3, 4]], 1e-3), ([[1.4, .2, 4], [3, 4, .7], [.4, 6, 1]], 1e-8)):
+        sk = SinkhornKnopp(epsilon=eps)
+        Pt = sk.fit(np.asarray(P))
+        assert sk._stopping_condition == 'epsilon'
+        for s in (Pt.sum(0), Pt.sum(1)):
+            assert np.all(s < 1 + eps) and np.all(s > 1 - eps)
+    sk = SinkhornKnopp()
+    P = np.eye(2)
+    assert np.all(sk.fit(P) == P)
+    assert sk._D1.ndim == 2 and np.all(sk._D1 == P) and np.all(sk._D2 == P)
+    # docstring known answer (sinkhorn_knopp.py:61-69)
+    P_ds = SinkhornKnopp().fit([[.011, .15], [1.71, .1]])
+    assert np.allclose(P_ds, [[0.06102561, 0.93897439], [0.93809928, 0.06190072]], atol=1e-8)
+
+
+@pytest.mark.parametrize("name", ["doc", "t2x2", "t3x3", "eye2", "rand64", "rand97_f32"])
+def test_sinkhorn_golden(golden_dir, name):
+    from hicembler_b200.sinkhorn_knopp import SinkhornKnopp
+    gold = np.load(os.path.join(golden_dir, "sinkhorn.npz"))
+    sk = SinkhornKnopp(epsilon=float(gold[name + "_eps"]))
+    out = sk.fit(gold[name + "_P"])
+    assert out.dtype == np.float64
+    assert np.allclose(out, gold[name + "_out"], rtol=1e-10, atol=0)
+    assert sk._iterations == int(gold[name + "_iter"])
+    assert sk._stopping_condition == str(gold[name + "_stop"])
+
+
+@pytest.mark.parametrize("key", ["norm150_float32", "norm257_float32", "norm120_float64"])
+def test_normalize_golden(golden_dir, key):
+    from hicembler_b200.bam2clusters import normalize
+    gold = np.load(os.path.join(golden_dir, "sinkhorn.npz"))
+    d = gold[key + "_in"].copy()
+    res = normalize(d)
+    assert np.array_equal(d, gold[key + "_mutated"])
+    want = gold[key + "_out"]
+    assert res.dtype == np.float64 and np.max(np.abs(res / want - 1)) <= 1e-5
+
+
+def test_normalize_medium_vs_oracle():
+    from hicembler_b200.bam2clusters import normalize
+    d = hic_like_counts(1203, 21)
+    want_sk = O.SinkhornKnopp(max_iter=1000, epsilon=0.00001)
+    want = O.normalize(d.copy(), sk=want_sk, materialize=False)
+    from hicembler_b200 import ops
+    from hicembler_b200.sinkhorn_knopp import SinkhornKnopp
+    X = torch.from_numpy(d.copy()).cuda()
+    _, vmax = ops.symmetrize_(X, add=1.0)
+    sk = SinkhornKnopp(max_iter=1000, epsilon=0.00001)
+    got = sk.fit_device(X, float(vmax.item())).cpu().numpy()
+    assert sk._iterations == want_sk._iterations and sk._stopping_condition == want_sk._stopping_condition
+    assert np.max(np.abs(got / want - 1)) <= 1e-5
+    res = ops.sinkhorn_fit(X, float(vmax.item()), 1000, 0.00001)
+    assert np.allclose(res.r.cpu().numpy(), want_sk._r, rtol=1e-9) and np.allclose(res.c.cpu().numpy(), want_sk._c, rtol=1e-9)
+
+
+# ------------------------------------------------------------------------------------------
+# K6 transform
+# ------------------------------------------------------------------------------------------
+def _ulp_diff(a, b):
+    a, b = np.asarray(a), np.asarray(b)
+    return np.max(np.abs(a - b) / np.spacing(np.maximum(np.abs(a), np.abs(b))))
+
+
+def test_distance_func_and_logmax():
+    from hicembler_b200.bam2clusters import distance_func
+    from hicembler_b200.array2scaffolds import transform
+    d = O.symmetrize(hic_like_counts(300, 5).astype(np.float64))
+    want = O.distance_func(d + 1, 0.37, 1.21)
+    got = distance_func(d + 1, 0.37, 1.21)
+    assert got.dtype == np.float64 and _ulp_diff(got, want) <= 2
+    assert distance_func(3.0, 0.5, 1.1) == O.distance_func(3.0, 0.5, 1.1)
+    d32 = d.astype(np.float32)
+    want32 = O.transform_logmax(d32)
+    got32 = transform(d32)
+    assert got32.dtype == np.float32 and np.max(np.abs(got32 - want32)) <= 4 * np.spacing(np.float32(want32.max()))
+    assert _ulp_diff(transform(d), O.transform_logmax(d)) <= 4
+
+
+def test_condense_and_working_matrix():
+    from hicembler_b200 import ops
+    d = np.random.default_rng(8).random((77, 77))
+    X = torch.from_numpy(d).cuda()
+    assert np.array_equal(ops.condense(X).cpu().numpy(), O.condense(d))
+    W, flags = ops.transform_to_working(X, ops.KIND_IDENTITY)
+    w = W.cpu().numpy()
+    up = np.triu(d, 1)
+    assert np.array_equal(np.triu(w, 1), up) and np.array_equal(np.tril(w, -1), up.T)
+    assert np.all(np.isinf(w.diagonal())) and flags[0].item() == 0
+    W2, _ = ops.expand_condensed(ops.condense(X), 77, square=True)
+    assert np.array_equal(np.triu(W2.cpu().numpy(), 1), up * up)
+
+
+# ------------------------------------------------------------------------------------------
+# K7 linkage
+# ------------------------------------------------------------------------------------------
+def _same_tree(Z, want, rtol=1e-12):
+    assert Z.shape == want.shape
+    assert np.array_equal(Z[:, [0, 1, 3]], want[:, [0, 1, 3]])
+    assert np.allclose(Z[:, 2], want[:, 2], rtol=rtol, atol=0)
+
+
+@pytest.mark.parametrize("method", ["ward", "average", "complete", "weighted"])
+@pytest.mark.parametrize("n", [2, 3, 5, 64, 333, 1500])
+def test_linkage_vs_oracle_random(n, method):
+    from hicembler_b200.fastcluster import linkage
+    y = np.random.default_rng(n).random(n * (n - 1) // 2)
+    Z = linkage(y, method)
+    _same_tree(Z, O.linkage_fastcluster(y, method))
+    assert np.array_equal(Z[:, 2], O.linkage_fastcluster(y, method)[:, 2])   # heights bit-identical
+
+
+@pytest.mark.parametrize("method", ["ward", "average"])
+def test_linkage_tie_heavy_and_jittered(golden_dir, method):
+    from hicembler_b200.fastcluster import linkage
+    g = np.load(os.path.join(golden_dir, "linkage.npz"))
+    for n in (40, 200, 777):
+        for tag in ("ties", "jitter"):
+            Z = linkage(g["n%d_%s_y" % (n, tag)], method)
+            want = g["n%d_%s_%s_fc" % (n, tag, method)]
+            _same_tree(Z, want)
+            assert np.array_equal(Z[:, 2], want[:, 2])
+        # tie-free input: scipy (the real library) agrees as well
+        _same_tree(linkage(g["n%d_jitter_y" % n], method), g["n%d_jitter_%s_scipy" % (n, method)])
+
+
+def test_linkage_scipy_known_answers():
+    from scipy.cluster.hierarchy.tests import hierarchy_test_data as T
+    from scipy.spatial.distance import pdist
+    from hicembler_b200.fastcluster import linkage
+    for m in ("complete", "average", "weighted"):
+        assert np.allclose(linkage(T.ytdist, m), getattr(T, "linkage_ytdist_" + m), atol=1e-10)
+    assert np.allclose(linkage(pdist(T.X), "ward"), T.linkage_X_ward, atol=1e-6)
+
+
+def test_linkage_errors():
+    from hicembler_b200.fastcluster import linkage
+    with pytest.raises(ValueError):
+        linkage(np.ones(4), "ward")
+    with pytest.raises(FloatingPointError):
+        linkage(np.array([1.0, np.nan, 2.0]), "average")
+    assert linkage(np.zeros(0), "ward").shape == (0, 4)
+
+
+def test_linkage_hic_distances_tie_heavy_medium():
+    """count-derived distances: few distinct values, ~40 % tied heights"""
+    from hicembler_b200.bam2clusters import array2Z
+    d = O.symmetrize(hic_like_counts(2500, 31, scale=6.0).astype(np.float64))
+    dist = O.transform_distance(d, 0.5, 1.1)
+    for m in ("ward", "average"):
+        want, stats = O.linkage_fastcluster(O.condense(dist), m, return_stats=True)
+        Z, st = array2Z(dist, m, return_stats=True)
+        _same_tree(Z, want)
+        assert st["scans"] == stats[0] and st["scan_active"] == stats[1]   # same chain, step for step
+
+
+def test_array2tree_newick_matches_reference_recursion():
+    import scipy.cluster.hierarchy as sch
+    from hicembler_b200.bam2clusters import array2tree, newick_from_linkage
+
+    def getNewick(node, newick, parentdist, leaf_names):   # bam2clusters.py:360-371
+        if node.is_leaf():
+            return "%s:%.2f%s" % (leaf_names[node.id], parentdist - node.dist, newick)
+        if len(newick) > 0:
+            newick = "):%.2f%s" % (parentdist - node.dist, newick)
+        else:
+            newick = ");"
+        newick = getNewick(node.get_left(), newick, node.dist, leaf_names)
+        newick = getNewick(node.get_right(), ",%s" % (newick), node.dist, leaf_names)
+        return "(%s" % (newick)
+    d = O.transform_distance(O.symmetrize(hic_like_counts(90, 3).astype(np.float64)), 0.5, 1.1)
+    names = ["c%d" % i for i in range(90)]
+    t = array2tree(d, names)
+    Z = O.array2Z(d)
+    tree = sch.to_tree(Z, False)
+    assert t.write() == getNewick(tree, "", tree.dist, names) == newick_from_linkage(Z, names)
+
+
+def test_cluster_contigs_with_injected_selections():
+    from hicembler_b200.bam2clusters import cluster_contigs
+    rng = np.random.default_rng(5)
+    n, k = 240, 6
+    lab = np.repeat(np.arange(k), n // k)
+    base = np.where(lab[:, None] == lab[None, :], 30.0, 2.0)
+    cnt = rng.poisson(base).astype(np.float64)
+    d = O.transform_distance(O.symmetrize(np.triu(cnt)), 0.5, 1.1)
+    subset = int(round(n * 0.66))
+    sels = [rng.permutation(n)[:subset] for _ in range(30)]
+    names = np.array(["c%d" % i for i in range(n)])
+    want, want_n, want_Z, want_msl = O.cluster_contigs(d, names, selections=sels)
+    got, got_n, got_Z, got_msl = cluster_contigs("", d, names, None, selections=sels, return_details=True)
+    assert got_n == want_n == k and got == want
+    assert np.array_equal(got_Z, want_Z) and np.array_equal(got_msl, want_msl)
+
+
+# ------------------------------------------------------------------------------------------
+# K8 + per-cluster sequence
+# ------------------------------------------------------------------------------------------
+def test_average_reduce_and_normalize_rows():
+    from hicembler_b200.bam2scaffolds import _average_reduce_2d, normalize_rows
+    g, rec = small_case(n_contigs=9, n_windows=70, window_bp=5000, n_pairs=30000)
+    wsz, windows, chr2window, _, _ = _tables(g, (5,))
+    d = O.symmetrize(O.bam2arrays(windows, wsz, chr2window, [sam_lines(g, rec)], 10)[0])
+    keys = np.array([c for c, s, e in windows[0]])
+    assert np.array_equal(_average_reduce_2d(d.copy(), keys), O._average_reduce_2d(d.copy(), keys))
+    a = d.copy()
+    want = O.normalize_rows(d.copy())
+    assert np.allclose(normalize_rows(a), want, rtol=2e-7, atol=0)
+
+
+def test_contigs2tree_sequence():
+    """contigs2scaffold up to the tree (bam2scaffolds.py:234-266) for one cluster, ws sweep 5/10/2 kb"""
+    from hicembler_b200.bam2scaffolds import contigs2tree
+    from hicembler_b200.FastaIndex import FastaIndex
+    g, rec = small_case(n_contigs=14, n_windows=150, window_bp=5000, n_chrom=2, n_pairs=60000, seed=12)
+    cluster = g.names[:8]
+    params = (0.5, 1.1)
+
+    class FI(FastaIndex):
+        def __init__(self, sizes):
+            self.id2stats = {c: [s] for c, s in sizes}
+            self.genomeSize = sum(s for _, s in sizes)
+    for ws in (5, 10, 2):
+        wsz, windows, chr2window, _, _ = O.fasta2windows(g.contig_sizes, [ws], contigs=set(cluster), filterwindows=0)
+        d = O.bam2arrays(windows, wsz, chr2window, [sam_lines(g, rec)], 10, regions=cluster)[0]
+        O.symmetrize(d)
+        keys = np.array([c for c, s, e in windows[0]])
+        red = O._average_reduce_2d(d, keys)
+        Z, uniq, dsym, bin_chr = contigs2tree([_bam(g, rec)], FI(g.contig_sizes), [ws], cluster, 10, params)
+        assert np.array_equal(dsym.cpu().numpy(), d) and list(uniq) == list(np.unique(keys))
+        # feed the oracle linkage the float64 distances of the float32 block means (NEP 50 promotion)
+        want = O.linkage_fastcluster(O.condense(O.distance_func(red + 1, np.float64(0.5), np.float64(1.1))), "ward")
+        _same_tree(Z, want, rtol=1e-9)
+
+
+def test_pairs_to_dendrogram_c1_end_to_end():
+    """configs[0] end to end with Sinkhorn switched on: pairs -> counts -> balance -> distance -> Z"""
+    from hicembler_b200 import ops, synth
+    from hicembler_b200.pipeline import pairs_to_dendrogram
+    cfg = synth.CONFIGS["C1"]
+    g = synth.make_genome(cfg["n_contigs"], cfg["n_windows"], cfg["window_bp"], cfg["n_chrom"], seed=2)
+    rec_t = synth.make_pairs(g, 300000, seed=2, device="cuda")
+    rec = synth.records_numpy(rec_t)
+    off = g.window_offsets()
+    res = pairs_to_dendrogram(rec_t, torch.from_numpy(off.astype(np.int32)).cuda(), g.window_bp, cfg["n_windows"],
+                              mapq=10, params=(0.5, 1.1), method="ward", balance=True, keep=True)
+    up = O.bin_records(rec, g.window_bp, off, cfg["n_windows"], 10)
+    sk = O.SinkhornKnopp(max_iter=1000, epsilon=0.00001)
+    bal = O.normalize(up.copy(), sk=sk, materialize=False)
+    assert res["sk_iterations"] == sk._iterations
+    r, c = res["r"].cpu().numpy(), res["c"].cpu().numpy()
+    assert np.allclose(r, sk._r, rtol=1e-9) and np.allclose(c, sk._c, rtol=1e-9)
+    # distances from the GPU's own r, c so that last-bit differences of pow() cannot flip ties
+    sym1 = O.symmetrize(up.copy()) + 1
+    P = sym1 / sym1.max()
+    bal_gpu = (r[:, None] * P.astype(np.float64)) * c[None, :]
+    assert np.max(np.abs(bal_gpu / bal - 1)) <= 1e-5
+    W = res["working"].cpu().numpy()
+    want_d = O.distance_func(bal_gpu + 1, 0.5, 1.1) ** 2
+    iu = np.triu_indices(cfg["n_windows"], 1)
+    assert np.allclose(W[iu], want_d[iu], rtol=1e-13)
+    want = O.linkage_fastcluster(np.sqrt(W[iu]), "ward")
+    _same_tree(res["Z"], want, rtol=1e-9)
