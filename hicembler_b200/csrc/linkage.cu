@@ -17,6 +17,7 @@
 // (no FMA contraction) in fastcluster's operation order so heights are bit-identical.
 #include <cooperative_groups.h>
 #include <math.h>
+#include <stdio.h>
 
 #include <algorithm>
 #include <numeric>
@@ -32,10 +33,10 @@ enum { M_SINGLE = 0, M_COMPLETE = 1, M_AVERAGE = 2, M_WEIGHTED = 3, M_WARD = 4 }
 constexpr int THREADS = 1024;
 constexpr int MAX_CS = 16;
 
+// (value, index) travel as an order-preserving 64-bit key + index so that the lexicographic argmin is
+// three redux.sync.min.u32 per warp instead of fifteen shuffles
 struct Slot {
-    double v;
-    int idx;
-    int pad;
+    uint32_t hi, lo, idx, pad;
 };
 
 struct LinkArgs {
@@ -46,12 +47,29 @@ struct LinkArgs {
     int *members_g;  // [cluster size][n]
     int *rec_a, *rec_b;
     double *rec_d;
-    long long *stats;  // scans, sum active over scans, merges, sum active over updates
+    long long *stats;  // scans, sum active over scans, merges, sum active over updates, cycle counters
     int chain_in_smem;
 };
 
-__device__ __forceinline__ bool lex_less(double v, int i, double bv, int bi) {
-    return v < bv || (v == bv && i < bi);
+constexpr unsigned long long KEY_NONE = 0xffffffffffffffffull;
+
+// monotone map double -> u64 (-0.0 is folded onto +0.0 first: they compare equal as doubles)
+__device__ __forceinline__ unsigned long long okey(double v) {
+    unsigned long long b = (unsigned long long)__double_as_longlong(__dadd_rn(v, 0.0));
+    return (b >> 63) ? ~b : (b | 0x8000000000000000ull);
+}
+__device__ __forceinline__ double okey_value(unsigned long long k) {
+    return __longlong_as_double((long long)((k >> 63) ? (k & 0x7fffffffffffffffull) : ~k));
+}
+
+// lexicographic (key, idx) minimum over the warp; every lane gets the result
+__device__ __forceinline__ void warp_argmin(unsigned long long &key, uint32_t &idx) {
+    const uint32_t hi = (uint32_t)(key >> 32), lo = (uint32_t)key;
+    const uint32_t mh = __reduce_min_sync(0xffffffffu, hi);
+    const uint32_t mlo = __reduce_min_sync(0xffffffffu, hi == mh ? lo : 0xffffffffu);
+    const uint32_t mi = __reduce_min_sync(0xffffffffu, (hi == mh && lo == mlo) ? idx : 0xffffffffu);
+    key = ((unsigned long long)mh << 32) | mlo;
+    idx = mi;
 }
 
 __device__ __forceinline__ double lw_update(int method, double a, double b, double m, double s1, double s2,
@@ -68,6 +86,12 @@ __device__ __forceinline__ double lw_update(int method, double a, double b, doub
     }
     }
 }
+
+__device__ __forceinline__ void cluster_barrier() {
+    asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+
+constexpr int EPT = 4;  // elements per thread per batch: all loads of a batch are issued before first use
 
 __global__ void __launch_bounds__(THREADS, 1) k_nnchain(LinkArgs a) {
     cg::cluster_group cluster = cg::this_cluster();
@@ -87,7 +111,11 @@ __global__ void __launch_bounds__(THREADS, 1) k_nnchain(LinkArgs a) {
         active[w] = rem >= 32 ? 0xffffffffu : ((1u << rem) - 1u);
     }
     for (int k = tid; k < n; k += THREADS) members[k] = 1;
+    if (tid < 2 * MAX_CS) {  // unused slots stay "none" so the combine can run over all MAX_CS
+        slots[tid].hi = slots[tid].lo = slots[tid].idx = 0xffffffffu;
+    }
     __syncthreads();
+    cluster_barrier();  // nobody publishes into a slot table that is still being initialised
 
     // column slice of this CTA
     const int S = (n + cs - 1) / cs;
@@ -97,54 +125,75 @@ __global__ void __launch_bounds__(THREADS, 1) k_nnchain(LinkArgs a) {
     int start = 0, tip = 0, idx1 = 0, idx2 = 0, nactive = n;
     double mind = 0;
     long long n_scans = 0, scan_sum = 0, upd_sum = 0;
+    long long t_scan = 0, t_scan_load = 0, t_scan_csync = 0, t_upd = 0, t_upd_csync = 0, t_upd_book = 0, t_total0 = clock64();
+    const double INF = __longlong_as_double(0x7ff0000000000000LL);
 
     // argmin over the active entries of row `row`, ties -> lowest index; then the
     // fastcluster rule: keep (prev, m0) unless something is strictly smaller
     auto argmin_row = [&](int row, double m0, int prev, double &m_out, int &i_out) {
         const double *Wr = W + (size_t)row * n;
-        double bv = __longlong_as_double(0x7ff0000000000000LL);
-        int bi = 0x7fffffff;
-        for (int k = lo + tid; k < hi; k += THREADS) {
-            if ((active[k >> 5] >> (k & 31)) & 1u) {
-                double v = __ldcg(Wr + k);  // diagonal holds +inf
-                if (v < bv) { bv = v; bi = k; }
+        unsigned long long bk = KEY_NONE;
+        uint32_t bi = 0xffffffffu;
+        const long long c0 = clock64();
+        for (int base = lo + tid; base < hi; base += EPT * THREADS) {
+            double v[EPT];
+#pragma unroll
+            for (int u = 0; u < EPT; ++u) {
+                const int k = base + u * THREADS;
+                const bool on = k < hi && ((active[k >> 5] >> (k & 31)) & 1u);
+                // diagonal holds +inf; the all-ones NaN pattern marks "skip" (inputs are NaN free)
+                v[u] = on ? __ldcg(Wr + k) : __longlong_as_double(-1LL);
+            }
+#pragma unroll
+            for (int u = 0; u < EPT; ++u) {
+                if (__double_as_longlong(v[u]) != -1LL) {
+                    const unsigned long long kk = okey(v[u]);
+                    if (kk < bk) { bk = kk; bi = (uint32_t)(base + u * THREADS); }
+                }
             }
         }
-#pragma unroll
-        for (int o = 16; o; o >>= 1) {
-            double ov = __shfl_xor_sync(0xffffffffu, bv, o);
-            int oi = __shfl_xor_sync(0xffffffffu, bi, o);
-            if (lex_less(ov, oi, bv, bi)) { bv = ov; bi = oi; }
+        warp_argmin(bk, bi);
+        if (lane == 0) {
+            wslots[warp].hi = (uint32_t)(bk >> 32);
+            wslots[warp].lo = (uint32_t)bk;
+            wslots[warp].idx = bi;
         }
-        if (lane == 0) { wslots[warp].v = bv; wslots[warp].idx = bi; }
         __syncthreads();
+        const long long c1 = clock64();
         if (warp == 0) {
-            bv = wslots[lane].v;
-            bi = wslots[lane].idx;
-#pragma unroll
-            for (int o = 16; o; o >>= 1) {
-                double ov = __shfl_xor_sync(0xffffffffu, bv, o);
-                int oi = __shfl_xor_sync(0xffffffffu, bi, o);
-                if (lex_less(ov, oi, bv, bi)) { bv = ov; bi = oi; }
-            }
+            const Slot s = wslots[lane];
+            bk = ((unsigned long long)s.hi << 32) | s.lo;
+            bi = s.idx;
+            warp_argmin(bk, bi);
             if (lane < cs) {  // publish this CTA's partial into every CTA's slot table
                 Slot *remote = cluster.map_shared_rank(slots + parity * MAX_CS + rank, lane);
-                remote->v = bv;
-                remote->idx = bi;
+                Slot o;
+                o.hi = (uint32_t)(bk >> 32);
+                o.lo = (uint32_t)bk;
+                o.idx = bi;
+                o.pad = 0;
+                *(uint4 *)remote = *(uint4 *)&o;
             }
         }
-        cluster.sync();
-        bv = __longlong_as_double(0x7ff0000000000000LL);
-        bi = 0x7fffffff;
-        for (int q = 0; q < cs; ++q) {
-            Slot s = slots[parity * MAX_CS + q];
-            if (lex_less(s.v, s.idx, bv, bi)) { bv = s.v; bi = s.idx; }
+        const long long c2 = clock64();
+        __syncwarp();
+        cluster_barrier();
+        const long long c3 = clock64();
+        {
+            const Slot s = slots[parity * MAX_CS + (lane & (MAX_CS - 1))];
+            bk = ((unsigned long long)s.hi << 32) | s.lo;
+            bi = s.idx;
+            warp_argmin(bk, bi);
         }
         parity ^= 1;
-        if (bv < m0) { m_out = bv; i_out = bi; }
+        const double bv = okey_value(bk);
+        if (bv < m0) { m_out = bv; i_out = (int)bi; }
         else { m_out = m0; i_out = prev; }
         n_scans++;
         scan_sum += nactive;
+        t_scan_load += c1 - c0;
+        t_scan_csync += c3 - c2;
+        t_scan += clock64() - c0;
     };
 
     for (int step = 0; step < n - 1; ++step) {
@@ -153,7 +202,7 @@ __global__ void __launch_bounds__(THREADS, 1) k_nnchain(LinkArgs a) {
             if (tid == 0) chain[0] = idx1;
             tip = 1;
             // the diagonal is +inf and idx1 itself is active: nothing is < +inf there
-            argmin_row(idx1, __longlong_as_double(0x7ff0000000000000LL), -1, mind, idx2);
+            argmin_row(idx1, INF, -1, mind, idx2);
         } else {
             tip -= 3;
             idx1 = chain[tip - 1];
@@ -176,6 +225,7 @@ __global__ void __launch_bounds__(THREADS, 1) k_nnchain(LinkArgs a) {
             a.rec_b[step] = idx2;
             a.rec_d[step] = mind;
         }
+        const long long u0 = clock64();
         const int i = min(idx1, idx2), j = max(idx1, idx2);
         const double s1 = (double)members[i], s2 = (double)members[j];
         __syncthreads();  // everyone has read members[i], members[j]
@@ -196,27 +246,56 @@ __global__ void __launch_bounds__(THREADS, 1) k_nnchain(LinkArgs a) {
         nactive--;
         upd_sum += nactive;
         __syncthreads();
-        // Lance-Williams: new D(k, j) for every active k != j
+        t_upd_book += clock64() - u0;
+        // Lance-Williams: new D(k, j) for every active k != j; loads of a batch first, then the stores
         const double avg_s = __ddiv_rn(s1, __dadd_rn(s1, s2)), avg_t = __ddiv_rn(s2, __dadd_rn(s1, s2));
         const double *Wi = W + (size_t)i * n;
         double *Wj = W + (size_t)j * n;
-        for (int k = lo + tid; k < hi; k += THREADS) {
-            if (k != j && ((active[k >> 5] >> (k & 31)) & 1u)) {
-                double da = __ldcg(Wi + k), db = __ldcg(Wj + k);
-                double v = a.method == M_WARD ? (double)members[k] : 0.0;
-                double nv = lw_update(a.method, da, db, mind, s1, s2, v, avg_s, avg_t);
-                Wj[k] = nv;
-                W[(size_t)k * n + j] = nv;
+        const int method = a.method;
+        for (int base = lo + tid; base < hi; base += EPT * THREADS) {
+            double da[EPT], db[EPT], mv[EPT];
+            bool on[EPT];
+#pragma unroll
+            for (int u = 0; u < EPT; ++u) {
+                const int k = base + u * THREADS;
+                on[u] = k < hi && k != j && ((active[k >> 5] >> (k & 31)) & 1u);
+                da[u] = db[u] = mv[u] = 0.0;
+                if (on[u]) {
+                    da[u] = __ldcg(Wi + k);
+                    db[u] = __ldcg(Wj + k);
+                    if (method == M_WARD) mv[u] = (double)members[k];
+                }
+            }
+#pragma unroll
+            for (int u = 0; u < EPT; ++u) {
+                if (on[u]) {
+                    const int k = base + u * THREADS;
+                    const double nv = lw_update(method, da[u], db[u], mind, s1, s2, mv[u], avg_s, avg_t);
+                    __stcg(Wj + k, nv);
+                    __stcg(W + (size_t)k * n + j, nv);
+                }
             }
         }
-        cluster.sync();  // row/column j visible to the whole cluster before the next scan
+        const long long u1 = clock64();
+        __syncwarp();
+        cluster_barrier();  // row/column j visible to the whole cluster before the next scan
+        t_upd_csync += clock64() - u1;
+        t_upd += clock64() - u0;
     }
     if (rank == 0 && tid == 0) {
         a.stats[0] = n_scans;
         a.stats[1] = scan_sum;
         a.stats[2] = n - 1;
         a.stats[3] = upd_sum;
+        a.stats[4] = t_scan;
+        a.stats[5] = t_scan_load;
+        a.stats[6] = t_scan_csync;
+        a.stats[7] = t_upd;
+        a.stats[8] = t_upd_csync;
+        a.stats[9] = clock64() - t_total0;
+        a.stats[10] = t_upd_book;
     }
+    cluster_barrier();  // no CTA exits while a peer may still write into its shared memory
 }
 
 size_t smem_bytes(int n, bool chain_in_smem) {
@@ -254,7 +333,7 @@ struct LinkBuffers {
 
 int carve_linkage(void *workspace, size_t bytes, int n, LinkArgs &a, LinkBuffers &lb) {
     hc::Carver ws(workspace, bytes);
-    lb.stats = a.stats = ws.take<long long>(8);
+    lb.stats = a.stats = ws.take<long long>(16);
     a.chain_g = ws.take<int>((size_t)MAX_CS * n);
     a.members_g = ws.take<int>((size_t)MAX_CS * n);
     lb.rec_a = a.rec_a = ws.take<int>(n);
@@ -333,7 +412,7 @@ extern "C" int hc_linkage_finish(int32_t n, int method, void *workspace, size_t 
     const int m = n - 1;
     std::vector<int> ra(m), rb(m);
     std::vector<double> rd(m);
-    long long st[8];
+    long long st[16];
     HC_CUDA_OK(cudaMemcpyAsync(ra.data(), lb.rec_a, m * sizeof(int), cudaMemcpyDeviceToHost, stream));
     HC_CUDA_OK(cudaMemcpyAsync(rb.data(), lb.rec_b, m * sizeof(int), cudaMemcpyDeviceToHost, stream));
     HC_CUDA_OK(cudaMemcpyAsync(rd.data(), lb.rec_d, m * sizeof(double), cudaMemcpyDeviceToHost, stream));
@@ -360,6 +439,13 @@ extern "C" int hc_linkage_finish(int32_t n, int method, void *workspace, size_t 
     }
     if (h_stats)
         for (int k = 0; k < 4; ++k) h_stats[k] = st[k];
+    if (getenv("HC_LINKAGE_PROFILE")) {  // SM-clock breakdown seen by thread 0 of cluster rank 0
+        double tot = (double)st[9];
+        fprintf(stderr, "[hc_linkage n=%d] cycles total %.3g | scans %lld: %.1f%% (load+block-reduce %.1f%%, cluster barrier %.1f%%) | "
+                "updates %lld: %.1f%% (bookkeeping %.1f%%, cluster barrier %.1f%%) | cyc/scan %.0f cyc/update %.0f\n", n, tot, st[0],
+                100.0 * st[4] / tot, 100.0 * st[5] / tot, 100.0 * st[6] / tot, st[2], 100.0 * st[7] / tot,
+                100.0 * st[10] / tot, 100.0 * st[8] / tot, (double)st[4] / (double)st[0], (double)st[7] / (double)st[2]);
+    }
     return HC_OK;
 }
 

@@ -1,0 +1,8 @@
+set -x
+mkdir -p gpurun_out
+timeout 900 python -m pytest tests -m gpu -x -q -k "linkage or dendrogram or tree or cluster_contigs" > gpurun_out/lt_pytest.log 2>&1; echo "pytest rc=$?"; tail -15 gpurun_out/lt_pytest.log
+for c in C1 C2 C3; do
+HC_LINKAGE_PROFILE=1 timeout 900 python bench.py --config $c --steps 2 --warmup 1 --no-cpu-baseline > gpurun_out/lp_$c.json 2> gpurun_out/lp_$c.err; echo "rc=$?"; grep hc_linkage gpurun_out/lp_$c.err | tail -1
+python -c "
+import json;d=json.load(open('gpurun_out/lp_$c.json'));print(d['ms_per_step'],d['stage_ms'])"
+done
