@@ -19,6 +19,8 @@
 // redone by the plain global-atomic kernel.
 #include <limits.h>
 
+#include <algorithm>
+
 #include "common.cuh"
 
 namespace {
@@ -34,6 +36,7 @@ struct BinArgs {
     const uint8_t *region_mask;
     int32_t n_contigs;
     uint32_t window_bp;
+    unsigned long long inv_bp;  // ceil(2^64 / window_bp): exact division of any u32 by one mul.hi.u64
     int32_t n_windows, mapq_min;
     uint32_t skip_flag;
     int32_t row0, row1;
@@ -52,6 +55,11 @@ struct BinArgs {
 
 enum { ST_FILTERED = 0, ST_OK = 1, ST_ABSENT = 2, ST_RANGE = 3, ST_KEY = 4 };
 
+// p / window_bp for p < 2^32, exact (p * (ceil(2^64/d) - 2^64/d) < 2^32 <= 2^64/d)
+__device__ __forceinline__ uint32_t div_bp(const BinArgs &a, uint32_t p) {
+    return a.window_bp == 1u ? p : (uint32_t)__umul64hi((unsigned long long)p, a.inv_bp);
+}
+
 __device__ __forceinline__ int decode(const BinArgs &a, uint2 q0, uint2 q1, uint2 q2, int32_t &row,
                                       int32_t &col) {
     const int32_t ref = (int32_t)q0.x, pos = (int32_t)q0.y;
@@ -69,8 +77,8 @@ __device__ __forceinline__ int decode(const BinArgs &a, uint2 q0, uint2 q1, uint
     const int32_t half = (lseq > 1 ? lseq : 1) >> 1;  // len("*") == 1; Py2 integer division
     const long long p1 = (long long)pos + 1 + half, p2 = (long long)npos + 1 + half;
     if (p1 < 0 || p2 < 0) return ST_RANGE;
-    const long long w1 = (long long)((uint32_t)p1 / a.window_bp) + o1;
-    const long long w2 = (long long)((uint32_t)p2 / a.window_bp) + o2;
+    const long long w1 = (long long)div_bp(a, (uint32_t)p1) + o1;
+    const long long w2 = (long long)div_bp(a, (uint32_t)p2) + o2;
     if (w1 >= a.n_windows || w2 >= a.n_windows) return ST_RANGE;
     row = (int32_t)w1;
     col = (int32_t)w2;
@@ -89,7 +97,7 @@ __global__ void k_lead(BinArgs a, int32_t *lead) {
         int32_t lseq = (int32_t)q2.x;
         long long p1 = (long long)(int32_t)q0.y + 1 + ((lseq > 1 ? lseq : 1) >> 1);
         if (o >= 0 && p1 >= 0) {
-            long long w = (long long)((uint32_t)p1 / a.window_bp) + o;
+            long long w = (long long)div_bp(a, (uint32_t)p1) + o;
             key = (int32_t)(w < a.n_windows ? w : a.n_windows - 1);
         }
     }
@@ -186,83 +194,119 @@ __global__ void k_tile_ranges(BinArgs a, long long *tile_clo, long long *tile_ch
     tile_chi[g] = lo;
 }
 
-// Main kernel: one CTA per (row group, column segment) tile.
+// Main kernel: persistent CTAs, each walks over (row group, column segment) tiles with stride
+// gridDim.x.  Per tile: stream the pair slice, accumulate into the shared-memory tile with
+// WARP-AGGREGATED atomics (Hi-C pairs pile up on the diagonal cell: without aggregation a third of
+// a row's records serialise on one shared-memory address), then one fused flush+zero pass that
+// writes every matrix cell of the tile exactly once with 16-byte coalesced stores.  The stores of
+// tile t drain while the records of tile t+1 are being loaded.
 template <int UNROLL>
 __global__ void __launch_bounds__(1024, 1) k_bin_tiles(BinArgs a) {
-    extern __shared__ uint32_t tile[];
-    const int g = blockIdx.x / a.n_segs, s = blockIdx.x - g * a.n_segs;
-    const int32_t r0 = a.row0 + g * a.R, r1 = min(r0 + a.R, a.row1);
-    const int32_t c0 = s * a.W, c1 = min(c0 + a.W, a.n_windows);
-    const int W = c1 - c0;
-    const int cells = (r1 - r0) * W;
-    for (int i = threadIdx.x; i < cells; i += blockDim.x) tile[i] = 0;
-    __syncthreads();
-
-    unsigned long long n_lines = 0, n_ok = 0, n_absent = 0, n_range = 0, n_key = 0, n_over = 0;
-    const long long clo = a.tile_clo[g], chi = a.tile_chi[g];
-    const long long beg = clo << CHUNK_LOG;
-    const long long end = min(chi << CHUNK_LOG, a.n_pairs);
+    extern __shared__ __align__(16) uint32_t tile[];
     const int T = blockDim.x, lane_id = threadIdx.x & 31;
-    // warp-uniform trip count (the straggler ballot below needs the whole warp)
-    for (long long wbase = beg + (threadIdx.x - lane_id); wbase < end; wbase += (long long)T * UNROLL) {
-        const long long base = wbase + lane_id;
-        uint2 q[UNROLL][3];
+    const int n_tiles = a.n_groups * a.n_segs;
+    const int max_cells = a.R * a.W;
+    for (int i = threadIdx.x; i < max_cells; i += T) tile[i] = 0;
+    __syncthreads();
+    uint32_t n_lines = 0, n_ok = 0, n_absent = 0, n_range = 0, n_key = 0, n_over = 0;
+    const bool vec_ok = ((a.n_windows & 3) == 0) && ((a.W & 3) == 0) && ((((uintptr_t)a.counts) & 15) == 0);
+
+    for (int t = blockIdx.x; t < n_tiles; t += gridDim.x) {
+        const int g = t / a.n_segs, s = t - g * a.n_segs;
+        const int32_t r0 = a.row0 + g * a.R, r1 = min(r0 + a.R, a.row1);
+        const int32_t c0 = s * a.W, c1 = min(c0 + a.W, a.n_windows);
+        const int W = c1 - c0;
+        const long long clo = a.tile_clo[g], chi = a.tile_chi[g];
+        const long long beg = clo << CHUNK_LOG;
+        const long long end = min(chi << CHUNK_LOG, a.n_pairs);
+        // warp-uniform trip count (the ballots / matches below need the whole warp)
+        for (long long wbase = beg + (threadIdx.x - lane_id); wbase < end; wbase += (long long)T * UNROLL) {
+            const long long base = wbase + lane_id;
+            uint2 q[UNROLL][3];
+            int32_t clo_[UNROLL], chi_[UNROLL];
 #pragma unroll
-        for (int u = 0; u < UNROLL; ++u) {
-            long long idx = base + (long long)u * T;
-            if (idx < end) {
-                const uint2 *p = a.pairs + 3 * idx;
-                q[u][0] = __ldg(p);
-                q[u][1] = __ldg(p + 1);
-                q[u][2] = __ldg(p + 2);
-            } else {
-                q[u][2].y = 0xffffu;  // every flag bit set -> filtered
-                q[u][0] = q[u][1] = make_uint2(0, 0);
-                q[u][2].x = 0;
+            for (int u = 0; u < UNROLL; ++u) {
+                const long long idx = base + (long long)u * T;
+                if (idx < end) {
+                    const uint2 *p = a.pairs + 3 * idx;
+                    q[u][0] = __ldg(p);
+                    q[u][1] = __ldg(p + 1);
+                    q[u][2] = __ldg(p + 2);
+                    const long long c = idx >> CHUNK_LOG;
+                    clo_[u] = __ldg(a.chunk_lo + c);
+                    chi_[u] = __ldg(a.chunk_hi + c);
+                } else {
+                    q[u][2].y = 0xffffu;  // every flag bit set -> filtered
+                    q[u][0] = q[u][1] = make_uint2(0, 0);
+                    q[u][2].x = 0;
+                    clo_[u] = chi_[u] = 0;
+                }
             }
-        }
 #pragma unroll
-        for (int u = 0; u < UNROLL; ++u) {
-            long long idx = base + (long long)u * T;
-            bool live = idx < end;
-            long long c = (live ? idx : beg) >> CHUNK_LOG;
-            int32_t row = 0, col = 0;
-            int st = live ? decode(a, q[u][0], q[u][1], q[u][2], row, col) : ST_FILTERED;
-            int32_t lo = __ldg(a.chunk_lo + c), hi = __ldg(a.chunk_hi + c);
-            bool owner = live && (lo == r0) && (s == 0);  // this CTA accounts for the record
-            if (owner) {
-                n_lines += st != ST_FILTERED;
-                n_ok += st == ST_OK;
-                n_absent += st == ST_ABSENT;
-                n_range += st == ST_RANGE;
-                n_key += st == ST_KEY;
-            }
-            bool ok = st == ST_OK;
-            if (ok && row >= r0 && row < r1 && col >= c0 && col < c1)
-                atomicAdd(&tile[(row - r0) * W + (col - c0)], 1u);
-            // straggler: row not advertised by its chunk -> nobody's tile sees it
-            bool strag = owner && ok && (row < lo || row >= hi) && row >= a.row0 && row < a.row1;
-            unsigned m = __ballot_sync(0xffffffffu, strag);
-            if (m) {
-                int lane = threadIdx.x & 31, leader = __ffs(m) - 1;
-                unsigned long long slot = 0;
-                if (lane == leader) slot = atomicAdd(a.overflow_count, (unsigned long long)__popc(m));
-                slot = __shfl_sync(0xffffffffu, slot, leader);
-                if (strag) {
-                    slot += __popc(m & ((1u << lane) - 1));
-                    if ((long long)slot < a.overflow_cap) a.overflow[slot] = make_uint2(row, col);
-                    n_over++;
+            for (int u = 0; u < UNROLL; ++u) {
+                const long long idx = base + (long long)u * T;
+                const bool live = idx < end;
+                int32_t row = 0, col = 0;
+                const int st = live ? decode(a, q[u][0], q[u][1], q[u][2], row, col) : ST_FILTERED;
+                const int32_t lo = clo_[u], hi = chi_[u];
+                const bool owner = live && (lo == r0) && (s == 0);  // this tile accounts for the record
+                if (owner) {
+                    n_lines += st != ST_FILTERED;
+                    n_ok += st == ST_OK;
+                    n_absent += st == ST_ABSENT;
+                    n_range += st == ST_RANGE;
+                    n_key += st == ST_KEY;
+                }
+                const bool ok = st == ST_OK;
+                const bool mine = ok && row >= r0 && row < r1 && col >= c0 && col < c1;
+                // warp-aggregated shared-memory atomics: one add per distinct cell per warp
+                const uint32_t cell = mine ? (uint32_t)((row - r0) * W + (col - c0)) : 0xffffffffu;
+                const unsigned peers = __match_any_sync(0xffffffffu, cell);
+                if (mine && (__ffs(peers) - 1) == lane_id) atomicAdd(&tile[cell], (uint32_t)__popc(peers));
+                // straggler: row not advertised by its chunk -> nobody's tile sees it
+                const bool strag = owner && ok && (row < lo || row >= hi) && row >= a.row0 && row < a.row1;
+                const unsigned m = __ballot_sync(0xffffffffu, strag);
+                if (m) {
+                    const int leader = __ffs(m) - 1;
+                    unsigned long long slot = 0;
+                    if (lane_id == leader) slot = atomicAdd(a.overflow_count, (unsigned long long)__popc(m));
+                    slot = __shfl_sync(0xffffffffu, slot, leader);
+                    if (strag) {
+                        slot += __popc(m & ((1u << lane_id) - 1));
+                        if ((long long)slot < a.overflow_cap) a.overflow[slot] = make_uint2(row, col);
+                        n_over++;
+                    }
                 }
             }
         }
-    }
-    __syncthreads();
-    // every tile row is written exactly once, coalesced
-    for (int rr = 0; rr < r1 - r0; ++rr) {
-        uint32_t *dst = a.counts + (size_t)(r0 - a.row0 + rr) * a.n_windows + c0;
-        const uint32_t *src = tile + rr * W;
-        if (a.accumulate) for (int i = threadIdx.x; i < W; i += blockDim.x) dst[i] += src[i];
-        else for (int i = threadIdx.x; i < W; i += blockDim.x) dst[i] = src[i];
+        __syncthreads();
+        // fused flush + zero: every tile cell is written to the matrix exactly once, coalesced
+        const int rows = r1 - r0;
+        if (vec_ok && ((c0 & 3) == 0) && ((W & 3) == 0)) {
+            const int W4 = W >> 2;
+            for (int i = threadIdx.x; i < rows * W4; i += T) {
+                const int rr = i / W4, cc = i - rr * W4;
+                uint4 *src = (uint4 *)(tile + rr * W) + cc;
+                uint4 *dst = (uint4 *)(a.counts + (size_t)(r0 - a.row0 + rr) * a.n_windows + c0) + cc;
+                uint4 v = *src;
+                if (a.accumulate) {
+                    const uint4 o = *dst;
+                    v.x += o.x; v.y += o.y; v.z += o.z; v.w += o.w;
+                }
+                __stcs(dst, v);
+                *src = make_uint4(0, 0, 0, 0);
+            }
+        } else {
+            for (int i = threadIdx.x; i < rows * W; i += T) {
+                const int rr = i / W, cc = i - rr * W;
+                uint32_t *dst = a.counts + (size_t)(r0 - a.row0 + rr) * a.n_windows + c0 + cc;
+                uint32_t v = tile[i];
+                if (a.accumulate) v += *dst;
+                *dst = v;
+                tile[i] = 0;
+            }
+        }
+        __syncthreads();
     }
     unsigned long long v[6] = {n_lines, n_ok, n_absent, n_range, n_key, n_over};
 #pragma unroll
@@ -460,6 +504,7 @@ extern "C" int hc_bin_pairs(const hc_pair_t *pairs, int64_t n_pairs, const int32
     a.region_mask = region_mask;
     a.n_contigs = n_contigs;
     a.window_bp = window_bp;
+    a.inv_bp = window_bp == 1u ? 0ull : (~0ull) / window_bp + 1ull;
     a.n_windows = n_windows;
     a.mapq_min = mapq_min;
     a.skip_flag = skip_flag;
@@ -477,8 +522,11 @@ extern "C" int hc_bin_pairs(const hc_pair_t *pairs, int64_t n_pairs, const int32
     if (const char *e = getenv("HC_BIN_MAX_CELLS")) max_cells = atoll(e);
     a.n_segs = (int)((n_windows + max_cells - 1) / max_cells);
     a.W = (n_windows + a.n_segs - 1) / a.n_segs;
+    if (a.n_segs > 1) a.W = (a.W + 3) & ~3;  // 16-byte aligned column segments
     int Rmax = (int)(max_cells / a.W);
     if (Rmax < 1) Rmax = 1;
+    // prefer tiles of at most half an SM's shared memory: two resident CTAs overlap flush and stream
+    if ((max_cells / 2) / a.W >= 1 && !getenv("HC_BIN_MAX_CELLS")) Rmax = (int)((max_cells / 2) / a.W);
     int Rwant = (rows + 4 * sms - 1) / (4 * sms);  // aim for >= 4 tiles per SM
     a.R = Rwant < 1 ? 1 : (Rwant > Rmax ? Rmax : Rwant);
     if (const char *e = getenv("HC_BIN_ROWS")) a.R = atoi(e) < 1 ? 1 : (atoi(e) > Rmax ? Rmax : atoi(e));
@@ -518,12 +566,19 @@ extern "C" int hc_bin_pairs(const hc_pair_t *pairs, int64_t n_pairs, const int32
         k_scan_apply<<<(int)nb, 1024, 0, stream>>>(lead, a.n_chunks, bmax);
         k_chunk_bounds<<<cb, 256, 0, stream>>>(a, lead, chunk_lo, chunk_hi);
         k_tile_ranges<<<(a.n_groups + 127) / 128, 128, 0, stream>>>(a, tile_clo, tile_chi);
-        size_t smem = (size_t)a.R * a.W * 4;
-        int threads = smem > 96 * 1024 ? 1024 : (smem > 32 * 1024 ? 512 : 256);
+        size_t smem = hc::align_up((size_t)a.R * a.W * 4, 16);
+        int threads = 1024;
         if (const char *e = getenv("HC_BIN_THREADS")) threads = atoi(e);
         HC_CUDA_OK(cudaFuncSetAttribute(k_bin_tiles<4>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                         smem_max));
-        k_bin_tiles<4><<<a.n_groups * a.n_segs, threads, smem, stream>>>(a);
+        // persistent: as many CTAs as fit (tiles <= ~110 KB let two CTAs share an SM and overlap
+        // one CTA's flush with the other's record stream)
+        int per_sm = (int)((size_t)(smem_max + 1024) / (smem + 1024));
+        if (per_sm > 2048 / threads) per_sm = 2048 / threads;
+        if (per_sm < 1) per_sm = 1;
+        long long n_tiles = (long long)a.n_groups * a.n_segs;
+        int grid = (int)std::min<long long>(n_tiles, (long long)sms * per_sm);
+        k_bin_tiles<4><<<grid, threads, smem, stream>>>(a);
         HC_CHECK_LAUNCH();
         k_apply_overflow<<<4 * sms, 256, 0, stream>>>(a);
         HC_CHECK_LAUNCH();

@@ -49,6 +49,9 @@ struct LinkArgs {
     double *rec_d;
     long long *stats;  // scans, sum active over scans, merges, sum active over updates, cycle counters
     int chain_in_smem;
+    double *nnv;  // [n] nearest-neighbour cache (value)
+    int *nni;     // [n] nearest-neighbour cache (index, < 0 = unknown)
+    int use_cache;
 };
 
 constexpr unsigned long long KEY_NONE = 0xffffffffffffffffull;
@@ -93,6 +96,48 @@ __device__ __forceinline__ void cluster_barrier() {
 
 constexpr int EPT = 4;  // elements per thread per batch: all loads of a batch are issued before first use
 
+// "First linkage pass": nearest neighbour (value, lowest index) of every row of the fresh working
+// matrix, all SMs, one streaming read of W.  Seeds the per-row NN cache of k_nnchain.
+__global__ void __launch_bounds__(256) k_row_argmin(const double *W, int n, double *nnv, int *nni) {
+    __shared__ Slot ws[8];
+    const int row = blockIdx.x, tid = threadIdx.x;
+    const double *Wr = W + (size_t)row * n;
+    unsigned long long bk = KEY_NONE;
+    uint32_t bi = 0xffffffffu;
+    for (int base = tid; base < n; base += EPT * 256) {
+        double v[EPT];
+#pragma unroll
+        for (int u = 0; u < EPT; ++u) {
+            const int k = base + u * 256;
+            v[u] = k < n ? __ldcs(Wr + k) : __longlong_as_double(-1LL);
+        }
+#pragma unroll
+        for (int u = 0; u < EPT; ++u) {
+            if (__double_as_longlong(v[u]) != -1LL) {
+                const unsigned long long kk = okey(v[u]);
+                if (kk < bk) { bk = kk; bi = (uint32_t)(base + u * 256); }
+            }
+        }
+    }
+    warp_argmin(bk, bi);
+    if ((tid & 31) == 0) {
+        ws[tid >> 5].hi = (uint32_t)(bk >> 32);
+        ws[tid >> 5].lo = (uint32_t)bk;
+        ws[tid >> 5].idx = bi;
+    }
+    __syncthreads();
+    if (tid < 32) {
+        const Slot s = ws[tid & 7];
+        bk = ((unsigned long long)s.hi << 32) | s.lo;
+        bi = s.idx;
+        warp_argmin(bk, bi);
+        if (tid == 0) {
+            nnv[row] = okey_value(bk);
+            nni[row] = (bi == 0xffffffffu || bk == KEY_NONE) ? -1 : (int)bi;
+        }
+    }
+}
+
 __global__ void __launch_bounds__(THREADS, 1) k_nnchain(LinkArgs a) {
     cg::cluster_group cluster = cg::this_cluster();
     const int cs = cluster.num_blocks(), rank = cluster.block_rank();
@@ -105,6 +150,9 @@ __global__ void __launch_bounds__(THREADS, 1) k_nnchain(LinkArgs a) {
     int *chain = a.chain_in_smem ? (int *)(active + n_words) : a.chain_g + (size_t)rank * n;
     int *members = a.members_g + (size_t)rank * n;
     double *W = a.W;
+    double *nnv = a.nnv;  // per-row nearest-neighbour cache: exact lexicographic (value, index) minimum over
+    int *nni = a.nni;     // the active entries of the row, or nni < 0 = unknown (rescan when visited)
+    const bool use_cache = a.use_cache != 0;
 
     for (int w = tid; w < n_words; w += THREADS) {
         int rem = n - (w << 5);
@@ -124,13 +172,61 @@ __global__ void __launch_bounds__(THREADS, 1) k_nnchain(LinkArgs a) {
     int parity = 0;
     int start = 0, tip = 0, idx1 = 0, idx2 = 0, nactive = n;
     double mind = 0;
-    long long n_scans = 0, scan_sum = 0, upd_sum = 0;
+    long long n_scans = 0, scan_sum = 0, upd_sum = 0, n_cached = 0, look_sum = 0;
     long long t_scan = 0, t_scan_load = 0, t_scan_csync = 0, t_upd = 0, t_upd_csync = 0, t_upd_book = 0, t_total0 = clock64();
     const double INF = __longlong_as_double(0x7ff0000000000000LL);
+    int last_j = -1, last_ji = -1;  // NN of the row rewritten by the latest merge (not yet visible in nnv/nni)
+    double last_jv = 0;
 
-    // argmin over the active entries of row `row`, ties -> lowest index; then the
-    // fastcluster rule: keep (prev, m0) unless something is strictly smaller
-    auto argmin_row = [&](int row, double m0, int prev, double &m_out, int &i_out) {
+    // lexicographic (key, index) minimum over the whole cluster; contains one cluster barrier with
+    // release/acquire semantics, so it also orders the global stores issued before it
+    auto cluster_argmin = [&](unsigned long long &bk, uint32_t &bi, long long &t_csync) {
+        warp_argmin(bk, bi);
+        if (lane == 0) {
+            wslots[warp].hi = (uint32_t)(bk >> 32);
+            wslots[warp].lo = (uint32_t)bk;
+            wslots[warp].idx = bi;
+        }
+        __syncthreads();
+        if (warp == 0) {
+            const Slot s = wslots[lane];
+            bk = ((unsigned long long)s.hi << 32) | s.lo;
+            bi = s.idx;
+            warp_argmin(bk, bi);
+            if (lane < cs) {  // publish this CTA's partial into every CTA's slot table
+                Slot *remote = cluster.map_shared_rank(slots + parity * MAX_CS + rank, lane);
+                Slot o;
+                o.hi = (uint32_t)(bk >> 32);
+                o.lo = (uint32_t)bk;
+                o.idx = bi;
+                o.pad = 0;
+                *(uint4 *)remote = *(uint4 *)&o;
+            }
+        }
+        const long long c2 = clock64();
+        __syncwarp();
+        cluster_barrier();
+        t_csync += clock64() - c2;
+        {
+            const Slot s = slots[parity * MAX_CS + (lane & (MAX_CS - 1))];
+            bk = ((unsigned long long)s.hi << 32) | s.lo;
+            bi = s.idx;
+            warp_argmin(bk, bi);
+        }
+        parity ^= 1;
+    };
+
+    // nearest neighbour of `row`: (value, lowest index) over its active entries
+    auto nn_of = [&](int row, double &v_out, int &i_out) {
+        if (use_cache) {
+            if (row == last_j) {
+                if (last_ji >= 0) { v_out = last_jv; i_out = last_ji; n_cached++; look_sum += nactive; return; }
+            } else {
+                const int ci = __ldcg(nni + row);
+                const double cv = __ldcg(nnv + row);
+                if (ci >= 0) { v_out = cv; i_out = ci; n_cached++; look_sum += nactive; return; }
+            }
+        }
         const double *Wr = W + (size_t)row * n;
         unsigned long long bk = KEY_NONE;
         uint32_t bi = 0xffffffffu;
@@ -152,47 +248,17 @@ __global__ void __launch_bounds__(THREADS, 1) k_nnchain(LinkArgs a) {
                 }
             }
         }
-        warp_argmin(bk, bi);
-        if (lane == 0) {
-            wslots[warp].hi = (uint32_t)(bk >> 32);
-            wslots[warp].lo = (uint32_t)bk;
-            wslots[warp].idx = bi;
-        }
-        __syncthreads();
         const long long c1 = clock64();
-        if (warp == 0) {
-            const Slot s = wslots[lane];
-            bk = ((unsigned long long)s.hi << 32) | s.lo;
-            bi = s.idx;
-            warp_argmin(bk, bi);
-            if (lane < cs) {  // publish this CTA's partial into every CTA's slot table
-                Slot *remote = cluster.map_shared_rank(slots + parity * MAX_CS + rank, lane);
-                Slot o;
-                o.hi = (uint32_t)(bk >> 32);
-                o.lo = (uint32_t)bk;
-                o.idx = bi;
-                o.pad = 0;
-                *(uint4 *)remote = *(uint4 *)&o;
-            }
+        cluster_argmin(bk, bi, t_scan_csync);
+        v_out = okey_value(bk);
+        i_out = (int)bi;
+        if (use_cache && rank == 0 && tid == 0) {  // read again only after a later cluster barrier
+            __stcg(nnv + row, v_out);
+            __stcg(nni + row, i_out);
         }
-        const long long c2 = clock64();
-        __syncwarp();
-        cluster_barrier();
-        const long long c3 = clock64();
-        {
-            const Slot s = slots[parity * MAX_CS + (lane & (MAX_CS - 1))];
-            bk = ((unsigned long long)s.hi << 32) | s.lo;
-            bi = s.idx;
-            warp_argmin(bk, bi);
-        }
-        parity ^= 1;
-        const double bv = okey_value(bk);
-        if (bv < m0) { m_out = bv; i_out = (int)bi; }
-        else { m_out = m0; i_out = prev; }
         n_scans++;
         scan_sum += nactive;
         t_scan_load += c1 - c0;
-        t_scan_csync += c3 - c2;
         t_scan += clock64() - c0;
     };
 
@@ -201,8 +267,7 @@ __global__ void __launch_bounds__(THREADS, 1) k_nnchain(LinkArgs a) {
             idx1 = start;
             if (tid == 0) chain[0] = idx1;
             tip = 1;
-            // the diagonal is +inf and idx1 itself is active: nothing is < +inf there
-            argmin_row(idx1, INF, -1, mind, idx2);
+            nn_of(idx1, mind, idx2);  // idx1 is the lowest active index: plain row minimum, lowest index on ties
         } else {
             tip -= 3;
             idx1 = chain[tip - 1];
@@ -212,11 +277,17 @@ __global__ void __launch_bounds__(THREADS, 1) k_nnchain(LinkArgs a) {
         int prev2;
         do {
             if (tid == 0) chain[tip] = idx2;
+            double v;
             int found;
-            argmin_row(idx2, mind, idx1, mind, found);
+            nn_of(idx2, v, found);
+            // fastcluster's scan starts from (previous element, its distance) and replaces only on a
+            // strictly smaller value: the previous element wins ties, else the lowest index
+            if (v < mind) mind = v;
+            else found = idx1;
             idx1 = idx2;  // == chain[tip]
             idx2 = found;
             tip++;
+            __syncthreads();  // chain[tip - 1] (written by thread 0 above) is visible
             prev2 = chain[tip - 2];
         } while (idx2 != prev2);
 
@@ -247,23 +318,33 @@ __global__ void __launch_bounds__(THREADS, 1) k_nnchain(LinkArgs a) {
         upd_sum += nactive;
         __syncthreads();
         t_upd_book += clock64() - u0;
-        // Lance-Williams: new D(k, j) for every active k != j; loads of a batch first, then the stores
+        // Lance-Williams: new D(k, j) for every active k != j; loads of a batch first, then the stores.
+        // The same pass maintains the NN cache of every row k (column i disappears, column j changes)
+        // and finds the NN of the rewritten row j.
         const double avg_s = __ddiv_rn(s1, __dadd_rn(s1, s2)), avg_t = __ddiv_rn(s2, __dadd_rn(s1, s2));
         const double *Wi = W + (size_t)i * n;
         double *Wj = W + (size_t)j * n;
         const int method = a.method;
+        unsigned long long jk = KEY_NONE;
+        uint32_t ji = 0xffffffffu;
         for (int base = lo + tid; base < hi; base += EPT * THREADS) {
-            double da[EPT], db[EPT], mv[EPT];
+            double da[EPT], db[EPT], mv[EPT], cv[EPT];
+            int ci[EPT];
             bool on[EPT];
 #pragma unroll
             for (int u = 0; u < EPT; ++u) {
                 const int k = base + u * THREADS;
                 on[u] = k < hi && k != j && ((active[k >> 5] >> (k & 31)) & 1u);
-                da[u] = db[u] = mv[u] = 0.0;
+                da[u] = db[u] = mv[u] = cv[u] = 0.0;
+                ci[u] = -1;
                 if (on[u]) {
                     da[u] = __ldcg(Wi + k);
                     db[u] = __ldcg(Wj + k);
                     if (method == M_WARD) mv[u] = (double)members[k];
+                    if (use_cache) {
+                        ci[u] = __ldcg(nni + k);
+                        cv[u] = __ldcg(nnv + k);
+                    }
                 }
             }
 #pragma unroll
@@ -273,18 +354,46 @@ __global__ void __launch_bounds__(THREADS, 1) k_nnchain(LinkArgs a) {
                     const double nv = lw_update(method, da[u], db[u], mind, s1, s2, mv[u], avg_s, avg_t);
                     __stcg(Wj + k, nv);
                     __stcg(W + (size_t)k * n + j, nv);
+                    if (use_cache) {
+                        const unsigned long long kk = okey(nv);
+                        if (kk < jk) { jk = kk; ji = (uint32_t)k; }
+                        if (ci[u] >= 0) {
+                            const bool hit = ci[u] == i || ci[u] == j;
+                            bool take;  // (nv, j) becomes the row's lexicographic minimum
+                            if (hit) {
+                                take = nv < cv[u] || (ci[u] == j && nv == cv[u]);
+                                if (!take) __stcg(nni + k, -1);  // its neighbour moved away: rescan when visited
+                            } else {
+                                take = nv < cv[u] || (nv == cv[u] && j < ci[u]);
+                            }
+                            if (take) {
+                                __stcg(nnv + k, nv);
+                                __stcg(nni + k, j);
+                            }
+                        }
+                    }
                 }
             }
         }
-        const long long u1 = clock64();
-        __syncwarp();
-        cluster_barrier();  // row/column j visible to the whole cluster before the next scan
-        t_upd_csync += clock64() - u1;
+        // NN of the rewritten row j (also the barrier that makes row/column j and the cache updates
+        // visible to the whole cluster before the next scan)
+        cluster_argmin(jk, ji, t_upd_csync);
+        if (use_cache) {
+            last_j = j;
+            last_ji = (jk == KEY_NONE) ? -1 : (int)ji;
+            last_jv = okey_value(jk);
+            if (rank == 0 && tid == 0) {
+                __stcg(nnv + j, last_jv);
+                __stcg(nni + j, last_ji);
+            }
+        }
         t_upd += clock64() - u0;
     }
     if (rank == 0 && tid == 0) {
-        a.stats[0] = n_scans;
-        a.stats[1] = scan_sum;
+        a.stats[0] = n_scans + n_cached;   // nearest-neighbour searches of the NN-chain (what the CPU library scans)
+        a.stats[1] = scan_sum + look_sum;  // sum of active sizes over them
+        a.stats[12] = n_scans;             // row scans actually executed (the rest came from the NN cache)
+        a.stats[13] = scan_sum;
         a.stats[2] = n - 1;
         a.stats[3] = upd_sum;
         a.stats[4] = t_scan;
@@ -294,6 +403,7 @@ __global__ void __launch_bounds__(THREADS, 1) k_nnchain(LinkArgs a) {
         a.stats[8] = t_upd_csync;
         a.stats[9] = clock64() - t_total0;
         a.stats[10] = t_upd_book;
+        a.stats[11] = n_cached;
     }
     cluster_barrier();  // no CTA exits while a peer may still write into its shared memory
 }
@@ -321,6 +431,7 @@ extern "C" size_t hc_linkage_workspace_bytes(int32_t n) {
     size_t b = 4096;
     b += hc::align_up((size_t)MAX_CS * n * 4, 256) * 2;  // chain + members copies
     b += hc::align_up((size_t)n * 4, 256) * 2 + hc::align_up((size_t)n * 8, 256);
+    b += hc::align_up((size_t)n * 8, 256) + hc::align_up((size_t)n * 4, 256);  // NN cache
     return b;
 }
 
@@ -339,6 +450,8 @@ int carve_linkage(void *workspace, size_t bytes, int n, LinkArgs &a, LinkBuffers
     lb.rec_a = a.rec_a = ws.take<int>(n);
     lb.rec_b = a.rec_b = ws.take<int>(n);
     lb.rec_d = a.rec_d = ws.take<double>(n);
+    a.nnv = ws.take<double>(n);
+    a.nni = ws.take<int>(n);
     return ws.ok() ? 0 : -1;
 }
 }  // namespace
@@ -392,6 +505,12 @@ extern "C" int hc_linkage_launch(double *W, int32_t n, int method, void *workspa
         (void)cudaGetLastError();
     }
     HC_REQUIRE(cs >= 1, "no cluster size fits");
+    a.use_cache = 1;
+    if (const char *e = getenv("HC_LINKAGE_NNCACHE")) a.use_cache = atoi(e) != 0;
+    if (a.use_cache) {  // first linkage pass: nearest neighbour of every row, all SMs
+        k_row_argmin<<<n, 256, 0, stream>>>(W, n, a.nnv, a.nni);
+        HC_CHECK_LAUNCH();
+    }
     HC_CUDA_OK(cudaLaunchKernelEx(&cfg, k_nnchain, a));
     return HC_OK;
 }
@@ -403,7 +522,7 @@ extern "C" int hc_linkage_finish(int32_t n, int method, void *workspace, size_t 
     cudaStream_t stream = (cudaStream_t)stream_;
     HC_REQUIRE(workspace && h_Z && n >= 1, "bad arguments");
     if (n < 2) {
-        if (h_stats) h_stats[0] = h_stats[1] = h_stats[2] = h_stats[3] = 0;
+        if (h_stats) memset(h_stats, 0, 8 * sizeof(int64_t));
         return HC_OK;
     }
     LinkArgs a;
@@ -437,14 +556,19 @@ extern "C" int hc_linkage_finish(int32_t n, int method, void *workspace, size_t 
         h_Z[4 * row + 3] = (double)size[next];
         next++;
     }
-    if (h_stats)
+    if (h_stats) {
         for (int k = 0; k < 4; ++k) h_stats[k] = st[k];
+        h_stats[4] = st[12];
+        h_stats[5] = st[13];
+        h_stats[6] = st[11];
+        h_stats[7] = 0;
+    }
     if (getenv("HC_LINKAGE_PROFILE")) {  // SM-clock breakdown seen by thread 0 of cluster rank 0
         double tot = (double)st[9];
-        fprintf(stderr, "[hc_linkage n=%d] cycles total %.3g | scans %lld: %.1f%% (load+block-reduce %.1f%%, cluster barrier %.1f%%) | "
-                "updates %lld: %.1f%% (bookkeeping %.1f%%, cluster barrier %.1f%%) | cyc/scan %.0f cyc/update %.0f\n", n, tot, st[0],
+        fprintf(stderr, "[hc_linkage n=%d] cached NN lookups %lld | cycles total %.3g | row scans %lld: %.1f%% (load+block-reduce %.1f%%, cluster barrier %.1f%%) | "
+                "updates %lld: %.1f%% (bookkeeping %.1f%%, cluster barrier %.1f%%) | cyc/scan %.0f cyc/update %.0f\n", n, st[11], tot, st[12],
                 100.0 * st[4] / tot, 100.0 * st[5] / tot, 100.0 * st[6] / tot, st[2], 100.0 * st[7] / tot,
-                100.0 * st[10] / tot, 100.0 * st[8] / tot, (double)st[4] / (double)st[0], (double)st[7] / (double)st[2]);
+                100.0 * st[10] / tot, 100.0 * st[8] / tot, (double)st[4] / (double)(st[12] ? st[12] : 1), (double)st[7] / (double)st[2]);
     }
     return HC_OK;
 }

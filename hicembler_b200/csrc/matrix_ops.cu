@@ -110,6 +110,104 @@ __global__ void __launch_bounds__(256) k_symmetrize(T *d, int n, T add, T *vmax)
     }
 }
 
+// ---- 64 x 64 tile-pair kernels for 4-byte element types (n % 4 == 0, 16-byte aligned base) ----
+// One CTA per unordered tile pair {(I,J),(J,I)}, I <= J (linear grid over the upper triangle of the
+// tile grid, no idle CTAs): 16-byte coalesced loads of both tiles into shared memory, one
+// barrier, 16-byte coalesced stores of both results.  u32 counts -> f32 (fold) or f32 in place.
+constexpr int T64 = 64;
+
+__device__ __forceinline__ void tile_pair_from_linear(long long t, int T, int &I, int &J) {
+    const double d = 2.0 * T + 1.0;
+    long long i = (long long)((d - sqrt(d * d - 8.0 * (double)t)) * 0.5);
+    if (i < 0) i = 0;
+    if (i > T - 1) i = T - 1;
+    // start(i) = i*T - i*(i-1)/2 = index of pair (i,i)
+    while (i > 0 && i * T - i * (i - 1) / 2 > t) --i;
+    while (i + 1 < T && (i + 1) * T - (i + 1) * i / 2 <= t) ++i;
+    I = (int)i;
+    J = (int)(i + (t - (i * T - i * (i - 1) / 2)));
+}
+
+template <typename TIn>
+__device__ __forceinline__ float pair_value(TIn a, TIn b, bool diag, float add);
+template <>
+__device__ __forceinline__ float pair_value<uint32_t>(uint32_t a, uint32_t b, bool diag, float add) {
+    return (float)(diag ? a : a + b) + add;
+}
+template <>
+__device__ __forceinline__ float pair_value<float>(float a, float b, bool diag, float add) {
+    return (diag ? a : a + b) + add;
+}
+
+// mode 0 (counts only): upper triangle incl. diagonal, zeros below; mode 1: symmetrised (+add)
+template <typename TIn>
+__global__ void __launch_bounds__(256) k_tilepair64(const TIn *C, int n, int T, int mode, float add, float *out,
+                                                    float *vmax) {
+    __shared__ TIn A[T64][T64 + 1], B[T64][T64 + 1];
+    __shared__ float shm[8];
+    int I, J;
+    tile_pair_from_linear(blockIdx.x, T, I, J);
+    const int tx = threadIdx.x & 15, ty = threadIdx.x >> 4;
+    const uint4 zero4 = make_uint4(0, 0, 0, 0);
+#pragma unroll
+    for (int p = 0; p < 4; ++p) {
+        const int r = ty + 16 * p;
+        const int i = I * T64 + r, j = J * T64 + tx * 4;
+        uint4 v = zero4, w = zero4;
+        if (i < n && j < n) v = *(const uint4 *)(C + (size_t)i * n + j);  // n % 4 == 0: j + 3 < n
+        const int i2 = J * T64 + r, j2 = I * T64 + tx * 4;
+        if (i2 < n && j2 < n) w = *(const uint4 *)(C + (size_t)i2 * n + j2);
+        const TIn *pv = (const TIn *)&v, *pw = (const TIn *)&w;
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+            A[r][tx * 4 + q] = pv[q];
+            B[r][tx * 4 + q] = pw[q];
+        }
+    }
+    __syncthreads();
+    float m = 0.f;
+#pragma unroll
+    for (int p = 0; p < 4; ++p) {
+        const int r = ty + 16 * p;
+        const int i = I * T64 + r, j = J * T64 + tx * 4;
+        if (i < n && j < n) {
+            float o[4];
+#pragma unroll
+            for (int q = 0; q < 4; ++q) {
+                const int c = tx * 4 + q;
+                float v = pair_value<TIn>(A[r][c], B[c][r], i == j + q, add);
+                if (mode == 0) v = (i <= j + q) ? v : 0.f;
+                o[q] = v;
+                m = fmaxf(m, v);
+            }
+            *(float4 *)(out + (size_t)i * n + j) = make_float4(o[0], o[1], o[2], o[3]);
+        }
+        if (I != J) {
+            const int i2 = J * T64 + r, j2 = I * T64 + tx * 4;
+            if (i2 < n && j2 < n) {
+                float o[4];
+#pragma unroll
+                for (int q = 0; q < 4; ++q) {
+                    const int c = tx * 4 + q;
+                    float v = (mode == 0) ? 0.f : pair_value<TIn>(B[r][c], A[c][r], false, add);
+                    o[q] = v;
+                    m = fmaxf(m, v);
+                }
+                *(float4 *)(out + (size_t)i2 * n + j2) = make_float4(o[0], o[1], o[2], o[3]);
+            }
+        }
+    }
+    if (vmax) {
+        for (int o = 16; o; o >>= 1) m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, o));
+        if ((threadIdx.x & 31) == 0) shm[threadIdx.x >> 5] = m;
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            for (int k = 1; k < 8; ++k) m = fmaxf(m, shm[k]);
+            atomic_max_nonneg(vmax, m);
+        }
+    }
+}
+
 struct Xform {
     int kind;
     double p0, p1;
@@ -304,8 +402,14 @@ extern "C" int hc_fold_counts(const uint32_t *counts, int32_t n, int mode, float
     cudaStream_t stream = (cudaStream_t)stream_;
     HC_REQUIRE(counts && out && n > 0 && (mode == 0 || mode == 1), "bad arguments");
     if (d_vmax) HC_CUDA_OK(cudaMemsetAsync(d_vmax, 0, sizeof(float), stream));
-    int T = (n + TS - 1) / TS;
-    k_fold_counts<<<dim3(T, T), dim3(TS, 8), 0, stream>>>(counts, n, mode, add, out, d_vmax);
+    if ((n & 3) == 0 && (((uintptr_t)counts | (uintptr_t)out) & 15) == 0 && !getenv("HC_FOLD_TS32")) {
+        const int T = (n + T64 - 1) / T64;
+        const long long pairs = (long long)T * (T + 1) / 2;
+        k_tilepair64<uint32_t><<<(unsigned)pairs, 256, 0, stream>>>(counts, n, T, mode, add, out, d_vmax);
+    } else {
+        int T = (n + TS - 1) / TS;
+        k_fold_counts<<<dim3(T, T), dim3(TS, 8), 0, stream>>>(counts, n, mode, add, out, d_vmax);
+    }
     HC_CHECK_LAUNCH();
     return HC_OK;
 }
@@ -315,7 +419,12 @@ extern "C" int hc_symmetrize(void *d, int32_t n, int dtype, double add, void *d_
     HC_REQUIRE(d && n > 0 && (dtype == 0 || dtype == 1), "bad arguments");
     int T = (n + TS - 1) / TS;
     if (d_vmax) HC_CUDA_OK(cudaMemsetAsync(d_vmax, 0, dtype ? 8 : 4, stream));
-    if (dtype == 0)
+    if (dtype == 0 && (n & 3) == 0 && ((uintptr_t)d & 15) == 0 && !getenv("HC_FOLD_TS32")) {
+        const int T6 = (n + T64 - 1) / T64;
+        const long long pairs = (long long)T6 * (T6 + 1) / 2;
+        k_tilepair64<float><<<(unsigned)pairs, 256, 0, stream>>>((const float *)d, n, T6, 1, (float)add, (float *)d,
+                                                                   (float *)d_vmax);
+    } else if (dtype == 0)
         k_symmetrize<float><<<dim3(T, T), dim3(TS, 8), 0, stream>>>((float *)d, n, (float)add, (float *)d_vmax);
     else
         k_symmetrize<double><<<dim3(T, T), dim3(TS, 8), 0, stream>>>((double *)d, n, add, (double *)d_vmax);

@@ -300,11 +300,12 @@ def linkage_working(W, method="ward", nan_flags=None, return_stats=False):
     L = _lib.lib()
     ws = torch.empty(L.hc_linkage_workspace_bytes(n), dtype=torch.uint8, device=W.device)
     Z = np.empty((max(n - 1, 0), 4), dtype=np.float64)
-    stats = (C.c_int64 * 4)()
+    stats = (C.c_int64 * 8)()
     _lib.check(L.hc_linkage(_ptr(W), n, METHODS[method], _ptr(ws), ws.numel(),
                             Z.ctypes.data_as(C.c_void_p), stats, _stream()))
     if return_stats:
-        return Z, dict(scans=stats[0], scan_active=stats[1], merges=stats[2], update_active=stats[3])
+        return Z, dict(scans=stats[0], scan_active=stats[1], merges=stats[2], update_active=stats[3],
+                       row_scans=stats[4], row_scan_active=stats[5], cached_lookups=stats[6])
     return Z
 
 

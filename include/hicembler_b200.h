@@ -168,8 +168,10 @@ int hc_expand_condensed(const double *y, int32_t n, int square, double *W, int32
  * sch.linkage (array2scaffolds.py:163).  W is the full symmetric float64 working matrix from
  * hc_transform_to_working / hc_expand_condensed (squared for ward) and is destroyed.
  * method: 0 single, 1 complete, 2 average, 3 weighted, 4 ward.
- * h_Z receives the scipy linkage array (n-1) x 4 float64 (host).  h_stats[4] = {NN scans,
- * sum of active sizes over scans, merges, sum of active sizes over updates}. */
+ * h_Z receives the scipy linkage array (n-1) x 4 float64 (host).  h_stats[8] = {NN searches
+ * of the chain, sum of active sizes over them, merges, sum of active sizes over updates, row scans
+ * actually executed (the others were answered by the per-row NN cache), sum of active sizes over
+ * executed scans, cached lookups, 0}.  The first four equal what the CPU library does step for step. */
 size_t hc_linkage_workspace_bytes(int32_t n);
 int hc_linkage(double *W, int32_t n, int method, void *workspace, size_t workspace_bytes,
                double *h_Z, int64_t *h_stats, void *stream);

@@ -395,6 +395,27 @@ def test_linkage_hic_distances_tie_heavy_medium():
         assert st["scans"] == stats[0] and st["scan_active"] == stats[1]   # same chain, step for step
 
 
+@pytest.mark.parametrize("method", ["ward", "average", "single", "complete", "weighted"])
+def test_linkage_nn_cache_on_off_identical(method, monkeypatch):
+    """the per-row nearest-neighbour cache must not change a single merge, ties included; with the
+    cache on, part of the chain's NN searches are answered without scanning a row"""
+    from hicembler_b200.bam2clusters import array2Z
+    d = O.symmetrize(hic_like_counts(1800, 7, scale=5.0).astype(np.float64))
+    dist = O.transform_distance(d, 0.5, 1.1)
+    want, stats = O.linkage_fastcluster(O.condense(dist), method, return_stats=True)
+    out = {}
+    for flag in ("0", "1"):
+        monkeypatch.setenv("HC_LINKAGE_NNCACHE", flag)
+        Z, st = array2Z(dist, method, return_stats=True)
+        _same_tree(Z, want)
+        assert np.array_equal(Z[:, 2], want[:, 2])
+        assert st["scans"] == stats[0] and st["scan_active"] == stats[1]
+        out[flag] = st
+    assert out["0"]["cached_lookups"] == 0 and out["0"]["row_scans"] == stats[0]
+    assert out["1"]["cached_lookups"] > 0
+    assert out["1"]["row_scans"] + out["1"]["cached_lookups"] == stats[0]
+
+
 def test_array2tree_newick_matches_reference_recursion():
     import scipy.cluster.hierarchy as sch
     from hicembler_b200.bam2clusters import array2tree, newick_from_linkage
