@@ -505,7 +505,10 @@ extern "C" int hc_linkage_launch(double *W, int32_t n, int method, void *workspa
         (void)cudaGetLastError();
     }
     HC_REQUIRE(cs >= 1, "no cluster size fits");
-    a.use_cache = 1;
+    // measured on B200 (profiles/r01_linkage_experiments.md): the NN cache removes ~1/3 of the row scans but
+    // its maintenance lengthens every Lance-Williams pass; it wins while a row slice is <= 1 element per
+    // thread (n <= 16 CTAs x 1024 threads) and loses beyond
+    a.use_cache = n <= MAX_CS * THREADS;
     if (const char *e = getenv("HC_LINKAGE_NNCACHE")) a.use_cache = atoi(e) != 0;
     if (a.use_cache) {  // first linkage pass: nearest neighbour of every row, all SMs
         k_row_argmin<<<n, 256, 0, stream>>>(W, n, a.nnv, a.nni);
