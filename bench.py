@@ -101,7 +101,7 @@ def cpu_reference_sample(cfg, seed=1, n_sample_pairs=1_000_000, n_small=4000):
     from hicembler_b200.pairs import records_to_sam
     N, P, ws = cfg["n_windows"], cfg["n_pairs"], cfg["window_bp"]
     # (1) binning: literal per-line loop over SAM text, same window table as the GPU arm
-    g = synth.make_genome(cfg["n_contigs"], N, ws, cfg["n_chrom"], seed=seed)
+    g = synth.make_genome(cfg["n_contigs"], N, ws, cfg["n_chrom"], seed=seed, min_tail=cfg.get("min_tail", 1))
     S = min(P, n_sample_pairs)
     rec = synth.records_numpy(synth.make_pairs(g, S, seed=seed))
     lines = records_to_sam(rec, g.names)
@@ -170,7 +170,7 @@ def run_ours(args, cfg, rank, world, local_rank):
     if world > 1:
         dist.init_process_group("nccl", device_id=dev)
     N, P, ws = cfg["n_windows"], cfg["n_pairs"], cfg["window_bp"]
-    g = synth.make_genome(cfg["n_contigs"], N, ws, cfg["n_chrom"], seed=1 + rank)
+    g = synth.make_genome(cfg["n_contigs"], N, ws, cfg["n_chrom"], seed=1 + rank, min_tail=cfg.get("min_tail", 1))
     records = synth.make_pairs(g, P, seed=1 + rank, device=dev)
     torch.cuda.synchronize()
     torch.cuda.empty_cache()
@@ -182,7 +182,7 @@ def run_ours(args, cfg, rank, world, local_rank):
 
     def step(rec, timer=None):
         return pairs_to_dendrogram(rec, offsets, ws, N, mapq=10, params=PARAMS, method=cfg["method"],
-                                   balance=not args.no_balance, timer=timer, workspace=workspace)
+                                   balance=not args.no_balance, timer=timer, workspace=workspace, engine=args.engine)
 
     def barrier():
         if world > 1:
@@ -241,7 +241,11 @@ def run_ours(args, cfg, rank, world, local_rank):
         "fold": 8.0 * N * N,
         "sinkhorn": sk_passes * 4.0 * N * N,
         "transform": 4.0 * N * (N - 1) / 2 + 8.0 * N * N,
-        "linkage": 8.0 * lst["scan_active"] + 24.0 * lst["update_active"],
+        # serial NN-chain: one f64 row per NN search, two rows read + one written per Lance-Williams update;
+        # round-parallel engine: 8 B per live column of a rescan, 24 B per live column of a merged-row build
+        # and per (row, pair) update (two reads, one write) -- counted by the kernels themselves
+        "linkage": (8.0 * lst["rescan_cols"] + 24.0 * lst["build_cols"] + 24.0 * lst["light_updates"])
+        if lst.get("engine") == "rounds" else (8.0 * lst["scan_active"] + 24.0 * lst["update_active"]),
     }
     roof = {}
     for k, b in bytes_alg.items():
@@ -253,10 +257,12 @@ def run_ours(args, cfg, rank, world, local_rank):
     dominant = max(roof, key=lambda k: roof[k]["ms"])
     main_roof = dict(roof[dominant], kernel={"bin_pairs": "k_bin_tiles", "fold": "k_fold_counts",
                                              "sinkhorn": "k_colpass+k_rowpass", "transform": "k_transform_working",
-                                             "linkage": "k_nnchain"}[dominant], peak_source=peak_src)
+                                             "linkage": "kr_light+kr_heavy" if lst.get("engine") == "rounds" else "k_nnchain"}[dominant],
+                     peak_source=peak_src)
     # launches per step: bin 8, fold 1, sinkhorn (colpass+finish)=2/pass ... counted from the call graph
     sk_launches = 0 if args.no_balance else (2 + 1 + 1 + 2 + 1 + 2 + sk_it * 5)
-    gpu_launches = K * 2 * (8 + 1 + sk_launches + 1 + 1)
+    link_launches = (3 + 3 * 8 * ((lst["rounds"] + 7) // 8) + 3 * lst["compactions"]) if lst.get("engine") == "rounds" else 1
+    gpu_launches = K * 2 * (8 + 1 + sk_launches + 1 + link_launches)
     cpu = None
     if world == 1 and not args.no_cpu_baseline:
         c = cpu_reference_sample(cfg)
@@ -270,6 +276,8 @@ def run_ours(args, cfg, rank, world, local_rank):
         "config": {"workload": cfg["name"], "n_contigs": cfg["n_contigs"], "n_windows": N, "n_pairs": P,
                    "window_bp": ws, "method": cfg["method"], "balance": not args.no_balance,
                    "l2": "inputs larger than L2 (records %.1f GB, matrix %.1f GB)" % (24e-9 * P, 4e-9 * N * N),
+                   "min_tail_bp": cfg.get("min_tail", 1),
+                   "linkage_engine": lst.get("engine"),
                    "parallelism": "replicas x%d" % world if world > 1 else "1 gpu"},
         "e2e": {"value": total_pairs / (ms_e2e * 1e-3), "unit": UNIT, "h2d_bytes_per_step": int(24 * P),
                 "d2h_bytes_per_step": int((N - 1) * 32 + 64 + 64), "ms_per_step": ms_e2e / K},
@@ -360,9 +368,17 @@ def main():
     ap.add_argument("--n", type=int, default=0, help="matrix size for --mode sinkhorn")
     ap.add_argument("--no-balance", action="store_true", help="reference HEAD behaviour: normalize() off")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--engine", default="auto", choices=["auto", "exact", "rounds"],
+                    help="linkage engine: round-parallel with certification (auto falls back to the serial NN-chain on ties)")
+    ap.add_argument("--min-tail", type=int, default=2000,
+                    help="shortest trailing (partial) window of a synthetic contig in bp.  Default 2000 = the reference's own "
+                         "shortest-sequence cutoff (minSize, bam2clusters.py:459).  1 leaves ~n_contigs*50/window_bp windows "
+                         "that no read midpoint can reach: identical empty rows = exact distance ties, which the "
+                         "round-parallel linkage refuses to certify, so the serial NN-chain engine runs instead")
     args = ap.parse_args()
     from hicembler_b200 import synth
-    cfg = dict(synth.CONFIGS[args.config], name=args.config + ": " + synth.CONFIG_DESCRIPTIONS[args.config])
+    cfg = dict(synth.CONFIGS[args.config], name=args.config + ": " + synth.CONFIG_DESCRIPTIONS[args.config],
+               min_tail=args.min_tail)
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))

@@ -12,6 +12,7 @@ LIB_PATH = os.path.join(_HERE, "libhicembler_b200.so")
 
 HC_OK, HC_EINVAL, HC_ERANGE, HC_EKEY, HC_ENAN, HC_ENEG, HC_ECUDA, HC_EWORKSPACE, HC_ENOTRI = \
     0, -1, -2, -3, -4, -5, -6, -7, -8
+HC_EAMBIGUOUS = 1
 
 _p, _i32, _i64, _u32, _dbl, _flt, _sz = (C.c_void_p, C.c_int32, C.c_int64, C.c_uint32, C.c_double,
                                          C.c_float, C.c_size_t)
@@ -47,6 +48,8 @@ SIGNATURES = {
     "hc_linkage": (C.c_int, [_p, _i32, C.c_int, _p, _sz, _p, _p, _p]),
     "hc_linkage_launch": (C.c_int, [_p, _i32, C.c_int, _p, _sz, _p]),
     "hc_linkage_finish": (C.c_int, [_i32, C.c_int, _p, _sz, _p, _p, _p]),
+    "hc_linkage_rounds_workspace_bytes": (_sz, [_i32]),
+    "hc_linkage_rounds": (C.c_int, [_p, _i32, C.c_int, _p, _sz, _p, _p, _p]),
     "hc_segment_mean_2d": (C.c_int, [_p, _i32, _p, _p, _i32, _p, _p, _p]),
     "hc_normalize_rows": (C.c_int, [_p, _i32, _p, _sz, _p]),
 }

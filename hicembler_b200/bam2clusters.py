@@ -317,7 +317,7 @@ def newick_from_linkage(Z, leaf_names):
     return "".join(out)
 
 
-def array2Z(d, method="ward", transform=None, return_stats=False):
+def array2Z(d, method="ward", transform=None, return_stats=False, engine="auto"):
     """Linkage array of ``d[np.triu_indices(n,1)]`` (bam2clusters.py:385) for a numpy or CUDA matrix.
     ``transform`` = None, ("power", a, b) for distance_func(x+1, a, b) or ("logmax", vmax)."""
     X = d if isinstance(d, torch.Tensor) else torch.from_numpy(np.ascontiguousarray(d)).cuda()
@@ -333,7 +333,7 @@ def array2Z(d, method="ward", transform=None, return_stats=False):
             raise ValueError(transform)
     if X.shape[0] < 2:
         return (np.empty((0, 4)), {}) if return_stats else np.empty((0, 4))
-    return linkage_square(X.contiguous(), method, kind, p0, p1, return_stats=return_stats)
+    return linkage_square(X.contiguous(), method, kind, p0, p1, return_stats=return_stats, engine=engine)
 
 
 def array2tree(d, names, outbase="", method="ward"):

@@ -19,8 +19,6 @@
 #include <math.h>
 #include <stdio.h>
 
-#include <algorithm>
-#include <numeric>
 #include <vector>
 
 #include "common.cuh"
@@ -414,17 +412,6 @@ size_t smem_bytes(int n, bool chain_in_smem) {
     return b + 16;
 }
 
-struct UF {
-    std::vector<int> parent;
-    explicit UF(int n) : parent(n) { std::iota(parent.begin(), parent.end(), 0); }
-    int find(int x) {
-        int root = x;
-        while (parent[root] != root) root = parent[root];
-        while (parent[x] != root) { int nx = parent[x]; parent[x] = root; x = nx; }
-        return root;
-    }
-};
-
 }  // namespace
 
 extern "C" size_t hc_linkage_workspace_bytes(int32_t n) {
@@ -540,25 +527,7 @@ extern "C" int hc_linkage_finish(int32_t n, int method, void *workspace, size_t 
     HC_CUDA_OK(cudaMemcpyAsync(rd.data(), lb.rec_d, m * sizeof(double), cudaMemcpyDeviceToHost, stream));
     HC_CUDA_OK(cudaMemcpyAsync(st, lb.stats, sizeof st, cudaMemcpyDeviceToHost, stream));
     HC_CUDA_OK(cudaStreamSynchronize(stream));
-    if (method == M_WARD)
-        for (int k = 0; k < m; ++k) rd[k] = sqrt(rd[k]);
-    std::vector<int> order(m);
-    std::iota(order.begin(), order.end(), 0);
-    std::stable_sort(order.begin(), order.end(), [&](int x, int y) { return rd[x] < rd[y]; });
-    UF uf(2 * n - 1);
-    std::vector<int> size(2 * n - 1, 1);
-    int next = n;
-    for (int row = 0; row < m; ++row) {
-        int k = order[row];
-        int x = uf.find(ra[k]), y = uf.find(rb[k]);
-        uf.parent[x] = uf.parent[y] = next;
-        size[next] = size[x] + size[y];
-        h_Z[4 * row + 0] = (double)std::min(x, y);
-        h_Z[4 * row + 1] = (double)std::max(x, y);
-        h_Z[4 * row + 2] = rd[k];
-        h_Z[4 * row + 3] = (double)size[next];
-        next++;
-    }
+    hc::records_to_Z(n, method == M_WARD, ra.data(), rb.data(), rd.data(), h_Z, 0.0, nullptr);
     if (h_stats) {
         for (int k = 0; k < 4; ++k) h_stats[k] = st[k];
         h_stats[4] = st[12];

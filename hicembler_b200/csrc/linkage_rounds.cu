@@ -1,0 +1,714 @@
+// K7b: round-parallel agglomeration -- every reciprocal-nearest-neighbour pair is merged in the same
+// round, on all SMs.  Second engine behind fastcluster.linkage / scipy linkage (reference
+// bam2clusters.py:385,403,411,430, array2scaffolds.py:163), next to the serial NN-chain of linkage.cu.
+//
+// Why it is allowed.  single/complete/average/weighted/ward are REDUCIBLE Lance-Williams schemes
+// (D(k, i+j) >= min(D(k,i), D(k,j))): merging a reciprocal-NN pair never destroys another reciprocal
+// pair, so the NN-chain -- which also only ever merges reciprocal pairs -- and "merge them all at
+// once" build the same tree whenever every decision is strict.  Where a decision is NOT strict (ties),
+// fastcluster's answer depends on its scan order; this engine then refuses: it CERTIFIES each merge
+// (both rows' minimum is separated from the second smallest entry by a relative margin far above
+// the measured rounding difference between the engines, MARGIN) and the sorted heights (records_to_Z near_ties), and returns
+// HC_EAMBIGUOUS otherwise, so the caller rebuilds the working matrix and runs the exact serial engine.
+// Heights agree with the serial order to rounding (the Lance-Williams operations are the same, their
+// interleaving differs); merge order and cluster sizes are identical.
+//
+// Why it is fast.  The serial chain is ~200k dependent steps of 2-5 us each at n = 50k (latency).
+// Here a round is three launches over all SMs and the whole run is bandwidth work:
+//   kr_select : row a and b = nn[a] are reciprocal -> pair list, certificate, merge record
+//   kr_light  : every surviving unmerged row k updates ITS OWN entries  D(k, j_q) for all pairs q
+//               (the matrix is full symmetric, so row k already holds D(k,i_q) and D(k,j_q): no
+//               transposed traffic, no inter-row hazard) and keeps its NN cache (min, argmin,
+//               lower bound of the rest) valid without a rescan whenever reducibility allows
+//   kr_heavy  : new row of every merged cluster from its two old rows (pair x pair entries by a
+//               fixed "lower j first" rule so both mirror entries get bit-identical values), exact
+//               rescans of rows whose cache could not be kept; the last CTA retires the pairs.
+// The host syncs once per batch of rounds and compacts the matrix (order preserving) whenever half of
+// the columns are dead, so rows stay short in the long tail of small rounds.
+#include <limits.h>
+#include <math.h>
+#include <stdlib.h>
+
+#include <vector>
+
+#include "common.cuh"
+
+namespace {
+
+enum { M_SINGLE = 0, M_COMPLETE = 1, M_AVERAGE = 2, M_WEIGHTED = 3, M_WARD = 4 };
+// Certificate thresholds.  The two engines differ only by the interleaving of the same Lance-Williams
+// operations; the largest relative difference between their heights measured on the bench workloads is
+// 3.2e-15 at n = 50 000 (ward), 4.4e-16 at n = 10 000 (average): profiles/r01_engine_discrepancy.md.
+constexpr double MARGIN = 1e-12;      // relative separation required of every decision (300 x the measured maximum)
+constexpr double HEIGHT_TOL = 2e-13;  // relative separation required of adjacent sorted heights (60 x)
+constexpr int ROLE_DEAD = -2, ROLE_FREE = -1;  // >= 0: 2*pair (i side, retires) / 2*pair+1 (j side, survives)
+constexpr int LIGHT_THREADS = 256, HEAVY_THREADS = 256, MAX_SEGS = 64;
+constexpr int HEAVY_GRID_MAX = 2048, SPLIT_ENTRIES = 2 * HEAVY_GRID_MAX;  // rows are split only while entries < 2 x grid
+
+struct __align__(16) Pair {  // 48 bytes; i < j, the merged cluster lives at j
+    int i, j;
+    double m, s1, s2, as, at;
+};
+
+struct RState {
+    int P, qlen, n_done, nactive, ambiguous, stuck, done, deferred, round, blocks_done, pad0, pad1;
+    int amb_r, amb_b, amb_sr, amb_sb;
+    double amb_v, amb_secr, amb_secb, amb_vb;
+    double gaps[16];  // relative gap (second minimum / minimum - 1) of the first near-tie observations
+    unsigned long long stats[10];  // 0 rescans, 1 rescan columns, 2 builds, 3 build columns, 4 light updates, 5 deferred
+};
+
+struct Cols {
+    int *role, *size, *nn_idx, *orig;
+    double *nn_val, *sec;
+    unsigned char *fresh, *need;
+};
+
+struct Part {  // partial (minimum, index, second minimum) of one column segment
+    double m1, m2;
+    int i1, pad;
+};
+
+struct RArgs {
+    Part *parts;     // [entries][max_segs]
+    int *seg_done;   // [entries] arrival counters, zero between rounds
+    int max_segs;
+    double *W;
+    long long stride;
+    int ncols, n, method, diag;
+    Cols c;
+    Pair *pairs;
+    int *rq, *rec_a, *rec_b;
+    double *rec_d;
+    RState *st;
+};
+
+__device__ __forceinline__ double lw(int method, double a, double b, const Pair &p, double v) {
+    switch (method) {
+    case M_SINGLE: return a < b ? a : b;
+    case M_COMPLETE: return a > b ? a : b;
+    case M_AVERAGE: return __dadd_rn(__dmul_rn(p.as, a), __dmul_rn(p.at, b));
+    case M_WEIGHTED: return __dmul_rn(__dadd_rn(a, b), 0.5);
+    default: {  // ward on squared distances: ((v+s1)*a - v*m + (v+s2)*b) / (s1+s2+v), fastcluster's order
+        double t = __dsub_rn(__dmul_rn(__dadd_rn(v, p.s1), a), __dmul_rn(v, p.m));
+        t = __dadd_rn(t, __dmul_rn(__dadd_rn(v, p.s2), b));
+        return __ddiv_rn(t, __dadd_rn(__dadd_rn(p.s1, p.s2), v));
+    }
+    }
+}
+
+// running (minimum, lowest index attaining it, second smallest value counting duplicates)
+struct Min2 {
+    double m1, m2;
+    int i1;
+    __device__ __forceinline__ void init() {
+        m1 = m2 = __longlong_as_double(0x7ff0000000000000LL);
+        i1 = INT_MAX;
+    }
+    __device__ __forceinline__ void push(double x, int c) {  // c ascending per thread
+        if (x < m1) { m2 = m1; m1 = x; i1 = c; }
+        else if (x < m2) m2 = x;
+    }
+    __device__ __forceinline__ void merge(double n1, int j1, double n2) {
+        if (n1 < m1 || (n1 == m1 && j1 < i1)) {
+            m2 = m1 < n2 ? m1 : n2;
+            m1 = n1;
+            i1 = j1;
+        } else {
+            m2 = n1 < m2 ? n1 : m2;
+        }
+    }
+    __device__ __forceinline__ void warp_reduce() {
+#pragma unroll
+        for (int o = 16; o; o >>= 1) {
+            const double n1 = __shfl_xor_sync(0xffffffffu, m1, o), n2 = __shfl_xor_sync(0xffffffffu, m2, o);
+            const int j1 = __shfl_xor_sync(0xffffffffu, i1, o);
+            merge(n1, j1, n2);
+        }
+    }
+};
+
+__global__ void kr_init(RArgs a) {
+    const int c = blockIdx.x * blockDim.x + threadIdx.x;
+    if (c < a.n) {
+        a.c.role[c] = ROLE_FREE;
+        a.c.size[c] = 1;
+        a.c.nn_idx[c] = -1;
+        a.c.orig[c] = c;
+        a.c.nn_val[c] = a.c.sec[c] = __longlong_as_double(0x7ff0000000000000LL);
+        a.c.fresh[c] = 0;
+        a.c.need[c] = 1;  // the first kr_light / kr_heavy pass is the initial NN scan of every row
+    }
+    if (c == 0) {
+        RState s;
+        memset(&s, 0, sizeof s);
+        s.nactive = a.n;
+        *a.st = s;
+    }
+}
+
+// ---- select: reciprocal nearest neighbours -> certified pair list ----------------------------
+__global__ void __launch_bounds__(256) kr_select(RArgs a) {
+    RState *st = a.st;
+    if (st->done) return;
+    const int r = blockIdx.x * blockDim.x + threadIdx.x, lane = threadIdx.x & 31;
+    bool emit = false;
+    int b = -1;
+    double va = 0;
+    if (r < a.ncols && a.c.role[r] == ROLE_FREE) {
+        b = a.c.nn_idx[r];
+        if (b > r && a.c.nn_idx[b] == r) {
+            va = a.c.nn_val[r];
+            // Margin 0 where both engines compute bit-identical entries: min/max updates commute exactly
+            // (single, complete), and for average/weighted every entry of a row whose cluster is still a
+            // single leaf went only through the OTHER cluster's merge tree, whose operation order is fixed
+            // (ward is excluded: its update uses the merge height, which is interleaving dependent).
+            // Elsewhere the engines interleave two merge trees differently: demand a relative MARGIN.
+            const bool exact_all = a.method == M_SINGLE || a.method == M_COMPLETE;
+            const bool leaf_exact = a.method == M_AVERAGE || a.method == M_WEIGHTED;
+            const double sr = a.c.sec[r], sb = a.c.sec[b];
+            const double thr = __dadd_rn(va, __dmul_rn(fabs(va), MARGIN));
+            const bool ok_r = sr > ((exact_all || (leaf_exact && a.c.size[r] == 1)) ? va : thr);
+            const bool ok_b = sb > ((exact_all || (leaf_exact && a.c.size[b] == 1)) ? va : thr);
+            const bool ok = ok_r && ok_b && a.c.nn_val[b] == va;
+            if (ok) emit = true;
+            else if (a.c.fresh[r] && a.c.fresh[b]) {
+                // Exact second minima and still too close.  A NEAR tie is left pending: the pair stays reciprocal
+                // (reducibility) and is merged in a later round if its rivals move away; all other certified
+                // merges go on (a run whose every merge is strict has a unique tree, whatever the order).  An
+                // EXACT tie (identical rows, e.g. empty windows) practically never resolves: stop at once.
+                st->amb_r = a.c.orig[r]; st->amb_b = a.c.orig[b];
+                st->amb_sr = a.c.size[r]; st->amb_sb = a.c.size[b];
+                st->amb_v = va; st->amb_vb = a.c.nn_val[b];
+                st->amb_secr = sr; st->amb_secb = sb;
+                const unsigned long long k_obs = atomicAdd(&st->stats[6], 1ull);
+                if (k_obs < 16) st->gaps[k_obs] = (fmin(sr, sb) - va) / fabs(va);
+                if (a.diag) emit = true;  // diagnostics only: merge anyway, the result is NOT certified
+                else if (!(sr > va) || !(sb > va) || a.c.nn_val[b] != va) st->ambiguous = 1;
+            }
+            else {  // the bound of "the rest" is stale: rescan both rows, decide next round
+                a.c.need[r] = 1;
+                a.c.need[b] = 1;
+                atomicAdd(&st->deferred, 1);
+            }
+        }
+    }
+    const unsigned m = __ballot_sync(0xffffffffu, emit);
+    if (!m) return;
+    int base = 0;
+    const int leader = __ffs(m) - 1;
+    if (lane == leader) base = atomicAdd(&st->P, __popc(m));
+    base = __shfl_sync(0xffffffffu, base, leader);
+    if (emit) {
+        const int slot = base + __popc(m & ((1u << lane) - 1));
+        Pair p;
+        p.i = r;
+        p.j = b;
+        p.m = va;
+        p.s1 = (double)a.c.size[r];
+        p.s2 = (double)a.c.size[b];
+        const double tot = __dadd_rn(p.s1, p.s2);
+        p.as = __ddiv_rn(p.s1, tot);
+        p.at = __ddiv_rn(p.s2, tot);
+        a.pairs[slot] = p;
+        a.c.role[r] = 2 * slot;
+        a.c.role[b] = 2 * slot + 1;
+        const int k = st->n_done + slot;
+        a.rec_a[k] = a.c.orig[r];
+        a.rec_b[k] = a.c.orig[b];
+        a.rec_d[k] = va;
+    }
+}
+
+// ---- light: every unmerged row updates its own D(k, j_q), keeps its NN cache --------------------
+// A row is owned by a group of G = min(32, pow2ceil(P)) lanes that strides over the pairs, so a round with
+// one pair handles 32 rows per warp and a round with thousands of pairs gives a row a whole warp.
+__global__ void __launch_bounds__(LIGHT_THREADS) kr_light(RArgs a) {
+    RState *st = a.st;
+    if (st->done) return;
+    const int P = st->P, method = a.method, lane = threadIdx.x & 31;
+    int G = 1;
+    while (G < 32 && G < P) G <<= 1;
+    const int rows_per_warp = 32 / G, g = lane / G, q0 = lane - g * G;
+    const long long warp0 = ((long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const long long nwarps = ((long long)gridDim.x * blockDim.x) >> 5;
+    unsigned long long upd = 0;
+    for (long long rbase = warp0 * rows_per_warp; rbase < a.ncols; rbase += nwarps * rows_per_warp) {
+        const int row = (int)rbase + g;
+        if (row >= a.ncols || a.c.role[row] != ROLE_FREE) continue;
+        const bool need = a.c.need[row] != 0;
+        if (P > 0) {
+            double *Wr = a.W + (size_t)row * a.stride;
+            const double v = (double)a.c.size[row];
+            const int nn = a.c.nn_idx[row];
+            for (int q = q0; q < P; q += 2 * G) {  // two pairs per lane in flight
+                const int q2 = q + G;
+                const bool two = q2 < P;
+                const Pair p = a.pairs[q];
+                const Pair p2 = a.pairs[two ? q2 : q];
+                const double A = __ldcg(Wr + p.i), B = __ldcg(Wr + p.j);
+                const double A2 = __ldcg(Wr + p2.i), B2 = __ldcg(Wr + p2.j);
+                const double x = lw(method, A, B, p, v);
+                Wr[p.j] = x;
+                int hj = -1;
+                double hx = 0;
+                if (nn == p.i || nn == p.j) { hx = x; hj = p.j; }
+                if (two) {
+                    const double x2 = lw(method, A2, B2, p2, v);
+                    Wr[p2.j] = x2;
+                    if (nn == p2.i || nn == p2.j) { hx = x2; hj = p2.j; }
+                }
+                if (hj >= 0) {  // the cached neighbour was merged (at most one pair of the round can hit): its
+                    // successor is still the minimum if it stays below the lower bound of all other entries
+                    if (hx < a.c.sec[row]) {
+                        a.c.nn_val[row] = hx;
+                        a.c.nn_idx[row] = hj;
+                    } else if (!need) {
+                        a.rq[atomicAdd(&st->qlen, 1)] = row;
+                    }
+                }
+            }
+            if (q0 == 0) {
+                a.c.fresh[row] = 0;  // sec is now a lower bound, no longer the exact second minimum
+                upd += P;
+            }
+        }
+        if (need && q0 == 0) a.rq[atomicAdd(&st->qlen, 1)] = row;  // kr_heavy clears the flag
+    }
+    if (upd) atomicAdd(&st->stats[4], upd);
+}
+
+// ---- heavy: new rows of merged clusters, exact rescans; the last CTA retires the pairs -----------
+// Work item = (entry, column segment).  With many entries a CTA takes whole rows; in the long tail of
+// rounds with one or two entries a row is cut into segments over many CTAs and the last CTA to finish
+// an entry combines the partial minima, so a round never waits for one CTA streaming a whole row.
+template <bool VEC>
+__device__ __forceinline__ void heavy_columns(const RArgs &a, int e, int P, int c_lo, int c_hi, Min2 &best) {
+    const int tid = threadIdx.x, method = a.method;
+    constexpr int V = VEC ? 2 : 1, U = 2;
+    if (e < P) {
+        const Pair p = a.pairs[e];
+        const double *Wi = a.W + (size_t)p.i * a.stride;
+        double *Wj = a.W + (size_t)p.j * a.stride;
+        const double ps = __dadd_rn(p.s1, p.s2);
+        for (int c0 = c_lo + tid * V; c0 < c_hi; c0 += U * V * HEAVY_THREADS) {
+            double A[U][V], B[U][V];
+            int rc[U][V], sz[U][V];
+#pragma unroll
+            for (int u = 0; u < U; ++u) {
+                const int c = c0 + u * V * HEAVY_THREADS;
+#pragma unroll
+                for (int k = 0; k < V; ++k) rc[u][k] = ROLE_DEAD;
+                if (VEC && c + 1 < c_hi) {
+                    const int2 r2 = *(const int2 *)(a.c.role + c), s2 = *(const int2 *)(a.c.size + c);
+                    const double2 a2 = __ldcs((const double2 *)(Wi + c)), b2 = __ldcg((const double2 *)(Wj + c));
+                    rc[u][0] = r2.x; rc[u][V - 1] = r2.y;
+                    sz[u][0] = s2.x; sz[u][V - 1] = s2.y;
+                    A[u][0] = a2.x; A[u][V - 1] = a2.y;
+                    B[u][0] = b2.x; B[u][V - 1] = b2.y;
+                } else if (c < c_hi) {
+                    rc[u][0] = a.c.role[c];
+                    sz[u][0] = a.c.size[c];
+                    A[u][0] = __ldcs(Wi + c);
+                    B[u][0] = __ldcg(Wj + c);
+                }
+            }
+#pragma unroll
+            for (int u = 0; u < U; ++u) {
+#pragma unroll
+                for (int k = 0; k < V; ++k) {
+                    const int c = c0 + u * V * HEAVY_THREADS + k, r = rc[u][k];
+                    if (r == ROLE_DEAD || (r >= 0 && !(r & 1)) || c == p.j) continue;
+                    double x;
+                    if (r == ROLE_FREE) {
+                        x = lw(method, A[u][k], B[u][k], p, (double)sz[u][k]);
+                    } else {  // c is the surviving side of another pair q: four old entries -> one new
+                        const Pair pq = a.pairs[r >> 1];
+                        const double Ai = __ldcg(Wi + pq.i), Bi = __ldcg(Wj + pq.i);
+                        if (p.j < pq.j) {  // p merges first
+                            const double b1 = lw(method, Ai, Bi, p, pq.s1), b2 = lw(method, A[u][k], B[u][k], p, pq.s2);
+                            x = lw(method, b1, b2, pq, ps);
+                        } else {  // q merges first
+                            const double a1 = lw(method, Ai, A[u][k], pq, p.s1), a2 = lw(method, Bi, B[u][k], pq, p.s2);
+                            x = lw(method, a1, a2, p, __dadd_rn(pq.s1, pq.s2));
+                        }
+                    }
+                    Wj[c] = x;
+                    best.push(x, c);
+                }
+            }
+        }
+    } else {
+        const int row = a.rq[e - P];
+        const double *Wr = a.W + (size_t)row * a.stride;
+        for (int c0 = c_lo + tid * V; c0 < c_hi; c0 += U * V * HEAVY_THREADS) {
+            double X[U][V];
+            int rc[U][V];
+#pragma unroll
+            for (int u = 0; u < U; ++u) {
+                const int c = c0 + u * V * HEAVY_THREADS;
+#pragma unroll
+                for (int k = 0; k < V; ++k) rc[u][k] = ROLE_DEAD;
+                if (VEC && c + 1 < c_hi) {
+                    const int2 r2 = *(const int2 *)(a.c.role + c);
+                    const double2 x2 = __ldcg((const double2 *)(Wr + c));
+                    rc[u][0] = r2.x; rc[u][V - 1] = r2.y;
+                    X[u][0] = x2.x; X[u][V - 1] = x2.y;
+                } else if (c < c_hi) {
+                    rc[u][0] = a.c.role[c];
+                    X[u][0] = __ldcg(Wr + c);
+                }
+            }
+#pragma unroll
+            for (int u = 0; u < U; ++u) {
+#pragma unroll
+                for (int k = 0; k < V; ++k) {
+                    const int c = c0 + u * V * HEAVY_THREADS + k, r = rc[u][k];
+                    if (r == ROLE_DEAD || (r >= 0 && !(r & 1)) || c == row) continue;
+                    best.push(X[u][k], c);
+                }
+            }
+        }
+    }
+}
+
+__global__ void __launch_bounds__(HEAVY_THREADS, 3) kr_heavy(RArgs a) {
+    __shared__ double s_m1[HEAVY_THREADS / 32], s_m2[HEAVY_THREADS / 32];
+    __shared__ int s_i1[HEAVY_THREADS / 32];
+    __shared__ int s_flag;
+    RState *st = a.st;
+    if (st->done) return;
+    const int P = st->P, total = P + st->qlen, tid = threadIdx.x, ncols = a.ncols;
+    // segments per entry: enough items to occupy the grid, segments of at least SEG_MIN columns (even)
+    constexpr int SEG_MIN = 2048;
+    int S = 1;
+    if (total > 0 && total < 2 * (int)gridDim.x) {
+        S = (2 * (int)gridDim.x + total - 1) / total;
+        const int smax = (ncols + SEG_MIN - 1) / SEG_MIN;
+        if (S > smax) S = smax;
+        if (S > a.max_segs) S = a.max_segs;
+        if (S < 1) S = 1;
+    }
+    int seg_len = (ncols + S - 1) / S;
+    seg_len = (seg_len + 1) & ~1;
+    const bool vec = (a.stride & 1) == 0;
+    const long long items = (long long)total * S;
+    for (long long w = blockIdx.x; w < items; w += gridDim.x) {
+        const int e = (int)(w / S), seg = (int)(w - (long long)e * S);
+        const int c_lo = seg * seg_len, c_hi = min(ncols, c_lo + seg_len);
+        Min2 best;
+        best.init();
+        if (c_lo < c_hi) {
+            if (vec) heavy_columns<true>(a, e, P, c_lo, c_hi, best);
+            else heavy_columns<false>(a, e, P, c_lo, c_hi, best);
+        }
+        best.warp_reduce();
+        if ((tid & 31) == 0) {
+            s_m1[tid >> 5] = best.m1;
+            s_m2[tid >> 5] = best.m2;
+            s_i1[tid >> 5] = best.i1;
+        }
+        __syncthreads();
+        if (tid < 32) {
+            Min2 r;
+            r.init();
+            if (tid < HEAVY_THREADS / 32) { r.m1 = s_m1[tid]; r.m2 = s_m2[tid]; r.i1 = s_i1[tid]; }
+            r.warp_reduce();
+            bool finish = S == 1;
+            if (S > 1) {  // publish the partial; the last segment of the entry combines them all
+                if (tid == 0) {
+                    Part pt;
+                    pt.m1 = r.m1; pt.m2 = r.m2; pt.i1 = r.i1; pt.pad = 0;
+                    a.parts[(size_t)e * a.max_segs + seg] = pt;
+                    __threadfence();
+                    s_flag = atomicAdd(&a.seg_done[e], 1) == S - 1;
+                }
+                __syncwarp();
+                finish = s_flag != 0;
+                if (finish) {
+                    __threadfence();
+                    r.init();
+                    for (int k = tid; k < S; k += 32) {
+                        const volatile Part *vp = &a.parts[(size_t)e * a.max_segs + k];
+                        Part pt;
+                        pt.m1 = vp->m1; pt.m2 = vp->m2; pt.i1 = vp->i1;
+                        r.merge(pt.m1, pt.i1, pt.m2);
+                    }
+                    r.warp_reduce();
+                }
+            }
+            if (finish && tid == 0) {
+                const int row = e < P ? a.pairs[e].j : a.rq[e - P];
+                a.c.nn_val[row] = r.m1;
+                a.c.nn_idx[row] = r.i1 == INT_MAX ? -1 : r.i1;
+                a.c.sec[row] = r.m2;
+                a.c.fresh[row] = 1;
+                a.c.need[row] = 0;
+                if (S > 1) a.seg_done[e] = 0;
+                atomicAdd(&st->stats[e < P ? 2 : 0], 1ull);
+                atomicAdd(&st->stats[e < P ? 3 : 1], (unsigned long long)st->nactive);
+            }
+        }
+        __syncthreads();
+    }
+    // last CTA out retires the pairs of this round and closes it
+    __syncthreads();
+    if (tid == 0) {
+        __threadfence();
+        s_flag = atomicAdd(&st->blocks_done, 1) == (int)gridDim.x - 1;
+    }
+    __syncthreads();
+    if (!s_flag) return;
+    __threadfence();
+    for (int q = tid; q < P; q += HEAVY_THREADS) {
+        const Pair p = a.pairs[q];
+        a.c.role[p.i] = ROLE_DEAD;
+        a.c.role[p.j] = ROLE_FREE;
+        a.c.size[p.j] = (int)(p.s1 + p.s2);
+    }
+    __syncthreads();
+    if (tid == 0) {
+        st->n_done += P;
+        st->nactive -= P;
+        st->stats[5] += st->deferred;
+        if (st->n_done >= a.n - 1) st->done = 1;
+        else if (st->ambiguous && !a.diag) st->done = 1;
+        else if (P == 0 && st->deferred == 0 && total == 0) { st->stuck = 1; st->done = 1; }  // only pending near-ties left
+        st->P = 0;
+        st->qlen = 0;
+        st->deferred = 0;
+        st->blocks_done = 0;
+        st->round += 1;
+    }
+}
+
+// ---- order-preserving compaction -----------------------------------------------------------------
+__global__ void __launch_bounds__(1024) kc_map(const int *role, int ncols, int *newidx, int *oldidx) {
+    __shared__ int s_warp[32];
+    __shared__ int s_base;
+    if (threadIdx.x == 0) s_base = 0;
+    __syncthreads();
+    for (int c0 = 0; c0 < ncols; c0 += 1024) {
+        const int c = c0 + threadIdx.x;
+        const bool live = c < ncols && role[c] != ROLE_DEAD;
+        const unsigned m = __ballot_sync(0xffffffffu, live);
+        if ((threadIdx.x & 31) == 0) s_warp[threadIdx.x >> 5] = __popc(m);
+        __syncthreads();
+        int before = s_base;
+        for (int w = 0; w < (int)(threadIdx.x >> 5); ++w) before += s_warp[w];
+        const int k = before + __popc(m & ((1u << (threadIdx.x & 31)) - 1));
+        if (c < ncols) newidx[c] = live ? k : -1;
+        if (live) oldidx[k] = c;
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            int t = 0;
+            for (int w = 0; w < 32; ++w) t += s_warp[w];
+            s_base += t;
+        }
+        __syncthreads();
+    }
+}
+
+__global__ void __launch_bounds__(256) kc_gather(const double *Wold, long long stride_old, double *Wnew,
+                                                 long long stride_new, const int *oldidx, int nnew) {
+    for (int r = blockIdx.x; r < nnew; r += gridDim.x) {
+        const double *src = Wold + (size_t)oldidx[r] * stride_old;
+        double *dst = Wnew + (size_t)r * stride_new;
+        for (int c = threadIdx.x; c < nnew; c += 256) dst[c] = __ldcs(src + oldidx[c]);
+    }
+}
+
+__global__ void kc_cols(Cols o, Cols d, const int *newidx, const int *oldidx, int nnew) {
+    const int k = blockIdx.x * blockDim.x + threadIdx.x;
+    if (k >= nnew) return;
+    const int c = oldidx[k];
+    d.role[k] = ROLE_FREE;
+    d.size[k] = o.size[c];
+    const int nn = o.nn_idx[c];
+    d.nn_idx[k] = nn >= 0 ? newidx[nn] : -1;
+    d.orig[k] = o.orig[c];
+    d.nn_val[k] = o.nn_val[c];
+    d.sec[k] = o.sec[c];
+    d.fresh[k] = o.fresh[c];
+    d.need[k] = o.need[c];
+}
+
+struct Layout {
+    RState *st;
+    Pair *pairs;
+    int *rq, *rec_a, *rec_b, *newidx, *oldidx;
+    double *rec_d;
+    Cols cols[2];
+    double *spare;
+    size_t spare_elems;
+    Part *parts;
+    int *seg_done;
+};
+
+size_t spare_elems_for(int n) {
+    const size_t h = (size_t)n / 2 + 1;
+    return h * h;
+}
+
+bool carve(void *workspace, size_t bytes, int n, Layout &L) {
+    hc::Carver ws(workspace, bytes);
+    L.st = ws.take<RState>(1);
+    L.pairs = ws.take<Pair>((size_t)n / 2 + 1);
+    L.rq = ws.take<int>(n);
+    L.rec_a = ws.take<int>(n);
+    L.rec_b = ws.take<int>(n);
+    L.newidx = ws.take<int>(n);
+    L.oldidx = ws.take<int>(n);
+    L.rec_d = ws.take<double>(n);
+    for (int k = 0; k < 2; ++k) {
+        L.cols[k].role = ws.take<int>(n);
+        L.cols[k].size = ws.take<int>(n);
+        L.cols[k].nn_idx = ws.take<int>(n);
+        L.cols[k].orig = ws.take<int>(n);
+        L.cols[k].nn_val = ws.take<double>(n);
+        L.cols[k].sec = ws.take<double>(n);
+        L.cols[k].fresh = ws.take<unsigned char>(n);
+        L.cols[k].need = ws.take<unsigned char>(n);
+    }
+    L.parts = ws.take<Part>((size_t)SPLIT_ENTRIES * MAX_SEGS);
+    L.seg_done = ws.take<int>(SPLIT_ENTRIES);
+    L.spare_elems = spare_elems_for(n);
+    L.spare = ws.take<double>(L.spare_elems);
+    return ws.ok();
+}
+
+}  // namespace
+
+extern "C" size_t hc_linkage_rounds_workspace_bytes(int32_t n) {
+    if (n < 1) n = 1;
+    size_t per_col = 4 * 5 + 8 + 2 * (4 * 4 + 8 * 2 + 2);
+    return 8192 + (size_t)n * per_col + ((size_t)n / 2 + 1) * sizeof(Pair) + 40 * 256 + spare_elems_for(n) * 8 +
+           (size_t)SPLIT_ENTRIES * (MAX_SEGS * sizeof(Part) + 4);
+}
+
+// W: n x n float64 full symmetric working matrix (squared distances for ward, +inf diagonal), destroyed.
+// Returns HC_OK with Z filled, or HC_EAMBIGUOUS (W is then garbage: rebuild it and call hc_linkage).
+// h_stats[10]: rounds, merges, rescans, sum of live columns over rescans, sum over merged-row builds,
+// row x pair light updates, compactions, near-tied sorted heights, near-tied pair observations (pairs left
+// pending for a round), pairs deferred for an exact rescan.
+extern "C" int hc_linkage_rounds(double *W, int32_t n, int method, void *workspace, size_t workspace_bytes,
+                                 double *h_Z, int64_t *h_stats, void *stream_) {
+    cudaStream_t stream = (cudaStream_t)stream_;
+    HC_REQUIRE(W && workspace && h_Z && n >= 1 && method >= 0 && method <= 4, "bad arguments");
+    if (h_stats) memset(h_stats, 0, 10 * sizeof(int64_t));
+    if (n < 2) return HC_OK;
+    Layout L;
+    if (workspace_bytes < hc_linkage_rounds_workspace_bytes(n) || !carve(workspace, workspace_bytes, n, L)) {
+        hc::set_error("hc_linkage_rounds: workspace too small");
+        return HC_EWORKSPACE;
+    }
+    const int sms = hc::sm_count();
+    RArgs a;
+    memset(&a, 0, sizeof a);
+    a.W = W;
+    a.stride = n;
+    a.ncols = n;
+    a.n = n;
+    a.method = method;
+    a.c = L.cols[0];
+    a.pairs = L.pairs;
+    a.rq = L.rq;
+    a.rec_a = L.rec_a;
+    a.rec_b = L.rec_b;
+    a.rec_d = L.rec_d;
+    a.st = L.st;
+    a.parts = L.parts;
+    a.seg_done = L.seg_done;
+    a.max_segs = MAX_SEGS;
+    a.diag = getenv("HC_ROUNDS_DIAG") != nullptr;  // count near-ties instead of stopping at the first (never certifies)
+    int cur = 0;          // which Cols set is live
+    bool in_spare = false;  // whether the live matrix is in the spare buffer
+    const bool compact = getenv("HC_ROUNDS_NOCOMPACT") == nullptr;
+    int batch = 8;
+    if (const char *e = getenv("HC_ROUNDS_BATCH")) batch = atoi(e) > 0 ? atoi(e) : 8;
+    long long compactions = 0;
+
+    auto light_heavy = [&]() {
+        int lg = (a.ncols + LIGHT_THREADS / 32 - 1) / (LIGHT_THREADS / 32);
+        if (lg > sms * 8) lg = sms * 8;
+        kr_light<<<lg, LIGHT_THREADS, 0, stream>>>(a);
+        int hg = sms * 8 < HEAVY_GRID_MAX ? sms * 8 : HEAVY_GRID_MAX;
+        if (a.ncols < 2 * 2048 && hg > a.ncols) hg = a.ncols;  // rows too short to be split: one CTA per entry at most
+        kr_heavy<<<hg, HEAVY_THREADS, 0, stream>>>(a);
+    };
+    HC_CUDA_OK(cudaMemsetAsync(L.seg_done, 0, SPLIT_ENTRIES * sizeof(int), stream));
+    kr_init<<<(n + 255) / 256, 256, 0, stream>>>(a);
+    light_heavy();  // initial nearest neighbour of every row ("first linkage pass")
+    HC_CHECK_LAUNCH();
+    RState h;
+    for (;;) {
+        for (int b = 0; b < batch; ++b) {
+            kr_select<<<(a.ncols + 255) / 256, 256, 0, stream>>>(a);
+            light_heavy();
+        }
+        HC_CHECK_LAUNCH();
+        HC_CUDA_OK(cudaMemcpyAsync(&h, L.st, sizeof h, cudaMemcpyDeviceToHost, stream));
+        HC_CUDA_OK(cudaStreamSynchronize(stream));
+        if (h.done) break;
+        if (compact && a.ncols >= 256 && (long long)h.nactive * 2 <= a.ncols) {
+            const int nnew = h.nactive;
+            double *dst = in_spare ? W : L.spare;
+            const long long stride_new = (nnew + 1) & ~1;  // even: rows stay 16-byte aligned for the vector loads
+            HC_REQUIRE(in_spare || (size_t)nnew * stride_new <= L.spare_elems, "compaction buffer too small");
+            kc_map<<<1, 1024, 0, stream>>>(a.c.role, a.ncols, L.newidx, L.oldidx);
+            kc_gather<<<nnew < sms * 8 ? nnew : sms * 8, 256, 0, stream>>>(a.W, a.stride, dst, stride_new, L.oldidx, nnew);
+            kc_cols<<<(nnew + 255) / 256, 256, 0, stream>>>(a.c, L.cols[cur ^ 1], L.newidx, L.oldidx, nnew);
+            HC_CHECK_LAUNCH();
+            cur ^= 1;
+            in_spare = !in_spare;
+            a.c = L.cols[cur];
+            a.W = dst;
+            a.stride = stride_new;
+            a.ncols = nnew;
+            compactions++;
+        }
+    }
+    const int m = n - 1;
+    const bool uncertified = h.ambiguous || h.stuck || h.n_done != m || (a.diag && h.stats[6]);
+    if (a.diag) {
+        fprintf(stderr, "[hc_linkage_rounds diag] n=%d rounds=%d merges=%d near-tie observations=%llu, relative gaps:", n, h.round,
+                h.n_done, h.stats[6]);
+        for (unsigned long long k = 0; k < h.stats[6] && k < 16; ++k) fprintf(stderr, " %.3g", h.gaps[k]);
+        fprintf(stderr, "\n");
+    }
+    if (uncertified) {
+        hc::set_error("hc_linkage_rounds: %s within %.0e relative after %d merges (round %d): not certified "
+                      "[leaves %d(size %d) ~ %d(size %d): d=%.17g/%.17g second minima %.17g %.17g]",
+                      h.stuck ? "only near-tied pairs left" : "exact tie", MARGIN, h.n_done,
+                      h.round, h.amb_r, h.amb_sr, h.amb_b, h.amb_sb, h.amb_v, h.amb_vb, h.amb_secr, h.amb_secb);
+        if (h_stats) { h_stats[0] = h.round; h_stats[1] = h.n_done; h_stats[8] = (int64_t)h.stats[6]; }
+        if (h.n_done != m) return HC_EAMBIGUOUS;  // (diagnostics mode finishes the run: Z is filled, but NOT certified)
+    }
+    std::vector<int> ra(m), rb(m);
+    std::vector<double> rd(m);
+    HC_CUDA_OK(cudaMemcpyAsync(ra.data(), L.rec_a, m * sizeof(int), cudaMemcpyDeviceToHost, stream));
+    HC_CUDA_OK(cudaMemcpyAsync(rb.data(), L.rec_b, m * sizeof(int), cudaMemcpyDeviceToHost, stream));
+    HC_CUDA_OK(cudaMemcpyAsync(rd.data(), L.rec_d, m * sizeof(double), cudaMemcpyDeviceToHost, stream));
+    HC_CUDA_OK(cudaStreamSynchronize(stream));
+    long long near = 0;
+    hc::records_to_Z(n, method == M_WARD, ra.data(), rb.data(), rd.data(), h_Z, HEIGHT_TOL, &near);
+    if (h_stats) {
+        h_stats[0] = h.round;
+        h_stats[1] = h.n_done;
+        h_stats[2] = (int64_t)h.stats[0];
+        h_stats[3] = (int64_t)h.stats[1];
+        h_stats[4] = (int64_t)h.stats[3];
+        h_stats[5] = (int64_t)h.stats[4];
+        h_stats[6] = compactions;
+        h_stats[7] = near;
+        h_stats[8] = (int64_t)h.stats[6];
+        h_stats[9] = (int64_t)h.stats[5];
+    }
+    if (uncertified) return HC_EAMBIGUOUS;
+    if (near) {
+        hc::set_error("hc_linkage_rounds: %lld sorted heights closer than %.0e relative: merge order not certified", near,
+                      HEIGHT_TOL);
+        return HC_EAMBIGUOUS;
+    }
+    return HC_OK;
+}

@@ -9,7 +9,7 @@ import torch
 from . import ops
 
 
-def linkage(X, method="single", metric="euclidean", preserve_input=True):
+def linkage(X, method="single", metric="euclidean", preserve_input=True, engine="auto"):
     """Hierarchical clustering of a condensed dissimilarity vector; returns the scipy-style
     linkage array (n-1, 4) float64.  Observation matrices (2-D X) are outside the hot path."""
     if isinstance(X, torch.Tensor):
@@ -33,13 +33,14 @@ def linkage(X, method="single", metric="euclidean", preserve_input=True):
     if N < 2:
         return np.empty((0, 4))
     y = y.cuda()
-    W, flags = ops.expand_condensed(y, N, square=(method == "ward"))
-    return ops.linkage_working(W, method, nan_flags=flags)
+    # engine="auto": round-parallel engine when every decision is certified tie-free, otherwise the serial
+    # NN-chain whose scan order reproduces fastcluster's tie-breaking (csrc/linkage_rounds.cu, linkage.cu)
+    return ops.linkage_auto(lambda: ops.expand_condensed(y, N, square=(method == "ward")), method, engine=engine)
 
 
 def linkage_square(D, method="ward", kind=ops.KIND_IDENTITY, p0=0.0, p1=1.0, r=None, c=None, vmax=1.0,
-                   return_stats=False):
+                   return_stats=False, engine="auto"):
     """Device fast path: linkage of ``transform(D)[np.triu_indices(n,1)]`` for a square CUDA matrix
     D without materialising the condensed vector (K6 fused into the working-matrix build)."""
-    W, flags = ops.transform_to_working(D, kind, p0, p1, r, c, vmax, square=(method == "ward"))
-    return ops.linkage_working(W, method, nan_flags=flags, return_stats=return_stats)
+    return ops.linkage_auto(lambda: ops.transform_to_working(D, kind, p0, p1, r, c, vmax, square=(method == "ward")),
+                            method, engine=engine, return_stats=return_stats)

@@ -9,6 +9,7 @@ HBM from pair records to the linkage array.
 from __future__ import annotations
 
 import ctypes as C
+import os
 import warnings
 
 import numpy as np
@@ -307,6 +308,58 @@ def linkage_working(W, method="ward", nan_flags=None, return_stats=False):
         return Z, dict(scans=stats[0], scan_active=stats[1], merges=stats[2], update_active=stats[3],
                        row_scans=stats[4], row_scan_active=stats[5], cached_lookups=stats[6])
     return Z
+
+
+def linkage_rounds(W, method="ward", nan_flags=None, workspace=None):
+    """Round-parallel linkage of a working matrix (destroyed), csrc/linkage_rounds.cu.  Returns
+    (Z, stats) when every merge and the sorted heights could be certified tie-free, else (None, stats):
+    the caller rebuilds W and uses linkage_working, whose scan order reproduces fastcluster's ties."""
+    _dev(W)
+    n = W.shape[0]
+    if nan_flags is not None and int(nan_flags[0].item()):
+        raise FloatingPointError("NaN dissimilarity value.")
+    L = _lib.lib()
+    need = L.hc_linkage_rounds_workspace_bytes(n)
+    ws = workspace if workspace is not None and workspace.numel() >= need else \
+        torch.empty(need, dtype=torch.uint8, device=W.device)
+    Z = np.empty((max(n - 1, 0), 4), dtype=np.float64)
+    stats = (C.c_int64 * 10)()
+    rc = L.hc_linkage_rounds(_ptr(W), n, METHODS[method], _ptr(ws), ws.numel(),
+                             Z.ctypes.data_as(C.c_void_p), stats, _stream())
+    st = dict(engine="rounds", rounds=stats[0], merges=stats[1], rescans=stats[2], rescan_cols=stats[3],
+              build_cols=stats[4], light_updates=stats[5], compactions=stats[6], near_tied_heights=stats[7],
+              pending_near_ties=stats[8], deferred_rescans=stats[9],
+              certified=(rc == _lib.HC_OK))
+    if rc == _lib.HC_EAMBIGUOUS:
+        st["reason"] = _lib.last_error()
+        if os.environ.get("HC_ROUNDS_DIAG") and st["merges"] == n - 1:
+            st["Z_uncertified"] = Z     # diagnostics only (tests / measurements), never returned as a result
+        return None, st
+    _lib.check(rc)
+    return Z, st
+
+
+def linkage_auto(make_working, method="ward", engine="auto", return_stats=False):
+    """make_working() -> (W, nan_flags) builds a fresh working matrix.  engine: "exact" = serial NN-chain
+    (fastcluster's tie order), "rounds" = round-parallel (raises if it cannot certify), "auto" = rounds,
+    falling back to exact on a fresh matrix when a tie is met."""
+    if engine not in ("auto", "exact", "rounds"):
+        raise ValueError("engine must be auto, exact or rounds")
+    W, flags = make_working()
+    if engine != "exact" and W.shape[0] >= 2:
+        Z, st = linkage_rounds(W, method, nan_flags=flags)
+        if Z is not None:
+            return (Z, st) if return_stats else Z
+        if engine == "rounds":
+            raise ArithmeticError("round-parallel linkage could not certify the merge order: " + st.get("reason", ""))
+        del W
+        W, flags = make_working()
+        Z, st2 = linkage_working(W, method, nan_flags=flags, return_stats=True)
+        st2.update(engine="exact", fallback_from_rounds=st)
+        return (Z, st2) if return_stats else Z
+    Z, st = linkage_working(W, method, nan_flags=flags, return_stats=True)
+    st["engine"] = "exact"
+    return (Z, st) if return_stats else Z
 
 
 def linkage_batch(Ws, method="ward"):

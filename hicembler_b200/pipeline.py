@@ -32,11 +32,12 @@ class StageTimer:
 
 def pairs_to_dendrogram(records, offsets, window_bp, n_windows, mapq=10, params=(0.5, 1.1), method="ward",
                         balance=False, max_iter=1000, epsilon=0.00001, keep=False, timer=None,
-                        member=None, region_mask=None, workspace=None):
+                        member=None, region_mask=None, workspace=None, engine="auto"):
     """records: int32 [P,6] CUDA tensor; offsets: int32 CUDA table refID -> first window.
 
     balance=False is the reference at HEAD (normalize() commented out, bam2clusters.py:512);
     balance=True applies normalize() (:36-49) before distance_func(x+1, a, b) (:516).
+    engine: "auto" (round-parallel linkage, exact serial NN-chain when a tie is met), "exact", "rounds".
     Returns dict(Z, stats, [r, c, sk_iterations, sk_stop, working, sym])."""
     t = timer or StageTimer(False)
     t.mark("start")
@@ -52,18 +53,27 @@ def pairs_to_dendrogram(records, offsets, window_bp, n_windows, mapq=10, params=
         res = ops.sinkhorn_fit(S1, vm, max_iter, epsilon)
         t.mark("sinkhorn")
         out.update(r=res.r, c=res.c, sk_iterations=res.iterations, sk_stop=res.stopping_condition, vmax=vm)
-        W, flags = ops.transform_to_working(S1, ops.KIND_POWER, a, b, res.r, res.c, vm, square=(method == "ward"))
+        def make_working():
+            return ops.transform_to_working(S1, ops.KIND_POWER, a, b, res.r, res.c, vm, square=(method == "ward"))
         sym = S1
     else:
         S, vmax = ops.fold_counts(counts, "sym", inplace=True)
         t.mark("fold")
-        W, flags = ops.transform_to_working(S, ops.KIND_POWER, a, b, square=(method == "ward"))
+        def make_working():
+            return ops.transform_to_working(S, ops.KIND_POWER, a, b, square=(method == "ward"))
         sym = S
-    t.mark("transform")
     if keep:
-        out["working"] = W.clone()
+        out["working"] = make_working()[0]
         out["sym"] = sym
-    Z, lst = ops.linkage_working(W, method, nan_flags=flags, return_stats=True)
+    built = []
+
+    def timed_make_working():      # the first build is the "transform" stage; a rebuild after an uncertified
+        r_ = make_working()        # round-parallel run is charged to "linkage"
+        if not built:
+            t.mark("transform")
+        built.append(1)
+        return r_
+    Z, lst = ops.linkage_auto(timed_make_working, method, engine=engine, return_stats=True)
     t.mark("linkage")
     out["Z"] = Z
     out["linkage_stats"] = lst

@@ -42,9 +42,14 @@ class Genome:
         return np.concatenate([[0], np.cumsum(n)[:-1]]).astype(np.int64)
 
 
-def make_genome(n_contigs, n_windows, window_bp, n_chrom, seed=1, sigma=0.8):
+def make_genome(n_contigs, n_windows, window_bp, n_chrom, seed=1, sigma=0.8, min_tail=1):
     """Contig lengths ~ lognormal(sigma) with every contig >= 2 windows and
-    sum(ceil(size/window_bp)) == n_windows exactly; contiguous runs of contigs form chromosomes."""
+    sum(ceil(size/window_bp)) == n_windows exactly; contiguous runs of contigs form chromosomes.
+    The trailing (partial) window of every contig is min_tail .. window_bp bases long.  A trailing
+    window shorter than half a read can never receive a read midpoint (get_window,
+    bam2clusters.py:119-126): with the default min_tail=1 about n_contigs * 50 / window_bp windows are
+    structurally empty, i.e. identical rows and exact distance ties; min_tail >= read length makes
+    every window mappable."""
     rng = np.random.Generator(np.random.PCG64(seed))
     assert n_windows >= 2 * n_contigs
     w = rng.lognormal(0.0, sigma, n_contigs)
@@ -53,6 +58,8 @@ def make_genome(n_contigs, n_windows, window_bp, n_chrom, seed=1, sigma=0.8):
     short = n_windows - int(n.sum())
     n[rng.choice(n_contigs, short, replace=False)] += 1  # floor leftovers: short < n_contigs
     sizes = n * window_bp - rng.integers(1, window_bp, n_contigs)
+    if min_tail > 1:  # same draws as min_tail=1 (fixtures keep their values), tails clipped from below
+        sizes = np.maximum(sizes, (n - 1) * window_bp + min(int(min_tail), window_bp))
     bounds = np.linspace(0, sizes.sum(), n_chrom + 1)[1:-1]
     chrom_of = np.searchsorted(bounds, np.cumsum(sizes) - sizes // 2, side="right")
     # make sure chromosome ids are contiguous 0..C-1 even if a chromosome came out empty

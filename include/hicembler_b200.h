@@ -32,7 +32,9 @@ typedef enum {
     HC_ENEG = -5,     /* negative entry in P: SinkhornKnopp.fit asserts (sinkhorn_knopp.py:110) */
     HC_ECUDA = -6,    /* CUDA runtime error */
     HC_EWORKSPACE = -7, /* workspace too small */
-    HC_ENOTRI = -8    /* condensed length is not n*(n-1)/2: fastcluster raises ValueError */
+    HC_ENOTRI = -8,   /* condensed length is not n*(n-1)/2: fastcluster raises ValueError */
+    HC_EAMBIGUOUS = 1 /* hc_linkage_rounds only, not an error: a tie keeps the round-parallel engine from
+                       * certifying fastcluster's merge order; rebuild W and call hc_linkage */
 } hc_status;
 
 /* One alignment record, 24 bytes, little endian (BAM core fields of
@@ -182,6 +184,21 @@ int hc_linkage_launch(double *W, int32_t n, int method, void *workspace, size_t 
                       void *stream);
 int hc_linkage_finish(int32_t n, int method, void *workspace, size_t workspace_bytes, double *h_Z,
                       int64_t *h_stats, void *stream);
+
+/* K7b  round-parallel engine for the same call sites (csrc/linkage_rounds.cu): merges every reciprocal
+ * nearest-neighbour pair per round on all SMs.  Same W contract as hc_linkage.  Every merge and the
+ * sorted heights are certified against ties (1e-12 / 2e-13 relative); when certification fails the
+ * call returns HC_EAMBIGUOUS with W destroyed and the caller falls back to hc_linkage, whose scan
+ * order reproduces fastcluster's tie-breaking.  When it returns HC_OK, Z[:,0:2] and Z[:,3] equal
+ * hc_linkage's and Z[:,2] agrees to rounding (same Lance-Williams operations, different interleaving).
+ * A NEAR tie only leaves its pair pending (it is merged in a later round once it is strict); the call
+ * gives up on an EXACT tie or when only near-tied pairs are left.
+ * h_stats[10]: rounds, merges, rescans, sum live columns over rescans, sum live columns over merged-row
+ * builds, row x pair updates, compactions, near-tied heights, pending near-tie observations, pairs
+ * deferred for an exact rescan. */
+size_t hc_linkage_rounds_workspace_bytes(int32_t n);
+int hc_linkage_rounds(double *W, int32_t n, int method, void *workspace, size_t workspace_bytes,
+                      double *h_Z, int64_t *h_stats, void *stream);
 
 /* ---------------------------------------------------------------------------------------
  * K8  block reductions on the resident matrix.

@@ -1,0 +1,9 @@
+set -x
+mkdir -p gpurun_out
+python -m hicembler_b200.build > /dev/null 2>&1 || echo BUILD FAILED
+for c in C2 C3; do
+timeout 600 python bench.py --config $c --steps 2 --warmup 1 --no-cpu-baseline > gpurun_out/r2_$c.json 2> gpurun_out/r2_$c.err; echo "rc=$?"; tail -3 gpurun_out/r2_$c.err
+python -c "
+import json;d=json.load(open('gpurun_out/r2_$c.json'));print(d['ms_per_step'],d['stage_ms']); print({k:round(v['frac'],3) for k,v in d['stage_rooflines'].items()}); print(d['linkage'])"
+done
+timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none -c 6000 --csv --log-file gpurun_out/r2_launches_C3.csv python bench.py --steps 1 --warmup 0 --no-cpu-baseline > gpurun_out/r2_ncu.log 2>&1; echo "ncu rc=$?"

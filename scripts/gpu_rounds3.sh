@@ -1,0 +1,14 @@
+set -x
+mkdir -p gpurun_out
+python -m hicembler_b200.build > /dev/null 2>&1 || echo BUILD FAILED
+make -s -C oracle libnnchain.so
+timeout 900 python -m pytest tests -m gpu -x -q -k "linkage or dendrogram or cluster_contigs or tree" > gpurun_out/r3_pytest.log 2>&1; echo "pytest rc=$?"; tail -15 gpurun_out/r3_pytest.log
+for c in C1 C2 C3; do
+timeout 600 python bench.py --config $c --steps 2 --warmup 1 --no-cpu-baseline > gpurun_out/r3_$c.json 2> gpurun_out/r3_$c.err; echo "rc=$?"; tail -3 gpurun_out/r3_$c.err
+python -c "
+import json;d=json.load(open('gpurun_out/r3_$c.json'));print(d['ms_per_step'],d['stage_ms']); print({k:round(v['frac'],3) for k,v in d['stage_rooflines'].items()}); print(d['linkage'])"
+done
+timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none -c 8000 --csv --log-file gpurun_out/r3_launches_C3.csv python bench.py --steps 1 --warmup 0 --no-cpu-baseline > gpurun_out/r3_ncu.log 2>&1; echo "ncu rc=$?"
+HC_ROUNDS_DIAG=1 timeout 600 python bench.py --config C3 --steps 1 --warmup 1 --no-cpu-baseline --min-tail 1 > gpurun_out/r3_C3_diag.json 2> gpurun_out/r3_C3_diag.err; echo "rc=$?"; grep diag gpurun_out/r3_C3_diag.err | tail -2
+python -c "
+import json;d=json.load(open('gpurun_out/r3_C3_diag.json'));print(d['ms_per_step'],d['stage_ms']); print(d['linkage'])"

@@ -346,9 +346,10 @@ def _same_tree(Z, want, rtol=1e-12):
 def test_linkage_vs_oracle_random(n, method):
     from hicembler_b200.fastcluster import linkage
     y = np.random.default_rng(n).random(n * (n - 1) // 2)
-    Z = linkage(y, method)
+    Z = linkage(y, method, engine="exact")
     _same_tree(Z, O.linkage_fastcluster(y, method))
     assert np.array_equal(Z[:, 2], O.linkage_fastcluster(y, method)[:, 2])   # heights bit-identical
+    _same_tree(linkage(y, method), O.linkage_fastcluster(y, method))          # default engine ("auto")
 
 
 @pytest.mark.parametrize("method", ["ward", "average"])
@@ -357,10 +358,11 @@ def test_linkage_tie_heavy_and_jittered(golden_dir, method):
     g = np.load(os.path.join(golden_dir, "linkage.npz"))
     for n in (40, 200, 777):
         for tag in ("ties", "jitter"):
-            Z = linkage(g["n%d_%s_y" % (n, tag)], method)
             want = g["n%d_%s_%s_fc" % (n, tag, method)]
+            Z = linkage(g["n%d_%s_y" % (n, tag)], method, engine="exact")
             _same_tree(Z, want)
             assert np.array_equal(Z[:, 2], want[:, 2])
+            _same_tree(linkage(g["n%d_%s_y" % (n, tag)], method), want)   # auto: certified or falls back
         # tie-free input: scipy (the real library) agrees as well
         _same_tree(linkage(g["n%d_jitter_y" % n], method), g["n%d_jitter_%s_scipy" % (n, method)])
 
@@ -390,9 +392,12 @@ def test_linkage_hic_distances_tie_heavy_medium():
     dist = O.transform_distance(d, 0.5, 1.1)
     for m in ("ward", "average"):
         want, stats = O.linkage_fastcluster(O.condense(dist), m, return_stats=True)
-        Z, st = array2Z(dist, m, return_stats=True)
+        Z, st = array2Z(dist, m, return_stats=True, engine="exact")
         _same_tree(Z, want)
         assert st["scans"] == stats[0] and st["scan_active"] == stats[1]   # same chain, step for step
+        Z, st = array2Z(dist, m, return_stats=True)   # auto: ties -> not certified -> exact engine
+        _same_tree(Z, want)
+        assert st["engine"] == "exact" and not st["fallback_from_rounds"]["certified"]
 
 
 @pytest.mark.parametrize("method", ["ward", "average", "single", "complete", "weighted"])
@@ -406,7 +411,7 @@ def test_linkage_nn_cache_on_off_identical(method, monkeypatch):
     out = {}
     for flag in ("0", "1"):
         monkeypatch.setenv("HC_LINKAGE_NNCACHE", flag)
-        Z, st = array2Z(dist, method, return_stats=True)
+        Z, st = array2Z(dist, method, return_stats=True, engine="exact")
         _same_tree(Z, want)
         assert np.array_equal(Z[:, 2], want[:, 2])
         assert st["scans"] == stats[0] and st["scan_active"] == stats[1]
@@ -414,6 +419,97 @@ def test_linkage_nn_cache_on_off_identical(method, monkeypatch):
     assert out["0"]["cached_lookups"] == 0 and out["0"]["row_scans"] == stats[0]
     assert out["1"]["cached_lookups"] > 0
     assert out["1"]["row_scans"] + out["1"]["cached_lookups"] == stats[0]
+
+
+# ---- K7b round-parallel engine ---------------------------------------------------------------
+@pytest.mark.parametrize("method", ["ward", "average", "single", "complete", "weighted"])
+@pytest.mark.parametrize("n", [2, 3, 4, 17, 257, 1000, 3001])
+def test_linkage_rounds_certified_equals_nnchain(n, method):
+    """tie-free input: the round-parallel engine must certify and give fastcluster's merge order and sizes,
+    heights to rounding (different interleaving of the same Lance-Williams operations)"""
+    from hicembler_b200 import ops
+    y = np.random.default_rng(1000 + n).random(n * (n - 1) // 2) + 0.05
+    W, flags = ops.expand_condensed(torch.from_numpy(y).cuda(), n, square=(method == "ward"))
+    Z, st = ops.linkage_rounds(W, method, nan_flags=flags)
+    assert Z is not None and st["certified"], st
+    assert st["merges"] == n - 1
+    _same_tree(Z, O.linkage_fastcluster(y, method), rtol=1e-12)
+
+
+@pytest.mark.parametrize("method", ["ward", "average"])
+def test_linkage_rounds_hic_balanced_matrix(method):
+    """Hi-C shaped input (Sinkhorn-balanced counts -> distance_func): long phases with one or two
+    reciprocal pairs per round, several compactions; must equal the serial chain"""
+    from hicembler_b200 import ops
+    n = 2600
+    d = O.symmetrize(hic_like_counts(n, 11, scale=6.0).astype(np.float64))
+    bal = O.normalize(np.triu(d).copy())
+    dist = O.distance_func(bal + 1, 0.5, 1.1)
+    y = O.condense(dist)
+    want = O.linkage_fastcluster(y, method)
+    W, flags = ops.expand_condensed(torch.from_numpy(y).cuda(), n, square=(method == "ward"))
+    Z, st = ops.linkage_rounds(W, method, nan_flags=flags)
+    assert Z is not None, st
+    assert st["compactions"] >= 2 and st["rounds"] < n
+    _same_tree(Z, want, rtol=1e-11)
+
+
+@pytest.mark.parametrize("env", [{}, {"HC_ROUNDS_NOCOMPACT": "1"}, {"HC_ROUNDS_BATCH": "1"}])
+def test_linkage_rounds_compaction_and_batching_do_not_change_results(env, monkeypatch):
+    from hicembler_b200 import ops
+    n = 1200
+    y = np.random.default_rng(5).random(n * (n - 1) // 2) + 0.1
+    want = O.linkage_fastcluster(y, "average")
+    for k, v in env.items():
+        monkeypatch.setenv(k, v)
+    W, flags = ops.expand_condensed(torch.from_numpy(y).cuda(), n)
+    Z, st = ops.linkage_rounds(W, "average", nan_flags=flags)
+    assert Z is not None
+    _same_tree(Z, want, rtol=1e-12)
+    ref = getattr(test_linkage_rounds_compaction_and_batching_do_not_change_results, "_ref", None)
+    if ref is None:
+        test_linkage_rounds_compaction_and_batching_do_not_change_results._ref = Z
+    else:
+        assert np.array_equal(Z, ref)    # bit-identical across compaction / batching settings
+
+
+def test_linkage_rounds_refuses_ties_and_auto_falls_back():
+    """count-derived distances are tie-heavy: the engine must say "not certified", never guess"""
+    from hicembler_b200 import ops
+    from hicembler_b200.fastcluster import linkage
+    d = O.symmetrize(hic_like_counts(900, 3, scale=5.0).astype(np.float64))
+    y = O.condense(O.transform_distance(d, 0.5, 1.1))
+    for method in ("ward", "average", "complete"):
+        W, flags = ops.expand_condensed(torch.from_numpy(y).cuda(), 900, square=(method == "ward"))
+        Z, st = ops.linkage_rounds(W, method, nan_flags=flags)
+        assert Z is None and not st["certified"]
+        with pytest.raises(ArithmeticError):
+            linkage(y, method, engine="rounds")
+        want = O.linkage_fastcluster(y, method)
+        Za = linkage(y, method)      # auto
+        _same_tree(Za, want)
+        assert np.array_equal(Za[:, 2], want[:, 2])
+    # exact duplicates of the smallest distance between disjoint pairs: heights tie -> not certified
+    y = np.random.default_rng(0).random(10 * 9 // 2) + 1.0
+    y[0] = y[-1] = 0.5            # d(0,1) == d(8,9)
+    W, flags = ops.expand_condensed(torch.from_numpy(y).cuda(), 10)
+    Z, st = ops.linkage_rounds(W, "average", nan_flags=flags)
+    assert Z is None and st["near_tied_heights"] >= 1
+    _same_tree(linkage(y, "average"), O.linkage_fastcluster(y, "average"))
+
+
+def test_linkage_rounds_chain_worst_case():
+    """points on a line with growing gaps: one reciprocal pair per round (n-1 rounds) must still be right"""
+    from hicembler_b200 import ops
+    n = 300
+    x = np.cumsum(1.0 + 0.01 * np.arange(n) + 1e-3 * np.random.default_rng(2).random(n))
+    from scipy.spatial.distance import pdist
+    y = pdist(x[:, None])
+    for method in ("single", "average", "ward"):
+        W, flags = ops.expand_condensed(torch.from_numpy(y).cuda(), n, square=(method == "ward"))
+        Z, st = ops.linkage_rounds(W, method, nan_flags=flags)
+        assert Z is not None, st
+        _same_tree(Z, O.linkage_fastcluster(y, method), rtol=1e-11)
 
 
 def test_array2tree_newick_matches_reference_recursion():
