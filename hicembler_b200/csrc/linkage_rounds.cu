@@ -39,8 +39,9 @@ enum { M_SINGLE = 0, M_COMPLETE = 1, M_AVERAGE = 2, M_WEIGHTED = 3, M_WARD = 4 }
 // Certificate thresholds.  The two engines differ only by the interleaving of the same Lance-Williams
 // operations; the largest relative difference between their heights measured on the bench workloads is
 // 3.2e-15 at n = 50 000 (ward), 4.4e-16 at n = 10 000 (average): profiles/r01_engine_discrepancy.md.
-constexpr double MARGIN = 1e-12;      // relative separation required of every decision (300 x the measured maximum)
-constexpr double HEIGHT_TOL = 2e-13;  // relative separation required of adjacent sorted heights (60 x)
+constexpr double MARGIN = 1e-13;      // relative separation required of every decision (30 x the measured maximum)
+constexpr double HEIGHT_TOL = 1e-13;  // relative separation required of adjacent sorted heights (30 x)
+// (HC_ROUNDS_MARGIN / HC_ROUNDS_HEIGHT_TOL override both for measurements)
 constexpr int ROLE_DEAD = -2, ROLE_FREE = -1;  // >= 0: 2*pair (i side, retires) / 2*pair+1 (j side, survives)
 constexpr int LIGHT_THREADS = 256, HEAVY_THREADS = 256, MAX_SEGS = 64;
 constexpr int HEAVY_GRID_MAX = 2048, SPLIT_ENTRIES = 2 * HEAVY_GRID_MAX;  // rows are split only while entries < 2 x grid
@@ -76,6 +77,7 @@ struct RArgs {
     double *W;
     long long stride;
     int ncols, n, method, diag;
+    double margin;
     Cols c;
     Pair *pairs;
     int *rq, *rec_a, *rec_b;
@@ -167,7 +169,7 @@ __global__ void __launch_bounds__(256) kr_select(RArgs a) {
             const bool exact_all = a.method == M_SINGLE || a.method == M_COMPLETE;
             const bool leaf_exact = a.method == M_AVERAGE || a.method == M_WEIGHTED;
             const double sr = a.c.sec[r], sb = a.c.sec[b];
-            const double thr = __dadd_rn(va, __dmul_rn(fabs(va), MARGIN));
+            const double thr = __dadd_rn(va, __dmul_rn(fabs(va), a.margin));
             const bool ok_r = sr > ((exact_all || (leaf_exact && a.c.size[r] == 1)) ? va : thr);
             const bool ok_b = sb > ((exact_all || (leaf_exact && a.c.size[b] == 1)) ? va : thr);
             const bool ok = ok_r && ok_b && a.c.nn_val[b] == va;
@@ -620,6 +622,10 @@ extern "C" int hc_linkage_rounds(double *W, int32_t n, int method, void *workspa
     a.parts = L.parts;
     a.seg_done = L.seg_done;
     a.max_segs = MAX_SEGS;
+    a.margin = MARGIN;
+    double height_tol = HEIGHT_TOL;
+    if (const char *e = getenv("HC_ROUNDS_MARGIN")) a.margin = atof(e);
+    if (const char *e = getenv("HC_ROUNDS_HEIGHT_TOL")) height_tol = atof(e);
     a.diag = getenv("HC_ROUNDS_DIAG") != nullptr;  // count near-ties instead of stopping at the first (never certifies)
     int cur = 0;          // which Cols set is live
     bool in_spare = false;  // whether the live matrix is in the spare buffer
@@ -679,7 +685,7 @@ extern "C" int hc_linkage_rounds(double *W, int32_t n, int method, void *workspa
     if (uncertified) {
         hc::set_error("hc_linkage_rounds: %s within %.0e relative after %d merges (round %d): not certified "
                       "[leaves %d(size %d) ~ %d(size %d): d=%.17g/%.17g second minima %.17g %.17g]",
-                      h.stuck ? "only near-tied pairs left" : "exact tie", MARGIN, h.n_done,
+                      h.stuck ? "only near-tied pairs left" : "exact tie", a.margin, h.n_done,
                       h.round, h.amb_r, h.amb_sr, h.amb_b, h.amb_sb, h.amb_v, h.amb_vb, h.amb_secr, h.amb_secb);
         if (h_stats) { h_stats[0] = h.round; h_stats[1] = h.n_done; h_stats[8] = (int64_t)h.stats[6]; }
         if (h.n_done != m) return HC_EAMBIGUOUS;  // (diagnostics mode finishes the run: Z is filled, but NOT certified)
@@ -691,7 +697,7 @@ extern "C" int hc_linkage_rounds(double *W, int32_t n, int method, void *workspa
     HC_CUDA_OK(cudaMemcpyAsync(rd.data(), L.rec_d, m * sizeof(double), cudaMemcpyDeviceToHost, stream));
     HC_CUDA_OK(cudaStreamSynchronize(stream));
     long long near = 0;
-    hc::records_to_Z(n, method == M_WARD, ra.data(), rb.data(), rd.data(), h_Z, HEIGHT_TOL, &near);
+    hc::records_to_Z(n, method == M_WARD, ra.data(), rb.data(), rd.data(), h_Z, height_tol, &near);
     if (h_stats) {
         h_stats[0] = h.round;
         h_stats[1] = h.n_done;
@@ -707,7 +713,7 @@ extern "C" int hc_linkage_rounds(double *W, int32_t n, int method, void *workspa
     if (uncertified) return HC_EAMBIGUOUS;
     if (near) {
         hc::set_error("hc_linkage_rounds: %lld sorted heights closer than %.0e relative: merge order not certified", near,
-                      HEIGHT_TOL);
+                      height_tol);
         return HC_EAMBIGUOUS;
     }
     return HC_OK;
