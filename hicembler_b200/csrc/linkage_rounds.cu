@@ -52,22 +52,29 @@ struct __align__(16) Pair {  // 48 bytes; i < j, the merged cluster lives at j
 };
 
 struct RState {
-    int P, qlen, n_done, nactive, ambiguous, stuck, done, deferred, round, blocks_done, pad0, pad1;
+    int P, qlen, n_done, nactive, ambiguous, stuck, done, deferred, round, blocks_done, last_P, last_q;
     int amb_r, amb_b, amb_sr, amb_sb;
     double amb_v, amb_secr, amb_secb, amb_vb;
     double gaps[16];  // relative gap (second minimum / minimum - 1) of the first near-tie observations
     unsigned long long stats[10];  // 0 rescans, 1 rescan columns, 2 builds, 3 build columns, 4 light updates, 5 deferred
 };
 
+// Per-row neighbour cache: the KC nearest live columns in ascending (value, index) order and, in slot KC
+// of cval, a lower bound of every live entry that is NOT listed.  A row is rescanned only when its list
+// runs empty, so a row that follows a growing cluster through KC merges costs one scan, not KC.
+constexpr int LC = 8, KC = LC - 1;  // LC = entries a scan keeps (power of two: bitonic merges), KC candidates + bound
+
 struct Cols {
-    int *role, *size, *nn_idx, *orig;
-    double *nn_val, *sec;
-    unsigned char *fresh, *need;
+    int *role, *size, *orig;
+    int *cidx;     // [ncols][LC]: candidate columns, -1 = none (slot KC unused)
+    double *cval;  // [ncols][LC]: candidate values; slot KC = lower bound of the unlisted entries
+    unsigned char *fresh, *need;  // fresh: the bound is the exact (count+1)-th smallest entry (set by a scan)
 };
 
-struct Part {  // partial (minimum, index, second minimum) of one column segment
-    double m1, m2;
-    int i1, pad;
+struct __align__(16) Part {  // partial candidate list of one column segment
+    double v[LC];
+    int i[LC];
+    double bound, pad;
 };
 
 struct RArgs {
@@ -99,33 +106,82 @@ __device__ __forceinline__ double lw(int method, double a, double b, const Pair 
     }
 }
 
-// running (minimum, lowest index attaining it, second smallest value counting duplicates)
-struct Min2 {
-    double m1, m2;
-    int i1;
+__device__ __forceinline__ bool lex_lt(double x, int c, double y, int d) { return x < y || (x == y && c < d); }
+
+// running LC smallest entries of a row in ascending (value, index) order, all in registers (static indexing only)
+struct TopL {
+    double v[LC];
+    int i[LC];
     __device__ __forceinline__ void init() {
-        m1 = m2 = __longlong_as_double(0x7ff0000000000000LL);
-        i1 = INT_MAX;
+#pragma unroll
+        for (int s = 0; s < LC; ++s) { v[s] = __longlong_as_double(0x7ff0000000000000LL); i[s] = INT_MAX; }
+    }
+    __device__ __forceinline__ void insert(double x, int c) {  // sorted insert, drops the largest
+#pragma unroll
+        for (int s = LC - 1; s > 0; --s) {
+            const bool shift = lex_lt(x, c, v[s - 1], i[s - 1]), here = lex_lt(x, c, v[s], i[s]);
+            v[s] = shift ? v[s - 1] : (here ? x : v[s]);
+            i[s] = shift ? i[s - 1] : (here ? c : i[s]);
+        }
+        if (lex_lt(x, c, v[0], i[0])) { v[0] = x; i[0] = c; }
     }
     __device__ __forceinline__ void push(double x, int c) {  // c ascending per thread
-        if (x < m1) { m2 = m1; m1 = x; i1 = c; }
-        else if (x < m2) m2 = x;
+        if (x < v[LC - 1]) insert(x, c);
     }
-    __device__ __forceinline__ void merge(double n1, int j1, double n2) {
-        if (n1 < m1 || (n1 == m1 && j1 < i1)) {
-            m2 = m1 < n2 ? m1 : n2;
-            m1 = n1;
-            i1 = j1;
-        } else {
-            m2 = n1 < m2 ? n1 : m2;
+    // this <- the LC smallest of (this U w); w ascending.  min(a[s], w[LC-1-s]) keeps exactly the LC smallest as a
+    // bitonic sequence, log2(LC) half-cleaner stages sort it.
+    __device__ __forceinline__ void merge_sorted(const double (&w)[LC], const int (&j)[LC]) {
+#pragma unroll
+        for (int s = 0; s < LC; ++s)
+            if (lex_lt(w[LC - 1 - s], j[LC - 1 - s], v[s], i[s])) { v[s] = w[LC - 1 - s]; i[s] = j[LC - 1 - s]; }
+#pragma unroll
+        for (int d = LC / 2; d > 0; d >>= 1) {
+#pragma unroll
+            for (int s = 0; s < LC; ++s) {
+                if ((s & d) == 0) {
+                    const int t = (s + d) & (LC - 1);
+                    if (lex_lt(v[t], i[t], v[s], i[s])) {
+                        const double tv = v[s]; v[s] = v[t]; v[t] = tv;
+                        const int ti = i[s]; i[s] = i[t]; i[t] = ti;
+                    }
+                }
+            }
         }
+    }
+    __device__ __forceinline__ void xmerge(int o) {  // butterfly step: both lanes end with the same merged list
+        double w[LC];
+        int j[LC];
+#pragma unroll
+        for (int s = 0; s < LC; ++s) {
+            w[s] = __shfl_xor_sync(0xffffffffu, v[s], o);
+            j[s] = __shfl_xor_sync(0xffffffffu, i[s], o);
+        }
+        merge_sorted(w, j);
     }
     __device__ __forceinline__ void warp_reduce() {
 #pragma unroll
-        for (int o = 16; o; o >>= 1) {
-            const double n1 = __shfl_xor_sync(0xffffffffu, m1, o), n2 = __shfl_xor_sync(0xffffffffu, m2, o);
-            const int j1 = __shfl_xor_sync(0xffffffffu, i1, o);
-            merge(n1, j1, n2);
+        for (int o = 16; o; o >>= 1) xmerge(o);
+    }
+};
+
+// Per-thread state of a row scan: the two smallest entries with their columns and the value of the third.
+// Candidates of a row = the two smallest of every thread; everything else is >= min over threads of m3.
+struct Min3 {
+    double m1, m2, m3;
+    int i1, i2;
+    __device__ __forceinline__ void init() {
+        m1 = m2 = m3 = __longlong_as_double(0x7ff0000000000000LL);
+        i1 = i2 = INT_MAX;
+    }
+    __device__ __forceinline__ void push(double x, int c) {  // c ascending per thread
+        if (x < m3) {
+            if (x < m2) {
+                m3 = m2;
+                if (x < m1) { m2 = m1; i2 = i1; m1 = x; i1 = c; }
+                else { m2 = x; i2 = c; }
+            } else {
+                m3 = x;
+            }
         }
     }
 };
@@ -135,9 +191,11 @@ __global__ void kr_init(RArgs a) {
     if (c < a.n) {
         a.c.role[c] = ROLE_FREE;
         a.c.size[c] = 1;
-        a.c.nn_idx[c] = -1;
         a.c.orig[c] = c;
-        a.c.nn_val[c] = a.c.sec[c] = __longlong_as_double(0x7ff0000000000000LL);
+        for (int k = 0; k < LC; ++k) {
+            a.c.cidx[(size_t)c * LC + k] = -1;
+            a.c.cval[(size_t)c * LC + k] = __longlong_as_double(0x7ff0000000000000LL);
+        }
         a.c.fresh[c] = 0;
         a.c.need[c] = 1;  // the first kr_light / kr_heavy pass is the initial NN scan of every row
     }
@@ -158,9 +216,15 @@ __global__ void __launch_bounds__(256) kr_select(RArgs a) {
     int b = -1;
     double va = 0;
     if (r < a.ncols && a.c.role[r] == ROLE_FREE) {
-        b = a.c.nn_idx[r];
-        if (b > r && a.c.nn_idx[b] == r) {
-            va = a.c.nn_val[r];
+        b = a.c.cidx[(size_t)r * LC];
+        if (b > r && a.c.cidx[(size_t)b * LC] == r) {
+            va = a.c.cval[(size_t)r * LC];
+            const double vb = a.c.cval[(size_t)b * LC];
+            // second smallest entry of either row: the next candidate (exact) or, with a single candidate left,
+            // the bound of the unlisted entries (exact only straight after a scan)
+            const bool two_r = a.c.cidx[(size_t)r * LC + 1] >= 0, two_b = a.c.cidx[(size_t)b * LC + 1] >= 0;
+            const double sr = a.c.cval[(size_t)r * LC + (two_r ? 1 : KC)], sb = a.c.cval[(size_t)b * LC + (two_b ? 1 : KC)];
+            const bool exact_r = two_r || a.c.fresh[r], exact_b = two_b || a.c.fresh[b];
             // Margin 0 where both engines compute bit-identical entries: min/max updates commute exactly
             // (single, complete), and for average/weighted every entry of a row whose cluster is still a
             // single leaf went only through the OTHER cluster's merge tree, whose operation order is fixed
@@ -168,25 +232,24 @@ __global__ void __launch_bounds__(256) kr_select(RArgs a) {
             // Elsewhere the engines interleave two merge trees differently: demand a relative MARGIN.
             const bool exact_all = a.method == M_SINGLE || a.method == M_COMPLETE;
             const bool leaf_exact = a.method == M_AVERAGE || a.method == M_WEIGHTED;
-            const double sr = a.c.sec[r], sb = a.c.sec[b];
             const double thr = __dadd_rn(va, __dmul_rn(fabs(va), a.margin));
             const bool ok_r = sr > ((exact_all || (leaf_exact && a.c.size[r] == 1)) ? va : thr);
             const bool ok_b = sb > ((exact_all || (leaf_exact && a.c.size[b] == 1)) ? va : thr);
-            const bool ok = ok_r && ok_b && a.c.nn_val[b] == va;
+            const bool ok = ok_r && ok_b && vb == va;
             if (ok) emit = true;
-            else if (a.c.fresh[r] && a.c.fresh[b]) {
+            else if (exact_r && exact_b) {
                 // Exact second minima and still too close.  A NEAR tie is left pending: the pair stays reciprocal
                 // (reducibility) and is merged in a later round if its rivals move away; all other certified
                 // merges go on (a run whose every merge is strict has a unique tree, whatever the order).  An
                 // EXACT tie (identical rows, e.g. empty windows) practically never resolves: stop at once.
                 st->amb_r = a.c.orig[r]; st->amb_b = a.c.orig[b];
                 st->amb_sr = a.c.size[r]; st->amb_sb = a.c.size[b];
-                st->amb_v = va; st->amb_vb = a.c.nn_val[b];
+                st->amb_v = va; st->amb_vb = vb;
                 st->amb_secr = sr; st->amb_secb = sb;
                 const unsigned long long k_obs = atomicAdd(&st->stats[6], 1ull);
                 if (k_obs < 16) st->gaps[k_obs] = (fmin(sr, sb) - va) / fabs(va);
                 if (a.diag) emit = true;  // diagnostics only: merge anyway, the result is NOT certified
-                else if (!(sr > va) || !(sb > va) || a.c.nn_val[b] != va) st->ambiguous = 1;
+                else if (!(sr > va) || !(sb > va) || vb != va) st->ambiguous = 1;
             }
             else {  // the bound of "the rest" is stale: rescan both rows, decide next round
                 a.c.need[r] = 1;
@@ -232,6 +295,7 @@ __global__ void __launch_bounds__(LIGHT_THREADS) kr_light(RArgs a) {
     int G = 1;
     while (G < 32 && G < P) G <<= 1;
     const int rows_per_warp = 32 / G, g = lane / G, q0 = lane - g * G;
+    const unsigned gmask = G == 32 ? 0xffffffffu : (((1u << G) - 1u) << (g * G));
     const long long warp0 = ((long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
     const long long nwarps = ((long long)gridDim.x * blockDim.x) >> 5;
     unsigned long long upd = 0;
@@ -242,7 +306,6 @@ __global__ void __launch_bounds__(LIGHT_THREADS) kr_light(RArgs a) {
         if (P > 0) {
             double *Wr = a.W + (size_t)row * a.stride;
             const double v = (double)a.c.size[row];
-            const int nn = a.c.nn_idx[row];
             for (int q = q0; q < P; q += 2 * G) {  // two pairs per lane in flight
                 const int q2 = q + G;
                 const bool two = q2 < P;
@@ -250,29 +313,52 @@ __global__ void __launch_bounds__(LIGHT_THREADS) kr_light(RArgs a) {
                 const Pair p2 = a.pairs[two ? q2 : q];
                 const double A = __ldcg(Wr + p.i), B = __ldcg(Wr + p.j);
                 const double A2 = __ldcg(Wr + p2.i), B2 = __ldcg(Wr + p2.j);
-                const double x = lw(method, A, B, p, v);
-                Wr[p.j] = x;
-                int hj = -1;
-                double hx = 0;
-                if (nn == p.i || nn == p.j) { hx = x; hj = p.j; }
-                if (two) {
-                    const double x2 = lw(method, A2, B2, p2, v);
-                    Wr[p2.j] = x2;
-                    if (nn == p2.i || nn == p2.j) { hx = x2; hj = p2.j; }
-                }
-                if (hj >= 0) {  // the cached neighbour was merged (at most one pair of the round can hit): its
-                    // successor is still the minimum if it stays below the lower bound of all other entries
-                    if (hx < a.c.sec[row]) {
-                        a.c.nn_val[row] = hx;
-                        a.c.nn_idx[row] = hj;
-                    } else if (!need) {
-                        a.rq[atomicAdd(&st->qlen, 1)] = row;
+                Wr[p.j] = lw(method, A, B, p, v);
+                if (two) Wr[p2.j] = lw(method, A2, B2, p2, v);
+            }
+            __syncwarp(gmask);  // the new entries of this row (written by the lanes of its group) are visible below
+            if (q0 == 0) {
+                a.c.fresh[row] = 0;  // the bound is no longer the exact next entry
+                upd += P;
+                if (!need) {
+                    // Candidates that were merged this round follow their cluster to column j with the new value.
+                    // Unlisted entries only move up (reducibility), so the bound stays valid; a candidate that rose
+                    // above the bound leaves the list, and an empty list asks for a rescan.
+                    const size_t base = (size_t)row * LC;
+                    double cv[KC];
+                    int ci[KC];
+#pragma unroll
+                    for (int k = 0; k < KC; ++k) { cv[k] = a.c.cval[base + k]; ci[k] = a.c.cidx[base + k]; }
+                    const double lb = a.c.cval[base + KC];
+                    bool hit = false;
+#pragma unroll
+                    for (int k = 0; k < KC; ++k) {
+                        if (ci[k] < 0) continue;
+                        const int r = a.c.role[ci[k]];
+                        if (r < 0) continue;
+                        hit = true;
+                        const int j = a.pairs[r >> 1].j;
+                        bool dup = false;  // both sides of the pair were listed: keep one
+#pragma unroll
+                        for (int t = 0; t < KC; ++t) dup |= (t != k) && (ci[t] == j) && ((r & 1) == 0 || t < k);
+                        if (dup && (r & 1) == 0) { ci[k] = -1; continue; }
+                        ci[k] = j;
+                        cv[k] = __ldcg(Wr + j);
+                    }
+                    if (hit) {
+                        TopL out;
+                        out.init();
+#pragma unroll
+                        for (int k = 0; k < KC; ++k)
+                            if (ci[k] >= 0 && cv[k] <= lb) out.insert(cv[k], ci[k]);
+#pragma unroll
+                        for (int k = 0; k < KC; ++k) {
+                            a.c.cval[base + k] = out.v[k];
+                            a.c.cidx[base + k] = out.i[k] == INT_MAX ? -1 : out.i[k];
+                        }
+                        if (out.i[0] == INT_MAX) a.rq[atomicAdd(&st->qlen, 1)] = row;
                     }
                 }
-            }
-            if (q0 == 0) {
-                a.c.fresh[row] = 0;  // sec is now a lower bound, no longer the exact second minimum
-                upd += P;
             }
         }
         if (need && q0 == 0) a.rq[atomicAdd(&st->qlen, 1)] = row;  // kr_heavy clears the flag
@@ -285,9 +371,9 @@ __global__ void __launch_bounds__(LIGHT_THREADS) kr_light(RArgs a) {
 // rounds with one or two entries a row is cut into segments over many CTAs and the last CTA to finish
 // an entry combines the partial minima, so a round never waits for one CTA streaming a whole row.
 template <bool VEC>
-__device__ __forceinline__ void heavy_columns(const RArgs &a, int e, int P, int c_lo, int c_hi, Min2 &best) {
+__device__ __forceinline__ void heavy_columns(const RArgs &a, int e, int P, int c_lo, int c_hi, Min3 &best) {
     const int tid = threadIdx.x, method = a.method;
-    constexpr int V = VEC ? 2 : 1, U = 2;
+    constexpr int V = VEC ? 2 : 1, U = 2, UR = 4;  // loads in flight per thread: builds 2 x (A, B), rescans 4
     if (e < P) {
         const Pair p = a.pairs[e];
         const double *Wi = a.W + (size_t)p.i * a.stride;
@@ -343,11 +429,11 @@ __device__ __forceinline__ void heavy_columns(const RArgs &a, int e, int P, int 
     } else {
         const int row = a.rq[e - P];
         const double *Wr = a.W + (size_t)row * a.stride;
-        for (int c0 = c_lo + tid * V; c0 < c_hi; c0 += U * V * HEAVY_THREADS) {
-            double X[U][V];
-            int rc[U][V];
+        for (int c0 = c_lo + tid * V; c0 < c_hi; c0 += UR * V * HEAVY_THREADS) {
+            double X[UR][V];
+            int rc[UR][V];
 #pragma unroll
-            for (int u = 0; u < U; ++u) {
+            for (int u = 0; u < UR; ++u) {
                 const int c = c0 + u * V * HEAVY_THREADS;
 #pragma unroll
                 for (int k = 0; k < V; ++k) rc[u][k] = ROLE_DEAD;
@@ -362,7 +448,7 @@ __device__ __forceinline__ void heavy_columns(const RArgs &a, int e, int P, int 
                 }
             }
 #pragma unroll
-            for (int u = 0; u < U; ++u) {
+            for (int u = 0; u < UR; ++u) {
 #pragma unroll
                 for (int k = 0; k < V; ++k) {
                     const int c = c0 + u * V * HEAVY_THREADS + k, r = rc[u][k];
@@ -375,8 +461,9 @@ __device__ __forceinline__ void heavy_columns(const RArgs &a, int e, int P, int 
 }
 
 __global__ void __launch_bounds__(HEAVY_THREADS, 3) kr_heavy(RArgs a) {
-    __shared__ double s_m1[HEAVY_THREADS / 32], s_m2[HEAVY_THREADS / 32];
-    __shared__ int s_i1[HEAVY_THREADS / 32];
+    __shared__ double s_v[HEAVY_THREADS / 32][LC];
+    __shared__ int s_i[HEAVY_THREADS / 32][LC];
+    __shared__ double s_b[HEAVY_THREADS / 32];
     __shared__ int s_flag;
     RState *st = a.st;
     if (st->done) return;
@@ -398,30 +485,51 @@ __global__ void __launch_bounds__(HEAVY_THREADS, 3) kr_heavy(RArgs a) {
     for (long long w = blockIdx.x; w < items; w += gridDim.x) {
         const int e = (int)(w / S), seg = (int)(w - (long long)e * S);
         const int c_lo = seg * seg_len, c_hi = min(ncols, c_lo + seg_len);
-        Min2 best;
-        best.init();
+        Min3 mine;
+        mine.init();
         if (c_lo < c_hi) {
-            if (vec) heavy_columns<true>(a, e, P, c_lo, c_hi, best);
-            else heavy_columns<false>(a, e, P, c_lo, c_hi, best);
+            if (vec) heavy_columns<true>(a, e, P, c_lo, c_hi, mine);
+            else heavy_columns<false>(a, e, P, c_lo, c_hi, mine);
         }
-        best.warp_reduce();
-        if ((tid & 31) == 0) {
-            s_m1[tid >> 5] = best.m1;
-            s_m2[tid >> 5] = best.m2;
-            s_i1[tid >> 5] = best.i1;
+        {
+            TopL best;
+            best.init();
+            best.v[0] = mine.m1; best.i[0] = mine.i1;
+            best.v[1] = mine.m2; best.i[1] = mine.i2;
+            double bw = mine.m3;
+#pragma unroll
+            for (int o = 16; o; o >>= 1) {
+                best.xmerge(o);
+                bw = fmin(bw, __shfl_xor_sync(0xffffffffu, bw, o));
+            }
+            if ((tid & 31) == 0) {
+#pragma unroll
+                for (int k = 0; k < LC; ++k) { s_v[tid >> 5][k] = best.v[k]; s_i[tid >> 5][k] = best.i[k]; }
+                s_b[tid >> 5] = bw;
+            }
         }
         __syncthreads();
         if (tid < 32) {
-            Min2 r;
+            TopL r;
             r.init();
-            if (tid < HEAVY_THREADS / 32) { r.m1 = s_m1[tid]; r.m2 = s_m2[tid]; r.i1 = s_i1[tid]; }
-            r.warp_reduce();
+            double bnd = __longlong_as_double(0x7ff0000000000000LL);  // lower bound of the entries no thread kept
+            if (tid < HEAVY_THREADS / 32) {
+#pragma unroll
+                for (int k = 0; k < LC; ++k) { r.v[k] = s_v[tid][k]; r.i[k] = s_i[tid][k]; }
+                bnd = s_b[tid];
+            }
+#pragma unroll
+            for (int o = HEAVY_THREADS / 64; o; o >>= 1) {
+                r.xmerge(o);
+                bnd = fmin(bnd, __shfl_xor_sync(0xffffffffu, bnd, o));
+            }
             bool finish = S == 1;
             if (S > 1) {  // publish the partial; the last segment of the entry combines them all
                 if (tid == 0) {
-                    Part pt;
-                    pt.m1 = r.m1; pt.m2 = r.m2; pt.i1 = r.i1; pt.pad = 0;
-                    a.parts[(size_t)e * a.max_segs + seg] = pt;
+                    Part *pt = &a.parts[(size_t)e * a.max_segs + seg];
+#pragma unroll
+                    for (int k = 0; k < LC; ++k) { pt->v[k] = r.v[k]; pt->i[k] = r.i[k]; }
+                    pt->bound = bnd;
                     __threadfence();
                     s_flag = atomicAdd(&a.seg_done[e], 1) == S - 1;
                 }
@@ -430,20 +538,36 @@ __global__ void __launch_bounds__(HEAVY_THREADS, 3) kr_heavy(RArgs a) {
                 if (finish) {
                     __threadfence();
                     r.init();
+                    bnd = __longlong_as_double(0x7ff0000000000000LL);
                     for (int k = tid; k < S; k += 32) {
-                        const volatile Part *vp = &a.parts[(size_t)e * a.max_segs + k];
-                        Part pt;
-                        pt.m1 = vp->m1; pt.m2 = vp->m2; pt.i1 = vp->i1;
-                        r.merge(pt.m1, pt.i1, pt.m2);
+                        const Part *pt = &a.parts[(size_t)e * a.max_segs + k];
+                        double wv[LC];
+                        int wi[LC];
+#pragma unroll
+                        for (int t = 0; t < LC; ++t) { wv[t] = __ldcg(&pt->v[t]); wi[t] = __ldcg(&pt->i[t]); }
+                        r.merge_sorted(wv, wi);
+                        bnd = fmin(bnd, __ldcg(&pt->bound));
                     }
-                    r.warp_reduce();
+#pragma unroll
+                    for (int o = 16; o; o >>= 1) {
+                        r.xmerge(o);
+                        bnd = fmin(bnd, __shfl_xor_sync(0xffffffffu, bnd, o));
+                    }
                 }
             }
             if (finish && tid == 0) {
                 const int row = e < P ? a.pairs[e].j : a.rq[e - P];
-                a.c.nn_val[row] = r.m1;
-                a.c.nn_idx[row] = r.i1 == INT_MAX ? -1 : r.i1;
-                a.c.sec[row] = r.m2;
+                const size_t base = (size_t)row * LC;
+#pragma unroll
+                // the smallest entry outside the list: the (KC+1)-th candidate or an entry no thread kept
+                const double lb = fmin(bnd, r.v[KC]);
+#pragma unroll
+                for (int k = 0; k < KC; ++k) {
+                    const bool keep = r.i[k] != INT_MAX && r.v[k] <= lb;
+                    a.c.cval[base + k] = keep ? r.v[k] : __longlong_as_double(0x7ff0000000000000LL);
+                    a.c.cidx[base + k] = keep ? r.i[k] : -1;
+                }
+                a.c.cval[base + KC] = lb;
                 a.c.fresh[row] = 1;
                 a.c.need[row] = 0;
                 if (S > 1) a.seg_done[e] = 0;
@@ -476,6 +600,8 @@ __global__ void __launch_bounds__(HEAVY_THREADS, 3) kr_heavy(RArgs a) {
         if (st->n_done >= a.n - 1) st->done = 1;
         else if (st->ambiguous && !a.diag) st->done = 1;
         else if (P == 0 && st->deferred == 0 && total == 0) { st->stuck = 1; st->done = 1; }  // only pending near-ties left
+        st->last_P = P;
+        st->last_q = total - P;
         st->P = 0;
         st->qlen = 0;
         st->deferred = 0;
@@ -526,11 +652,12 @@ __global__ void kc_cols(Cols o, Cols d, const int *newidx, const int *oldidx, in
     const int c = oldidx[k];
     d.role[k] = ROLE_FREE;
     d.size[k] = o.size[c];
-    const int nn = o.nn_idx[c];
-    d.nn_idx[k] = nn >= 0 ? newidx[nn] : -1;
+    for (int t = 0; t < LC; ++t) {
+        const int nn = o.cidx[(size_t)c * LC + t];
+        d.cidx[(size_t)k * LC + t] = nn >= 0 ? newidx[nn] : -1;
+        d.cval[(size_t)k * LC + t] = o.cval[(size_t)c * LC + t];
+    }
     d.orig[k] = o.orig[c];
-    d.nn_val[k] = o.nn_val[c];
-    d.sec[k] = o.sec[c];
     d.fresh[k] = o.fresh[c];
     d.need[k] = o.need[c];
 }
@@ -565,10 +692,9 @@ bool carve(void *workspace, size_t bytes, int n, Layout &L) {
     for (int k = 0; k < 2; ++k) {
         L.cols[k].role = ws.take<int>(n);
         L.cols[k].size = ws.take<int>(n);
-        L.cols[k].nn_idx = ws.take<int>(n);
+        L.cols[k].cidx = ws.take<int>((size_t)n * LC);
         L.cols[k].orig = ws.take<int>(n);
-        L.cols[k].nn_val = ws.take<double>(n);
-        L.cols[k].sec = ws.take<double>(n);
+        L.cols[k].cval = ws.take<double>((size_t)n * LC);
         L.cols[k].fresh = ws.take<unsigned char>(n);
         L.cols[k].need = ws.take<unsigned char>(n);
     }
@@ -583,7 +709,7 @@ bool carve(void *workspace, size_t bytes, int n, Layout &L) {
 
 extern "C" size_t hc_linkage_rounds_workspace_bytes(int32_t n) {
     if (n < 1) n = 1;
-    size_t per_col = 4 * 5 + 8 + 2 * (4 * 4 + 8 * 2 + 2);
+    size_t per_col = 4 * 5 + 8 + 2 * (4 * 3 + 12 * LC + 2);
     return 8192 + (size_t)n * per_col + ((size_t)n / 2 + 1) * sizeof(Pair) + 40 * 256 + spare_elems_for(n) * 8 +
            (size_t)SPLIT_ENTRIES * (MAX_SEGS * sizeof(Part) + 4);
 }
@@ -633,6 +759,10 @@ extern "C" int hc_linkage_rounds(double *W, int32_t n, int method, void *workspa
     int batch = 8;
     if (const char *e = getenv("HC_ROUNDS_BATCH")) batch = atoi(e) > 0 ? atoi(e) : 8;
     long long compactions = 0;
+    const bool trace = getenv("HC_ROUNDS_TRACE") != nullptr;  // diagnostics: one line per round on stderr (syncs every round)
+    if (trace) batch = 1;
+    cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+    if (trace) { cudaEventCreate(&ev0); cudaEventCreate(&ev1); }
 
     auto light_heavy = [&]() {
         int lg = (a.ncols + LIGHT_THREADS / 32 - 1) / (LIGHT_THREADS / 32);
@@ -648,13 +778,21 @@ extern "C" int hc_linkage_rounds(double *W, int32_t n, int method, void *workspa
     HC_CHECK_LAUNCH();
     RState h;
     for (;;) {
+        if (trace) cudaEventRecord(ev0, stream);
         for (int b = 0; b < batch; ++b) {
             kr_select<<<(a.ncols + 255) / 256, 256, 0, stream>>>(a);
             light_heavy();
         }
+        if (trace) cudaEventRecord(ev1, stream);
         HC_CHECK_LAUNCH();
         HC_CUDA_OK(cudaMemcpyAsync(&h, L.st, sizeof h, cudaMemcpyDeviceToHost, stream));
         HC_CUDA_OK(cudaStreamSynchronize(stream));
+        if (trace) {
+            float ms = 0;
+            cudaEventElapsedTime(&ms, ev0, ev1);
+            fprintf(stderr, "[rounds trace] round %d pairs %d rescans %d ncols %d nactive %d us %.1f\n", h.round, h.last_P, h.last_q,
+                    a.ncols, h.nactive, ms * 1e3f);
+        }
         if (h.done) break;
         if (compact && a.ncols >= 256 && (long long)h.nactive * 2 <= a.ncols) {
             const int nnew = h.nactive;
@@ -674,6 +812,7 @@ extern "C" int hc_linkage_rounds(double *W, int32_t n, int method, void *workspa
             compactions++;
         }
     }
+    if (trace) { cudaEventDestroy(ev0); cudaEventDestroy(ev1); }
     const int m = n - 1;
     const bool uncertified = h.ambiguous || h.stuck || h.n_done != m || (a.diag && h.stats[6]);
     if (a.diag) {

@@ -1,0 +1,7 @@
+mkdir -p gpurun_out
+python -m hicembler_b200.build > /dev/null 2>&1 || echo BUILD FAILED
+make -s -C oracle libnnchain.so
+timeout 900 python -m pytest tests -m gpu -x -q -k "linkage or dendrogram or cluster_contigs or tree or rounds or pipeline" > gpurun_out/s3c_pytest.log 2>&1; echo "pytest rc=$?"; tail -5 gpurun_out/s3c_pytest.log
+timeout 600 python scripts/rounds_seeds.py C3 1 2 3 > gpurun_out/s3c_seeds_C3.jsonl 2> gpurun_out/s3c_seeds_C3.err; echo "rc=$?"; tail -3 gpurun_out/s3c_seeds_C3.err
+cut -c1-330 gpurun_out/s3c_seeds_C3.jsonl
+timeout 300 python scripts/rounds_trace.py C3 > gpurun_out/s3c_trace.out 2> gpurun_out/s3c_trace.err; echo rc=$?; grep trace gpurun_out/s3c_trace.err | awk 'NR<14 || NR%60==0'; tail -1 gpurun_out/s3c_trace.out
