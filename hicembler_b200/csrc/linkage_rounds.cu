@@ -43,7 +43,7 @@ constexpr double MARGIN = 1e-13;      // relative separation required of every d
 constexpr double HEIGHT_TOL = 1e-13;  // relative separation required of adjacent sorted heights (30 x)
 // (HC_ROUNDS_MARGIN / HC_ROUNDS_HEIGHT_TOL override both for measurements)
 constexpr int ROLE_DEAD = -2, ROLE_FREE = -1;  // >= 0: 2*pair (i side, retires) / 2*pair+1 (j side, survives)
-constexpr int LIGHT_THREADS = 256, HEAVY_THREADS = 256, MAX_SEGS = 64;
+constexpr int LIGHT_THREADS = 256, HEAVY_THREADS = 256, MAX_SEGS = 8;
 constexpr int HEAVY_GRID_MAX = 2048, SPLIT_ENTRIES = 2 * HEAVY_GRID_MAX;  // rows are split only while entries < 2 x grid
 
 struct __align__(16) Pair {  // 48 bytes; i < j, the merged cluster lives at j
@@ -71,10 +71,10 @@ struct Cols {
     unsigned char *fresh, *need;  // fresh: the bound is the exact (count+1)-th smallest entry (set by a scan)
 };
 
-struct __align__(16) Part {  // partial candidate list of one column segment
-    double v[LC];
+struct __align__(16) Part {  // partial candidate list of one column segment (values as order-preserving keys)
+    unsigned long long k[LC];
     int i[LC];
-    double bound, pad;
+    unsigned long long bound, pad;
 };
 
 struct RArgs {
@@ -460,14 +460,50 @@ __device__ __forceinline__ void heavy_columns(const RArgs &a, int e, int P, int 
     }
 }
 
+// ---- warp-level selection of the LC smallest out of 64 candidates (two sorted per lane) ---------------
+// Values travel as order-preserving 64-bit keys so a warp minimum is two redux.sync instructions.
+constexpr unsigned long long KEY_INF = 0xfff0000000000000ull;  // dkey(+inf)
+__device__ __forceinline__ unsigned long long dkey(double x) {
+    const unsigned long long b = (unsigned long long)__double_as_longlong(x);
+    return b ^ ((b >> 63) ? ~0ull : 0x8000000000000000ull);
+}
+__device__ __forceinline__ double dunkey(unsigned long long k) {
+    return __longlong_as_double((long long)((k >> 63) ? (k ^ 0x8000000000000000ull) : ~k));
+}
+__device__ __forceinline__ unsigned long long warp_min_u64(unsigned long long k) {
+    const unsigned hi = (unsigned)(k >> 32);
+    const unsigned mh = __reduce_min_sync(0xffffffffu, hi);
+    const unsigned ml = __reduce_min_sync(0xffffffffu, hi == mh ? (unsigned)k : 0xffffffffu);
+    return ((unsigned long long)mh << 32) | ml;
+}
+// in: per lane two candidates k1 <= k2 (KEY_INF / INT_MAX = none) and kb = lower bound of what the lane dropped.
+// out: lane s < LC holds the s-th smallest candidate of the warp; bound (all lanes) = smallest value not selected.
+__device__ __forceinline__ void warp_select(unsigned long long k1, int i1, unsigned long long k2, int i2,
+                                            unsigned long long kb, unsigned long long &okey, int &oidx,
+                                            unsigned long long &obound) {
+    const int lane = threadIdx.x & 31;
+    okey = KEY_INF;
+    oidx = INT_MAX;
+#pragma unroll
+    for (int s = 0; s < LC; ++s) {
+        const unsigned long long m = warp_min_u64(k1);
+        const int wl = __ffs(__ballot_sync(0xffffffffu, k1 == m)) - 1;
+        const int wi = __shfl_sync(0xffffffffu, i1, wl);
+        if (lane == s) { okey = m; oidx = wi; }
+        if (lane == wl) { k1 = k2; i1 = i2; k2 = KEY_INF; i2 = INT_MAX; }
+    }
+    const unsigned long long r1 = warp_min_u64(kb), r2 = warp_min_u64(k1);
+    obound = r1 < r2 ? r1 : r2;
+}
+
 __global__ void __launch_bounds__(HEAVY_THREADS, 3) kr_heavy(RArgs a) {
-    __shared__ double s_v[HEAVY_THREADS / 32][LC];
-    __shared__ int s_i[HEAVY_THREADS / 32][LC];
-    __shared__ double s_b[HEAVY_THREADS / 32];
+    __shared__ unsigned long long s_k[HEAVY_THREADS / 32 * LC], s_b[HEAVY_THREADS / 32];
+    __shared__ int s_i[HEAVY_THREADS / 32 * LC];
     __shared__ int s_flag;
+    static_assert(HEAVY_THREADS / 32 * LC == 64 && MAX_SEGS * LC == 64, "warp_select takes 64 candidates");
     RState *st = a.st;
     if (st->done) return;
-    const int P = st->P, total = P + st->qlen, tid = threadIdx.x, ncols = a.ncols;
+    const int P = st->P, total = P + st->qlen, tid = threadIdx.x, lane = tid & 31, ncols = a.ncols;
     // segments per entry: enough items to occupy the grid, segments of at least SEG_MIN columns (even)
     constexpr int SEG_MIN = 2048;
     int S = 1;
@@ -491,88 +527,56 @@ __global__ void __launch_bounds__(HEAVY_THREADS, 3) kr_heavy(RArgs a) {
             if (vec) heavy_columns<true>(a, e, P, c_lo, c_hi, mine);
             else heavy_columns<false>(a, e, P, c_lo, c_hi, mine);
         }
-        {
-            TopL best;
-            best.init();
-            best.v[0] = mine.m1; best.i[0] = mine.i1;
-            best.v[1] = mine.m2; best.i[1] = mine.i2;
-            double bw = mine.m3;
-#pragma unroll
-            for (int o = 16; o; o >>= 1) {
-                best.xmerge(o);
-                bw = fmin(bw, __shfl_xor_sync(0xffffffffu, bw, o));
-            }
-            if ((tid & 31) == 0) {
-#pragma unroll
-                for (int k = 0; k < LC; ++k) { s_v[tid >> 5][k] = best.v[k]; s_i[tid >> 5][k] = best.i[k]; }
-                s_b[tid >> 5] = bw;
-            }
-        }
+        unsigned long long key, bound;
+        int idx;
+        warp_select(dkey(mine.m1), mine.i1, dkey(mine.m2), mine.i2, dkey(mine.m3), key, idx, bound);
+        if (lane < LC) { s_k[(tid >> 5) * LC + lane] = key; s_i[(tid >> 5) * LC + lane] = idx; }
+        if (lane == 0) s_b[tid >> 5] = bound;
         __syncthreads();
         if (tid < 32) {
-            TopL r;
-            r.init();
-            double bnd = __longlong_as_double(0x7ff0000000000000LL);  // lower bound of the entries no thread kept
-            if (tid < HEAVY_THREADS / 32) {
-#pragma unroll
-                for (int k = 0; k < LC; ++k) { r.v[k] = s_v[tid][k]; r.i[k] = s_i[tid][k]; }
-                bnd = s_b[tid];
-            }
-#pragma unroll
-            for (int o = HEAVY_THREADS / 64; o; o >>= 1) {
-                r.xmerge(o);
-                bnd = fmin(bnd, __shfl_xor_sync(0xffffffffu, bnd, o));
-            }
+            // lane t takes entries 2t, 2t+1 of the 64 (sorted within a warp's list)
+            warp_select(s_k[2 * lane], s_i[2 * lane], s_k[2 * lane + 1], s_i[2 * lane + 1],
+                        lane < HEAVY_THREADS / 32 ? s_b[lane] : KEY_INF, key, idx, bound);
             bool finish = S == 1;
             if (S > 1) {  // publish the partial; the last segment of the entry combines them all
-                if (tid == 0) {
-                    Part *pt = &a.parts[(size_t)e * a.max_segs + seg];
-#pragma unroll
-                    for (int k = 0; k < LC; ++k) { pt->v[k] = r.v[k]; pt->i[k] = r.i[k]; }
-                    pt->bound = bnd;
-                    __threadfence();
-                    s_flag = atomicAdd(&a.seg_done[e], 1) == S - 1;
-                }
+                Part *pt = &a.parts[(size_t)e * a.max_segs + seg];
+                if (lane < LC) { pt->k[lane] = key; pt->i[lane] = idx; }
+                if (lane == 0) pt->bound = bound;
+                __threadfence();
+                __syncwarp();
+                if (lane == 0) s_flag = atomicAdd(&a.seg_done[e], 1) == S - 1;
                 __syncwarp();
                 finish = s_flag != 0;
                 if (finish) {
                     __threadfence();
-                    r.init();
-                    bnd = __longlong_as_double(0x7ff0000000000000LL);
-                    for (int k = tid; k < S; k += 32) {
-                        const Part *pt = &a.parts[(size_t)e * a.max_segs + k];
-                        double wv[LC];
-                        int wi[LC];
-#pragma unroll
-                        for (int t = 0; t < LC; ++t) { wv[t] = __ldcg(&pt->v[t]); wi[t] = __ldcg(&pt->i[t]); }
-                        r.merge_sorted(wv, wi);
-                        bnd = fmin(bnd, __ldcg(&pt->bound));
-                    }
-#pragma unroll
-                    for (int o = 16; o; o >>= 1) {
-                        r.xmerge(o);
-                        bnd = fmin(bnd, __shfl_xor_sync(0xffffffffu, bnd, o));
-                    }
+                    const int part = lane >> 2, off = (lane & 3) * 2;  // 8 parts x 8 entries = 64 candidates
+                    const Part *pp = &a.parts[(size_t)e * a.max_segs + part];
+                    const bool live = part < S;
+                    const unsigned long long k1 = live ? __ldcg(&pp->k[off]) : KEY_INF, k2 = live ? __ldcg(&pp->k[off + 1]) : KEY_INF;
+                    const int i1 = live ? __ldcg(&pp->i[off]) : INT_MAX, i2 = live ? __ldcg(&pp->i[off + 1]) : INT_MAX;
+                    const unsigned long long kb = (live && off == 0) ? __ldcg(&pp->bound) : KEY_INF;
+                    warp_select(k1, i1, k2, i2, kb, key, idx, bound);
                 }
             }
-            if (finish && tid == 0) {
+            if (finish) {
                 const int row = e < P ? a.pairs[e].j : a.rq[e - P];
                 const size_t base = (size_t)row * LC;
-#pragma unroll
-                // the smallest entry outside the list: the (KC+1)-th candidate or an entry no thread kept
-                const double lb = fmin(bnd, r.v[KC]);
-#pragma unroll
-                for (int k = 0; k < KC; ++k) {
-                    const bool keep = r.i[k] != INT_MAX && r.v[k] <= lb;
-                    a.c.cval[base + k] = keep ? r.v[k] : __longlong_as_double(0x7ff0000000000000LL);
-                    a.c.cidx[base + k] = keep ? r.i[k] : -1;
+                // the smallest entry outside the list: the (KC+1)-th candidate or an entry nobody kept
+                const unsigned long long last = __shfl_sync(0xffffffffu, key, KC);
+                const unsigned long long lb = bound < last ? bound : last;
+                if (lane < KC) {
+                    const bool keep = idx != INT_MAX && key <= lb;
+                    a.c.cval[base + lane] = keep ? dunkey(key) : __longlong_as_double(0x7ff0000000000000LL);
+                    a.c.cidx[base + lane] = keep ? idx : -1;
                 }
-                a.c.cval[base + KC] = lb;
-                a.c.fresh[row] = 1;
-                a.c.need[row] = 0;
-                if (S > 1) a.seg_done[e] = 0;
-                atomicAdd(&st->stats[e < P ? 2 : 0], 1ull);
-                atomicAdd(&st->stats[e < P ? 3 : 1], (unsigned long long)st->nactive);
+                if (lane == KC) a.c.cval[base + KC] = dunkey(lb);
+                if (lane == 0) {
+                    a.c.fresh[row] = 1;
+                    a.c.need[row] = 0;
+                    if (S > 1) a.seg_done[e] = 0;
+                    atomicAdd(&st->stats[e < P ? 2 : 0], 1ull);
+                    atomicAdd(&st->stats[e < P ? 3 : 1], (unsigned long long)st->nactive);
+                }
             }
         }
         __syncthreads();
