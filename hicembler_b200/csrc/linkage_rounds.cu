@@ -43,8 +43,8 @@ constexpr double MARGIN = 1e-13;      // relative separation required of every d
 constexpr double HEIGHT_TOL = 1e-13;  // relative separation required of adjacent sorted heights (30 x)
 // (HC_ROUNDS_MARGIN / HC_ROUNDS_HEIGHT_TOL override both for measurements)
 constexpr int ROLE_DEAD = -2, ROLE_FREE = -1;  // >= 0: 2*pair (i side, retires) / 2*pair+1 (j side, survives)
-constexpr int LIGHT_THREADS = 256, HEAVY_THREADS = 256, MAX_SEGS = 8;
-constexpr int HEAVY_GRID_MAX = 2048, SPLIT_ENTRIES = 2 * HEAVY_GRID_MAX;  // rows are split only while entries < 2 x grid
+constexpr int LIGHT_THREADS = 256, HEAVY_THREADS = 256, MAX_SEGS = 32;
+constexpr int HEAVY_GRID_MAX = 2048, SPLIT_ENTRIES = 4 * HEAVY_GRID_MAX;  // rows are split only while entries < warps / 2
 
 struct __align__(16) Pair {  // 48 bytes; i < j, the merged cluster lives at j
     int i, j;
@@ -372,19 +372,19 @@ __global__ void __launch_bounds__(LIGHT_THREADS) kr_light(RArgs a) {
 // an entry combines the partial minima, so a round never waits for one CTA streaming a whole row.
 template <bool VEC>
 __device__ __forceinline__ void heavy_columns(const RArgs &a, int e, int P, int c_lo, int c_hi, Min3 &best) {
-    const int tid = threadIdx.x, method = a.method;
+    const int tid = threadIdx.x & 31, method = a.method;  // one warp per (entry, segment)
     constexpr int V = VEC ? 2 : 1, U = 2, UR = 4;  // loads in flight per thread: builds 2 x (A, B), rescans 4
     if (e < P) {
         const Pair p = a.pairs[e];
         const double *Wi = a.W + (size_t)p.i * a.stride;
         double *Wj = a.W + (size_t)p.j * a.stride;
         const double ps = __dadd_rn(p.s1, p.s2);
-        for (int c0 = c_lo + tid * V; c0 < c_hi; c0 += U * V * HEAVY_THREADS) {
+        for (int c0 = c_lo + tid * V; c0 < c_hi; c0 += U * V * 32) {
             double A[U][V], B[U][V];
             int rc[U][V], sz[U][V];
 #pragma unroll
             for (int u = 0; u < U; ++u) {
-                const int c = c0 + u * V * HEAVY_THREADS;
+                const int c = c0 + u * V * 32;
 #pragma unroll
                 for (int k = 0; k < V; ++k) rc[u][k] = ROLE_DEAD;
                 if (VEC && c + 1 < c_hi) {
@@ -405,7 +405,7 @@ __device__ __forceinline__ void heavy_columns(const RArgs &a, int e, int P, int 
             for (int u = 0; u < U; ++u) {
 #pragma unroll
                 for (int k = 0; k < V; ++k) {
-                    const int c = c0 + u * V * HEAVY_THREADS + k, r = rc[u][k];
+                    const int c = c0 + u * V * 32 + k, r = rc[u][k];
                     if (r == ROLE_DEAD || (r >= 0 && !(r & 1)) || c == p.j) continue;
                     double x;
                     if (r == ROLE_FREE) {
@@ -429,12 +429,12 @@ __device__ __forceinline__ void heavy_columns(const RArgs &a, int e, int P, int 
     } else {
         const int row = a.rq[e - P];
         const double *Wr = a.W + (size_t)row * a.stride;
-        for (int c0 = c_lo + tid * V; c0 < c_hi; c0 += UR * V * HEAVY_THREADS) {
+        for (int c0 = c_lo + tid * V; c0 < c_hi; c0 += UR * V * 32) {
             double X[UR][V];
             int rc[UR][V];
 #pragma unroll
             for (int u = 0; u < UR; ++u) {
-                const int c = c0 + u * V * HEAVY_THREADS;
+                const int c = c0 + u * V * 32;
 #pragma unroll
                 for (int k = 0; k < V; ++k) rc[u][k] = ROLE_DEAD;
                 if (VEC && c + 1 < c_hi) {
@@ -451,7 +451,7 @@ __device__ __forceinline__ void heavy_columns(const RArgs &a, int e, int P, int 
             for (int u = 0; u < UR; ++u) {
 #pragma unroll
                 for (int k = 0; k < V; ++k) {
-                    const int c = c0 + u * V * HEAVY_THREADS + k, r = rc[u][k];
+                    const int c = c0 + u * V * 32 + k, r = rc[u][k];
                     if (r == ROLE_DEAD || (r >= 0 && !(r & 1)) || c == row) continue;
                     best.push(X[u][k], c);
                 }
@@ -497,18 +497,19 @@ __device__ __forceinline__ void warp_select(unsigned long long k1, int i1, unsig
 }
 
 __global__ void __launch_bounds__(HEAVY_THREADS, 3) kr_heavy(RArgs a) {
-    __shared__ unsigned long long s_k[HEAVY_THREADS / 32 * LC], s_b[HEAVY_THREADS / 32];
-    __shared__ int s_i[HEAVY_THREADS / 32 * LC];
     __shared__ int s_flag;
-    static_assert(HEAVY_THREADS / 32 * LC == 64 && MAX_SEGS * LC == 64, "warp_select takes 64 candidates");
+    static_assert(MAX_SEGS <= 32, "one lane per partial list in the final selection");
     RState *st = a.st;
     if (st->done) return;
     const int P = st->P, total = P + st->qlen, tid = threadIdx.x, lane = tid & 31, ncols = a.ncols;
-    // segments per entry: enough items to occupy the grid, segments of at least SEG_MIN columns (even)
-    constexpr int SEG_MIN = 2048;
+    const int nwarps = (int)gridDim.x * (HEAVY_THREADS / 32), gwarp = (int)blockIdx.x * (HEAVY_THREADS / 32) + (tid >> 5);
+    // One warp per (entry, column segment): warps never wait for each other, so short rows in the long tail of
+    // small rounds cost one load latency plus one selection.  Segments per entry: enough items for every
+    // resident warp, at least SEG_MIN columns each (even length keeps the 16-byte loads aligned).
+    constexpr int SEG_MIN = 512;
     int S = 1;
-    if (total > 0 && total < 2 * (int)gridDim.x) {
-        S = (2 * (int)gridDim.x + total - 1) / total;
+    if (total > 0 && total < nwarps / 2) {
+        S = (nwarps / 2 + total - 1) / total;
         const int smax = (ncols + SEG_MIN - 1) / SEG_MIN;
         if (S > smax) S = smax;
         if (S > a.max_segs) S = a.max_segs;
@@ -518,7 +519,7 @@ __global__ void __launch_bounds__(HEAVY_THREADS, 3) kr_heavy(RArgs a) {
     seg_len = (seg_len + 1) & ~1;
     const bool vec = (a.stride & 1) == 0;
     const long long items = (long long)total * S;
-    for (long long w = blockIdx.x; w < items; w += gridDim.x) {
+    for (long long w = gwarp; w < items; w += nwarps) {
         const int e = (int)(w / S), seg = (int)(w - (long long)e * S);
         const int c_lo = seg * seg_len, c_hi = min(ncols, c_lo + seg_len);
         Min3 mine;
@@ -530,56 +531,67 @@ __global__ void __launch_bounds__(HEAVY_THREADS, 3) kr_heavy(RArgs a) {
         unsigned long long key, bound;
         int idx;
         warp_select(dkey(mine.m1), mine.i1, dkey(mine.m2), mine.i2, dkey(mine.m3), key, idx, bound);
-        if (lane < LC) { s_k[(tid >> 5) * LC + lane] = key; s_i[(tid >> 5) * LC + lane] = idx; }
-        if (lane == 0) s_b[tid >> 5] = bound;
-        __syncthreads();
-        if (tid < 32) {
-            // lane t takes entries 2t, 2t+1 of the 64 (sorted within a warp's list)
-            warp_select(s_k[2 * lane], s_i[2 * lane], s_k[2 * lane + 1], s_i[2 * lane + 1],
-                        lane < HEAVY_THREADS / 32 ? s_b[lane] : KEY_INF, key, idx, bound);
-            bool finish = S == 1;
-            if (S > 1) {  // publish the partial; the last segment of the entry combines them all
-                Part *pt = &a.parts[(size_t)e * a.max_segs + seg];
-                if (lane < LC) { pt->k[lane] = key; pt->i[lane] = idx; }
-                if (lane == 0) pt->bound = bound;
-                __threadfence();
-                __syncwarp();
-                if (lane == 0) s_flag = atomicAdd(&a.seg_done[e], 1) == S - 1;
-                __syncwarp();
-                finish = s_flag != 0;
-                if (finish) {
-                    __threadfence();
-                    const int part = lane >> 2, off = (lane & 3) * 2;  // 8 parts x 8 entries = 64 candidates
-                    const Part *pp = &a.parts[(size_t)e * a.max_segs + part];
-                    const bool live = part < S;
-                    const unsigned long long k1 = live ? __ldcg(&pp->k[off]) : KEY_INF, k2 = live ? __ldcg(&pp->k[off + 1]) : KEY_INF;
-                    const int i1 = live ? __ldcg(&pp->i[off]) : INT_MAX, i2 = live ? __ldcg(&pp->i[off + 1]) : INT_MAX;
-                    const unsigned long long kb = (live && off == 0) ? __ldcg(&pp->bound) : KEY_INF;
-                    warp_select(k1, i1, k2, i2, kb, key, idx, bound);
-                }
-            }
+        bool finish = S == 1;
+        if (S > 1) {  // publish the partial; the last segment of the entry combines them all
+            Part *pt = &a.parts[(size_t)e * a.max_segs + seg];
+            if (lane < LC) { pt->k[lane] = key; pt->i[lane] = idx; }
+            if (lane == 0) pt->bound = bound;
+            __threadfence();
+            __syncwarp();
+            int last = 0;
+            if (lane == 0) last = atomicAdd(&a.seg_done[e], 1) == S - 1;
+            finish = __shfl_sync(0xffffffffu, last, 0) != 0;
             if (finish) {
-                const int row = e < P ? a.pairs[e].j : a.rq[e - P];
-                const size_t base = (size_t)row * LC;
-                // the smallest entry outside the list: the (KC+1)-th candidate or an entry nobody kept
-                const unsigned long long last = __shfl_sync(0xffffffffu, key, KC);
-                const unsigned long long lb = bound < last ? bound : last;
-                if (lane < KC) {
-                    const bool keep = idx != INT_MAX && key <= lb;
-                    a.c.cval[base + lane] = keep ? dunkey(key) : __longlong_as_double(0x7ff0000000000000LL);
-                    a.c.cidx[base + lane] = keep ? idx : -1;
+                __threadfence();
+                // lane < S takes the sorted partial list of segment `lane`
+                const Part *pp = &a.parts[(size_t)e * a.max_segs + lane];
+                unsigned long long pk[LC], kb = KEY_INF;
+                int pi[LC];
+#pragma unroll
+                for (int t = 0; t < LC; ++t) {
+                    pk[t] = lane < S ? __ldcg(&pp->k[t]) : KEY_INF;
+                    pi[t] = lane < S ? __ldcg(&pp->i[t]) : INT_MAX;
                 }
-                if (lane == KC) a.c.cval[base + KC] = dunkey(lb);
-                if (lane == 0) {
-                    a.c.fresh[row] = 1;
-                    a.c.need[row] = 0;
-                    if (S > 1) a.seg_done[e] = 0;
-                    atomicAdd(&st->stats[e < P ? 2 : 0], 1ull);
-                    atomicAdd(&st->stats[e < P ? 3 : 1], (unsigned long long)st->nactive);
+                if (lane < S) kb = __ldcg(&pp->bound);
+                key = KEY_INF;
+                idx = INT_MAX;
+#pragma unroll
+                for (int sel = 0; sel < LC; ++sel) {
+                    const unsigned long long m = warp_min_u64(pk[0]);
+                    const int wl = __ffs(__ballot_sync(0xffffffffu, pk[0] == m)) - 1;
+                    const int wi = __shfl_sync(0xffffffffu, pi[0], wl);
+                    if (lane == sel) { key = m; idx = wi; }
+                    if (lane == wl) {
+#pragma unroll
+                        for (int t = 0; t + 1 < LC; ++t) { pk[t] = pk[t + 1]; pi[t] = pi[t + 1]; }
+                        pk[LC - 1] = KEY_INF;
+                        pi[LC - 1] = INT_MAX;
+                    }
                 }
+                const unsigned long long r1 = warp_min_u64(kb), r2 = warp_min_u64(pk[0]);
+                bound = r1 < r2 ? r1 : r2;
             }
         }
-        __syncthreads();
+        if (finish) {
+            const int row = e < P ? a.pairs[e].j : a.rq[e - P];
+            const size_t base = (size_t)row * LC;
+            // the smallest entry outside the list: the (KC+1)-th candidate or an entry nobody kept
+            const unsigned long long last = __shfl_sync(0xffffffffu, key, KC);
+            const unsigned long long lb = bound < last ? bound : last;
+            if (lane < KC) {
+                const bool keep = idx != INT_MAX && key <= lb;
+                a.c.cval[base + lane] = keep ? dunkey(key) : __longlong_as_double(0x7ff0000000000000LL);
+                a.c.cidx[base + lane] = keep ? idx : -1;
+            }
+            if (lane == KC) a.c.cval[base + KC] = dunkey(lb);
+            if (lane == 0) {
+                a.c.fresh[row] = 1;
+                a.c.need[row] = 0;
+                if (S > 1) a.seg_done[e] = 0;
+                atomicAdd(&st->stats[e < P ? 2 : 0], 1ull);
+                atomicAdd(&st->stats[e < P ? 3 : 1], (unsigned long long)st->nactive);
+            }
+        }
     }
     // last CTA out retires the pairs of this round and closes it
     __syncthreads();
