@@ -371,15 +371,16 @@ __global__ void __launch_bounds__(LIGHT_THREADS) kr_light(RArgs a) {
 // rounds with one or two entries a row is cut into segments over many CTAs and the last CTA to finish
 // an entry combines the partial minima, so a round never waits for one CTA streaming a whole row.
 template <bool VEC>
-__device__ __forceinline__ void heavy_columns(const RArgs &a, int e, int P, int c_lo, int c_hi, Min3 &best) {
-    const int tid = threadIdx.x & 31, method = a.method;  // one warp per (entry, segment)
-    constexpr int V = VEC ? 2 : 1, U = 2, UR = 4;  // loads in flight per thread: builds 2 x (A, B), rescans 4
+__device__ __forceinline__ void heavy_columns(const RArgs &a, int e, int P, int seg, int S, int c_lo, int c_hi,
+                                              bool all_free, Min3 &best) {
+    const int lane = threadIdx.x & 31, method = a.method;  // one warp per (entry, segment)
+    constexpr int V = VEC ? 2 : 1, U = 2, UR = 4;  // loads in flight per thread: builds 2 x (A, B), rescans 4 (8 when all live)
     if (e < P) {
         const Pair p = a.pairs[e];
         const double *Wi = a.W + (size_t)p.i * a.stride;
         double *Wj = a.W + (size_t)p.j * a.stride;
-        const double ps = __dadd_rn(p.s1, p.s2);
-        for (int c0 = c_lo + tid * V; c0 < c_hi; c0 += U * V * 32) {
+        // Phase A: columns of clusters that do not merge this round -- coalesced, no divergent work.
+        for (int c0 = c_lo + lane * V; c0 < c_hi; c0 += U * V * 32) {
             double A[U][V], B[U][V];
             int rc[U][V], sz[U][V];
 #pragma unroll
@@ -405,31 +406,65 @@ __device__ __forceinline__ void heavy_columns(const RArgs &a, int e, int P, int 
             for (int u = 0; u < U; ++u) {
 #pragma unroll
                 for (int k = 0; k < V; ++k) {
-                    const int c = c0 + u * V * 32 + k, r = rc[u][k];
-                    if (r == ROLE_DEAD || (r >= 0 && !(r & 1)) || c == p.j) continue;
-                    double x;
-                    if (r == ROLE_FREE) {
-                        x = lw(method, A[u][k], B[u][k], p, (double)sz[u][k]);
-                    } else {  // c is the surviving side of another pair q: four old entries -> one new
-                        const Pair pq = a.pairs[r >> 1];
-                        const double Ai = __ldcg(Wi + pq.i), Bi = __ldcg(Wj + pq.i);
-                        if (p.j < pq.j) {  // p merges first
-                            const double b1 = lw(method, Ai, Bi, p, pq.s1), b2 = lw(method, A[u][k], B[u][k], p, pq.s2);
-                            x = lw(method, b1, b2, pq, ps);
-                        } else {  // q merges first
-                            const double a1 = lw(method, Ai, A[u][k], pq, p.s1), a2 = lw(method, Bi, B[u][k], pq, p.s2);
-                            x = lw(method, a1, a2, p, __dadd_rn(pq.s1, pq.s2));
-                        }
-                    }
+                    if (rc[u][k] != ROLE_FREE) continue;  // dead, or a side of some pair (phase B)
+                    const int c = c0 + u * V * 32 + k;
+                    const double x = lw(method, A[u][k], B[u][k], p, (double)sz[u][k]);
                     Wj[c] = x;
                     best.push(x, c);
+                }
+            }
+        }
+        // Phase B: the surviving column of every OTHER pair q: four old entries -> one new, "lower j first" so that
+        // both mirror entries get bit-identical values.  The pairs of this round are dealt over the segments of
+        // the entry; all four gathers of a lane are independent.  Nobody else reads or writes these entries:
+        // phase A skips them and every pair owns its two columns.
+        const double ps = __dadd_rn(p.s1, p.s2);
+        for (int q = seg + S * lane; q < P; q += S * 32) {
+            if (q == e) continue;
+            const Pair pq = a.pairs[q];
+            const double Ai = __ldcg(Wi + pq.i), Bi = __ldcg(Wj + pq.i), Aj = __ldcg(Wi + pq.j), Bj = __ldcg(Wj + pq.j);
+            double x;
+            if (p.j < pq.j) {  // p merges first
+                const double b1 = lw(method, Ai, Bi, p, pq.s1), b2 = lw(method, Aj, Bj, p, pq.s2);
+                x = lw(method, b1, b2, pq, ps);
+            } else {  // q merges first
+                const double a1 = lw(method, Ai, Aj, pq, p.s1), a2 = lw(method, Bi, Bj, pq, p.s2);
+                x = lw(method, a1, a2, p, __dadd_rn(pq.s1, pq.s2));
+            }
+            Wj[pq.j] = x;
+            best.push(x, pq.j);
+        }
+    } else if (all_free) {  // initial scan: every column is a live singleton, no role lookups
+        const int row = a.rq[e - P];
+        const double *Wr = a.W + (size_t)row * a.stride;
+        constexpr int UA = 8;
+        for (int c0 = c_lo + lane * V; c0 < c_hi; c0 += UA * V * 32) {
+            double X[UA][V];
+#pragma unroll
+            for (int u = 0; u < UA; ++u) {
+                const int c = c0 + u * V * 32;
+#pragma unroll
+                for (int k = 0; k < V; ++k) X[u][k] = __longlong_as_double(0x7ff0000000000000LL);
+                if (VEC && c + 1 < c_hi) {
+                    const double2 x2 = __ldcs((const double2 *)(Wr + c));
+                    X[u][0] = x2.x; X[u][V - 1] = x2.y;
+                } else if (c < c_hi) {
+                    X[u][0] = __ldcs(Wr + c);
+                }
+            }
+#pragma unroll
+            for (int u = 0; u < UA; ++u) {
+#pragma unroll
+                for (int k = 0; k < V; ++k) {
+                    const int c = c0 + u * V * 32 + k;
+                    if (c != row) best.push(X[u][k], c);  // (+inf padding never enters)
                 }
             }
         }
     } else {
         const int row = a.rq[e - P];
         const double *Wr = a.W + (size_t)row * a.stride;
-        for (int c0 = c_lo + tid * V; c0 < c_hi; c0 += UR * V * 32) {
+        for (int c0 = c_lo + lane * V; c0 < c_hi; c0 += UR * V * 32) {
             double X[UR][V];
             int rc[UR][V];
 #pragma unroll
@@ -517,17 +552,15 @@ __global__ void __launch_bounds__(HEAVY_THREADS, 3) kr_heavy(RArgs a) {
     }
     int seg_len = (ncols + S - 1) / S;
     seg_len = (seg_len + 1) & ~1;
-    const bool vec = (a.stride & 1) == 0;
+    const bool vec = (a.stride & 1) == 0, all_free = st->round == 0;
     const long long items = (long long)total * S;
     for (long long w = gwarp; w < items; w += nwarps) {
         const int e = (int)(w / S), seg = (int)(w - (long long)e * S);
         const int c_lo = seg * seg_len, c_hi = min(ncols, c_lo + seg_len);
         Min3 mine;
         mine.init();
-        if (c_lo < c_hi) {
-            if (vec) heavy_columns<true>(a, e, P, c_lo, c_hi, mine);
-            else heavy_columns<false>(a, e, P, c_lo, c_hi, mine);
-        }
+        if (vec) heavy_columns<true>(a, e, P, seg, S, c_lo, c_hi, all_free, mine);
+        else heavy_columns<false>(a, e, P, seg, S, c_lo, c_hi, all_free, mine);
         unsigned long long key, bound;
         int idx;
         warp_select(dkey(mine.m1), mine.i1, dkey(mine.m2), mine.i2, dkey(mine.m3), key, idx, bound);
