@@ -214,7 +214,17 @@ struct Xform {
     const double *r, *c;
     double vmax;
     int square;
+    double inv_p1, K;  // 1/p1 and (1/p0)^(1/p1), set by make_xform
 };
+
+static Xform make_xform(int kind, double p0, double p1, const double *r, const double *c, double vmax, int square) {
+    Xform t{kind, p0, p1, r, c, vmax, square, 0.0, 0.0};
+    if (kind == 1 || kind == 3) {
+        t.inv_p1 = 1.0 / p1;
+        t.K = pow(1.0 / p0, t.inv_p1);
+    }
+    return t;
+}
 
 // value of the distance for upper-triangle entry (i,j), i<j, given raw X[i][j]
 template <typename T>
@@ -230,7 +240,36 @@ __device__ __forceinline__ double xform(const Xform &t, T raw, int i, int j) {
         v = (double)raw;
     }
     double out;
-    if (t.kind == 1 || t.kind == 3) out = pow(1.0 / (t.p0 * v), 1.0 / t.p1);
+    if (t.kind == 1 || t.kind == 3) {
+        // (1/(a x))^(1/b) (bam2clusters.py:248-251) = K * exp(-log(x)/b), K = (1/a)^(1/b).  Nearly every entry of a
+        // balanced (or empty) Hi-C matrix is x = 1 + y with y <= 2^-10 (y = v - 1 is exact): two short series replace
+        // the division, log and exp (~120 FP64 instructions -> ~15), truncation error < 2^-60.  Elsewhere pow() is
+        // ~3x the FP64 work of exp(e*log(u)); that form is used only while |e*log(u)| < 1, where the error of the
+        // exponent is not amplified (<= 3 ulp in all).
+        const double e = t.inv_p1, y = v - 1.0;
+        if (y >= 0.0 && y <= 0x1p-10) {
+            double L = fma(y, -1.0 / 6.0, 0.2);
+            L = fma(y, L, -0.25);
+            L = fma(y, L, 1.0 / 3.0);
+            L = fma(y, L, -0.5);
+            L = fma(y, L, 1.0);
+            const double z = -__dmul_rn(e, __dmul_rn(y, L));  // -log1p(y)/b
+            double E = fma(z, 1.0 / 120.0, 1.0 / 24.0);
+            E = fma(z, E, 1.0 / 6.0);
+            E = fma(z, E, 0.5);
+            E = fma(z, E, 1.0);
+            out = fma(t.K, __dmul_rn(z, E), t.K);  // K * (1 + expm1(z))
+        } else {
+            const double u = 1.0 / (t.p0 * v);
+            const double lg = log(u), z = __dmul_rn(e, lg), zl = fma(e, lg, -z);  // z + zl = e*lg exactly
+            if (fabs(z) < 1.0) {
+                out = exp(z);
+                out = fma(out, zl, out);
+            } else {
+                out = pow(u, e);
+            }
+        }
+    }
     else if (t.kind == 2) {
         if (sizeof(T) == 4 && !t.r) out = (double)(logf((float)t.p0) - logf((float)v));
         else out = log(t.p0) - log(t.r ? v + 1.0 : v);
@@ -266,6 +305,61 @@ __global__ void __launch_bounds__(256) k_transform_working(const T *X, int n, Xf
         if (I != J) {
             int i2 = J * TS + r, j2 = I * TS + tx;  // lower tile: W[i2][j2] = f(X[j2][i2])
             if (i2 < n && j2 < n) W[(size_t)i2 * n + j2] = A[tx][r];
+        }
+    }
+    if (bad) atomicOr(flags, 1);
+}
+
+// 64 x 64 tile version for the float matrix (n % 4 == 0): one CTA per tile pair of the upper triangle, float4
+// loads, the transformed tile staged once in shared memory as f64, both mirror tiles written with 16-byte stores.
+__global__ void __launch_bounds__(256) k_transform_tile64(const float *X, int n, int T, Xform t, double *W,
+                                                           int32_t *flags) {
+    __shared__ double A[T64][T64 + 1];
+    int I, J;
+    tile_pair_from_linear(blockIdx.x, T, I, J);
+    const int tx = threadIdx.x & 15, ty = threadIdx.x >> 4;
+    bool bad = false;
+#pragma unroll
+    for (int p = 0; p < 4; ++p) {
+        const int r = ty + 16 * p;
+        const int i = I * T64 + r, j = J * T64 + tx * 4;
+        float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (i < n && j < n && i < j + 3) v = __ldcs((const float4 *)(X + (size_t)i * n + j));
+        const float *pv = (const float *)&v;
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+            double o = 0;
+            if (i < n && j + q < n && i < j + q) {
+                o = xform<float>(t, pv[q], i, j + q);
+                bad |= isnan(o);
+            }
+            A[r][tx * 4 + q] = o;
+        }
+    }
+    __syncthreads();
+    const double inf = __longlong_as_double(0x7ff0000000000000LL);
+#pragma unroll
+    for (int p = 0; p < 4; ++p) {
+        const int r = ty + 16 * p;
+        const int i = I * T64 + r, j = J * T64 + tx * 4;
+        if (i < n && j < n) {
+            double o[4];
+#pragma unroll
+            for (int q = 0; q < 4; ++q) {
+                const int c = tx * 4 + q;
+                o[q] = (i < j + q) ? A[r][c] : (i == j + q ? inf : A[c][r]);  // (I == J only below the diagonal)
+            }
+            double2 *dst = (double2 *)(W + (size_t)i * n + j);
+            dst[0] = make_double2(o[0], o[1]);
+            dst[1] = make_double2(o[2], o[3]);
+        }
+        if (I != J) {
+            const int i2 = J * T64 + r, j2 = I * T64 + tx * 4;
+            if (i2 < n && j2 < n) {
+                double2 *dst = (double2 *)(W + (size_t)i2 * n + j2);
+                dst[0] = make_double2(A[tx * 4 + 0][r], A[tx * 4 + 1][r]);
+                dst[1] = make_double2(A[tx * 4 + 2][r], A[tx * 4 + 3][r]);
+            }
         }
     }
     if (bad) atomicOr(flags, 1);
@@ -438,10 +532,14 @@ extern "C" int hc_transform_to_working(const void *X, int dtype, int32_t n, int 
     cudaStream_t stream = (cudaStream_t)stream_;
     HC_REQUIRE(X && W && d_flags && n > 0 && kind >= 0 && kind <= 3 && (dtype == 0 || dtype == 1), "bad arguments");
     HC_REQUIRE((r == nullptr) == (c == nullptr), "r and c must be given together");
-    Xform t{kind, p0, p1, r, c, vmax, square};
+    Xform t = make_xform(kind, p0, p1, r, c, vmax, square);
     int T = (n + TS - 1) / TS;
     HC_CUDA_OK(cudaMemsetAsync(d_flags, 0, sizeof(int32_t), stream));
-    if (dtype == 0)
+    if (dtype == 0 && (n & 3) == 0 && (((uintptr_t)X | (uintptr_t)W) & 15) == 0 && !getenv("HC_FOLD_TS32")) {
+        const int T6 = (n + T64 - 1) / T64;
+        const long long pairs = (long long)T6 * (T6 + 1) / 2;
+        k_transform_tile64<<<(unsigned)pairs, 256, 0, stream>>>((const float *)X, n, T6, t, W, d_flags);
+    } else if (dtype == 0)
         k_transform_working<float><<<dim3(T, T), dim3(TS, 8), 0, stream>>>((const float *)X, n, t, W, d_flags);
     else
         k_transform_working<double><<<dim3(T, T), dim3(TS, 8), 0, stream>>>((const double *)X, n, t, W, d_flags);
@@ -453,7 +551,7 @@ extern "C" int hc_transform(const void *X, int dtype, int64_t count, int kind, d
                             int out_dtype, void *stream_) {
     cudaStream_t stream = (cudaStream_t)stream_;
     HC_REQUIRE(X && out && count >= 0 && kind >= 0 && kind <= 3, "bad arguments");
-    Xform t{kind, p0, p1, nullptr, nullptr, 1.0, 0};
+    Xform t = make_xform(kind, p0, p1, nullptr, nullptr, 1.0, 0);
     if (count == 0) return HC_OK;
     int blocks = 8 * hc::sm_count();
     if (dtype == 0 && out_dtype == 0)
