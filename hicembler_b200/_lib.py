@@ -50,6 +50,7 @@ SIGNATURES = {
     "hc_linkage_finish": (C.c_int, [_i32, C.c_int, _p, _sz, _p, _p, _p]),
     "hc_linkage_rounds_workspace_bytes": (_sz, [_i32]),
     "hc_linkage_rounds": (C.c_int, [_p, _i32, C.c_int, _p, _sz, _p, _p, _p]),
+    "hc_merges_to_linkage": (C.c_int, [_i32, C.c_int, _p, _p, _p, _p, C.c_double, _p]),
     "hc_segment_mean_2d": (C.c_int, [_p, _i32, _p, _p, _i32, _p, _p, _p]),
     "hc_normalize_rows": (C.c_int, [_p, _i32, _p, _sz, _p]),
 }

@@ -1,6 +1,7 @@
 // Error reporting and device queries shared by all entry points.
 #include <stdarg.h>
 #include <stdlib.h>
+#include <time.h>
 
 #include "common.cuh"
 
@@ -13,6 +14,12 @@ void set_error(const char *fmt, ...) {
     va_start(ap, fmt);
     vsnprintf(g_err, sizeof g_err, fmt, ap);
     va_end(ap);
+}
+
+double wall_seconds() {
+    timespec ts;
+    clock_gettime(CLOCK_MONOTONIC, &ts);
+    return (double)ts.tv_sec + 1e-9 * (double)ts.tv_nsec;
 }
 
 int sm_count() {

@@ -11,6 +11,7 @@ namespace hc {
 
 void set_error(const char *fmt, ...);
 int sm_count();
+double wall_seconds();
 // merge records -> scipy linkage array (dendrogram.cu)
 void records_to_Z(int n, bool ward, const int *ra, const int *rb, double *rd, double *h_Z, double rel_tol,
                   long long *near_ties);

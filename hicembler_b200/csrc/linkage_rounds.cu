@@ -805,8 +805,8 @@ extern "C" int hc_linkage_rounds(double *W, int32_t n, int method, void *workspa
     int cur = 0;          // which Cols set is live
     bool in_spare = false;  // whether the live matrix is in the spare buffer
     const bool compact = getenv("HC_ROUNDS_NOCOMPACT") == nullptr;
-    int batch = 8;
-    if (const char *e = getenv("HC_ROUNDS_BATCH")) batch = atoi(e) > 0 ? atoi(e) : 8;
+    int batch = 16;  // rounds per host synchronisation (a round after the last merge is three empty launches)
+    if (const char *e = getenv("HC_ROUNDS_BATCH")) batch = atoi(e) > 0 ? atoi(e) : 16;
     long long compactions = 0;
     const bool trace = getenv("HC_ROUNDS_TRACE") != nullptr;  // diagnostics: one line per round on stderr (syncs every round)
     if (trace) batch = 1;
@@ -823,8 +823,16 @@ extern "C" int hc_linkage_rounds(double *W, int32_t n, int method, void *workspa
     };
     HC_CUDA_OK(cudaMemsetAsync(L.seg_done, 0, SPLIT_ENTRIES * sizeof(int), stream));
     kr_init<<<(n + 255) / 256, 256, 0, stream>>>(a);
+    if (trace) cudaEventRecord(ev0, stream);
     light_heavy();  // initial nearest neighbour of every row ("first linkage pass")
     HC_CHECK_LAUNCH();
+    if (trace) {
+        cudaEventRecord(ev1, stream);
+        cudaEventSynchronize(ev1);
+        float ms = 0;
+        cudaEventElapsedTime(&ms, ev0, ev1);
+        fprintf(stderr, "[rounds trace] initial scan us %.1f\n", ms * 1e3f);
+    }
     RState h;
     for (;;) {
         if (trace) cudaEventRecord(ev0, stream);
@@ -848,10 +856,18 @@ extern "C" int hc_linkage_rounds(double *W, int32_t n, int method, void *workspa
             double *dst = in_spare ? W : L.spare;
             const long long stride_new = (nnew + 1) & ~1;  // even: rows stay 16-byte aligned for the vector loads
             HC_REQUIRE(in_spare || (size_t)nnew * stride_new <= L.spare_elems, "compaction buffer too small");
+            if (trace) cudaEventRecord(ev0, stream);
             kc_map<<<1, 1024, 0, stream>>>(a.c.role, a.ncols, L.newidx, L.oldidx);
             kc_gather<<<nnew < sms * 8 ? nnew : sms * 8, 256, 0, stream>>>(a.W, a.stride, dst, stride_new, L.oldidx, nnew);
             kc_cols<<<(nnew + 255) / 256, 256, 0, stream>>>(a.c, L.cols[cur ^ 1], L.newidx, L.oldidx, nnew);
             HC_CHECK_LAUNCH();
+            if (trace) {
+                cudaEventRecord(ev1, stream);
+                cudaEventSynchronize(ev1);
+                float ms = 0;
+                cudaEventElapsedTime(&ms, ev0, ev1);
+                fprintf(stderr, "[rounds trace] compaction %d -> %d us %.1f\n", a.ncols, nnew, ms * 1e3f);
+            }
             cur ^= 1;
             in_spare = !in_spare;
             a.c = L.cols[cur];
@@ -885,7 +901,9 @@ extern "C" int hc_linkage_rounds(double *W, int32_t n, int method, void *workspa
     HC_CUDA_OK(cudaMemcpyAsync(rd.data(), L.rec_d, m * sizeof(double), cudaMemcpyDeviceToHost, stream));
     HC_CUDA_OK(cudaStreamSynchronize(stream));
     long long near = 0;
+    const double t_host0 = trace ? hc::wall_seconds() : 0.0;
     hc::records_to_Z(n, method == M_WARD, ra.data(), rb.data(), rd.data(), h_Z, height_tol, &near);
+    if (trace) fprintf(stderr, "[rounds trace] records_to_Z host us %.1f\n", (hc::wall_seconds() - t_host0) * 1e6);
     if (h_stats) {
         h_stats[0] = h.round;
         h_stats[1] = h.n_done;

@@ -187,7 +187,8 @@ int hc_linkage_finish(int32_t n, int method, void *workspace, size_t workspace_b
 
 /* K7b  round-parallel engine for the same call sites (csrc/linkage_rounds.cu): merges every reciprocal
  * nearest-neighbour pair per round on all SMs.  Same W contract as hc_linkage.  Every merge and the
- * sorted heights are certified against ties (1e-12 / 2e-13 relative); when certification fails the
+ * sorted heights are certified against ties (1e-13 relative, 30 x the largest height difference
+ * measured between the two engines); when certification fails the
  * call returns HC_EAMBIGUOUS with W destroyed and the caller falls back to hc_linkage, whose scan
  * order reproduces fastcluster's tie-breaking.  When it returns HC_OK, Z[:,0:2] and Z[:,3] equal
  * hc_linkage's and Z[:,2] agrees to rounding (same Lance-Williams operations, different interleaving).
@@ -199,6 +200,15 @@ int hc_linkage_finish(int32_t n, int method, void *workspace, size_t workspace_b
 size_t hc_linkage_rounds_workspace_bytes(int32_t n);
 int hc_linkage_rounds(double *W, int32_t n, int method, void *workspace, size_t workspace_bytes,
                       double *h_Z, int64_t *h_stats, void *stream);
+
+/* Host-only tail shared by both engines (csrc/dendrogram.cu): n-1 merge records (a leaf of either cluster,
+ * merge height; squared heights when ward != 0) -> scipy linkage array Z[(n-1)*4], as fastcluster's
+ * generate_SciPy_dendrogram does after NN_chain_core (behind bam2clusters.py:385, array2scaffolds.py:163):
+ * STABLE sort by height, union-find relabelling, row = (min label, max label, height, size).  h_d is
+ * overwritten (sqrt for ward).  h_near_ties (may be NULL) receives the number of adjacent sorted heights
+ * closer than rel_tol (relative).  No device work. */
+int hc_merges_to_linkage(int32_t n, int ward, const int32_t *h_a, const int32_t *h_b, double *h_d, double *h_Z,
+                         double rel_tol, int64_t *h_near_ties);
 
 /* ---------------------------------------------------------------------------------------
  * K8  block reductions on the resident matrix.
