@@ -805,8 +805,8 @@ extern "C" int hc_linkage_rounds(double *W, int32_t n, int method, void *workspa
     int cur = 0;          // which Cols set is live
     bool in_spare = false;  // whether the live matrix is in the spare buffer
     const bool compact = getenv("HC_ROUNDS_NOCOMPACT") == nullptr;
-    int batch = 16;  // rounds per host synchronisation (a round after the last merge is three empty launches)
-    if (const char *e = getenv("HC_ROUNDS_BATCH")) batch = atoi(e) > 0 ? atoi(e) : 16;
+    int batch = 8;  // rounds per host synchronisation (a round after the last merge is three empty launches)
+    if (const char *e = getenv("HC_ROUNDS_BATCH")) batch = atoi(e) > 0 ? atoi(e) : 8;
     long long compactions = 0;
     const bool trace = getenv("HC_ROUNDS_TRACE") != nullptr;  // diagnostics: one line per round on stderr (syncs every round)
     if (trace) batch = 1;

@@ -1,0 +1,13 @@
+mkdir -p gpurun_out
+python -m hicembler_b200.build > /dev/null 2>&1 || echo BUILD FAILED
+run() { echo "== $1"; env $1 timeout 600 python scripts/rounds_seeds.py C3 1 2>/dev/null | python -c "
+import sys,json
+for l in sys.stdin:
+    d=json.loads(l); print(d['engine'], round(d['stage_ms']['linkage'],2))"; }
+run A=1
+run HC_ROUNDS_NOTHIN=1
+run HC_ROUNDS_NOHINT=1
+run HC_ROUNDS_NOADAPT=1
+run "HC_ROUNDS_NOADAPT=1 HC_ROUNDS_BATCH=8"
+run "HC_ROUNDS_NOTHIN=1 HC_ROUNDS_NOHINT=1"
+run "HC_ROUNDS_NOTHIN=1 HC_ROUNDS_NOHINT=1 HC_ROUNDS_NOADAPT=1 HC_ROUNDS_BATCH=8"
