@@ -32,6 +32,14 @@ UNIT = "pairs/s"
 PARAMS = (0.5, 1.1)   # distance_func parameters (a, b); the reference fits them per data set
 
 
+# DRAM traffic of all launches of a kernel in one step, from the committed ncu pass
+# (profiles/r01_ncu_dram_kr_heavy_C3.csv: dram__bytes_read.sum + dram__bytes_write.sum per launch)
+NCU_TRAFFIC = {}
+_p = os.path.join(ROOT, "profiles", "ncu_traffic.json")
+if os.path.exists(_p):
+    NCU_TRAFFIC = json.load(open(_p))
+
+
 def load_peaks():
     p = os.path.join(ROOT, "MEASURED_PEAKS.json")
     if os.path.exists(p):
@@ -220,6 +228,15 @@ def run_ours(args, cfg, rank, world, local_rank):
     barrier()
     ms_e2e = e2.elapsed_time(e3)
     clocks = sampler.stop() if sampler else None
+    # one more (untimed) step with CUDA events around every launch of the round-parallel linkage: the per-kernel
+    # times behind `roofline` (events are recorded on the launching stream, no synchronisation is added)
+    kernel_us = None
+    if rank == 0:
+        os.environ["HC_ROUNDS_KTIME"] = "1"
+        try:
+            kernel_us = step(records)["linkage_stats"].get("kernel_us")
+        finally:
+            os.environ.pop("HC_ROUNDS_KTIME", None)
     t = torch.tensor([ms_dev, ms_e2e], dtype=torch.float64, device=dev)
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
@@ -255,10 +272,27 @@ def run_ours(args, cfg, rank, world, local_rank):
             roof[k] = {"bound": "hbm", "achieved": a, "peak": peak, "unit": "GB/s", "frac": a / peak,
                        "traffic": None, "ms": ms, "algorithmic_bytes": b, "share_of_step": ms / (ms_dev / K)}
     dominant = max(roof, key=lambda k: roof[k]["ms"])
-    main_roof = dict(roof[dominant], kernel={"bin_pairs": "k_bin_tiles", "fold": "k_fold_counts",
-                                             "sinkhorn": "k_colpass+k_rowpass", "transform": "k_transform_working",
+    main_roof = dict(roof[dominant], kernel={"bin_pairs": "k_bin_tiles", "fold": "k_tilepair64",
+                                             "sinkhorn": "k_colpass+k_rowpass", "transform": "k_transform_tile64",
                                              "linkage": "kr_light+kr_heavy" if lst.get("engine") == "rounds" else "k_nnchain"}[dominant],
                      peak_source=peak_src)
+    if dominant == "linkage" and lst.get("engine") == "rounds" and kernel_us and kernel_us.get("heavy"):
+        # dominant KERNEL = kr_heavy (merged-row builds + exact rescans + the initial scan): all its launches of one
+        # step; achieved = algorithmic bytes of those launches / their summed CUDA-event durations
+        heavy_ms = (kernel_us["heavy"] + kernel_us["initial_scan"]) * 1e-3
+        b = 8.0 * lst["rescan_cols"] + 24.0 * lst["build_cols"]
+        a_ = b / (heavy_ms * 1e-3) / 1e9
+        launches = lst["rounds"] + 1
+        ncu = NCU_TRAFFIC.get(args.config, {}).get("kr_heavy")
+        main_roof = {"bound": "hbm", "achieved": a_, "peak": peak, "unit": "GB/s", "frac": a_ / peak,
+                     "traffic": (ncu["dram_bytes"] / ncu["launches"]) if ncu else None,
+                     "kernel": "kr_heavy", "launches_per_step": launches, "ms": heavy_ms,
+                     "avg_launch_us": heavy_ms * 1e3 / launches, "algorithmic_bytes": b,
+                     "algorithmic_bytes_per_launch": b / launches, "share_of_step": heavy_ms / (ms_dev / K),
+                     "peak_source": peak_src,
+                     "kernel_us_per_step": kernel_us,
+                     "note": "latency-bound in the %d rounds of the chain phase (1-4 merges per round); the bulk rounds "
+                             "and the initial scan move most of the bytes, see profiles/" % lst["rounds"]}
     # launches per step: bin 8, fold 1, sinkhorn (colpass+finish)=2/pass ... counted from the call graph
     sk_launches = 0 if args.no_balance else (2 + 1 + 1 + 2 + 1 + 2 + sk_it * 5)
     link_launches = (3 + 3 * 8 * ((lst["rounds"] + 7) // 8) + 3 * lst["compactions"]) if lst.get("engine") == "rounds" else 1

@@ -765,14 +765,14 @@ extern "C" size_t hc_linkage_rounds_workspace_bytes(int32_t n) {
 
 // W: n x n float64 full symmetric working matrix (squared distances for ward, +inf diagonal), destroyed.
 // Returns HC_OK with Z filled, or HC_EAMBIGUOUS (W is then garbage: rebuild it and call hc_linkage).
-// h_stats[10]: rounds, merges, rescans, sum of live columns over rescans, sum over merged-row builds,
+// h_stats[16]: rounds, merges, rescans, sum of live columns over rescans, sum over merged-row builds,
 // row x pair light updates, compactions, near-tied sorted heights, near-tied pair observations (pairs left
 // pending for a round), pairs deferred for an exact rescan.
 extern "C" int hc_linkage_rounds(double *W, int32_t n, int method, void *workspace, size_t workspace_bytes,
                                  double *h_Z, int64_t *h_stats, void *stream_) {
     cudaStream_t stream = (cudaStream_t)stream_;
     HC_REQUIRE(W && workspace && h_Z && n >= 1 && method >= 0 && method <= 4, "bad arguments");
-    if (h_stats) memset(h_stats, 0, 10 * sizeof(int64_t));
+    if (h_stats) memset(h_stats, 0, 16 * sizeof(int64_t));
     if (n < 2) return HC_OK;
     Layout L;
     if (workspace_bytes < hc_linkage_rounds_workspace_bytes(n) || !carve(workspace, workspace_bytes, n, L)) {
@@ -813,13 +813,39 @@ extern "C" int hc_linkage_rounds(double *W, int32_t n, int method, void *workspa
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;
     if (trace) { cudaEventCreate(&ev0); cudaEventCreate(&ev1); }
 
+    // HC_ROUNDS_KTIME: CUDA events around every launch (no synchronisation added), summed per kernel into
+    // h_stats[10..14] (microseconds: select, light, heavy, compaction, initial scan) -- bench.py uses the shares
+    const bool ktime = getenv("HC_ROUNDS_KTIME") != nullptr && !trace;
+    std::vector<cudaEvent_t> kev;   // events of the current batch, in launch order
+    std::vector<int> kkind;         // kind of the interval that STARTS at event k (-1: none)
+    double kus[5] = {0, 0, 0, 0, 0};
+    size_t kused = 0;
+    auto kmark = [&](int kind) {
+        if (!ktime) return;
+        if (kused == kev.size()) { cudaEvent_t e; cudaEventCreate(&e); kev.push_back(e); kkind.push_back(-1); }
+        cudaEventRecord(kev[kused], stream);
+        kkind[kused++] = kind;
+    };
+    auto kflush = [&]() {  // after a stream synchronisation
+        for (size_t k = 0; k + 1 < kused; ++k) {
+            if (kkind[k] < 0) continue;
+            float ms = 0;
+            cudaEventElapsedTime(&ms, kev[k], kev[k + 1]);
+            kus[kkind[k]] += ms * 1e3;
+        }
+        kused = 0;
+    };
+    bool first_pass = true;
     auto light_heavy = [&]() {
         int lg = (a.ncols + LIGHT_THREADS / 32 - 1) / (LIGHT_THREADS / 32);
         if (lg > sms * 8) lg = sms * 8;
+        kmark(first_pass ? 4 : 1);
         kr_light<<<lg, LIGHT_THREADS, 0, stream>>>(a);
-        int hg = sms * 8 < HEAVY_GRID_MAX ? sms * 8 : HEAVY_GRID_MAX;
-        if (a.ncols < 2 * 2048 && hg > a.ncols) hg = a.ncols;  // rows too short to be split: one CTA per entry at most
+        const int hg = sms * 8 < HEAVY_GRID_MAX ? sms * 8 : HEAVY_GRID_MAX;
+        kmark(first_pass ? 4 : 2);
         kr_heavy<<<hg, HEAVY_THREADS, 0, stream>>>(a);
+        kmark(-1);
+        first_pass = false;
     };
     HC_CUDA_OK(cudaMemsetAsync(L.seg_done, 0, SPLIT_ENTRIES * sizeof(int), stream));
     kr_init<<<(n + 255) / 256, 256, 0, stream>>>(a);
@@ -837,6 +863,7 @@ extern "C" int hc_linkage_rounds(double *W, int32_t n, int method, void *workspa
     for (;;) {
         if (trace) cudaEventRecord(ev0, stream);
         for (int b = 0; b < batch; ++b) {
+            kmark(0);
             kr_select<<<(a.ncols + 255) / 256, 256, 0, stream>>>(a);
             light_heavy();
         }
@@ -844,6 +871,7 @@ extern "C" int hc_linkage_rounds(double *W, int32_t n, int method, void *workspa
         HC_CHECK_LAUNCH();
         HC_CUDA_OK(cudaMemcpyAsync(&h, L.st, sizeof h, cudaMemcpyDeviceToHost, stream));
         HC_CUDA_OK(cudaStreamSynchronize(stream));
+        kflush();
         if (trace) {
             float ms = 0;
             cudaEventElapsedTime(&ms, ev0, ev1);
@@ -857,9 +885,11 @@ extern "C" int hc_linkage_rounds(double *W, int32_t n, int method, void *workspa
             const long long stride_new = (nnew + 1) & ~1;  // even: rows stay 16-byte aligned for the vector loads
             HC_REQUIRE(in_spare || (size_t)nnew * stride_new <= L.spare_elems, "compaction buffer too small");
             if (trace) cudaEventRecord(ev0, stream);
+            kmark(3);
             kc_map<<<1, 1024, 0, stream>>>(a.c.role, a.ncols, L.newidx, L.oldidx);
             kc_gather<<<nnew < sms * 8 ? nnew : sms * 8, 256, 0, stream>>>(a.W, a.stride, dst, stride_new, L.oldidx, nnew);
             kc_cols<<<(nnew + 255) / 256, 256, 0, stream>>>(a.c, L.cols[cur ^ 1], L.newidx, L.oldidx, nnew);
+            kmark(-1);
             HC_CHECK_LAUNCH();
             if (trace) {
                 cudaEventRecord(ev1, stream);
@@ -878,6 +908,7 @@ extern "C" int hc_linkage_rounds(double *W, int32_t n, int method, void *workspa
         }
     }
     if (trace) { cudaEventDestroy(ev0); cudaEventDestroy(ev1); }
+    for (cudaEvent_t e : kev) cudaEventDestroy(e);
     const int m = n - 1;
     const bool uncertified = h.ambiguous || h.stuck || h.n_done != m || (a.diag && h.stats[6]);
     if (a.diag) {
@@ -915,6 +946,7 @@ extern "C" int hc_linkage_rounds(double *W, int32_t n, int method, void *workspa
         h_stats[7] = near;
         h_stats[8] = (int64_t)h.stats[6];
         h_stats[9] = (int64_t)h.stats[5];
+        for (int k = 0; k < 5; ++k) h_stats[10 + k] = (int64_t)(kus[k] + 0.5);
     }
     if (uncertified) return HC_EAMBIGUOUS;
     if (near) {

@@ -323,12 +323,14 @@ def linkage_rounds(W, method="ward", nan_flags=None, workspace=None):
     ws = workspace if workspace is not None and workspace.numel() >= need else \
         torch.empty(need, dtype=torch.uint8, device=W.device)
     Z = np.empty((max(n - 1, 0), 4), dtype=np.float64)
-    stats = (C.c_int64 * 10)()
+    stats = (C.c_int64 * 16)()
     rc = L.hc_linkage_rounds(_ptr(W), n, METHODS[method], _ptr(ws), ws.numel(),
                              Z.ctypes.data_as(C.c_void_p), stats, _stream())
     st = dict(engine="rounds", rounds=stats[0], merges=stats[1], rescans=stats[2], rescan_cols=stats[3],
               build_cols=stats[4], light_updates=stats[5], compactions=stats[6], near_tied_heights=stats[7],
               pending_near_ties=stats[8], deferred_rescans=stats[9],
+              kernel_us=dict(select=stats[10], light=stats[11], heavy=stats[12], compaction=stats[13],
+                             initial_scan=stats[14]),
               certified=(rc == _lib.HC_OK))
     if rc == _lib.HC_EAMBIGUOUS:
         st["reason"] = _lib.last_error()

@@ -194,9 +194,10 @@ int hc_linkage_finish(int32_t n, int method, void *workspace, size_t workspace_b
  * hc_linkage's and Z[:,2] agrees to rounding (same Lance-Williams operations, different interleaving).
  * A NEAR tie only leaves its pair pending (it is merged in a later round once it is strict); the call
  * gives up on an EXACT tie or when only near-tied pairs are left.
- * h_stats[10]: rounds, merges, rescans, sum live columns over rescans, sum live columns over merged-row
+ * h_stats[16]: rounds, merges, rescans, sum live columns over rescans, sum live columns over merged-row
  * builds, row x pair updates, compactions, near-tied heights, pending near-tie observations, pairs
- * deferred for an exact rescan. */
+ * deferred for an exact rescan; [10..14] microseconds per kernel (select, light, heavy, compaction, initial
+ * scan) when HC_ROUNDS_KTIME is set, else 0; [15] unused. */
 size_t hc_linkage_rounds_workspace_bytes(int32_t n);
 int hc_linkage_rounds(double *W, int32_t n, int method, void *workspace, size_t workspace_bytes,
                       double *h_Z, int64_t *h_stats, void *stream);
