@@ -44,7 +44,7 @@ constexpr double HEIGHT_TOL = 1e-13;  // relative separation required of adjacen
 // (HC_ROUNDS_MARGIN / HC_ROUNDS_HEIGHT_TOL override both for measurements)
 constexpr int ROLE_DEAD = -2, ROLE_FREE = -1;  // >= 0: 2*pair (i side, retires) / 2*pair+1 (j side, survives)
 constexpr int LIGHT_THREADS = 256, HEAVY_THREADS = 256, MAX_SEGS = 32;
-constexpr int HEAVY_GRID_MAX = 2048, SPLIT_ENTRIES = 4 * HEAVY_GRID_MAX;  // rows are split only while entries < warps / 2
+constexpr int HEAVY_GRID_MAX = 2048;
 
 struct __align__(16) Pair {  // 48 bytes; i < j, the merged cluster lives at j
     int i, j;
@@ -83,7 +83,7 @@ struct RArgs {
     int max_segs;
     double *W;
     long long stride;
-    int ncols, n, method, diag;
+    int ncols, n, method, diag, bulk_segs;
     double margin;
     Cols c;
     Pair *pairs;
@@ -390,7 +390,7 @@ __device__ __forceinline__ void heavy_columns(const RArgs &a, int e, int P, int 
                 for (int k = 0; k < V; ++k) rc[u][k] = ROLE_DEAD;
                 if (VEC && c + 1 < c_hi) {
                     const int2 r2 = *(const int2 *)(a.c.role + c), s2 = *(const int2 *)(a.c.size + c);
-                    const double2 a2 = __ldcs((const double2 *)(Wi + c)), b2 = __ldcg((const double2 *)(Wj + c));
+                    const double2 a2 = __ldcg((const double2 *)(Wi + c)), b2 = __ldcg((const double2 *)(Wj + c));
                     rc[u][0] = r2.x; rc[u][V - 1] = r2.y;
                     sz[u][0] = s2.x; sz[u][V - 1] = s2.y;
                     A[u][0] = a2.x; A[u][V - 1] = a2.y;
@@ -398,7 +398,7 @@ __device__ __forceinline__ void heavy_columns(const RArgs &a, int e, int P, int 
                 } else if (c < c_hi) {
                     rc[u][0] = a.c.role[c];
                     sz[u][0] = a.c.size[c];
-                    A[u][0] = __ldcs(Wi + c);
+                    A[u][0] = __ldcg(Wi + c);
                     B[u][0] = __ldcg(Wj + c);
                 }
             }
@@ -543,8 +543,12 @@ __global__ void __launch_bounds__(HEAVY_THREADS, 3) kr_heavy(RArgs a) {
     // resident warp, at least SEG_MIN columns each (even length keeps the 16-byte loads aligned).
     constexpr int SEG_MIN = 512;
     int S = 1;
-    if (total > 0 && total < nwarps / 2) {
-        S = (nwarps / 2 + total - 1) / total;
+    if (total > 0) {
+        if (total < nwarps / 2) S = (nwarps / 2 + total - 1) / total;
+        // Big rounds: the pair x pair gathers of a merged row (phase B) re-read the two old rows.  With every row
+        // cut into many segments only ~100 rows are being built at a time (2 x 8 x ncols bytes each), so the
+        // gathers and the second write of a sector find them in the 126 MB L2 instead of going back to HBM.
+        if (P >= 64 && S < a.bulk_segs) S = a.bulk_segs;
         const int smax = (ncols + SEG_MIN - 1) / SEG_MIN;
         if (S > smax) S = smax;
         if (S > a.max_segs) S = a.max_segs;
@@ -747,8 +751,8 @@ bool carve(void *workspace, size_t bytes, int n, Layout &L) {
         L.cols[k].fresh = ws.take<unsigned char>(n);
         L.cols[k].need = ws.take<unsigned char>(n);
     }
-    L.parts = ws.take<Part>((size_t)SPLIT_ENTRIES * MAX_SEGS);
-    L.seg_done = ws.take<int>(SPLIT_ENTRIES);
+    L.parts = ws.take<Part>((size_t)n * MAX_SEGS);
+    L.seg_done = ws.take<int>(n);
     L.spare_elems = spare_elems_for(n);
     L.spare = ws.take<double>(L.spare_elems);
     return ws.ok();
@@ -760,7 +764,7 @@ extern "C" size_t hc_linkage_rounds_workspace_bytes(int32_t n) {
     if (n < 1) n = 1;
     size_t per_col = 4 * 5 + 8 + 2 * (4 * 3 + 12 * LC + 2);
     return 8192 + (size_t)n * per_col + ((size_t)n / 2 + 1) * sizeof(Pair) + 40 * 256 + spare_elems_for(n) * 8 +
-           (size_t)SPLIT_ENTRIES * (MAX_SEGS * sizeof(Part) + 4);
+           (size_t)n * (MAX_SEGS * sizeof(Part) + 4) + 512;
 }
 
 // W: n x n float64 full symmetric working matrix (squared distances for ward, +inf diagonal), destroyed.
@@ -797,6 +801,8 @@ extern "C" int hc_linkage_rounds(double *W, int32_t n, int method, void *workspa
     a.parts = L.parts;
     a.seg_done = L.seg_done;
     a.max_segs = MAX_SEGS;
+    a.bulk_segs = 1;  // (32 measured slower at C3: 17.8 vs 13.8 ms in the largest round; kept for experiments)
+    if (const char *e = getenv("HC_ROUNDS_BULK_SEGS")) a.bulk_segs = atoi(e);
     a.margin = MARGIN;
     double height_tol = HEIGHT_TOL;
     if (const char *e = getenv("HC_ROUNDS_MARGIN")) a.margin = atof(e);
@@ -847,7 +853,7 @@ extern "C" int hc_linkage_rounds(double *W, int32_t n, int method, void *workspa
         kmark(-1);
         first_pass = false;
     };
-    HC_CUDA_OK(cudaMemsetAsync(L.seg_done, 0, SPLIT_ENTRIES * sizeof(int), stream));
+    HC_CUDA_OK(cudaMemsetAsync(L.seg_done, 0, (size_t)n * sizeof(int), stream));
     kr_init<<<(n + 255) / 256, 256, 0, stream>>>(a);
     if (trace) cudaEventRecord(ev0, stream);
     light_heavy();  // initial nearest neighbour of every row ("first linkage pass")
