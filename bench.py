@@ -184,8 +184,6 @@ def run_ours(args, cfg, rank, world, local_rank):
     torch.cuda.empty_cache()
     offsets = torch.from_numpy(g.window_offsets().astype(np.int32)).to(dev)
     workspace = torch.empty(int(ops._lib.lib().hc_bin_pairs_workspace_bytes(P, N)), dtype=torch.uint8, device=dev)
-    host_records = torch.empty(records.shape, dtype=records.dtype, pin_memory=True)
-    host_records.copy_(records)
     launches = {"n": 0}
 
     def step(rec, timer=None):
@@ -213,17 +211,31 @@ def run_ours(args, cfg, rank, world, local_rank):
     e1.record()
     barrier()
     ms_dev = e0.elapsed_time(e1)
-    # ---- timed: end to end from pinned host records ----
-    dev_in = torch.empty_like(records)
+    # ---- timed: end to end from pinned host records (16-byte wire form by default, --wire 24 for hc_pair_t) ----
+    from hicembler_b200.pipeline import host_pairs_to_dendrogram
+    from hicembler_b200.pairs import pack_pairs16
+    if args.wire == 16:
+        packed = pack_pairs16(records)                      # (outside the timed region: the decoder's output)
+        host_wire = torch.empty(packed.shape, dtype=torch.int32, pin_memory=True)
+        host_wire.copy_(packed)
+        del packed
+    else:
+        host_wire = torch.empty(records.shape, dtype=records.dtype, pin_memory=True)
+        host_wire.copy_(records)
+    staging = {"rec24": torch.empty_like(records)}
+    torch.cuda.synchronize()
+
+    def step_e2e():
+        return host_pairs_to_dendrogram(host_wire, offsets, ws, N, staging=staging, mapq=10, params=PARAMS,
+                                        method=cfg["method"], balance=not args.no_balance, workspace=workspace,
+                                        engine=args.engine)
     for _ in range(min(args.warmup, 1)):
-        dev_in.copy_(host_records, non_blocking=True)
-        step(dev_in)
+        step_e2e()
     barrier()
     e2, e3 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e2.record()
     for _ in range(args.steps):
-        dev_in.copy_(host_records, non_blocking=True)
-        res = step(dev_in)           # res["Z"] is a host numpy array: D2H is inside hc_linkage
+        res = step_e2e()             # res["Z"] is a host numpy array: D2H is inside the linkage call
     e3.record()
     barrier()
     ms_e2e = e2.elapsed_time(e3)
@@ -296,7 +308,7 @@ def run_ours(args, cfg, rank, world, local_rank):
     # launches per step: bin 8, fold 1, sinkhorn (colpass+finish)=2/pass ... counted from the call graph
     sk_launches = 0 if args.no_balance else (2 + 1 + 1 + 2 + 1 + 2 + sk_it * 5)
     link_launches = (3 + 3 * 8 * ((lst["rounds"] + 7) // 8) + 3 * lst["compactions"]) if lst.get("engine") == "rounds" else 1
-    gpu_launches = K * 2 * (8 + 1 + sk_launches + 1 + link_launches)
+    gpu_launches = K * 2 * (8 + 1 + sk_launches + 1 + link_launches) + (K if args.wire == 16 else 0)  # + unpack
     cpu = None
     if world == 1 and not args.no_cpu_baseline:
         c = cpu_reference_sample(cfg)
@@ -313,8 +325,10 @@ def run_ours(args, cfg, rank, world, local_rank):
                    "min_tail_bp": cfg.get("min_tail", 1),
                    "linkage_engine": lst.get("engine"),
                    "parallelism": "replicas x%d" % world if world > 1 else "1 gpu"},
-        "e2e": {"value": total_pairs / (ms_e2e * 1e-3), "unit": UNIT, "h2d_bytes_per_step": int(24 * P),
-                "d2h_bytes_per_step": int((N - 1) * 32 + 64 + 64), "ms_per_step": ms_e2e / K},
+        "e2e": {"value": total_pairs / (ms_e2e * 1e-3), "unit": UNIT, "h2d_bytes_per_step": int(args.wire * P),
+                "d2h_bytes_per_step": int((N - 1) * 32 + 64 + 64), "ms_per_step": ms_e2e / K,
+                "host_record_bytes": args.wire,
+                "api": "hicembler_b200.pipeline.host_pairs_to_dendrogram (pinned host records -> Z on the host)"},
         "gpu_launches": gpu_launches,
         "clocks": clocks,
         "roofline": main_roof,
@@ -402,6 +416,9 @@ def main():
     ap.add_argument("--n", type=int, default=0, help="matrix size for --mode sinkhorn")
     ap.add_argument("--no-balance", action="store_true", help="reference HEAD behaviour: normalize() off")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--wire", type=int, default=16, choices=[16, 24],
+                    help="bytes per host record in the e2e leg: 16 = hc_pair16_t (midpoints, unpacked on the device), "
+                         "24 = hc_pair_t")
     ap.add_argument("--engine", default="auto", choices=["auto", "exact", "rounds"],
                     help="linkage engine: round-parallel with certification (auto falls back to the serial NN-chain on ties)")
     ap.add_argument("--min-tail", type=int, default=2000,

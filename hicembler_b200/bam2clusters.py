@@ -250,6 +250,25 @@ def normalize(d, max_iter=1000, epsilon=0.00001):
     return sk.fit_device(X, float(vmax.item())).cpu().numpy()
 
 
+def normalize_diagional(d, bin_chr, bin_position):
+    """Return symmetric and diagonal normalised matrix -- bam2clusters.py:51-66 (the caller's ``d`` is left
+    untouched: the reference's fancy indexing copies it first)."""
+    logger("Diagonal normalisation...")
+    d = np.asarray(d)
+    if d.dtype not in (np.float32, np.float64):
+        d = d.astype(np.float64)
+    indices = d.diagonal() != 0                                   # :55
+    keep = torch.from_numpy(np.flatnonzero(indices).astype(np.int32)).cuda()
+    X = ops.gather_square(torch.from_numpy(np.ascontiguousarray(d)).cuda(), keep)   # :56-57
+    bin_chr = bin_chr[indices]
+    bin_position = bin_position[indices, :]
+    if X.shape[0]:
+        ops.symmetrize_(X)                                        # :61-62 (d += d.T; d -= diag/2: same values)
+        mean = np.mean(X.diagonal().cpu().numpy())                # :64, numpy's own summation
+        X = ops.diag_normalize(X, mean)                           # :65
+    return X.cpu().numpy(), bin_chr, bin_position
+
+
 def distance_func(x, a, b, maxv=float('inf')):
     """Distance from normalised contact frequency -- bam2clusters.py:248-251."""
     if isinstance(x, torch.Tensor):

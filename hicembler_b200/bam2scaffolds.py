@@ -80,6 +80,22 @@ def _average_reduce_2d(A, keys):
     return out if dev_in else out.cpu().numpy()
 
 
+def normalize_window_size(d, bin_chr, bin_position, windowSize=0):
+    """Return symmetric and normalised matrix by window size -- bam2scaffolds.py:28-41 (mutates ``d``)."""
+    from collections import Counter
+    logger("Window-size normalisation...")
+    X = torch.from_numpy(np.ascontiguousarray(d)).cuda()
+    ops.symmetrize_(X)                                            # :32-33
+    sizes = np.diff(bin_position, axis=1)                         # :36
+    if not windowSize:
+        c = Counter(sizes.reshape(len(sizes)).tolist())
+        windowSize, occurencies = c.most_common(1)[0]
+        print(windowSize, occurencies)                            # :39
+    ops.window_size_normalize_(X, torch.from_numpy(sizes.reshape(-1).astype(np.int64)).cuda(), windowSize)  # :40
+    d[...] = X.cpu().numpy()
+    return d, bin_chr, bin_position
+
+
 def normalize_rows(a):
     """Normalise rows so the sums among rows are identical -- bam2scaffolds.py:43-51 (in place)."""
     if isinstance(a, torch.Tensor):

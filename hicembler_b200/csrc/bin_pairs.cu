@@ -652,3 +652,33 @@ extern "C" int hc_contig_region_filter(const hc_pair_t *pairs, int64_t n_pairs, 
     HC_CHECK_LAUNCH();
     return HC_OK;
 }
+
+// ---- compact wire format (16 bytes per record) -> hc_pair_t -------------------------------------------
+// Host records cross PCIe once per job; at 55 GB/s the 24-byte form costs 0.22 s for 5e8 records, more than
+// the whole device path.  hc_pair16_t carries exactly what get_window (bam2clusters.py:119-126) and the
+// samtools filter (:108-111) consume: the two read MIDPOINTS (pos + len(SEQ)//2, the only way POS and SEQ
+// enter, :123 and :155-156), both reference ids, FLAG and MAPQ.  Expanded records have pos = midpoint and
+// l_seq = 0 (SEQ "*": len//2 == 0), so every window, filter decision and count is unchanged.
+__global__ void __launch_bounds__(256) k_unpack_pairs16(const uint4 *packed, long long n, uint2 *out) {
+    for (long long k = blockIdx.x * (long long)blockDim.x + threadIdx.x; k < n;
+         k += (long long)gridDim.x * blockDim.x) {
+        const uint4 q = __ldcs(packed + k);
+        const uint32_t r1 = q.z & 0xfffffu, r2 = q.w & 0xfffffu;
+        const int32_t ref = r1 == 0xfffffu ? -1 : (int32_t)r1, nref = r2 == 0xfffffu ? -1 : (int32_t)r2;
+        const uint32_t flag = q.z >> 20, mapq = (q.w >> 20) & 0xffu;
+        uint2 *o = out + 3 * k;
+        o[0] = make_uint2((uint32_t)ref, q.x);
+        o[1] = make_uint2((uint32_t)nref, q.y);
+        o[2] = make_uint2(0u, flag | (mapq << 16));
+    }
+}
+
+extern "C" int hc_unpack_pairs16(const hc_pair16_t *packed, int64_t n_pairs, hc_pair_t *pairs, void *stream_) {
+    cudaStream_t stream = (cudaStream_t)stream_;
+    HC_REQUIRE(n_pairs >= 0 && (n_pairs == 0 || (packed && pairs)), "bad arguments");
+    HC_REQUIRE((((uintptr_t)packed) & 15) == 0 && (((uintptr_t)pairs) & 7) == 0, "misaligned buffers");
+    if (n_pairs == 0) return HC_OK;
+    k_unpack_pairs16<<<16 * hc::sm_count(), 256, 0, stream>>>((const uint4 *)packed, n_pairs, (uint2 *)pairs);
+    HC_CHECK_LAUNCH();
+    return HC_OK;
+}

@@ -489,6 +489,48 @@ __global__ void k_contig_normalize(const uint32_t *C, int n, const int32_t *size
     out[(size_t)i * n + j] = v;
 }
 
+// ---- alternative normalisations ---------------------------------------------------
+// d[indices, :][:, indices] (bam2clusters.py:55-57)
+template <typename T>
+__global__ void k_gather_square(const T *X, int n, const int32_t *keep, int m, T *out) {
+    const int i = blockIdx.y;
+    const T *src = X + (size_t)keep[i] * n;
+    for (int j = blockIdx.x * blockDim.x + threadIdx.x; j < m; j += gridDim.x * blockDim.x)
+        out[(size_t)i * m + j] = src[keep[j]];
+}
+
+// d *= (d*n2).T*n2 with n2 = mean(diag)/diag (bam2clusters.py:64-65), all in the matrix dtype like numpy:
+// out[i][j] = d[i][j] * ((d[j][i] * n2[i]) * n2[j])
+template <typename T>
+__global__ void k_diag_normalize(const T *D, int n, T mean, T *out) {
+    __shared__ T tile[TS][TS + 1];
+    const int I = blockIdx.y, J = blockIdx.x, tx = threadIdx.x;
+    for (int r = threadIdx.y; r < TS; r += 8) {  // tile (J, I) of D, read along rows
+        const int i = J * TS + r, j = I * TS + tx;
+        tile[r][tx] = (i < n && j < n) ? D[(size_t)i * n + j] : (T)0;
+    }
+    __syncthreads();
+    for (int r = threadIdx.y; r < TS; r += 8) {
+        const int i = I * TS + r, j = J * TS + tx;
+        if (i < n && j < n) {
+            const T n2i = mean / D[(size_t)i * n + i], n2j = mean / D[(size_t)j * n + j];
+            const T f = (tile[tx][r] * n2i) * n2j;  // d[j][i] * n2[i] * n2[j]
+            out[(size_t)i * n + j] = D[(size_t)i * n + j] * f;
+        }
+    }
+}
+
+// d *= 1. * windowSize**2 / (sizes * sizes.T) (bam2scaffolds.py:40): float64 factor, product cast back to T
+template <typename T>
+__global__ void k_window_size_normalize(T *D, int n, const long long *sizes, double ws2) {
+    const int i = blockIdx.y;
+    const long long si = sizes[i];
+    for (int j = blockIdx.x * blockDim.x + threadIdx.x; j < n; j += gridDim.x * blockDim.x) {
+        const double f = ws2 / (double)(si * sizes[j]);
+        D[(size_t)i * n + j] = (T)((double)D[(size_t)i * n + j] * f);
+    }
+}
+
 }  // namespace
 
 extern "C" int hc_fold_counts(const uint32_t *counts, int32_t n, int mode, float add, float *out,
@@ -623,6 +665,43 @@ extern "C" int hc_contig_normalize(const uint32_t *counts, int32_t n, const int3
     cudaStream_t stream = (cudaStream_t)stream_;
     HC_REQUIRE(counts && sizes && out && n > 0, "bad arguments");
     k_contig_normalize<<<dim3((n + 255) / 256, n), 256, 0, stream>>>(counts, n, sizes, out);
+    HC_CHECK_LAUNCH();
+    return HC_OK;
+}
+
+extern "C" int hc_gather_square(const void *X, int dtype, int32_t n, const int32_t *keep, int32_t m, void *out,
+                                void *stream_) {
+    cudaStream_t stream = (cudaStream_t)stream_;
+    HC_REQUIRE(X && out && n > 0 && m >= 0 && (m == 0 || keep) && (dtype == 0 || dtype == 1), "bad arguments");
+    if (m == 0) return HC_OK;
+    const dim3 grid(min((m + 255) / 256, 64), m);
+    if (dtype == 0) k_gather_square<float><<<grid, 256, 0, stream>>>((const float *)X, n, keep, m, (float *)out);
+    else k_gather_square<double><<<grid, 256, 0, stream>>>((const double *)X, n, keep, m, (double *)out);
+    HC_CHECK_LAUNCH();
+    return HC_OK;
+}
+
+extern "C" int hc_diag_normalize(const void *D, int dtype, int32_t n, double mean, void *out, void *stream_) {
+    cudaStream_t stream = (cudaStream_t)stream_;
+    HC_REQUIRE(D && out && D != out && n > 0 && (dtype == 0 || dtype == 1), "bad arguments");
+    const int T = (n + TS - 1) / TS;
+    if (dtype == 0)
+        k_diag_normalize<float><<<dim3(T, T), dim3(TS, 8), 0, stream>>>((const float *)D, n, (float)mean, (float *)out);
+    else
+        k_diag_normalize<double><<<dim3(T, T), dim3(TS, 8), 0, stream>>>((const double *)D, n, mean, (double *)out);
+    HC_CHECK_LAUNCH();
+    return HC_OK;
+}
+
+extern "C" int hc_window_size_normalize(void *D, int dtype, int32_t n, const int64_t *sizes, double ws2,
+                                        void *stream_) {
+    cudaStream_t stream = (cudaStream_t)stream_;
+    HC_REQUIRE(D && sizes && n > 0 && (dtype == 0 || dtype == 1), "bad arguments");
+    const dim3 grid(min((n + 255) / 256, 64), n);
+    if (dtype == 0)
+        k_window_size_normalize<float><<<grid, 256, 0, stream>>>((float *)D, n, (const long long *)sizes, ws2);
+    else
+        k_window_size_normalize<double><<<grid, 256, 0, stream>>>((double *)D, n, (const long long *)sizes, ws2);
     HC_CHECK_LAUNCH();
     return HC_OK;
 }

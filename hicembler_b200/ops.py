@@ -403,6 +403,43 @@ def segment_mean_2d(A, seg_begin, seg_end):
     return out
 
 
+def unpack_pairs16(packed, out=None):
+    """int32 [n, 4] CUDA tensor of hc_pair16_t -> int32 [n, 6] hc_pair_t records (csrc/bin_pairs.cu)."""
+    _dev(packed)
+    n = packed.shape[0]
+    assert packed.dtype == torch.int32 and packed.shape[1] == 4 and packed.is_contiguous()
+    if out is None:
+        out = torch.empty((n, 6), dtype=torch.int32, device=packed.device)
+    _lib.check(_lib.lib().hc_unpack_pairs16(_ptr(packed), n, _ptr(out), _stream()))
+    return out
+
+
+def gather_square(X, keep):
+    """X[keep][:, keep] for an int32 index tensor (bam2clusters.py:55-57, :428)."""
+    _dev(X)
+    n, m = X.shape[0], int(keep.numel())
+    out = torch.empty((m, m), dtype=X.dtype, device=X.device)
+    _lib.check(_lib.lib().hc_gather_square(_ptr(X), _dtype_code(X), n, _ptr(keep), m, _ptr(out), _stream()))
+    return out
+
+
+def diag_normalize(D, mean):
+    """D * ((D*n2).T*n2), n2 = mean/diag(D) (bam2clusters.py:64-65); returns a new tensor."""
+    _dev(D)
+    out = torch.empty_like(D)
+    _lib.check(_lib.lib().hc_diag_normalize(_ptr(D), _dtype_code(D), D.shape[0], float(mean), _ptr(out), _stream()))
+    return out
+
+
+def window_size_normalize_(D, sizes, window_size):
+    """In place D *= 1.*windowSize**2 / (sizes*sizes.T) (bam2scaffolds.py:40); sizes int64 tensor [n]."""
+    _dev(D)
+    assert sizes.dtype == torch.int64 and sizes.numel() == D.shape[0]
+    _lib.check(_lib.lib().hc_window_size_normalize(_ptr(D), _dtype_code(D), D.shape[0], _ptr(sizes),
+                                                   1. * window_size ** 2, _stream()))
+    return D
+
+
 def normalize_rows_(A):
     _dev(A)
     n = A.shape[0]

@@ -23,6 +23,62 @@ assert PAIR_DTYPE.itemsize == 24
 SKIP_FLAG = 3980  # bam2clusters.py:108
 
 
+PAIR16_DTYPE = np.dtype([("mid", "<u4"), ("next_mid", "<u4"), ("ref_flag", "<u4"), ("nref_mapq", "<u4")])
+PAIR16_MAX_CONTIGS = (1 << 20) - 1
+
+
+def pack_pairs16(rec):
+    """24-byte records -> the 16-byte wire form of include/hicembler_b200.h (hc_pair16_t): read midpoints
+    (get_window, bam2clusters.py:123: pos + len(SEQ)//2, len("*") == 1), 20-bit reference ids, FLAG, MAPQ.
+    ``rec``: structured PAIR_DTYPE array, or an int32 [n, 6] numpy array / torch tensor (any device)."""
+    try:
+        import torch
+    except ImportError:  # pragma: no cover
+        torch = None
+    if torch is not None and isinstance(rec, torch.Tensor):
+        res = torch.empty((rec.shape[0], 4), dtype=torch.int32, device=rec.device)
+        step = 1 << 25                                     # bounded temporaries for 5e8-record inputs
+        for s0 in range(0, rec.shape[0], step):
+            r = rec[s0:s0 + step].to(torch.int64)
+            ref, pos, nref, npos, lseq, fm = (r[:, k] for k in range(6))
+            if int(torch.maximum(ref.max(), nref.max())) >= PAIR16_MAX_CONTIGS:
+                raise ValueError("hc_pair16_t holds reference ids below 2**20 - 1")
+            half = torch.where(lseq > 0, lseq, torch.ones_like(lseq)) // 2
+            out = torch.empty((r.shape[0], 4), dtype=torch.int64, device=rec.device)
+            out[:, 0] = (pos + half) & 0xffffffff
+            out[:, 1] = (npos + half) & 0xffffffff
+            out[:, 2] = (ref & 0xfffff) | ((fm & 0xfff) << 20)
+            out[:, 3] = (nref & 0xfffff) | (((fm >> 16) & 0xff) << 20)
+            # two's complement wrap into int32 storage (torch has no uint32 arithmetic)
+            res[s0:s0 + step] = torch.where(out >= 2 ** 31, out - 2 ** 32, out).to(torch.int32)
+        return res
+    if rec.dtype != PAIR_DTYPE:
+        rec = np.ascontiguousarray(rec, dtype=np.int32).view(PAIR_DTYPE).reshape(-1)
+    if len(rec) and max(int(rec["refID"].max()), int(rec["next_refID"].max())) >= PAIR16_MAX_CONTIGS:
+        raise ValueError("hc_pair16_t holds reference ids below 2**20 - 1")
+    half = np.where(rec["l_seq"] > 0, rec["l_seq"], 1).astype(np.int64) // 2
+    out = np.empty(len(rec), dtype=PAIR16_DTYPE)
+    out["mid"] = ((rec["pos"].astype(np.int64) + half) & 0xffffffff).astype(np.uint32)
+    out["next_mid"] = ((rec["next_pos"].astype(np.int64) + half) & 0xffffffff).astype(np.uint32)
+    out["ref_flag"] = (rec["refID"].astype(np.int64) & 0xfffff) | ((rec["flag"].astype(np.int64) & 0xfff) << 20)
+    out["nref_mapq"] = (rec["next_refID"].astype(np.int64) & 0xfffff) | (rec["mapq"].astype(np.int64) << 20)
+    return out
+
+
+def unpack_pairs16(packed):
+    """numpy restatement of hc_unpack_pairs16 (tests): pos = midpoint, l_seq = 0."""
+    rec = np.zeros(len(packed), dtype=PAIR_DTYPE)
+    r1 = (packed["ref_flag"] & 0xfffff).astype(np.int64)
+    r2 = (packed["nref_mapq"] & 0xfffff).astype(np.int64)
+    rec["refID"] = np.where(r1 == 0xfffff, -1, r1)
+    rec["next_refID"] = np.where(r2 == 0xfffff, -1, r2)
+    rec["pos"] = packed["mid"].view(np.int32)
+    rec["next_pos"] = packed["next_mid"].view(np.int32)
+    rec["flag"] = packed["ref_flag"] >> 20
+    rec["mapq"] = (packed["nref_mapq"] >> 20) & 0xff
+    return rec
+
+
 def records_from_columns(refID, pos, next_refID, next_pos, l_seq, flag, mapq):
     rec = np.zeros(len(refID), dtype=PAIR_DTYPE)
     rec["refID"], rec["pos"], rec["next_refID"], rec["next_pos"] = refID, pos, next_refID, next_pos

@@ -78,3 +78,29 @@ def pairs_to_dendrogram(records, offsets, window_bp, n_windows, mapq=10, params=
     out["Z"] = Z
     out["linkage_stats"] = lst
     return out
+
+
+def host_pairs_to_dendrogram(host_records, offsets, window_bp, n_windows, staging=None, **kw):
+    """The same path from HOST records (what a BAM decoder hands over): ``host_records`` is a (pinned) CPU int32
+    tensor, [P, 6] = hc_pair_t or [P, 4] = the 16-byte wire form hc_pair16_t (pairs.pack_pairs16), which is
+    expanded on the device (hc_unpack_pairs16).  ``staging``: dict reused between calls for the device
+    buffers.  Everything after the copy is pairs_to_dendrogram."""
+    dev = offsets.device
+    staging = {} if staging is None else staging
+    P, width = host_records.shape
+    if width not in (4, 6):
+        raise ValueError("host records must be int32 [P, 6] (hc_pair_t) or [P, 4] (hc_pair16_t)")
+
+    def buf(name, w):
+        t = staging.get(name)
+        if t is None or t.shape[0] < P:
+            t = staging[name] = torch.empty((P, w), dtype=torch.int32, device=dev)
+        return t[:P]
+    if width == 6:
+        rec = buf("rec24", 6)
+        rec.copy_(host_records, non_blocking=True)
+    else:
+        wire = buf("rec16", 4)
+        wire.copy_(host_records, non_blocking=True)
+        rec = ops.unpack_pairs16(wire, out=buf("rec24", 6))
+    return pairs_to_dendrogram(rec, offsets, window_bp, n_windows, **kw)

@@ -45,6 +45,17 @@ typedef struct {
     uint8_t mapq, pad;
 } hc_pair_t;
 
+/* Compact wire form of the same record, 16 bytes, for records that cross PCIe (host decoder -> device):
+ *   mid      = pos + len(SEQ)//2       (0-based; the only way POS and SEQ enter get_window, bam2clusters.py:123)
+ *   next_mid = next_pos + len(SEQ)//2  (the mate's window uses read 1's length, :155-156)
+ *   ref_flag = refID (20 bits, 0xFFFFF = "*") | FLAG << 20;  nref_mapq = next_refID (20 bits) | MAPQ << 20.
+ * hc_unpack_pairs16 expands it on the device to hc_pair_t with pos = mid, next_pos = next_mid, l_seq = 0
+ * (SEQ "*": len//2 == 0): windows, -q/-F decisions and counts are those of the original records.
+ * Needs n_contigs < 2^20 - 1; TLEN / CIGAR side arrays of the contig-level path are not carried. */
+typedef struct {
+    uint32_t mid, next_mid, ref_flag, nref_mapq;
+} hc_pair16_t;
+
 int hc_version(void);
 int hc_last_error(char *h_buf, size_t n);
 /* number of SMs / bytes of HBM of the current device (for grid sizing by the caller) */
@@ -79,6 +90,8 @@ int hc_bin_pairs(const hc_pair_t *pairs, int64_t n_pairs,
                  int32_t mapq_min, uint32_t skip_flag, int32_t row0, int32_t row1,
                  uint32_t *counts, void *workspace, size_t workspace_bytes,
                  int mode, int64_t *h_stats, void *stream);
+
+int hc_unpack_pairs16(const hc_pair16_t *packed, int64_t n_pairs, hc_pair_t *pairs, void *stream);
 
 /* ``upto`` of bam2arrays (:139-141): number of leading records that contain exactly ``upto``
  * lines surviving -q/-F/regions (n_pairs if fewer survive).  workspace >= 8*(n_pairs/4096+2). */
@@ -221,6 +234,18 @@ int hc_merges_to_linkage(int32_t n, int ward, const int32_t *h_a, const int32_t 
 int hc_segment_mean_2d(const float *A, int32_t n, const int32_t *seg_begin, const int32_t *seg_end,
                        int32_t n_seg, float *tmp, float *out, void *stream);
 int hc_normalize_rows(float *A, int32_t n, void *workspace, size_t workspace_bytes, void *stream);
+
+/* Alternative normalisations of the symmetric matrix, dtype 0 = float32, 1 = float64.
+ * hc_gather_square: out (m x m) = X[keep][:, keep], the zero-diagonal filter of normalize_diagional
+ *   (bam2clusters.py:55-57); also the sub-matrix selection of cluster_contigs (:428).
+ * hc_diag_normalize: out = d * ((d*n2).T*n2), n2 = mean/diag(d) in the matrix dtype (bam2clusters.py:64-65);
+ *   `mean` = np.mean(d.diagonal()) supplied by the caller (numpy's pairwise float32 sum stays numpy's);
+ *   out must not alias D.
+ * hc_window_size_normalize: d *= 1.*windowSize**2 / (sizes*sizes.T) in place (bam2scaffolds.py:40);
+ *   sizes = int64 window lengths, ws2 = windowSize**2; float64 factor, product cast back to the dtype. */
+int hc_gather_square(const void *X, int dtype, int32_t n, const int32_t *keep, int32_t m, void *out, void *stream);
+int hc_diag_normalize(const void *D, int dtype, int32_t n, double mean, void *out, void *stream);
+int hc_window_size_normalize(void *D, int dtype, int32_t n, const int64_t *sizes, double ws2, void *stream);
 
 #ifdef __cplusplus
 }

@@ -421,6 +421,19 @@ def normalize_diagional(d, bin_chr, bin_position):
     return d, bin_chr, bin_position
 
 
+def normalize_window_size(d, bin_chr, bin_position, windowSize=0):
+    """bam2scaffolds.py:28-41."""
+    from collections import Counter
+    d += d.T
+    d -= np.diag(d.diagonal() / 2)
+    sizes = np.diff(bin_position, axis=1)
+    if not windowSize:
+        c = Counter(sizes.reshape(len(sizes)).tolist())
+        windowSize, occurencies = c.most_common(1)[0]
+    d *= 1. * windowSize ** 2 / (sizes * sizes.T)
+    return d, bin_chr, bin_position
+
+
 def _func_reduce(A, keys, func, allkeys=None):
     """bam2scaffolds.py:53-65."""
     unique_keys = np.unique(keys)

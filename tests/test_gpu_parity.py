@@ -106,6 +106,27 @@ def test_upto_regions_absent_contigs_two_bams():
         assert np.array_equal(got, want), upto
 
 
+def test_pair16_unpack_and_binning_bit_exact():
+    """16-byte wire records -> hc_unpack_pairs16 -> hc_bin_pairs == the 24-byte path == the oracle."""
+    from hicembler_b200 import ops, synth
+    from hicembler_b200.pairs import pack_pairs16, unpack_pairs16, PAIR_DTYPE
+    g, rec = small_case(n_contigs=40, n_windows=400, n_pairs=200000, with_mates=True, bad_flag_frac=0.03,
+                        vary_len=True)
+    rec = rec.copy()
+    rec["l_seq"][::11] = 0
+    packed = pack_pairs16(rec)
+    dev = torch.from_numpy(packed.view(np.int32).reshape(-1, 4)).cuda()
+    got = ops.unpack_pairs16(dev).cpu().numpy().view(PAIR_DTYPE).reshape(-1)
+    want = unpack_pairs16(packed)
+    assert got.tobytes() == want.tobytes()
+    ws = g.window_bp
+    off = torch.from_numpy(g.window_offsets().astype(np.int32)).cuda()
+    c24 = ops.bin_pairs(synth.records_tensor(rec, "cuda"), off, ws, g.n_windows(), 10)
+    c16 = ops.bin_pairs(ops.unpack_pairs16(dev), off, ws, g.n_windows(), 10)
+    assert torch.equal(c24, c16)
+    assert ops.unpack_pairs16(dev[:0]).shape == (0, 6)
+
+
 def test_empty_input():
     from hicembler_b200.bam2clusters import bam2arrays
     g, rec = small_case(n_pairs=100)
@@ -567,6 +588,32 @@ def test_average_reduce_and_normalize_rows():
     a = d.copy()
     want = O.normalize_rows(d.copy())
     assert np.allclose(normalize_rows(a), want, rtol=2e-7, atol=0)
+
+
+@pytest.mark.parametrize("dt", [np.float32, np.float64])
+def test_normalize_diagional_and_window_size(dt, capsys):
+    """bam2clusters.py:51-66 and bam2scaffolds.py:28-41 against the numpy restatement."""
+    from hicembler_b200.bam2clusters import normalize_diagional
+    from hicembler_b200.bam2scaffolds import normalize_window_size
+    n = 150
+    d = np.triu(hic_like_counts(n, 7)).astype(dt)
+    d[np.arange(0, n, 13), np.arange(0, n, 13)] = 0            # zero-diagonal windows are dropped
+    bin_chr = np.array(["c%d" % (i // 10) for i in range(n)])
+    ends = np.cumsum(np.where(np.arange(n) % 10 == 9, 700, 1000))
+    bin_position = np.stack([ends - np.where(np.arange(n) % 10 == 9, 700, 1000), ends], axis=1)
+    d0 = d.copy()
+    got, gc, gp = normalize_diagional(d, bin_chr, bin_position)
+    want, wc, wp = O.normalize_diagional(d0.copy(), bin_chr, bin_position)
+    assert np.array_equal(d, d0)                                # the reference leaves the caller's array alone
+    assert got.dtype == want.dtype and got.shape == want.shape == (n - len(range(0, n, 13)),) * 2
+    assert np.array_equal(gc, wc) and np.array_equal(gp, wp)
+    assert np.allclose(got, want, rtol=4 * np.finfo(dt).eps, atol=0)   # mean/diag, two products: <= 4 ulp
+    for ws in (0, 1000):
+        a, b = d0.copy(), d0.copy()
+        got, _, _ = normalize_window_size(a, bin_chr, bin_position, ws)
+        want, _, _ = O.normalize_window_size(b, bin_chr, bin_position, ws)
+        assert got is a and np.array_equal(a, b)                # in place, bit exact (one f64 product per cell)
+    assert "1000 135" in capsys.readouterr().out                # the reference prints the modal window size (:39)
 
 
 def test_contigs2tree_sequence():

@@ -105,3 +105,49 @@ def test_golden_binning(golden_dir):
         assert np.array_equal(O.bin_records(rec, int(ws), off, a.shape[0], 10, member=member), a)
     a = gld["array0_upto1500"]
     assert np.array_equal(O.bin_records(rec, int(gld["window_bp"][0]), member, a.shape[0], 10, upto=1500), a)
+
+
+def test_normalize_window_size_restatement():
+    """bam2scaffolds.py:28-41 on a 3-window case worked by hand."""
+    d = np.array([[2., 3., 0.], [0., 4., 5.], [0., 0., 6.]])
+    pos = np.array([[0, 10], [10, 20], [20, 25]])
+    out, _, _ = O.normalize_window_size(d, np.array(["a"] * 3), pos)       # modal size 10
+    want = np.array([[2., 3., 0.], [3., 4., 10.], [0., 10., 24.]])
+    assert out is d and np.array_equal(out, want)
+    d2 = np.array([[1., 1.], [0., 1.]])
+    out2, _, _ = O.normalize_window_size(d2, None, np.array([[0, 5], [5, 15]]), windowSize=10)
+    assert np.array_equal(out2, np.array([[4., 2.], [2., 1.]]))
+
+
+def test_pair16_wire_format_keeps_windows_and_filters():
+    """hc_pair16_t (include/hicembler_b200.h): the midpoint form bins exactly like the 24-byte records."""
+    import torch
+    from hicembler_b200.pairs import pack_pairs16, unpack_pairs16, PAIR16_DTYPE, records_from_columns
+    from hicembler_b200 import synth
+    from util import small_case
+    g, rec = small_case(n_pairs=3000, with_mates=True, bad_flag_frac=0.05, vary_len=True)
+    rec = rec.copy()
+    rec["l_seq"][::7] = 0            # SEQ "*": len == 1 in the reference, 1//2 == 0
+    rec["refID"][5] = -1             # RNAME "*"
+    rec["next_refID"][9] = -1
+    packed = pack_pairs16(rec)
+    assert packed.dtype == PAIR16_DTYPE and packed.itemsize == 16
+    back = unpack_pairs16(packed)
+    for f in ("refID", "next_refID", "flag", "mapq"):
+        assert np.array_equal(back[f], rec[f])
+    half = np.where(rec["l_seq"] > 0, rec["l_seq"], 1) // 2
+    assert np.array_equal(back["pos"], rec["pos"] + half) and np.array_equal(back["next_pos"], rec["next_pos"] + half)
+    assert not back["l_seq"].any()
+    # same counts through the oracle's record binner
+    for ws in (5000, 1700):
+        off = g.window_offsets(ws)
+        ok = rec["refID"] >= 0
+        a = O.bin_records(rec[ok & (rec["next_refID"] >= 0)], ws, off, g.n_windows(ws), 10)
+        b = O.bin_records(back[ok & (rec["next_refID"] >= 0)], ws, off, g.n_windows(ws), 10)
+        assert np.array_equal(a[0] if isinstance(a, tuple) else a, b[0] if isinstance(b, tuple) else b)
+    # the torch packer (used for device-resident synthetic data) writes the same bytes
+    t = pack_pairs16(synth.records_tensor(rec)).numpy().view(PAIR16_DTYPE).reshape(-1)
+    assert np.array_equal(t, packed)
+    big = records_from_columns([1 << 20], [0], [0], [0], [10], [99], [60])
+    with pytest.raises(ValueError):
+        pack_pairs16(big)
