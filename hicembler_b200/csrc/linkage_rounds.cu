@@ -418,21 +418,26 @@ __device__ __forceinline__ void heavy_columns(const RArgs &a, int e, int P, int 
         // both mirror entries get bit-identical values.  The pairs of this round are dealt over the segments of
         // the entry; all four gathers of a lane are independent.  Nobody else reads or writes these entries:
         // phase A skips them and every pair owns its two columns.
+        // Both merge orders are the same three Lance-Williams steps on permuted operands: select the operands,
+        // not the code path (lanes of a warp hold different q, a branch would run both orders for every lane).
         const double ps = __dadd_rn(p.s1, p.s2);
-        for (int q = seg + S * lane; q < P; q += S * 32) {
+        auto combine = [&](const Pair &pq, double Ai, double Bi, double Aj, double Bj) {
+            const bool pf = p.j < pq.j;  // p merges first
+            Pair F, Sd;
+            F.m = pf ? p.m : pq.m; F.s1 = pf ? p.s1 : pq.s1; F.s2 = pf ? p.s2 : pq.s2; F.as = pf ? p.as : pq.as; F.at = pf ? p.at : pq.at;
+            Sd.m = pf ? pq.m : p.m; Sd.s1 = pf ? pq.s1 : p.s1; Sd.s2 = pf ? pq.s2 : p.s2; Sd.as = pf ? pq.as : p.as; Sd.at = pf ? pq.at : p.at;
+            F.i = F.j = Sd.i = Sd.j = 0;
+            const double t1 = lw(method, Ai, pf ? Bi : Aj, F, pf ? pq.s1 : p.s1);
+            const double t2 = lw(method, pf ? Aj : Bi, Bj, F, pf ? pq.s2 : p.s2);
+            const double x = lw(method, t1, t2, Sd, pf ? ps : __dadd_rn(pq.s1, pq.s2));
+            Wj[pq.j] = x;
+            best.push(x, pq.j);
+        };
+        for (int q = seg + S * lane; q < P; q += S * 32) {  // (two pairs per lane in flight measured no faster)
             if (q == e) continue;
             const Pair pq = a.pairs[q];
             const double Ai = __ldcg(Wi + pq.i), Bi = __ldcg(Wj + pq.i), Aj = __ldcg(Wi + pq.j), Bj = __ldcg(Wj + pq.j);
-            double x;
-            if (p.j < pq.j) {  // p merges first
-                const double b1 = lw(method, Ai, Bi, p, pq.s1), b2 = lw(method, Aj, Bj, p, pq.s2);
-                x = lw(method, b1, b2, pq, ps);
-            } else {  // q merges first
-                const double a1 = lw(method, Ai, Aj, pq, p.s1), a2 = lw(method, Bi, Bj, pq, p.s2);
-                x = lw(method, a1, a2, p, __dadd_rn(pq.s1, pq.s2));
-            }
-            Wj[pq.j] = x;
-            best.push(x, pq.j);
+            combine(pq, Ai, Bi, Aj, Bj);
         }
     } else if (all_free) {  // initial scan: every column is a live singleton, no role lookups
         const int row = a.rq[e - P];
@@ -531,7 +536,8 @@ __device__ __forceinline__ void warp_select(unsigned long long k1, int i1, unsig
     obound = r1 < r2 ? r1 : r2;
 }
 
-__global__ void __launch_bounds__(HEAVY_THREADS, 3) kr_heavy(RArgs a) {
+template <int MINB>
+__global__ void __launch_bounds__(HEAVY_THREADS, MINB) kr_heavy(RArgs a) {
     __shared__ int s_flag;
     static_assert(MAX_SEGS <= 32, "one lane per partial list in the final selection");
     RState *st = a.st;
@@ -842,6 +848,8 @@ extern "C" int hc_linkage_rounds(double *W, int32_t n, int method, void *workspa
         kused = 0;
     };
     bool first_pass = true;
+    int heavy_occ = 2;  // CTAs per SM the kernel is compiled for: 3 (80 registers, some spills) or 2 (128 registers)
+    if (const char *e = getenv("HC_ROUNDS_HEAVY_OCC")) heavy_occ = atoi(e);
     auto light_heavy = [&]() {
         int lg = (a.ncols + LIGHT_THREADS / 32 - 1) / (LIGHT_THREADS / 32);
         if (lg > sms * 8) lg = sms * 8;
@@ -849,7 +857,8 @@ extern "C" int hc_linkage_rounds(double *W, int32_t n, int method, void *workspa
         kr_light<<<lg, LIGHT_THREADS, 0, stream>>>(a);
         const int hg = sms * 8 < HEAVY_GRID_MAX ? sms * 8 : HEAVY_GRID_MAX;
         kmark(first_pass ? 4 : 2);
-        kr_heavy<<<hg, HEAVY_THREADS, 0, stream>>>(a);
+        if (heavy_occ == 2) kr_heavy<2><<<hg, HEAVY_THREADS, 0, stream>>>(a);
+        else kr_heavy<3><<<hg, HEAVY_THREADS, 0, stream>>>(a);
         kmark(-1);
         first_pass = false;
     };
