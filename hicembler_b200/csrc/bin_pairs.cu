@@ -282,7 +282,27 @@ __global__ void __launch_bounds__(1024, 1) k_bin_tiles(BinArgs a) {
         __syncthreads();
         // fused flush + zero: every tile cell is written to the matrix exactly once, coalesced
         const int rows = r1 - r0;
-        if (vec_ok && ((c0 & 3) == 0) && ((W & 3) == 0)) {
+        if (vec_ok && ((c0 & 3) == 0) && ((W & 3) == 0) && rows == 1) {
+            // one matrix row per tile (N > ~29 000): no index arithmetic in the loop
+            const int W4 = W >> 2;
+            uint4 *src = (uint4 *)tile;
+            uint4 *dst = (uint4 *)(a.counts + (size_t)(r0 - a.row0) * a.n_windows + c0);
+            if (a.accumulate) {
+                for (int i = threadIdx.x; i < W4; i += T) {
+                    uint4 v = src[i];
+                    const uint4 o = dst[i];
+                    v.x += o.x; v.y += o.y; v.z += o.z; v.w += o.w;
+                    __stcs(dst + i, v);
+                    src[i] = make_uint4(0, 0, 0, 0);
+                }
+            } else {
+#pragma unroll 4
+                for (int i = threadIdx.x; i < W4; i += T) {
+                    __stcs(dst + i, src[i]);
+                    src[i] = make_uint4(0, 0, 0, 0);
+                }
+            }
+        } else if (vec_ok && ((c0 & 3) == 0) && ((W & 3) == 0)) {
             const int W4 = W >> 2;
             for (int i = threadIdx.x; i < rows * W4; i += T) {
                 const int rr = i / W4, cc = i - rr * W4;
