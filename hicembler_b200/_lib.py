@@ -54,6 +54,9 @@ SIGNATURES = {
     "hc_segment_mean_2d": (C.c_int, [_p, _i32, _p, _p, _i32, _p, _p, _p]),
     "hc_normalize_rows": (C.c_int, [_p, _i32, _p, _sz, _p]),
     "hc_unpack_pairs16": (C.c_int, [_p, C.c_int64, _p, _p]),
+    "hc_bam_open": (C.c_int, [C.c_char_p, _i32, _p, _p, _p]),
+    "hc_bam_next": (C.c_int, [_p, _i32, _p, C.c_int64, _p, _p, _p]),
+    "hc_bam_close": (C.c_int, [_p]),
     "hc_gather_square": (C.c_int, [_p, C.c_int, _i32, _p, _i32, _p, _p]),
     "hc_diag_normalize": (C.c_int, [_p, C.c_int, _i32, C.c_double, _p, _p]),
     "hc_window_size_normalize": (C.c_int, [_p, C.c_int, _i32, _p, C.c_double, _p]),

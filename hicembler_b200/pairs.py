@@ -11,6 +11,7 @@ from __future__ import annotations
 
 import gzip
 import io
+import os
 import struct
 import zlib
 
@@ -252,6 +253,92 @@ def read_bam(path):
     return names, sizes, rec, np.array(tl, dtype=np.int32), np.array(span, dtype=np.int32)
 
 
+def read_bam_header(path):
+    """(names, sizes) of a BAM: inflates only as many leading BGZF blocks as the header needs."""
+    raw = b""
+    with open(path, "rb") as f:
+        def more():
+            nonlocal raw
+            head = f.read(18)
+            if len(head) < 18 or head[:4] != b"\x1f\x8b\x08\x04":
+                raise ValueError("%s: truncated BAM header" % path)
+            xlen = struct.unpack_from("<H", head, 10)[0]
+            extra = head[12:] + f.read(max(0, xlen - 6))
+            bsize, q = None, 0
+            while q + 4 <= len(extra):
+                si1, si2, slen = struct.unpack_from("<BBH", extra, q)
+                if si1 == 66 and si2 == 67:
+                    bsize = struct.unpack_from("<H", extra, q + 4)[0] + 1
+                q += 4 + slen
+            if bsize is None:
+                raise ValueError("%s: BGZF block without BC subfield" % path)
+            raw += zlib.decompress(f.read(bsize - 12 - xlen - 8), -15)
+            f.read(8)
+
+        def need(n):
+            while len(raw) < n:
+                more()
+        need(12)
+        if raw[:4] != b"BAM\x01":
+            raise ValueError("%s: bad BAM magic" % path)
+        l_text = struct.unpack_from("<i", raw, 4)[0]
+        need(12 + l_text)
+        n_ref = struct.unpack_from("<i", raw, 8 + l_text)[0]
+        p = 12 + l_text
+        names, sizes = [], []
+        for _ in range(n_ref):
+            need(p + 4)
+            l_name = struct.unpack_from("<i", raw, p)[0]
+            need(p + 8 + l_name)
+            names.append(raw[p + 4:p + 4 + l_name - 1].decode())
+            sizes.append(struct.unpack_from("<i", raw, p + 4 + l_name)[0])
+            p += 8 + l_name
+    return names, sizes
+
+
+def read_bam_native(path, wire=24, threads=0, side_arrays=True, pinned=False, chunk=1 << 22):
+    """Decode a BAM with the native multi-threaded decoder (csrc/bam_decode.cu: hc_bam_open / hc_bam_next).
+    Returns (names, sizes, records, tlen, ref_span) like read_bam; records are PAIR_DTYPE (wire=24) or
+    PAIR16_DTYPE (wire=16: read midpoints, see pack_pairs16).  ``pinned=True`` returns the records as a pinned
+    torch int32 tensor [n, wire/4] ready for the H2D copy (pipeline.host_pairs_to_dendrogram)."""
+    import ctypes as C
+    from . import _lib
+    L = _lib.lib()
+    names, sizes = read_bam_header(path)
+    h, n_ref, ubytes = C.c_void_p(), C.c_int32(), C.c_int64()
+    _lib.check(L.hc_bam_open(os.fsencode(path), int(threads), C.byref(h), C.byref(n_ref), C.byref(ubytes)))
+    dt = PAIR_DTYPE if wire == 24 else PAIR16_DTYPE
+    parts, tls, sps = [], [], []
+    try:
+        if n_ref.value != len(names):
+            raise ValueError("%s: reference count mismatch" % path)
+        while True:
+            rec = np.empty(chunk, dtype=dt)
+            tl = np.empty(chunk, dtype=np.int32) if side_arrays else None
+            sp = np.empty(chunk, dtype=np.int32) if side_arrays else None
+            n = C.c_int64()
+            _lib.check(L.hc_bam_next(h, int(wire), rec.ctypes.data_as(C.c_void_p), chunk,
+                                     tl.ctypes.data_as(C.c_void_p) if side_arrays else None,
+                                     sp.ctypes.data_as(C.c_void_p) if side_arrays else None, C.byref(n)))
+            if n.value == 0:
+                break
+            parts.append(rec[:n.value])
+            if side_arrays:
+                tls.append(tl[:n.value])
+                sps.append(sp[:n.value])
+    finally:
+        L.hc_bam_close(h)
+    rec = np.concatenate(parts) if parts else np.zeros(0, dtype=dt)
+    tlen = (np.concatenate(tls) if tls else np.zeros(0, np.int32)) if side_arrays else None
+    span = (np.concatenate(sps) if sps else np.zeros(0, np.int32)) if side_arrays else None
+    if pinned:
+        import torch
+        t = torch.empty((len(rec), wire // 4), dtype=torch.int32, pin_memory=torch.cuda.is_available())
+        t.numpy().view(dt).reshape(-1)[:] = rec
+        rec = t
+    return names, sizes, rec, tlen, span
+
+
 def load_alignments(src, name2id=None):
     """Resolve one entry of the reference's ``bam`` list to (records, tlen, ref_span, names).
 
@@ -270,6 +357,6 @@ def load_alignments(src, name2id=None):
             n2i = name2id or {n: i for i, n in enumerate(names)}
             rec, tl, sp = sam_to_records(lines, n2i)
             return rec, tl, sp, names or None
-        names, sizes, rec, tl, sp = read_bam(src)
+        names, sizes, rec, tl, sp = read_bam_native(src)   # native zlib workers; read_bam is the restatement
         return rec, tl, sp, names
     raise TypeError("unsupported alignment source: %r" % type(src))

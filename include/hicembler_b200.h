@@ -93,6 +93,18 @@ int hc_bin_pairs(const hc_pair_t *pairs, int64_t n_pairs,
 
 int hc_unpack_pairs16(const hc_pair16_t *packed, int64_t n_pairs, hc_pair_t *pairs, void *stream);
 
+/* Host-only BAM decoder (csrc/bam_decode.cu): replaces the `samtools view` text pipe of
+ * bam2clusters.py:108-117,139-146.  BGZF blocks (bin/snap/SNAPLib/Bam.h:322-350) are inflated and CRC-checked
+ * by n_threads zlib workers (0 = all cores); alignment records (Bam.h:91-105) are handed over in file order,
+ * unfiltered (-q / -F run in hc_bin_pairs), as hc_pair_t (wire 24) or hc_pair16_t (wire 16), straight into the
+ * caller's (pinned) buffer.  h_tlen / h_ref_span (may be NULL): TLEN and the CIGAR reference span (>= 1) for
+ * the contig-level path (:183-189).  hc_bam_next returns up to `capacity` records per call, *h_n = 0 at end. */
+int hc_bam_open(const char *path, int32_t n_threads, void **h_handle, int32_t *h_n_ref,
+                int64_t *h_uncompressed_bytes);
+int hc_bam_next(void *handle, int32_t wire, void *h_out, int64_t capacity, int32_t *h_tlen,
+                int32_t *h_ref_span, int64_t *h_n);
+int hc_bam_close(void *handle);
+
 /* ``upto`` of bam2arrays (:139-141): number of leading records that contain exactly ``upto``
  * lines surviving -q/-F/regions (n_pairs if fewer survive).  workspace >= 8*(n_pairs/4096+2). */
 int hc_upto_cutoff(const hc_pair_t *pairs, int64_t n_pairs, const uint8_t *region_mask,

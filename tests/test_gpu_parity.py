@@ -669,3 +669,26 @@ def test_pairs_to_dendrogram_c1_end_to_end():
     assert np.allclose(W[iu], want_d[iu], rtol=1e-13)
     want = O.linkage_fastcluster(np.sqrt(W[iu]), "ward")
     _same_tree(res["Z"], want, rtol=1e-9)
+
+
+def test_bam_file_to_dendrogram_through_the_host_entry(tmp_path):
+    """BAM on disk -> native decoder (16-byte wire records, pinned) -> host_pairs_to_dendrogram: the same Z as
+    the device-resident path from the 24-byte records, and the same counts as the oracle's SAM-text loop."""
+    from hicembler_b200 import pairs, synth
+    from hicembler_b200.pipeline import pairs_to_dendrogram, host_pairs_to_dendrogram
+    g, rec = small_case(n_contigs=20, n_windows=240, window_bp=5000, n_pairs=40000, with_mates=True,
+                        bad_flag_frac=0.02, vary_len=True)
+    path = str(tmp_path / "hic.bam")
+    pairs.write_bam(path, rec, g.names, [int(s) for s in g.sizes])
+    names, sizes, wire, _, _ = pairs.read_bam_native(path, wire=16, pinned=True, side_arrays=False)
+    assert names == g.names
+    off = torch.from_numpy(g.window_offsets().astype(np.int32)).cuda()
+    kw = dict(mapq=10, params=(0.5, 1.1), method="ward", balance=True)
+    a = host_pairs_to_dendrogram(wire, off, g.window_bp, g.n_windows(), **kw)
+    b = pairs_to_dendrogram(synth.records_tensor(rec, "cuda"), off, g.window_bp, g.n_windows(), **kw)
+    assert np.array_equal(a["Z"], b["Z"])
+    assert a["stats"]["binned"] == b["stats"]["binned"] == int(O.bin_records(rec, g.window_bp, g.window_offsets(),
+                                                                             g.n_windows(), 10).sum())
+    h24 = torch.from_numpy(rec.view(np.int32).reshape(-1, 6).copy())
+    c = host_pairs_to_dendrogram(h24, off, g.window_bp, g.n_windows(), **kw)
+    assert np.array_equal(c["Z"], b["Z"])
