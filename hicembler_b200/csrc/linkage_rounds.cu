@@ -850,17 +850,47 @@ extern "C" int hc_linkage_rounds(double *W, int32_t n, int method, void *workspa
     bool first_pass = true;
     int heavy_occ = 2;  // CTAs per SM the kernel is compiled for: 3 (80 registers, some spills) or 2 (128 registers)
     if (const char *e = getenv("HC_ROUNDS_HEAVY_OCC")) heavy_occ = atoi(e);
-    auto light_heavy = [&]() {
+    auto light_heavy_on = [&](cudaStream_t sq, bool mark) {
         int lg = (a.ncols + LIGHT_THREADS / 32 - 1) / (LIGHT_THREADS / 32);
         if (lg > sms * 8) lg = sms * 8;
-        kmark(first_pass ? 4 : 1);
-        kr_light<<<lg, LIGHT_THREADS, 0, stream>>>(a);
+        if (mark) kmark(first_pass ? 4 : 1);
+        kr_light<<<lg, LIGHT_THREADS, 0, sq>>>(a);
         const int hg = sms * 8 < HEAVY_GRID_MAX ? sms * 8 : HEAVY_GRID_MAX;
-        kmark(first_pass ? 4 : 2);
-        if (heavy_occ == 2) kr_heavy<2><<<hg, HEAVY_THREADS, 0, stream>>>(a);
-        else kr_heavy<3><<<hg, HEAVY_THREADS, 0, stream>>>(a);
-        kmark(-1);
+        if (mark) kmark(first_pass ? 4 : 2);
+        if (heavy_occ == 2) kr_heavy<2><<<hg, HEAVY_THREADS, 0, sq>>>(a);
+        else kr_heavy<3><<<hg, HEAVY_THREADS, 0, sq>>>(a);
+        if (mark) kmark(-1);
         first_pass = false;
+    };
+    auto light_heavy = [&]() { light_heavy_on(stream, true); };
+    auto rounds_on = [&](cudaStream_t sq, bool mark) {
+        for (int b = 0; b < batch; ++b) {
+            if (mark) kmark(0);
+            kr_select<<<(a.ncols + 255) / 256, 256, 0, sq>>>(a);
+            light_heavy_on(sq, mark);
+        }
+    };
+    // A batch of rounds (3 x batch launches with fixed arguments between two compactions) is captured once into a
+    // CUDA graph on a private stream and replayed on the caller's stream: the chain phase is ~1700 launches of
+    // 5-20 us kernels, so the launch gaps matter.
+    bool use_graph = !trace && !ktime && getenv("HC_ROUNDS_NOGRAPH") == nullptr;
+    cudaStream_t cap_stream = nullptr;
+    cudaGraphExec_t gexec = nullptr;
+    auto drop_graph = [&]() {
+        if (gexec) cudaGraphExecDestroy(gexec);
+        gexec = nullptr;
+    };
+    auto build_graph = [&]() -> bool {
+        drop_graph();
+        if (!cap_stream && cudaStreamCreateWithFlags(&cap_stream, cudaStreamNonBlocking) != cudaSuccess) return false;
+        cudaGraph_t g = nullptr;
+        if (cudaStreamBeginCapture(cap_stream, cudaStreamCaptureModeThreadLocal) != cudaSuccess) return false;
+        rounds_on(cap_stream, false);
+        if (cudaStreamEndCapture(cap_stream, &g) != cudaSuccess || !g) { cudaGetLastError(); return false; }
+        const cudaError_t e = cudaGraphInstantiate(&gexec, g, 0);
+        cudaGraphDestroy(g);
+        if (e != cudaSuccess) { gexec = nullptr; cudaGetLastError(); return false; }
+        return true;
     };
     HC_CUDA_OK(cudaMemsetAsync(L.seg_done, 0, (size_t)n * sizeof(int), stream));
     kr_init<<<(n + 255) / 256, 256, 0, stream>>>(a);
@@ -877,11 +907,11 @@ extern "C" int hc_linkage_rounds(double *W, int32_t n, int method, void *workspa
     RState h;
     for (;;) {
         if (trace) cudaEventRecord(ev0, stream);
-        for (int b = 0; b < batch; ++b) {
-            kmark(0);
-            kr_select<<<(a.ncols + 255) / 256, 256, 0, stream>>>(a);
-            light_heavy();
-        }
+        // (instantiating a graph costs ~0.1 ms: only worth it for the long epochs of big problems)
+        const bool graph_now = use_graph && a.ncols >= 16384;
+        if (graph_now && !gexec && !build_graph()) use_graph = false;
+        if (graph_now && use_graph) HC_CUDA_OK(cudaGraphLaunch(gexec, stream));
+        else rounds_on(stream, true);
         if (trace) cudaEventRecord(ev1, stream);
         HC_CHECK_LAUNCH();
         HC_CUDA_OK(cudaMemcpyAsync(&h, L.st, sizeof h, cudaMemcpyDeviceToHost, stream));
@@ -913,6 +943,7 @@ extern "C" int hc_linkage_rounds(double *W, int32_t n, int method, void *workspa
                 cudaEventElapsedTime(&ms, ev0, ev1);
                 fprintf(stderr, "[rounds trace] compaction %d -> %d us %.1f\n", a.ncols, nnew, ms * 1e3f);
             }
+            drop_graph();  // the kernel arguments change
             cur ^= 1;
             in_spare = !in_spare;
             a.c = L.cols[cur];
@@ -924,6 +955,8 @@ extern "C" int hc_linkage_rounds(double *W, int32_t n, int method, void *workspa
     }
     if (trace) { cudaEventDestroy(ev0); cudaEventDestroy(ev1); }
     for (cudaEvent_t e : kev) cudaEventDestroy(e);
+    drop_graph();
+    if (cap_stream) cudaStreamDestroy(cap_stream);
     const int m = n - 1;
     const bool uncertified = h.ambiguous || h.stuck || h.n_done != m || (a.diag && h.stats[6]);
     if (a.diag) {
