@@ -692,3 +692,44 @@ def test_bam_file_to_dendrogram_through_the_host_entry(tmp_path):
     h24 = torch.from_numpy(rec.view(np.int32).reshape(-1, 6).copy())
     c = host_pairs_to_dendrogram(h24, off, g.window_bp, g.n_windows(), **kw)
     assert np.array_equal(c["Z"], b["Z"])
+
+
+def test_host_entry_chunked_overlap_equals_one_piece():
+    """host_pairs_to_dendrogram bins contig-aligned pieces under the H2D copy: same counts and Z as one piece;
+    input that is not sorted by contig, absent contigs and trailing unmapped records are handled."""
+    from hicembler_b200 import ops, pairs, synth
+    from hicembler_b200.pipeline import pairs_to_dendrogram, host_pairs_to_dendrogram, _chunk_plan
+    g, rec = small_case(n_contigs=40, n_windows=300, window_bp=5000, n_pairs=120000)
+    rec = rec.copy()
+    unm = rec[:50].copy()
+    unm["refID"], unm["flag"] = -1, 4 | 1                       # unplaced unmapped reads close a sorted BAM
+    rec = np.concatenate([rec, unm])
+    off_np = g.window_offsets().astype(np.int32)
+    off = torch.from_numpy(off_np).cuda()
+    kw = dict(mapq=10, params=(0.5, 1.1), method="average", balance=True)
+    want = pairs_to_dendrogram(synth.records_tensor(rec, "cuda"), off, g.window_bp, g.n_windows(), keep=True, **kw)
+    for width in (4, 6):
+        host = torch.from_numpy(pairs.pack_pairs16(rec).view(np.int32).reshape(-1, 4).copy() if width == 4
+                                else rec.view(np.int32).reshape(-1, 6).copy())
+        st = {"chunks": 6, "min_chunk_records": 1000}
+        plan = _chunk_plan(host, off_np, g.n_windows(), 6)
+        assert plan is not None and len(plan) >= 4 and plan[0][0] == 0 and plan[-1][1] == len(rec)
+        got = host_pairs_to_dendrogram(host, off, g.window_bp, g.n_windows(), staging=st, keep=True, **kw)
+        assert got["stats"]["chunks"] == len(plan) and got["stats"]["binned"] == want["stats"]["binned"]
+        assert torch.equal(got["sym"], want["sym"]) and np.array_equal(got["Z"], want["Z"])
+    # contigs swapped out of order: the guard sees it and the call bins in one piece
+    order = np.argsort(-rec["refID"], kind="stable")
+    host = torch.from_numpy(rec[order].view(np.int32).reshape(-1, 6).copy())
+    got = host_pairs_to_dendrogram(host, off, g.window_bp, g.n_windows(),
+                                   staging={"chunks": 6, "min_chunk_records": 1000}, keep=True, **kw)
+    assert "chunks" not in got["stats"] and torch.equal(got["sym"], want["sym"])
+    # a window table with absent contigs (offset -1) still tiles the rows
+    off2 = off_np.copy()
+    off2[5] = off2[17] = -1
+    want2 = pairs_to_dendrogram(synth.records_tensor(rec, "cuda"), torch.from_numpy(off2).cuda(), g.window_bp,
+                                g.n_windows(), keep=True, **kw)
+    host = torch.from_numpy(rec.view(np.int32).reshape(-1, 6).copy())
+    got2 = host_pairs_to_dendrogram(host, torch.from_numpy(off2).cuda(), g.window_bp, g.n_windows(),
+                                    staging={"chunks": 6, "min_chunk_records": 1000}, keep=True, **kw)
+    assert got2["stats"]["skipped_absent"] == want2["stats"]["skipped_absent"] > 0
+    assert torch.equal(got2["sym"], want2["sym"])
