@@ -848,6 +848,8 @@ extern "C" int hc_linkage_rounds(double *W, int32_t n, int method, void *workspa
         kused = 0;
     };
     bool first_pass = true;
+    int heavy_launches = 0, bulk3 = 2;
+    if (const char *e = getenv("HC_ROUNDS_BULK3")) bulk3 = atoi(e);
     int heavy_occ = 2;  // CTAs per SM the kernel is compiled for: 3 (80 registers, some spills) or 2 (128 registers)
     if (const char *e = getenv("HC_ROUNDS_HEAVY_OCC")) heavy_occ = atoi(e);
     auto light_heavy_on = [&](cudaStream_t sq, bool mark) {
@@ -857,9 +859,11 @@ extern "C" int hc_linkage_rounds(double *W, int32_t n, int method, void *workspa
         kr_light<<<lg, LIGHT_THREADS, 0, sq>>>(a);
         const int hg = sms * 8 < HEAVY_GRID_MAX ? sms * 8 : HEAVY_GRID_MAX;
         if (mark) kmark(first_pass ? 4 : 2);
-        if (heavy_occ == 2) kr_heavy<2><<<hg, HEAVY_THREADS, 0, sq>>>(a);
+        // the first rounds after the initial scan are dominated by merged-row builds, where the 3-CTA build wins
+        if (heavy_occ == 2 && !(heavy_launches >= 1 && heavy_launches <= bulk3)) kr_heavy<2><<<hg, HEAVY_THREADS, 0, sq>>>(a);
         else kr_heavy<3><<<hg, HEAVY_THREADS, 0, sq>>>(a);
         if (mark) kmark(-1);
+        heavy_launches++;
         first_pass = false;
     };
     auto light_heavy = [&]() { light_heavy_on(stream, true); };
