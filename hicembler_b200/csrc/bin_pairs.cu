@@ -200,12 +200,16 @@ __global__ void k_tile_ranges(BinArgs a, long long *tile_clo, long long *tile_ch
 // a row's records serialise on one shared-memory address), then one fused flush+zero pass that
 // writes every matrix cell of the tile exactly once with 16-byte coalesced stores.  The stores of
 // tile t drain while the records of tile t+1 are being loaded.
-template <int UNROLL>
-__global__ void __launch_bounds__(1024, 1) k_bin_tiles(BinArgs a) {
+// CELL16: tile cells are 16 bits, two per shared-memory word, so a 50 000-column row takes 100 KB and TWO CTAs
+// (512 threads each) share an SM: one streams its records while the other flushes.  A cell never overflows its
+// half word: the add that carries the stored value across a multiple of 16 384 takes 16 384 back out and files it
+// in the overflow list (weight bit), so the stored value stays below 16 384 + what is in flight (< 65 536).
+template <int UNROLL, bool CELL16>
+__global__ void __launch_bounds__(CELL16 ? 512 : 1024, CELL16 ? 2 : 1) k_bin_tiles(BinArgs a) {
     extern __shared__ __align__(16) uint32_t tile[];
     const int T = blockDim.x, lane_id = threadIdx.x & 31;
     const int n_tiles = a.n_groups * a.n_segs;
-    const int max_cells = a.R * a.W;
+    const int max_cells = CELL16 ? (a.R * a.W + 1) / 2 : a.R * a.W;  // shared-memory words
     for (int i = threadIdx.x; i < max_cells; i += T) tile[i] = 0;
     __syncthreads();
     uint32_t n_lines = 0, n_ok = 0, n_absent = 0, n_range = 0, n_key = 0, n_over = 0;
@@ -262,7 +266,33 @@ __global__ void __launch_bounds__(1024, 1) k_bin_tiles(BinArgs a) {
                 // warp-aggregated shared-memory atomics: one add per distinct cell per warp
                 const uint32_t cell = mine ? (uint32_t)((row - r0) * W + (col - c0)) : 0xffffffffu;
                 const unsigned peers = __match_any_sync(0xffffffffu, cell);
-                if (mine && (__ffs(peers) - 1) == lane_id) atomicAdd(&tile[cell], (uint32_t)__popc(peers));
+                bool spill = false;
+                if (mine && (__ffs(peers) - 1) == lane_id) {
+                    const uint32_t inc = (uint32_t)__popc(peers);
+                    if (CELL16) {
+                        const uint32_t sh = (cell & 1u) * 16u;
+                        const uint32_t h = (atomicAdd(&tile[cell >> 1], inc << sh) >> sh) & 0xffffu;
+                        if (((h + inc) >> 14) != (h >> 14)) {
+                            atomicSub(&tile[cell >> 1], 0x4000u << sh);
+                            spill = true;
+                        }
+                    } else {
+                        atomicAdd(&tile[cell], inc);
+                    }
+                }
+                if (CELL16) {
+                    const unsigned ms = __ballot_sync(0xffffffffu, spill);
+                    if (ms) {
+                        const int leader = __ffs(ms) - 1;
+                        unsigned long long slot = 0;
+                        if (lane_id == leader) slot = atomicAdd(a.overflow_count, (unsigned long long)__popc(ms));
+                        slot = __shfl_sync(0xffffffffu, slot, leader);
+                        if (spill) {
+                            slot += __popc(ms & ((1u << lane_id) - 1));
+                            if ((long long)slot < a.overflow_cap) a.overflow[slot] = make_uint2((uint32_t)row | 0x80000000u, col);
+                        }
+                    }
+                }
                 // straggler: row not advertised by its chunk -> nobody's tile sees it
                 const bool strag = owner && ok && (row < lo || row >= hi) && row >= a.row0 && row < a.row1;
                 const unsigned m = __ballot_sync(0xffffffffu, strag);
@@ -282,7 +312,22 @@ __global__ void __launch_bounds__(1024, 1) k_bin_tiles(BinArgs a) {
         __syncthreads();
         // fused flush + zero: every tile cell is written to the matrix exactly once, coalesced
         const int rows = r1 - r0;
-        if (vec_ok && ((c0 & 3) == 0) && ((W & 3) == 0) && rows == 1) {
+        if (CELL16) {  // (the host picks this kernel only when vec_ok, c0 % 4 == 0 and W % 4 == 0)
+            const int W4 = W >> 2;
+            for (int i = threadIdx.x; i < rows * W4; i += T) {
+                const int rr = rows == 1 ? 0 : i / W4, cc = i - rr * W4;
+                uint2 *src = (uint2 *)(tile + rr * (W >> 1)) + cc;  // four 16-bit cells
+                uint4 *dst = (uint4 *)(a.counts + (size_t)(r0 - a.row0 + rr) * a.n_windows + c0) + cc;
+                const uint2 w = *src;
+                uint4 v = make_uint4(w.x & 0xffffu, w.x >> 16, w.y & 0xffffu, w.y >> 16);
+                if (a.accumulate) {
+                    const uint4 o = *dst;
+                    v.x += o.x; v.y += o.y; v.z += o.z; v.w += o.w;
+                }
+                __stcs(dst, v);
+                *src = make_uint2(0, 0);
+            }
+        } else if (vec_ok && ((c0 & 3) == 0) && ((W & 3) == 0) && rows == 1) {
             // one matrix row per tile (N > ~29 000): no index arithmetic in the loop
             const int W4 = W >> 2;
             uint4 *src = (uint4 *)tile;
@@ -340,8 +385,9 @@ __global__ void k_apply_overflow(BinArgs a) {
     long long n = min((long long)*a.overflow_count, a.overflow_cap);
     for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n;
          i += (long long)gridDim.x * blockDim.x) {
-        uint2 e = a.overflow[i];
-        atomicAdd(a.counts + (size_t)((int32_t)e.x - a.row0) * a.n_windows + e.y, 1u);
+        uint2 e = a.overflow[i];  // top bit of the row: a 16-bit tile cell handed 16 384 counts over
+        const uint32_t w = (e.x & 0x80000000u) ? 0x4000u : 1u;
+        atomicAdd(a.counts + (size_t)((int32_t)(e.x & 0x7fffffffu) - a.row0) * a.n_windows + e.y, w);
     }
 }
 
@@ -538,7 +584,12 @@ extern "C" int hc_bin_pairs(const hc_pair_t *pairs, int64_t n_pairs, const int32
     HC_CUDA_OK(cudaGetDevice(&dev));
     HC_CUDA_OK(cudaDeviceGetAttribute(&smem_max, cudaDevAttrMaxSharedMemoryPerBlockOptin, dev));
     const int sms = hc::sm_count();
-    long long max_cells = (smem_max - 1024) / 4;
+    // 16-bit tile cells when a u32 row no longer leaves room for two CTAs per SM (n_windows > ~29 000) and the
+    // vector flush applies (n_windows % 4 == 0, 16-byte aligned matrix); HC_BIN_CELL16=0/1 overrides
+    const bool vec_host = (n_windows & 3) == 0 && (((uintptr_t)counts) & 15) == 0;
+    bool cell16 = vec_host && (long long)n_windows * 4 > (smem_max - 1024) / 2;
+    if (const char *e = getenv("HC_BIN_CELL16")) cell16 = vec_host && atoi(e) != 0;
+    long long max_cells = (smem_max - 1024) / (cell16 ? 2 : 4);
     if (const char *e = getenv("HC_BIN_MAX_CELLS")) max_cells = atoll(e);
     a.n_segs = (int)((n_windows + max_cells - 1) / max_cells);
     a.W = (n_windows + a.n_segs - 1) / a.n_segs;
@@ -550,6 +601,7 @@ extern "C" int hc_bin_pairs(const hc_pair_t *pairs, int64_t n_pairs, const int32
     int Rwant = (rows + 4 * sms - 1) / (4 * sms);  // aim for >= 4 tiles per SM
     a.R = Rwant < 1 ? 1 : (Rwant > Rmax ? Rmax : Rwant);
     if (const char *e = getenv("HC_BIN_ROWS")) a.R = atoi(e) < 1 ? 1 : (atoi(e) > Rmax ? Rmax : atoi(e));
+    if (cell16 && (a.W & 3) != 0) cell16 = false;  // (cannot happen: W = n_windows or a multiple of 4)
     a.n_groups = (rows + a.R - 1) / a.R;
 
     hc::Carver ws(workspace, workspace_bytes);
@@ -586,19 +638,24 @@ extern "C" int hc_bin_pairs(const hc_pair_t *pairs, int64_t n_pairs, const int32
         k_scan_apply<<<(int)nb, 1024, 0, stream>>>(lead, a.n_chunks, bmax);
         k_chunk_bounds<<<cb, 256, 0, stream>>>(a, lead, chunk_lo, chunk_hi);
         k_tile_ranges<<<(a.n_groups + 127) / 128, 128, 0, stream>>>(a, tile_clo, tile_chi);
-        size_t smem = hc::align_up((size_t)a.R * a.W * 4, 16);
-        int threads = 1024;
+        size_t smem = hc::align_up((size_t)a.R * a.W * (cell16 ? 2 : 4), 16);
+        int threads = cell16 ? 512 : 1024;
         if (const char *e = getenv("HC_BIN_THREADS")) threads = atoi(e);
-        HC_CUDA_OK(cudaFuncSetAttribute(k_bin_tiles<4>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                        smem_max));
+        if (cell16 && threads > 512) threads = 512;
+        if (cell16)
+            HC_CUDA_OK(cudaFuncSetAttribute(k_bin_tiles<4, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_max));
+        else
+            HC_CUDA_OK(cudaFuncSetAttribute(k_bin_tiles<4, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_max));
         // persistent: as many CTAs as fit (tiles <= ~110 KB let two CTAs share an SM and overlap
         // one CTA's flush with the other's record stream)
         int per_sm = (int)((size_t)(smem_max + 1024) / (smem + 1024));
         if (per_sm > 2048 / threads) per_sm = 2048 / threads;
+        if (cell16 && per_sm > 2) per_sm = 2;
         if (per_sm < 1) per_sm = 1;
         long long n_tiles = (long long)a.n_groups * a.n_segs;
         int grid = (int)std::min<long long>(n_tiles, (long long)sms * per_sm);
-        k_bin_tiles<4><<<grid, threads, smem, stream>>>(a);
+        if (cell16) k_bin_tiles<4, true><<<grid, threads, smem, stream>>>(a);
+        else k_bin_tiles<4, false><<<grid, threads, smem, stream>>>(a);
         HC_CHECK_LAUNCH();
         k_apply_overflow<<<4 * sms, 256, 0, stream>>>(a);
         HC_CHECK_LAUNCH();

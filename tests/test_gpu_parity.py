@@ -50,7 +50,9 @@ def test_bam2arrays_multi_window_bit_exact(kw):
 
 
 @pytest.mark.parametrize("mode", [0, 1])
-@pytest.mark.parametrize("env", [dict(), dict(HC_BIN_MAX_CELLS="700", HC_BIN_ROWS="3")])
+@pytest.mark.parametrize("env", [dict(), dict(HC_BIN_MAX_CELLS="700", HC_BIN_ROWS="3"), dict(HC_BIN_CELL16="1"),
+                                 dict(HC_BIN_CELL16="1", HC_BIN_MAX_CELLS="1200", HC_BIN_ROWS="3"),
+                                 dict(HC_BIN_CELL16="0")])
 def test_bin_pairs_paths_agree(mode, env, monkeypatch):
     """shared-memory tile path (also with several column segments / odd tile heights) and the
     global-atomic path give the same full-orientation counts"""
@@ -69,6 +71,37 @@ def test_bin_pairs_paths_agree(mode, env, monkeypatch):
     assert st["lines"] == int(kept.sum())
     up, _ = ops.fold_counts(cnt, "upper")
     assert np.array_equal(up.cpu().numpy(), want)
+
+
+@pytest.mark.parametrize("cell16", ["0", "1"])
+def test_bin_hot_cells_beyond_16_bits(cell16, monkeypatch):
+    """16-bit tile cells hand 16 384 counts at a time to the overflow list: cells far beyond 65 535 stay exact
+    (both halves of a shared-memory word, accumulate mode included)."""
+    from hicembler_b200 import ops
+    from hicembler_b200.pairs import records_from_columns
+    monkeypatch.setenv("HC_BIN_CELL16", cell16)
+    n_win, ws = 64, 1000
+    off = torch.arange(0, n_win, 16, dtype=torch.int32).cuda()            # 4 contigs of 16 windows
+    hot = [(0, 2500, 0, 2500, 200001), (0, 2500, 0, 3500, 70000), (1, 500, 2, 9500, 131073), (1, 700, 1, 1700, 16384),
+           (3, 15100, 3, 15200, 65536)]
+    cols = [[], [], [], []]
+    for r1, p1, r2, p2, k in hot:
+        for c, v in zip(cols, (r1, p1, r2, p2)):
+            c.append(np.full(k, v, dtype=np.int64))
+    ref, pos, nref, npos = (np.concatenate(c) for c in cols)
+    order = np.lexsort((pos, ref))
+    n = len(ref)
+    rec = records_from_columns(ref[order], pos[order], nref[order], npos[order], np.full(n, 100), np.full(n, 99),
+                               np.full(n, 60))
+    dev = ops.to_device_records(rec)
+    cnt, st = ops.bin_pairs(dev, off, ws, n_win, 10, return_stats=True)
+    want = np.zeros((n_win, n_win), dtype=np.int64)
+    for r1, p1, r2, p2, k in hot:
+        want[r1 * 16 + (p1 + 51) // ws, r2 * 16 + (p2 + 51) // ws] += k
+    assert st["fast_path"] and st["binned"] == n
+    assert np.array_equal(cnt.cpu().numpy().view(np.uint32).astype(np.int64), want)
+    cnt2 = ops.bin_pairs(dev, off, ws, n_win, 10, mode=2, out=cnt)         # accumulate a second "BAM"
+    assert np.array_equal(cnt2.cpu().numpy().view(np.uint32).astype(np.int64), 2 * want)
 
 
 def test_unsorted_input_falls_back_and_stays_exact():
