@@ -264,7 +264,7 @@ def run_ours(args, cfg, rank, world, local_rank):
     lst = res["linkage_stats"]
     sk_it = res.get("sk_iterations", 0)
     # algorithmic bytes per launch (DESIGN.md section "Kernels and rooflines")
-    sk_passes = (2 * sk_it + 4) if not args.no_balance else 0      # matrix reads of 4 N^2 bytes each
+    sk_passes = res.get("sk_passes", 2 * sk_it + 4) if not args.no_balance else 0      # matrix reads of 4 N^2 bytes each
     bytes_alg = {
         "bin_pairs": 24.0 * P + 4.0 * N * N,
         "fold": 8.0 * N * N,
@@ -307,6 +307,8 @@ def run_ours(args, cfg, rank, world, local_rank):
                              "and the initial scan move most of the bytes, see profiles/" % lst["rounds"]}
     # launches per step: bin 8, fold 1, sinkhorn (colpass+finish)=2/pass ... counted from the call graph
     sk_launches = 0 if args.no_balance else (2 + 1 + 1 + 2 + 1 + 2 + sk_it * 5)
+    if sk_launches:   # the raw row-sum pass is skipped when a column sum already decides the first test
+        sk_launches += -1 if sk_passes == 2 * sk_it + 3 else 1
     link_launches = (3 + 3 * 8 * ((lst["rounds"] + 7) // 8) + 3 * lst["compactions"]) if lst.get("engine") == "rounds" else 1
     gpu_launches = K * 2 * (8 + 1 + sk_launches + 1 + link_launches) + (K if args.wire == 16 else 0)  # + unpack
     cpu = None
@@ -395,7 +397,7 @@ def run_sinkhorn_mode(args, cfg, rank, world, local_rank):
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
     if rank == 0:
         ms = t.item() / args.steps
-        passes = 2 * res.iterations + 4
+        passes = res.matrix_passes
         peak, src = load_peaks()
         gbs = passes * 4.0 * N * N / (ms * 1e-3) / 1e9
         print(json.dumps({"mode": "sinkhorn", "n_windows": N, "n_gpus": world, "iterations": res.iterations,

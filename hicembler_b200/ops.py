@@ -155,7 +155,7 @@ def symmetrize_(d, add=0.0):
 # K3-K5
 # ---------------------------------------------------------------------------------------------
 class SinkhornResult:
-    __slots__ = ("r", "c", "iterations", "stopping_condition", "warned")
+    __slots__ = ("r", "c", "iterations", "stopping_condition", "warned", "matrix_passes")
 
 
 class _CudaSinkhornPasses:
@@ -175,10 +175,12 @@ class _CudaSinkhornPasses:
         self.flags = torch.zeros(8, dtype=torch.int32, device=X.device)
         self.outside = torch.zeros(1, dtype=torch.int32, device=X.device)
         self.s = _stream()
+        self.matrix_passes = 0   # full reads of the row block
 
     def colpass(self, use_r, check=False):
         """y_local = P_block^T r (r = ones when use_r is False); returns the tensor to all-reduce"""
         L = self.L
+        self.matrix_passes += 1
         _lib.check(L.hc_sk_colpass(_ptr(self.X), self.dt, self.nrows, self.n, self.vmax,
                                    _ptr(self.r) if use_r else None, _ptr(self.ypart),
                                    _ptr(self.flags) if check else None, self.s))
@@ -199,17 +201,24 @@ class _CudaSinkhornPasses:
         return True
 
     def raw_outside(self):
-        """first evaluation of the while test on P itself (row sums, column sums); local flag tensor"""
+        """first evaluation of the while test on P itself (row sums, column sums); local flag tensor.
+        The test is an OR over all row and column sums: the column sums are already there (first column pass,
+        all-reduced when sharded, so every rank decides alike), and only if none of them is outside 1 +- eps
+        does the row-sum pass over the matrix have to run (never for an unnormalised contact matrix)."""
         L = self.L
+        _lib.check(L.hc_sk_outside(_ptr(self.y), self.n, self.eps, _ptr(self.outside), self.s))
+        if bool(self.outside.item()):
+            return self.outside
+        self.matrix_passes += 1
         _lib.check(L.hc_sk_rowpass(_ptr(self.X), self.dt, self.nrows, self.n, self.vmax, None, _ptr(self.x), None,
                                    _ptr(self.flags), self.s))
         self.flags[4] = 0
         _lib.check(L.hc_sk_outside(_ptr(self.x), self.nrows, self.eps, _ptr(self.outside), self.s))
-        _lib.check(L.hc_sk_outside(_ptr(self.y), self.n, self.eps, _ptr(self.outside), self.s))
         return self.outside
 
     def rowpass(self):
         """r = 1/(P_block c)"""
+        self.matrix_passes += 1
         _lib.check(self.L.hc_sk_rowpass(_ptr(self.X), self.dt, self.nrows, self.n, self.vmax, _ptr(self.c),
                                         _ptr(self.x), _ptr(self.r), _ptr(self.flags), self.s))
 
@@ -233,6 +242,7 @@ def sinkhorn_fit(X, vmax=1.0, max_iter=1000, epsilon=1e-3, iterations0=0, allred
     iterations, stop, warned = sinkhorn_driver(passes, max_iter, iterations0, allreduce)
     res = SinkhornResult()
     res.r, res.c, res.iterations, res.stopping_condition, res.warned = passes.r, passes.c, iterations, stop, warned
+    res.matrix_passes = passes.matrix_passes
     return res
 
 
