@@ -306,9 +306,7 @@ def run_ours(args, cfg, rank, world, local_rank):
                      "note": "latency-bound in the %d rounds of the chain phase (1-4 merges per round); the bulk rounds "
                              "and the initial scan move most of the bytes, see profiles/" % lst["rounds"]}
     # launches per step: bin 8, fold 1, sinkhorn (colpass+finish)=2/pass ... counted from the call graph
-    sk_launches = 0 if args.no_balance else (2 + 1 + 1 + 2 + 1 + 2 + sk_it * 5)
-    if sk_launches:   # the raw row-sum pass is skipped when a column sum already decides the first test
-        sk_launches += -1 if sk_passes == 2 * sk_it + 3 else 1
+    sk_launches = 0 if args.no_balance else res["sk_launches"]      # counted by ops._CudaSinkhornPasses
     link_launches = (3 + 3 * 8 * ((lst["rounds"] + 7) // 8) + 3 * lst["compactions"]) if lst.get("engine") == "rounds" else 1
     gpu_launches = K * 2 * (8 + 1 + sk_launches + 1 + link_launches) + (K if args.wire == 16 else 0)  # + unpack
     cpu = None

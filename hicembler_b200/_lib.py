@@ -35,6 +35,10 @@ SIGNATURES = {
     "hc_sk_num_row_chunks": (_i32, [_i32]),
     "hc_sk_colpass": (C.c_int, [_p, C.c_int, _i32, _i32, _dbl, _p, _p, _p, _p]),
     "hc_sk_colfinish": (C.c_int, [_p, _i32, _i32, _p, _p]),
+    "hc_sk_sym_num_blocks": (_i32, [_i32]),
+    "hc_sk_sympass": (C.c_int, [_p, C.c_int, _i32, _dbl, _p, _p, _p, _p]),
+    "hc_sk_symfinish": (C.c_int, [_p, _i32, _p, _p, _p, _p]),
+    "hc_selftest_scaled_division": (C.c_int, [_p, _i32, _p, _p]),
     "hc_sk_update_c": (C.c_int, [_p, _p, _i32, _dbl, _p, _p, _p]),
     "hc_sk_outside": (C.c_int, [_p, _i32, _dbl, _p, _p]),
     "hc_sk_rowpass": (C.c_int, [_p, C.c_int, _i32, _i32, _dbl, _p, _p, _p, _p, _p]),

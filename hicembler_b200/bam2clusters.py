@@ -243,11 +243,11 @@ def normalize(d, max_iter=1000, epsilon=0.00001):
     sk = SinkhornKnopp(max_iter=max_iter, epsilon=epsilon)
     if isinstance(d, torch.Tensor):
         _, vmax = ops.symmetrize_(d, add=1.0)
-        return sk.fit_device(d, float(vmax.item()))
+        return sk.fit_device(d, float(vmax.item()), symmetric=True)    # d + d.T is symmetric bitwise
     X = torch.from_numpy(d).cuda() if d.flags.c_contiguous else torch.from_numpy(np.ascontiguousarray(d)).cuda()
     _, vmax = ops.symmetrize_(X, add=1.0)
     d[...] = X.cpu().numpy()
-    return sk.fit_device(X, float(vmax.item())).cpu().numpy()
+    return sk.fit_device(X, float(vmax.item()), symmetric=True).cpu().numpy()
 
 
 def normalize_diagional(d, bin_chr, bin_position):

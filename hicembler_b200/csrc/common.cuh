@@ -64,6 +64,49 @@ __device__ __forceinline__ double warp_sum_f64(double v) {
     return v;
 }
 
+// a / b for a loop-invariant divisor: the correctly rounded reciprocal is taken once, each element then
+// costs FMUL + 2 FFMA (q = a*y; e = a - b*q exactly; q + e*y rounds to RN(a/b) when y = RN(1/b) and no
+// intermediate leaves the normal range).  A group of operands is tested together: if any of them (or b) is
+// outside [2^-60, 2^60) -- zero, negative, subnormal, inf/NaN included -- the whole group takes the plain
+// IEEE division, so the result is a / b bit for bit in every case (checked against the IEEE division over
+// whole binades by hc_selftest_scaled_division).
+struct ScaledDivF {
+    float b, y;
+    bool ok;
+    __device__ __forceinline__ explicit ScaledDivF(float b_) : b(b_), y(1.0f / b_) {
+        ok = (__float_as_uint(b_) - 0x21800000u) < 0x3C000000u;
+    }
+    template <int N>
+    __device__ __forceinline__ void apply(const float (&a)[N], float (&p)[N]) const {
+        unsigned m = 0;
+#pragma unroll
+        for (int k = 0; k < N; ++k) m = max(m, __float_as_uint(a[k]) - 0x21800000u);
+        if (ok && m < 0x3C000000u) {
+#pragma unroll
+            for (int k = 0; k < N; ++k) {
+                const float q = __fmul_rn(a[k], y);
+                const float e = __fmaf_rn(-b, q, a[k]);
+                p[k] = __fmaf_rn(e, y, q);
+            }
+        } else {
+#pragma unroll
+            for (int k = 0; k < N; ++k) p[k] = a[k] / b;
+        }
+    }
+};
+struct ScaledDivD {     // float64 matrices are not on the hot path
+    double b;
+    __device__ __forceinline__ explicit ScaledDivD(double b_) : b(b_) {}
+    template <int N>
+    __device__ __forceinline__ void apply(const double (&a)[N], double (&p)[N]) const {
+#pragma unroll
+        for (int k = 0; k < N; ++k) p[k] = a[k] / b;
+    }
+};
+template <typename T> struct ScaledDiv;
+template <> struct ScaledDiv<float> { typedef ScaledDivF type; };
+template <> struct ScaledDiv<double> { typedef ScaledDivD type; };
+
 // streaming 16-byte load that does not pollute L1
 __device__ __forceinline__ uint4 ld_stream_u4(const void *p) {
     uint4 r;

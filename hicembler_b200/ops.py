@@ -155,32 +155,48 @@ def symmetrize_(d, add=0.0):
 # K3-K5
 # ---------------------------------------------------------------------------------------------
 class SinkhornResult:
-    __slots__ = ("r", "c", "iterations", "stopping_condition", "warned", "matrix_passes")
+    __slots__ = ("r", "c", "iterations", "stopping_condition", "warned", "matrix_passes", "launches")
 
 
 class _CudaSinkhornPasses:
     """The per-rank kernels behind sk_driver.sinkhorn_driver: one row block of P = X / vmax."""
 
-    def __init__(self, X, vmax, epsilon):
+    def __init__(self, X, vmax, epsilon, symmetric=False):
         _dev(X)
         self.L = _lib.lib()
         self.X, self.vmax, self.eps = X, float(vmax), float(epsilon)
         self.nrows, self.n = X.shape
         self.dt = _dtype_code(X)
         f64 = dict(dtype=torch.float64, device=X.device)
-        self.nchunks = self.L.hc_sk_num_row_chunks(self.nrows)
+        # symmetric P, whole matrix on this rank: both matvecs read the upper triangle only
+        self.sym = bool(symmetric) and self.nrows == self.n
+        self.nchunks = self.L.hc_sk_sym_num_blocks(self.n) if self.sym else self.L.hc_sk_num_row_chunks(self.nrows)
         self.ypart = torch.empty((self.nchunks, self.n), **f64)
         self.y, self.c, self.c_new = (torch.empty(self.n, **f64) for _ in range(3))
         self.x, self.r = torch.empty(self.nrows, **f64), torch.empty(self.nrows, **f64)
         self.flags = torch.zeros(8, dtype=torch.int32, device=X.device)
         self.outside = torch.zeros(1, dtype=torch.int32, device=X.device)
         self.s = _stream()
-        self.matrix_passes = 0   # full reads of the row block
+        self.matrix_passes = 0   # full reads of the row block (a symmetric pass counts (nb+1)/(2 nb))
+        self.launches = 0
+
+    def _sympass(self, v, y, r=None, check=False):
+        L = self.L
+        self.matrix_passes += (self.nchunks + 1) / (2.0 * self.nchunks)
+        self.launches += 2
+        _lib.check(L.hc_sk_sympass(_ptr(self.X), self.dt, self.n, self.vmax, _ptr(v) if v is not None else None,
+                                   _ptr(self.ypart), _ptr(self.flags) if check else None, self.s))
+        _lib.check(L.hc_sk_symfinish(_ptr(self.ypart), self.n, _ptr(y), _ptr(r) if r is not None else None,
+                                     _ptr(self.flags), self.s))
 
     def colpass(self, use_r, check=False):
         """y_local = P_block^T r (r = ones when use_r is False); returns the tensor to all-reduce"""
+        if self.sym:
+            self._sympass(self.r if use_r else None, self.y, check=check)
+            return self.y
         L = self.L
         self.matrix_passes += 1
+        self.launches += 2
         _lib.check(L.hc_sk_colpass(_ptr(self.X), self.dt, self.nrows, self.n, self.vmax,
                                    _ptr(self.r) if use_r else None, _ptr(self.ypart),
                                    _ptr(self.flags) if check else None, self.s))
@@ -189,6 +205,7 @@ class _CudaSinkhornPasses:
 
     def update_c(self, test):
         """c = 1/y; with test=True first evaluates the column-sum test on c*y -> True if outside"""
+        self.launches += 1
         if test:
             self.flags[3] = 0
             _lib.check(self.L.hc_sk_update_c(_ptr(self.y), _ptr(self.c), self.n, self.eps, _ptr(self.c_new),
@@ -206,10 +223,12 @@ class _CudaSinkhornPasses:
         all-reduced when sharded, so every rank decides alike), and only if none of them is outside 1 +- eps
         does the row-sum pass over the matrix have to run (never for an unnormalised contact matrix)."""
         L = self.L
+        self.launches += 1
         _lib.check(L.hc_sk_outside(_ptr(self.y), self.n, self.eps, _ptr(self.outside), self.s))
-        if bool(self.outside.item()):
+        if self.sym or bool(self.outside.item()):     # symmetric: the row sums ARE the column sums
             return self.outside
         self.matrix_passes += 1
+        self.launches += 2
         _lib.check(L.hc_sk_rowpass(_ptr(self.X), self.dt, self.nrows, self.n, self.vmax, None, _ptr(self.x), None,
                                    _ptr(self.flags), self.s))
         self.flags[4] = 0
@@ -218,7 +237,11 @@ class _CudaSinkhornPasses:
 
     def rowpass(self):
         """r = 1/(P_block c)"""
+        if self.sym:
+            self._sympass(self.c, self.x, self.r)
+            return
         self.matrix_passes += 1
+        self.launches += 1
         _lib.check(self.L.hc_sk_rowpass(_ptr(self.X), self.dt, self.nrows, self.n, self.vmax, _ptr(self.c),
                                         _ptr(self.x), _ptr(self.r), _ptr(self.flags), self.s))
 
@@ -230,19 +253,20 @@ class _CudaSinkhornPasses:
         return bool(t.item())
 
 
-def sinkhorn_fit(X, vmax=1.0, max_iter=1000, epsilon=1e-3, iterations0=0, allreduce=None):
+def sinkhorn_fit(X, vmax=1.0, max_iter=1000, epsilon=1e-3, iterations0=0, allreduce=None, symmetric=False):
     """Sinkhorn-Knopp scaling vectors for P = X / vmax (sinkhorn_knopp.py:93-163).
 
     X: (nrows, n) CUDA float32/float64 row block (the whole matrix when not sharded).
     ``allreduce(t)`` sums a tensor over ranks in place (row-sharded use: the float64 column-sum
     vector once per column pass).  ``iterations0`` is SinkhornKnopp._iterations carried over from
-    earlier fits (:150-152)."""
+    earlier fits (:150-152).  ``symmetric=True`` is the caller's promise that X == X.T bitwise (the folded
+    contact matrix): the whole-matrix fit then reads the upper triangle only."""
     from .sk_driver import sinkhorn_driver
-    passes = _CudaSinkhornPasses(X, vmax, epsilon)
+    passes = _CudaSinkhornPasses(X, vmax, epsilon, symmetric)
     iterations, stop, warned = sinkhorn_driver(passes, max_iter, iterations0, allreduce)
     res = SinkhornResult()
     res.r, res.c, res.iterations, res.stopping_condition, res.warned = passes.r, passes.c, iterations, stop, warned
-    res.matrix_passes = passes.matrix_passes
+    res.matrix_passes, res.launches = passes.matrix_passes, passes.launches
     return res
 
 

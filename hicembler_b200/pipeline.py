@@ -53,10 +53,10 @@ def pairs_to_dendrogram(records, offsets, window_bp, n_windows, mapq=10, params=
         S1, vmax = ops.fold_counts(counts, "sym", add=1.0, inplace=True)
         t.mark("fold")
         vm = float(vmax.item())
-        res = ops.sinkhorn_fit(S1, vm, max_iter, epsilon)
+        res = ops.sinkhorn_fit(S1, vm, max_iter, epsilon, symmetric=True)   # S1 = d + d.T
         t.mark("sinkhorn")
         out.update(r=res.r, c=res.c, sk_iterations=res.iterations, sk_stop=res.stopping_condition, vmax=vm,
-                   sk_passes=res.matrix_passes)
+                   sk_passes=res.matrix_passes, sk_launches=res.launches)
         def make_working():
             return ops.transform_to_working(S1, ops.KIND_POWER, a, b, res.r, res.c, vm, square=(method == "ward"))
         sym = S1

@@ -26,11 +26,12 @@ class SinkhornKnopp:
         self._D1 = np.ones(1)
         self._D2 = np.ones(1)
 
-    def fit_device(self, X, vmax=1.0, out_dtype=torch.float64, materialize=True, allreduce=None):
+    def fit_device(self, X, vmax=1.0, out_dtype=torch.float64, materialize=True, allreduce=None, symmetric=False):
         """Device-resident fit: X is a CUDA float32/float64 (row block of a) square matrix, P = X/vmax.
         Returns the balanced matrix as a CUDA tensor (or None when ``materialize`` is False); the
-        scaling vectors stay available as ``self._r`` / ``self._c`` (CUDA float64)."""
-        res = ops.sinkhorn_fit(X, vmax, self._max_iter, self._epsilon, self._iterations, allreduce)
+        scaling vectors stay available as ``self._r`` / ``self._c`` (CUDA float64).  ``symmetric=True``: the
+        caller knows X == X.T bitwise; the passes then read the upper triangle only."""
+        res = ops.sinkhorn_fit(X, vmax, self._max_iter, self._epsilon, self._iterations, allreduce, symmetric)
         self._iterations = res.iterations
         # sticky, as in the reference (:154-157): only the first non-None value survives
         if res.stopping_condition == "max_iter":

@@ -153,7 +153,14 @@ int hc_contig_normalize(const uint32_t *counts, int32_t n, const int32_t *sizes,
  *   hc_sk_rowpass : x[i] = sum_j P[i][j]*c[j]  (c NULL = ones); r[i] = 1/x[i] if r != NULL
  *   hc_sk_apply   : out[i][j] = (r[i]*P[i][j])*c[j]   (out dtype 0 = f32, 1 = f64)
  * Row-sharded use: every rank runs colpass+colfinish on its block, all-reduces y (NCCL sum), then
- * update_c / rowpass locally. */
+ * update_c / rowpass locally.
+ * Symmetric P (the folded contact matrix d + d.T of bam2clusters.py:505-509 always is): both matvecs
+ * are y = P v and read the upper triangle of 256 x 256 tiles only (2 n^2 bytes instead of 4 n^2):
+ *   hc_sk_sympass  : part[b][k] = contribution of tile (min(K,b), max(K,b)) to y[k], k in block K
+ *                    (v NULL = ones; part holds hc_sk_sym_num_blocks(n) x n float64; d_flags != NULL
+ *                    also flags negative / NaN entries in d_flags[0])
+ *   hc_sk_symfinish: y[k] = sum_b part[b][k] in fixed order; if r != NULL: r = 1/y and
+ *                    d_flags[4] |= any(y == 0) */
 int32_t hc_sk_num_row_chunks(int32_t nrows);
 int hc_sk_colpass(const void *X, int dtype, int32_t nrows, int32_t n, double vmax,
                   const double *r, double *ypart, int32_t *d_flags, void *stream);
@@ -162,6 +169,14 @@ int hc_sk_update_c(const double *y, const double *c_prev, int32_t n, double eps,
                    int32_t *d_flags, void *stream);
 int hc_sk_rowpass(const void *X, int dtype, int32_t nrows, int32_t n, double vmax,
                   const double *c, double *x, double *r, int32_t *d_flags, void *stream);
+int32_t hc_sk_sym_num_blocks(int32_t n);
+int hc_sk_sympass(const void *X, int dtype, int32_t n, double vmax, const double *v, double *part,
+                  int32_t *d_flags, void *stream);
+int hc_sk_symfinish(const double *part, int32_t n, double *y, double *r, int32_t *d_flags, void *stream);
+/* Self-check of the hoisted-reciprocal form of P = X / vmax used by the float32 passes: every float of
+ * the binades [1,4) divided by each of the nb divisors d_b must equal the IEEE division bit for bit;
+ * *d_mismatches (device u64) receives the number of differences (expected 0). */
+int hc_selftest_scaled_division(const float *d_b, int32_t nb, unsigned long long *d_mismatches, void *stream);
 /* *d_flag |= any(v outside 1 +- eps): the first evaluation of the while test (:138-141) on raw P */
 int hc_sk_outside(const double *v, int32_t n, double eps, int32_t *d_flag, void *stream);
 int hc_sk_apply(const void *X, int dtype, int32_t nrows, int32_t n, double vmax, const double *r,

@@ -349,6 +349,86 @@ def test_normalize_medium_vs_oracle():
     assert np.allclose(res.r.cpu().numpy(), want_sk._r, rtol=1e-9) and np.allclose(res.c.cpu().numpy(), want_sk._c, rtol=1e-9)
 
 
+@pytest.mark.parametrize("n,dtype", [(1203, np.float32), (256, np.float32), (257, np.float32), (1022, np.float32),
+                                     (37, np.float64), (771, np.float64)])
+def test_sinkhorn_symmetric_pass(n, dtype):
+    """upper-triangle passes (hc_sk_sympass) against the general column / row passes and the oracle:
+    same iteration count and stopping condition, scaling vectors to rounding (different summation order)"""
+    from hicembler_b200 import ops
+    d = hic_like_counts(n, 21 + n).astype(dtype)
+    X = torch.from_numpy(d.copy()).cuda()
+    _, vmax = ops.symmetrize_(X, add=1.0)
+    assert torch.equal(X, X.T)
+    vm = float(vmax.item())
+    gen = ops.sinkhorn_fit(X, vm, 1000, 0.00001)
+    sym = ops.sinkhorn_fit(X, vm, 1000, 0.00001, symmetric=True)
+    assert sym.iterations == gen.iterations and sym.stopping_condition == gen.stopping_condition
+    nb = (n + 255) // 256
+    assert abs(sym.matrix_passes - gen.matrix_passes * (nb + 1) / (2.0 * nb)) < 1e-9
+    for a, b in ((sym.r, gen.r), (sym.c, gen.c)):
+        assert torch.allclose(a, b, rtol=1e-12, atol=0)
+    want_sk = O.SinkhornKnopp(max_iter=1000, epsilon=0.00001)
+    O.normalize(d.copy(), sk=want_sk, materialize=False)
+    assert sym.iterations == want_sk._iterations
+    assert np.allclose(sym.r.cpu().numpy(), want_sk._r, rtol=1e-9) and np.allclose(sym.c.cpu().numpy(), want_sk._c, rtol=1e-9)
+    # deterministic: the partial sums are combined in a fixed order
+    again = ops.sinkhorn_fit(X, vm, 1000, 0.00001, symmetric=True)
+    assert torch.equal(again.r, sym.r) and torch.equal(again.c, sym.c)
+
+
+def test_scaled_division_is_ieee():
+    """P = X / vmax with the reciprocal taken once (common.cuh ScaledDivF) must be the IEEE division bit for bit:
+    all 2^24 floats of two binades against 3000 divisors, then odd operands through the symmetric pass itself"""
+    from hicembler_b200 import _lib
+    L = _lib.lib()
+    rng = np.random.default_rng(11)
+    b = np.concatenate([
+        rng.integers(0x3F800000, 0x40000000, 2900, dtype=np.uint32).view(np.float32) * np.float32(2.0) ** rng.integers(-40, 40, 2900),
+        np.array([1, 2, 3, 7, 1.9999999, 1.0000001, 41, 50001, 2 ** 32, 4294967040.0, 1e-30, 1e30, 3e-39, 5e-18, 7e17,
+                  0.3333333, 16777215, 16777216, 0.99999994, 123456.79], dtype=np.float32)]).astype(np.float32)
+    d_b = torch.from_numpy(b).cuda()
+    bad = torch.zeros(1, dtype=torch.int64, device="cuda")
+    _lib.check(L.hc_selftest_scaled_division(d_b.data_ptr(), b.size, bad.data_ptr(), None))
+    torch.cuda.synchronize()
+    assert int(bad.item()) == 0
+    # through hc_sk_sympass: y = P e_j is column j of X / vmax exactly
+    n = 300
+    A = (rng.integers(0, 0x5F000000, (n, n), dtype=np.uint32).view(np.float32)).copy()   # subnormals up to 2^63
+    # (finite quotients only: 0 * inf would turn the unit-vector matvec into NaN)
+    A[rng.random((n, n)) < 0.1] = 0.0
+    A = np.triu(A) + np.triu(A, 1).T
+    X = torch.from_numpy(A).cuda()
+    nb = L.hc_sk_sym_num_blocks(n)
+    part = torch.empty((nb, n), dtype=torch.float64, device="cuda")
+    y = torch.empty(n, dtype=torch.float64, device="cuda")
+    for vmax in (3.0, 41.0, 1.0e-15, 7.0e29, 123456.79):
+        for j in (0, 17, 255, 256, 299):
+            v = torch.zeros(n, dtype=torch.float64, device="cuda")
+            v[j] = 1.0
+            _lib.check(L.hc_sk_sympass(X.data_ptr(), 0, n, vmax, v.data_ptr(), part.data_ptr(), None, None))
+            _lib.check(L.hc_sk_symfinish(part.data_ptr(), n, y.data_ptr(), None, None, None))
+            with np.errstate(over="ignore", under="ignore"):
+                want = (A[:, j] / np.float32(vmax)).astype(np.float64)
+            assert np.array_equal(y.cpu().numpy(), want), (vmax, j)
+
+
+def test_sinkhorn_symmetric_pass_flags():
+    from hicembler_b200 import ops
+    X = torch.ones((300, 300), dtype=torch.float32, device="cuda")
+    X[5, :] = 0
+    X[:, 5] = 0
+    with pytest.warns(UserWarning):
+        ops.sinkhorn_fit(X, 1.0, 10, 1e-3, symmetric=True)
+    X = torch.ones((300, 300), dtype=torch.float32, device="cuda")
+    X[299, 7] = X[7, 299] = -1.0
+    with pytest.raises(AssertionError):
+        ops.sinkhorn_fit(X, 1.0, 10, 1e-3, symmetric=True)
+    # an already doubly stochastic symmetric matrix: zero iterations
+    X = torch.full((512, 512), 1.0 / 512, dtype=torch.float64, device="cuda")
+    res = ops.sinkhorn_fit(X, 1.0, 10, 1e-3, symmetric=True)
+    assert res.iterations == 0 and res.stopping_condition == "epsilon"
+
+
 # ------------------------------------------------------------------------------------------
 # K6 transform
 # ------------------------------------------------------------------------------------------
