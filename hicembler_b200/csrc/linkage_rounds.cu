@@ -670,14 +670,16 @@ __global__ void __launch_bounds__(HEAVY_THREADS, MINB) kr_heavy(RArgs a) {
 }
 
 // ---- order-preserving compaction -----------------------------------------------------------------
-__global__ void __launch_bounds__(1024) kc_map(const int *role, int ncols, int *newidx, int *oldidx) {
+// drop_i: the i side of this round's pairs is dropped as well (kb_rebuild merges and compacts in one pass)
+__global__ void __launch_bounds__(1024) kc_map(const int *role, int ncols, int *newidx, int *oldidx, bool drop_i) {
     __shared__ int s_warp[32];
     __shared__ int s_base;
     if (threadIdx.x == 0) s_base = 0;
     __syncthreads();
     for (int c0 = 0; c0 < ncols; c0 += 1024) {
         const int c = c0 + threadIdx.x;
-        const bool live = c < ncols && role[c] != ROLE_DEAD;
+        const int rc = c < ncols ? role[c] : ROLE_DEAD;
+        const bool live = rc != ROLE_DEAD && !(drop_i && rc >= 0 && !(rc & 1));
         const unsigned m = __ballot_sync(0xffffffffu, live);
         if ((threadIdx.x & 31) == 0) s_warp[threadIdx.x >> 5] = __popc(m);
         __syncthreads();
@@ -721,6 +723,167 @@ __global__ void kc_cols(Cols o, Cols d, const int *newidx, const int *oldidx, in
     d.need[k] = o.need[c];
 }
 
+// ---- bulk round: merge + compact in ONE pass over the matrix ---------------------------------------
+// In the first rounds a fifth or more of all clusters merge at once: kr_light then touches nearly every
+// sector of every free row, kr_heavy streams two old rows per pair and scans the new one, and soon after
+// a compaction copies everything again.  kb_rebuild does the same arithmetic (same Lance-Williams calls on
+// the same operands: free x pair as kr_light, pair x free as phase A, pair x pair by the "lower j first"
+// rule of phase B) while it writes the NEXT matrix -- dead and retiring columns dropped, order preserved --
+// and takes every row's candidate list on the way: the old matrix is read once, the new one written once.
+//   desc[k] = {old column, its role, its size, old column of the pair's i side} of new column k, and the pair's
+//   m, s1, s2, as, at per NEW column in colp (kb_desc): all per-column data of a row pass are coalesced streams
+//   out of L2, only the i-side entries are gathers (they sit next to the j side for Hi-C shaped input).
+__global__ void kb_desc(Cols o, Cols d, const Pair *pairs, const int *oldidx, int nnew, int4 *desc, double *colp,
+                        long long cstride) {
+    const int k = blockIdx.x * blockDim.x + threadIdx.x;
+    if (k >= nnew) return;
+    const int c = oldidx[k], rc = o.role[c], sz = o.size[c];
+    int ci = c, nsz = sz;
+    if (rc >= 0) {
+        const Pair p = pairs[rc >> 1];
+        ci = p.i;
+        nsz = (int)(p.s1 + p.s2);
+        colp[k] = p.m;
+        colp[cstride + k] = p.s1;
+        colp[2 * cstride + k] = p.s2;
+        colp[3 * cstride + k] = p.as;
+        colp[4 * cstride + k] = p.at;
+    }
+    desc[k] = make_int4(c, rc, sz, ci);
+    d.role[k] = ROLE_FREE;
+    d.size[k] = nsz;
+    d.orig[k] = o.orig[c];
+}
+
+template <int METHOD>
+__global__ void __launch_bounds__(HEAVY_THREADS, 2) kb_rebuild(RArgs a, Cols d, const int4 *__restrict__ desc,
+                                                               const double *__restrict__ colp, long long cstride,
+                                                               double *__restrict__ Wn, long long stride_n, int nnew) {
+    const int lane = threadIdx.x & 31;
+    const int nwarps = (int)gridDim.x * (HEAVY_THREADS / 32), gwarp = (int)blockIdx.x * (HEAVY_THREADS / 32) + (threadIdx.x >> 5);
+    const double INF = __longlong_as_double(0x7ff0000000000000LL);
+    constexpr int U = 2;
+    constexpr bool NEED_S = METHOD == M_WARD, NEED_A = METHOD == M_AVERAGE;
+    for (int rn = gwarp; rn < nnew; rn += nwarps) {
+        const int4 dr = __ldg(desc + rn);
+        const bool prow = dr.y >= 0;
+        Pair p;
+        p.i = dr.w;
+        p.j = dr.x;
+        p.m = p.s1 = p.s2 = p.as = p.at = 0.0;
+        if (prow) {
+            p.m = __ldg(colp + rn); p.s1 = __ldg(colp + cstride + rn); p.s2 = __ldg(colp + 2 * cstride + rn);
+            p.as = __ldg(colp + 3 * cstride + rn); p.at = __ldg(colp + 4 * cstride + rn);
+        }
+        const double *Wj = a.W + (size_t)dr.x * a.stride;                  // the row itself / the j side of its pair
+        const double *Wi = a.W + (size_t)dr.w * a.stride;                  // the i side (pair rows only)
+        const double vR = (double)dr.z, ps = __dadd_rn(p.s1, p.s2);
+        double *dst = Wn + (size_t)rn * stride_n;
+        Min3 best;
+        best.init();
+        const int4 dummy = make_int4(dr.x, ROLE_FREE, 1, dr.x);
+        int4 dc[U];
+#pragma unroll
+        for (int u = 0; u < U; ++u) dc[u] = lane + 32 * u < nnew ? __ldg(desc + lane + 32 * u) : dummy;
+        for (int c0 = lane; c0 < nnew; c0 += 32 * U) {
+            double A[U], B[U], Ai[U], Bi[U], qm[U], qs1[U], qs2[U], qas[U], qat[U];
+#pragma unroll
+            for (int u = 0; u < U; ++u) {
+                const int c = c0 + 32 * u;
+                const bool pc = dc[u].y >= 0;
+                B[u] = __ldg(Wj + dc[u].x);
+                A[u] = prow ? __ldg(Wi + dc[u].x) : 0.0;
+                Bi[u] = pc ? __ldg(Wj + dc[u].w) : 0.0;
+                Ai[u] = pc && prow ? __ldg(Wi + dc[u].w) : 0.0;
+                qm[u] = qs1[u] = qs2[u] = qas[u] = qat[u] = 0.0;
+                if (pc) {
+                    if (NEED_S) { qm[u] = __ldg(colp + c); qs1[u] = __ldg(colp + cstride + c); qs2[u] = __ldg(colp + 2 * cstride + c); }
+                    if (NEED_A) { qas[u] = __ldg(colp + 3 * cstride + c); qat[u] = __ldg(colp + 4 * cstride + c); }
+                }
+            }
+            int4 dn[U];
+#pragma unroll
+            for (int u = 0; u < U; ++u) {
+                const int cn = c0 + 32 * (U + u);
+                dn[u] = cn < nnew ? __ldg(desc + cn) : dummy;
+            }
+#pragma unroll
+            for (int u = 0; u < U; ++u) {
+                const int c = c0 + 32 * u;
+                if (c < nnew) {
+                    const int rc = dc[u].y;
+                    double x;
+                    if (c == rn) x = INF;
+                    else if (rc < 0) x = prow ? lw(METHOD, A[u], B[u], p, (double)dc[u].z) : B[u];
+                    else {
+                        Pair pq;
+                        pq.i = dc[u].w; pq.j = dc[u].x;
+                        pq.m = qm[u]; pq.s1 = qs1[u]; pq.s2 = qs2[u]; pq.as = qas[u]; pq.at = qat[u];
+                        if (!prow) x = lw(METHOD, Bi[u], B[u], pq, vR);                 // as kr_light
+                        else {                                                          // as phase B of kr_heavy
+                            const double Aj = A[u], Bj = B[u];
+                            const bool pf = p.j < pq.j;  // p merges first
+                            Pair F, Sd;
+                            F.m = pf ? p.m : pq.m; F.s1 = pf ? p.s1 : pq.s1; F.s2 = pf ? p.s2 : pq.s2; F.as = pf ? p.as : pq.as; F.at = pf ? p.at : pq.at;
+                            Sd.m = pf ? pq.m : p.m; Sd.s1 = pf ? pq.s1 : p.s1; Sd.s2 = pf ? pq.s2 : p.s2; Sd.as = pf ? pq.as : p.as; Sd.at = pf ? pq.at : p.at;
+                            F.i = F.j = Sd.i = Sd.j = 0;
+                            const double t1 = lw(METHOD, Ai[u], pf ? Bi[u] : Aj, F, pf ? pq.s1 : p.s1);
+                            const double t2 = lw(METHOD, pf ? Aj : Bi[u], Bj, F, pf ? pq.s2 : p.s2);
+                            x = lw(METHOD, t1, t2, Sd, pf ? ps : __dadd_rn(pq.s1, pq.s2));
+                        }
+                    }
+                    dst[c] = x;
+                    if (c != rn) best.push(x, c);
+                }
+            }
+#pragma unroll
+            for (int u = 0; u < U; ++u) dc[u] = dn[u];
+        }
+        unsigned long long key, bound;
+        int idx;
+        warp_select(dkey(best.m1), best.i1, dkey(best.m2), best.i2, dkey(best.m3), key, idx, bound);
+        const size_t base = (size_t)rn * LC;
+        const unsigned long long last = __shfl_sync(0xffffffffu, key, KC);
+        const unsigned long long lb = bound < last ? bound : last;
+        if (lane < KC) {
+            const bool keep = idx != INT_MAX && key <= lb;
+            d.cval[base + lane] = keep ? dunkey(key) : INF;
+            d.cidx[base + lane] = keep ? idx : -1;
+        }
+        if (lane == KC) {
+            d.cval[base + KC] = dunkey(lb);
+            d.cidx[base + KC] = -1;   // (unused slot, but kc_cols copies it)
+        }
+        if (lane == 0) {
+            d.fresh[rn] = 1;
+            d.need[rn] = 0;
+        }
+    }
+}
+
+// closes a bulk round like the last CTA of kr_heavy does
+__global__ void kb_retire(RArgs a, int nnew) {
+    RState *st = a.st;
+    const int P = st->P;
+    const unsigned long long nfree = (unsigned long long)(nnew - P), oldcols = (unsigned long long)st->nactive;
+    st->stats[0] += nfree;
+    st->stats[1] += nfree * oldcols;
+    st->stats[2] += (unsigned long long)P;
+    st->stats[3] += (unsigned long long)P * oldcols;
+    st->stats[4] += nfree * (unsigned long long)P;
+    st->n_done += P;
+    st->nactive -= P;
+    st->stats[5] += st->deferred;
+    if (st->n_done >= a.n - 1) st->done = 1;
+    else if (st->ambiguous && !a.diag) st->done = 1;
+    st->last_P = P;
+    st->last_q = nnew - P;
+    st->P = 0;
+    st->qlen = 0;
+    st->deferred = 0;
+    st->round += 1;
+}
+
 struct Layout {
     RState *st;
     Pair *pairs;
@@ -731,10 +894,13 @@ struct Layout {
     size_t spare_elems;
     Part *parts;
     int *seg_done;
+    int4 *desc;
+    double *colp;   // [5][n]: m, s1, s2, as, at of the pair behind a new column
 };
 
+// second matrix buffer: a compaction halves the columns, a bulk round (>= 1/5 of the columns merge) keeps <= 4/5
 size_t spare_elems_for(int n) {
-    const size_t h = (size_t)n / 2 + 1;
+    const size_t h = (size_t)n * 4 / 5 + 2;
     return h * h;
 }
 
@@ -759,6 +925,8 @@ bool carve(void *workspace, size_t bytes, int n, Layout &L) {
     }
     L.parts = ws.take<Part>((size_t)n * MAX_SEGS);
     L.seg_done = ws.take<int>(n);
+    L.desc = ws.take<int4>(n);
+    L.colp = ws.take<double>((size_t)n * 5);
     L.spare_elems = spare_elems_for(n);
     L.spare = ws.take<double>(L.spare_elems);
     return ws.ok();
@@ -770,7 +938,7 @@ extern "C" size_t hc_linkage_rounds_workspace_bytes(int32_t n) {
     if (n < 1) n = 1;
     size_t per_col = 4 * 5 + 8 + 2 * (4 * 3 + 12 * LC + 2);
     return 8192 + (size_t)n * per_col + ((size_t)n / 2 + 1) * sizeof(Pair) + 40 * 256 + spare_elems_for(n) * 8 +
-           (size_t)n * (MAX_SEGS * sizeof(Part) + 4) + 512;
+           (size_t)n * (MAX_SEGS * sizeof(Part) + 4 + 16 + 40) + 1024;
 }
 
 // W: n x n float64 full symmetric working matrix (squared distances for ward, +inf diagonal), destroyed.
@@ -911,6 +1079,63 @@ extern "C" int hc_linkage_rounds(double *W, int32_t n, int method, void *workspa
         fprintf(stderr, "[rounds trace] initial scan us %.1f\n", ms * 1e3f);
     }
     RState h;
+    // Bulk rounds: while a fifth or more of the columns merge in one round, merge and compact in one pass
+    // (kb_rebuild) instead of kr_light + kr_heavy + a later compaction.  The pair count is only known after
+    // kr_select, so these few rounds synchronise once each.  HC_ROUNDS_REBUILD=0 switches the path off.
+    int rebuild_min = 2048;  // columns: below this a round is launch latency, not traffic
+    if (const char *e = getenv("HC_ROUNDS_REBUILD")) rebuild_min = atoi(e) > 0 ? atoi(e) : INT_MAX;
+    long long rebuilds = 0;
+    while (a.ncols >= rebuild_min) {
+        if (trace) cudaEventRecord(ev0, stream);
+        kmark(0);
+        kr_select<<<(a.ncols + 255) / 256, 256, 0, stream>>>(a);
+        kmark(-1);
+        HC_CHECK_LAUNCH();
+        HC_CUDA_OK(cudaMemcpyAsync(&h, L.st, sizeof h, cudaMemcpyDeviceToHost, stream));
+        HC_CUDA_OK(cudaStreamSynchronize(stream));
+        const int nnew = h.nactive - h.P;
+        const long long stride_new = (nnew + 1) & ~1;
+        const bool bulk = !h.done && !h.ambiguous && (long long)h.P * 5 >= a.ncols && nnew >= 2 &&
+                          (in_spare || (size_t)nnew * stride_new <= L.spare_elems);
+        if (!bulk) {            // finish this round the ordinary way and go on in batches
+            light_heavy();
+            HC_CHECK_LAUNCH();
+            break;
+        }
+        double *dst = in_spare ? W : L.spare;
+        kmark(3);
+        kc_map<<<1, 1024, 0, stream>>>(a.c.role, a.ncols, L.newidx, L.oldidx, true);
+        kb_desc<<<(nnew + 255) / 256, 256, 0, stream>>>(a.c, L.cols[cur ^ 1], a.pairs, L.oldidx, nnew, L.desc, L.colp, n);
+        kmark(2);
+        {
+            const int rg = sms * 8;
+            const Cols dc = L.cols[cur ^ 1];
+            switch (method) {
+            case M_SINGLE: kb_rebuild<M_SINGLE><<<rg, HEAVY_THREADS, 0, stream>>>(a, dc, L.desc, L.colp, n, dst, stride_new, nnew); break;
+            case M_COMPLETE: kb_rebuild<M_COMPLETE><<<rg, HEAVY_THREADS, 0, stream>>>(a, dc, L.desc, L.colp, n, dst, stride_new, nnew); break;
+            case M_AVERAGE: kb_rebuild<M_AVERAGE><<<rg, HEAVY_THREADS, 0, stream>>>(a, dc, L.desc, L.colp, n, dst, stride_new, nnew); break;
+            case M_WEIGHTED: kb_rebuild<M_WEIGHTED><<<rg, HEAVY_THREADS, 0, stream>>>(a, dc, L.desc, L.colp, n, dst, stride_new, nnew); break;
+            default: kb_rebuild<M_WARD><<<rg, HEAVY_THREADS, 0, stream>>>(a, dc, L.desc, L.colp, n, dst, stride_new, nnew); break;
+            }
+        }
+        kmark(-1);
+        kb_retire<<<1, 1, 0, stream>>>(a, nnew);
+        HC_CHECK_LAUNCH();
+        if (trace) {
+            cudaEventRecord(ev1, stream);
+            cudaEventSynchronize(ev1);
+            float ms = 0;
+            cudaEventElapsedTime(&ms, ev0, ev1);
+            fprintf(stderr, "[rounds trace] bulk round pairs %d ncols %d -> %d us %.1f\n", h.P, a.ncols, nnew, ms * 1e3f);
+        }
+        cur ^= 1;
+        in_spare = !in_spare;
+        a.c = L.cols[cur];
+        a.W = dst;
+        a.stride = stride_new;
+        a.ncols = nnew;
+        rebuilds++;
+    }
     for (;;) {
         if (trace) cudaEventRecord(ev0, stream);
         // (instantiating a graph costs ~0.1 ms: only worth it for the long epochs of big problems)
@@ -937,7 +1162,7 @@ extern "C" int hc_linkage_rounds(double *W, int32_t n, int method, void *workspa
             HC_REQUIRE(in_spare || (size_t)nnew * stride_new <= L.spare_elems, "compaction buffer too small");
             if (trace) cudaEventRecord(ev0, stream);
             kmark(3);
-            kc_map<<<1, 1024, 0, stream>>>(a.c.role, a.ncols, L.newidx, L.oldidx);
+            kc_map<<<1, 1024, 0, stream>>>(a.c.role, a.ncols, L.newidx, L.oldidx, false);
             kc_gather<<<nnew < sms * 8 ? nnew : sms * 8, 256, 0, stream>>>(a.W, a.stride, dst, stride_new, L.oldidx, nnew);
             kc_cols<<<(nnew + 255) / 256, 256, 0, stream>>>(a.c, L.cols[cur ^ 1], L.newidx, L.oldidx, nnew);
             kmark(-1);
@@ -996,7 +1221,7 @@ extern "C" int hc_linkage_rounds(double *W, int32_t n, int method, void *workspa
         h_stats[3] = (int64_t)h.stats[1];
         h_stats[4] = (int64_t)h.stats[3];
         h_stats[5] = (int64_t)h.stats[4];
-        h_stats[6] = compactions;
+        h_stats[6] = compactions + rebuilds;
         h_stats[7] = near;
         h_stats[8] = (int64_t)h.stats[6];
         h_stats[9] = (int64_t)h.stats[5];

@@ -590,7 +590,8 @@ def test_linkage_rounds_hic_balanced_matrix(method):
 
 
 @pytest.mark.parametrize("env", [{}, {"HC_ROUNDS_NOCOMPACT": "1"}, {"HC_ROUNDS_BATCH": "1"}, {"HC_ROUNDS_BULK_SEGS": "32"},
-                                 {"HC_ROUNDS_KTIME": "1"}, {"HC_ROUNDS_TRACE": "1"}])
+                                 {"HC_ROUNDS_KTIME": "1"}, {"HC_ROUNDS_TRACE": "1"}, {"HC_ROUNDS_REBUILD": "16"},
+                                 {"HC_ROUNDS_REBUILD": "0"}])
 def test_linkage_rounds_compaction_and_batching_do_not_change_results(env, monkeypatch):
     from hicembler_b200 import ops
     n = 1200
@@ -608,6 +609,39 @@ def test_linkage_rounds_compaction_and_batching_do_not_change_results(env, monke
         test_linkage_rounds_compaction_and_batching_do_not_change_results._ref = Z
     else:
         assert np.array_equal(Z, ref)    # bit-identical across compaction / batching settings
+
+
+@pytest.mark.parametrize("method", ["ward", "average", "single", "complete", "weighted"])
+@pytest.mark.parametrize("n", [40, 257, 1000, 3001])
+def test_linkage_rounds_bulk_rebuild(n, method, monkeypatch):
+    """bulk rounds (a fifth or more of the columns merge): merge + compact in one pass (kb_rebuild) must give
+    the very same records as kr_light + kr_heavy, and fastcluster's tree"""
+    from hicembler_b200 import ops
+    y = np.random.default_rng(2000 + n).random(n * (n - 1) // 2) + 0.05
+    out = {}
+    for flag in ("0", "16"):
+        monkeypatch.setenv("HC_ROUNDS_REBUILD", flag)
+        W, flags = ops.expand_condensed(torch.from_numpy(y).cuda(), n, square=(method == "ward"))
+        Z, st = ops.linkage_rounds(W, method, nan_flags=flags)
+        assert Z is not None and st["certified"], st
+        out[flag] = (Z, st)
+    assert np.array_equal(out["0"][0], out["16"][0])
+    assert out["16"][1]["rounds"] == out["0"][1]["rounds"] and out["16"][1]["compactions"] >= 1
+    _same_tree(out["16"][0], O.linkage_fastcluster(y, method), rtol=1e-12)
+
+
+def test_linkage_rounds_bulk_rebuild_hic(monkeypatch):
+    from hicembler_b200 import ops
+    n = 2600
+    d = O.symmetrize(hic_like_counts(n, 11, scale=6.0).astype(np.float64))
+    bal = O.normalize(np.triu(d).copy())
+    y = O.condense(O.distance_func(bal + 1, 0.5, 1.1))
+    want = O.linkage_fastcluster(y, "ward")
+    monkeypatch.setenv("HC_ROUNDS_REBUILD", "64")
+    W, flags = ops.expand_condensed(torch.from_numpy(y).cuda(), n, square=True)
+    Z, st = ops.linkage_rounds(W, "ward", nan_flags=flags)
+    assert Z is not None, st
+    _same_tree(Z, want, rtol=1e-11)
 
 
 def test_linkage_rounds_refuses_ties_and_auto_falls_back():
