@@ -289,7 +289,8 @@ def run_ours(args, cfg, rank, world, local_rank):
                                              "linkage": "kr_light+kr_heavy" if lst.get("engine") == "rounds" else "k_nnchain"}[dominant],
                      peak_source=peak_src)
     if dominant == "linkage" and lst.get("engine") == "rounds" and kernel_us and kernel_us.get("heavy"):
-        # dominant KERNEL = kr_heavy (merged-row builds + exact rescans + the initial scan): all its launches of one
+        # dominant KERNEL = kr_heavy (merged-row builds + exact rescans + the initial scan) with kb_rebuild, the same
+        # work done as one merge+compact pass in the bulk rounds: all their launches of one
         # step; achieved = algorithmic bytes of those launches / their summed CUDA-event durations
         heavy_ms = (kernel_us["heavy"] + kernel_us["initial_scan"]) * 1e-3
         b = 8.0 * lst["rescan_cols"] + 24.0 * lst["build_cols"]
@@ -298,7 +299,7 @@ def run_ours(args, cfg, rank, world, local_rank):
         ncu = NCU_TRAFFIC.get(args.config, {}).get("kr_heavy")
         main_roof = {"bound": "hbm", "achieved": a_, "peak": peak, "unit": "GB/s", "frac": a_ / peak,
                      "traffic": (ncu["dram_bytes"] / ncu["launches"]) if ncu else None,
-                     "kernel": "kr_heavy", "launches_per_step": launches, "ms": heavy_ms,
+                     "kernel": "kr_heavy+kb_rebuild", "launches_per_step": launches, "ms": heavy_ms,
                      "avg_launch_us": heavy_ms * 1e3 / launches, "algorithmic_bytes": b,
                      "algorithmic_bytes_per_launch": b / launches, "share_of_step": heavy_ms / (ms_dev / K),
                      "peak_source": peak_src,
@@ -307,7 +308,7 @@ def run_ours(args, cfg, rank, world, local_rank):
                              "and the initial scan move most of the bytes, see profiles/" % lst["rounds"]}
     # launches per step: bin 8, fold 1, sinkhorn (colpass+finish)=2/pass ... counted from the call graph
     sk_launches = 0 if args.no_balance else res["sk_launches"]      # counted by ops._CudaSinkhornPasses
-    link_launches = (3 + 3 * 8 * ((lst["rounds"] + 7) // 8) + 3 * lst["compactions"]) if lst.get("engine") == "rounds" else 1
+    link_launches = lst["launches"] if lst.get("engine") == "rounds" else 1     # counted by hc_linkage_rounds
     gpu_launches = K * 2 * (8 + 1 + sk_launches + 1 + link_launches) + (K if args.wire == 16 else 0)  # + unpack
     cpu = None
     if world == 1 and not args.no_cpu_baseline:

@@ -364,7 +364,7 @@ def linkage_rounds(W, method="ward", nan_flags=None, workspace=None):
               build_cols=stats[4], light_updates=stats[5], compactions=stats[6], near_tied_heights=stats[7],
               pending_near_ties=stats[8], deferred_rescans=stats[9],
               kernel_us=dict(select=stats[10], light=stats[11], heavy=stats[12], compaction=stats[13],
-                             initial_scan=stats[14]),
+                             initial_scan=stats[14]), launches=stats[15],
               certified=(rc == _lib.HC_OK))
     if rc == _lib.HC_EAMBIGUOUS:
         st["reason"] = _lib.last_error()

@@ -237,7 +237,9 @@ int hc_linkage_finish(int32_t n, int method, void *workspace, size_t workspace_b
  * h_stats[16]: rounds, merges, rescans, sum live columns over rescans, sum live columns over merged-row
  * builds, row x pair updates, compactions, near-tied heights, pending near-tie observations, pairs
  * deferred for an exact rescan; [10..14] microseconds per kernel (select, light, heavy, compaction, initial
- * scan) when HC_ROUNDS_KTIME is set, else 0; [15] unused. */
+ * scan; a bulk round's merge+compact pass counts as heavy) when HC_ROUNDS_KTIME is set, else 0; [15] kernels
+ * launched.  Bulk rounds (a fifth or more of the columns merge) are done as one merge+compact pass over the
+ * matrix and count as a compaction; HC_ROUNDS_REBUILD=0 switches that path off. */
 size_t hc_linkage_rounds_workspace_bytes(int32_t n);
 int hc_linkage_rounds(double *W, int32_t n, int method, void *workspace, size_t workspace_bytes,
                       double *h_Z, int64_t *h_stats, void *stream);
