@@ -286,6 +286,88 @@ def contact_func(x, a, b):
 
 
 # ---------------------------------------------------------------------------------------------
+# distance-decay fit (host side: a few thousand numbers; the matrices behind it come from K1)
+# ---------------------------------------------------------------------------------------------
+def get_distances_contacts(bam, mapq, contig2size, windowSize, icontigs=5, upto=1e7, names=None):
+    """Return contacts grouped by genomic distance for the longest contigs -- bam2clusters.py:257-288.
+
+    One intra-contig matrix per contig is binned on the GPU (``bam2arrays`` with ``regions=[c]``,
+    :273); the per-distance groups are the matrix diagonals.  The reference's double loop (:281-286)
+    visits offsets 0..n-2 of the leading (n-1) x (n-1) block, so distance 0 holds the diagonal
+    twice (:279 and j == i) and distances are ``k*windowSize // 1000`` (Python-2 integer division)."""
+    logger(" Estimating distance parameters...")
+    d2c = {0: []}
+    longest_contigs = sorted(contig2size, key=lambda c: contig2size[c], reverse=True)
+    maxdist = 0.75 * contig2size[longest_contigs[0]] / 1000.
+    bam = [Alignments.load(b, names) for b in bam]
+    for c in longest_contigs[:icontigs]:
+        n = contig2size[c] // windowSize + 1
+        d = bam2arrays([range(n)], [windowSize], [{c: 0}], bam, mapq, upto=int(upto), regions=[c], verbose=0)[0]
+        d += d.T - np.diag(d.diagonal())
+        d2c[0].append(d.diagonal()[:n - 1])
+        m = n - 1  # len(positions)
+        blk = d[:m, :m]
+        for k in range(m):
+            # rows i = 0..m-2 only (:281): offset k has m-k cells, the last of them (i = m-1) only for k = 0
+            diag = blk.diagonal(k)
+            diag = diag[:m - 1] if k == 0 else diag
+            if len(diag):
+                d2c.setdefault(k * windowSize // 1000, []).append(diag)
+    dists = np.array([x for x in sorted(d2c) if x < maxdist])
+    contacts = [np.concatenate(d2c[x]) if len(d2c[x]) else np.empty(0, dtype=np.float32) for x in dists]
+    return dists, contacts
+
+
+def _insert_size_profile(contig2size, windowSize, c2dists, limit, contigs):
+    """x / yn / dists / contacts of bam2clusters.py:304-330 from the insert sizes bam2array collects
+    (abs(TLEN), -1 for mates on another contig).  Bins are visited in ascending order: CPython 2's
+    ``Counter.iteritems()`` order for small-int keys once the table outgrows the largest key."""
+    edges = np.arange(-windowSize, (limit + 11) * windowSize, windowSize)
+    nb = len(edges) + 1
+    per_bin = [[] for _ in range(nb)]
+    x, yn = [], []
+    if contigs:
+        contig2size = {c: s for c, s in contig2size.items() if c in contigs}
+    for c in sorted(contig2size, key=lambda c: contig2size[c], reverse=True)[:50]:
+        v = np.asarray(c2dists[c], dtype=np.int64)
+        if not v.max():  # ValueError on an empty list, like max([]) at :308
+            continue
+        hist = np.bincount(np.searchsorted(edges, v, side="left"), minlength=nb)
+        total = int(v.sum())
+        for b in np.flatnonzero(hist):
+            nc = 1e6 * int(hist[b]) / total
+            per_bin[b - 1].append(nc)
+            x.append(edges[b - 1] / 1000.)
+            yn.append(nc)
+    keep = [(e / 1000., cs) for e, cs in zip(edges[1:-1], per_bin[1:-1]) if cs]
+    return x, yn, [e for e, _ in keep][:limit], [cs for _, cs in keep][:limit]
+
+
+def estimate_distance_parameters(outbase, bam=None, mapq=10, contig2size=None, windowSize=2000,
+                                 skipfirst=5, icontigs=5, c2dists={}, limit=30, upto=1e7, contigs=[]):
+    """Return estimated fit parameters (a, b) of contact_func -- bam2clusters.py:290-358.
+
+    ``bam``, ``contig2size`` & ``windowSize`` or ``c2dists`` have to be provided.  The boxplot / fit
+    figures (:326-335,350-356) are left out (no graphics stack on this box); ``outbase +
+    ".distance.params"`` is written like :346-348."""
+    from scipy.optimize import curve_fit
+    x, yn = [], []
+    if bam and not c2dists:
+        dists, contacts = get_distances_contacts(bam, mapq, contig2size, windowSize, icontigs, upto)
+        dists, contacts = dists[:limit], contacts[:limit]
+    else:
+        logger(" Estimating distance parameters...")
+        x, yn, dists, contacts = _insert_size_profile(contig2size, windowSize, c2dists, limit, contigs)
+    if not x:
+        x, yn = dists, np.array([np.median(c) for c in contacts])
+    params, pcov = curve_fit(contact_func, x[skipfirst:], yn[skipfirst:], maxfev=1000)
+    if outbase:
+        with open(outbase + ".distance.params", "wb") as out:
+            pickle.dump(params, out)
+    return params
+
+
+# ---------------------------------------------------------------------------------------------
 # K6-K7: tree
 # ---------------------------------------------------------------------------------------------
 class HCTree:
@@ -403,4 +485,66 @@ def cluster_contigs(outbase, d, bin_chr, bin_position, threads=4, frac=0.66, ite
         clusters[i].append(c)
     if return_details:
         return clusters, nchr, Z, mean_step_len
+    return clusters
+
+
+def bam2clusters(bam, fasta, outdir, minSize=2000, mapq=10, threads=4, dpi=100, upto=0, nchr=0,
+                 verbose=1, minchr=3, method="ward", contigs=[], selections=None):
+    """Return clusters computed from the contig-level contact matrix -- bam2clusters.py:459-537.
+
+    Same files as the reference under ``outdir``: ``auto|chr_N`` + ``.windows.tab.gz``, ``.npz``,
+    ``.distance.params`` (cache, reused on the next call like :490-506) and ``.clusters.tab``.  The
+    matrix stays on the GPU from ``bam2array`` through symmetrisation (:511), the distance transform
+    (:516) and the 1 + 30 ward linkages of ``cluster_contigs``; ``selections`` is handed to
+    ``cluster_contigs`` (the reference draws from the unseeded global RNG).  Like the reference,
+    ``method`` is accepted and unused (cluster_contigs is ward only, :411)."""
+    logger("=== Clustering ===")
+    outbase = os.path.join(outdir, "chr_%s" % nchr if nchr else "auto")
+    # link with auto (:466-469)
+    if nchr and os.path.isfile(os.path.join(outdir, "auto.npz")) and not os.path.isfile(outbase + ".npz"):
+        logger(" reusing %s/auto.* ..." % outbase)
+        for ext in (".npz", ".windows.tab.gz", ".distance.params"):
+            if os.path.lexists(outbase + ext):
+                os.unlink(outbase + ext)
+            os.symlink("auto" + ext, outbase + ext)
+    # load clusters (:472-476)
+    fname = outbase + ".clusters.tab"
+    if os.path.isfile(fname):
+        clusters = [l[:-1].split('\t') for l in open(fname)]
+        logger("  %s clusters loaded from %s." % (len(clusters), fname))
+        return clusters
+    minSize, windows, chr2window, contig2size = contigs2windows(fasta, minSize, verbose, contigs=contigs)
+    bin_chr = np.array([c for c, s, e in windows])
+    bin_position = np.array([(s, e) for c, s, e in windows])
+    if not os.path.isfile(outbase + ".npz"):
+        logger("Parsing BAM...")
+        D, c2dists = bam2array(windows, contig2size, chr2window, bam, mapq, upto, threads=threads,
+                               minSize=minSize, device_out=True)
+        logger("Saving array...")
+        with gzip.open(outbase + ".windows.tab.gz", "wt") as out:
+            out.write("\n".join("\t".join(map(str, w)) for w in windows) + "\n")
+        with open(outbase + ".npz", "wb") as out:
+            np.savez_compressed(out, D.cpu().numpy())
+        params = estimate_distance_parameters(outbase, contig2size=contig2size, c2dists=c2dists,
+                                              windowSize=minSize, contigs=contigs)
+    else:
+        npy = np.load(outbase + ".npz")
+        D = torch.from_numpy(np.ascontiguousarray(npy[npy.files[0]], dtype=np.float64)).cuda()
+        with open(outbase + ".distance.params", "rb") as fh:
+            params = pickle.load(fh)
+    # make symmetric (:511) and get clusters on the transformed matrix (:516-522), all on the device
+    ops.symmetrize_(D)
+    dist = ops.transform(D, ops.KIND_POWER, float(params[0]), float(params[1]))
+    clusters = cluster_contigs(outbase, dist, bin_chr, bin_position, dpi=dpi, minchr=minchr, nchr=nchr,
+                               selections=selections)
+    # skip empty clusters (:525-535)
+    clusters = [c for c in clusters if c]
+    totsize = ncontigs = 0
+    logger("Reporting %s clusters to %s ..." % (len(clusters), fname))
+    with open(fname, "w") as out:
+        for cluster in clusters:
+            totsize += sum(contig2size[c] for c in cluster)
+            ncontigs += len(cluster)
+            out.write("\t".join(cluster) + "\n")
+    logger("  %3s bp in %s clusters generated from %s contigs." % (totsize, len(clusters), ncontigs))
     return clusters

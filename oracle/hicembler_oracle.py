@@ -645,3 +645,82 @@ def cluster_contigs(d, bin_chr, frac=0.66, iterations=30, maxnumchr=500, minchr=
     for i, c in zip(assignments - 1, bin_chr):
         clusters[i].append(c)
     return clusters, nchr, Z, mean_step_len
+
+
+# ---------------------------------------------------------------------------------------------
+# distance-decay fit and the bam2clusters() driver -- plots left out
+# ---------------------------------------------------------------------------------------------
+def get_distances_contacts(sam, mapq, contig2size, windowSize, icontigs=5, upto=1e7):
+    """bam2clusters.py:257-288.  ``sam`` = list of SAM line lists (one per BAM); the
+    ``regions=[c]`` query of :273 is restated as "read-1 reference is c".  Py2 traps: ``s /
+    windowSize`` (:268) and ``(positions[j]-positions[i]) / 1000`` (:283) are integer divisions;
+    ``sorted(contig2size, ...)`` (:262) is a stable sort of dict order -> callers pass an
+    ordered dict."""
+    d2c = {0: []}
+    longest_contigs = sorted(contig2size, key=lambda x: contig2size[x], reverse=True)
+    maxdist = 0.75 * contig2size[longest_contigs[0]] / 1000.
+    for c in longest_contigs[:icontigs]:
+        s = contig2size[c]
+        n = s // windowSize + 1
+        positions = list(range(windowSize, n * windowSize, windowSize))
+        arrays = [np.zeros((n, n), dtype='float32')]
+        chr2window = [{c: 0}]
+        sub = [[l for l in lines if l.split('\t')[2] == c] for lines in sam]
+        arrays = bam2arrays(arrays, [windowSize], chr2window, sub, mapq, upto=upto, verbose=0)
+        d = arrays[0]
+        d += d.T - np.diag(d.diagonal())
+        d2c[0] += [d[i][i] for i in range(d.shape[0] - 1)]
+        for i in range(len(positions) - 1):
+            for j in range(i, len(positions)):
+                dist = (positions[j] - positions[i]) // 1000
+                if dist not in d2c:
+                    d2c[dist] = []
+                d2c[dist].append(d[i][j])
+    dists = np.array([d for d in sorted(d2c) if d < maxdist])
+    contacts = [d2c[d] for d in dists]
+    return dists, contacts
+
+
+def distance_fit_inputs(contig2size=None, windowSize=2000, c2dists=None, limit=30, contigs=()):
+    """The x / yn / dists / contacts that bam2clusters.py:304-330 hands to curve_fit when insert
+    sizes are given.  ``Counter(...).iteritems()`` (:315) runs in ascending key order here: that is
+    CPython 2's order for small-int keys once the dict table is larger than the largest key."""
+    from collections import Counter
+    x, yn = [], []
+    dists = list(range(-windowSize, (limit + 11) * windowSize, windowSize))
+    contacts = [[] for i in range(len(dists) + 1)]
+    if contigs:
+        contig2size = {c: s for c, s in contig2size.items() if c in contigs}
+    longest_contigs = sorted(contig2size, key=lambda x: contig2size[x], reverse=True)[:50]
+    for c in longest_contigs:
+        maxc = max(c2dists[c])
+        if not maxc:
+            continue
+        for i, nc in sorted(Counter(np.digitize(c2dists[c], dists, right=True).tolist()).items()):
+            nc = 1e6 * nc / sum(c2dists[c])
+            contacts[i - 1].append(nc)
+            x.append(dists[i - 1] / 1000.)
+            yn.append(nc)
+    _dists, _contacts = dists[1:-1], contacts[1:-1]
+    dists, contacts = [], []
+    for d, c in zip(_dists, _contacts):
+        if c:
+            dists.append(d / 1000.)
+            contacts.append(c)
+    return x, yn, dists[:limit], contacts[:limit]
+
+
+def estimate_distance_parameters(sam=None, mapq=10, contig2size=None, windowSize=2000, skipfirst=5,
+                                 icontigs=5, c2dists=None, limit=30, upto=1e7, contigs=()):
+    """bam2clusters.py:290-358 without the figures and the pickle: returns ``params``."""
+    from scipy.optimize import curve_fit
+    x, yn = [], []
+    if sam and not c2dists:
+        dists, contacts = get_distances_contacts(sam, mapq, contig2size, windowSize, icontigs, upto)
+        dists, contacts = dists[:limit], contacts[:limit]
+    else:
+        x, yn, dists, contacts = distance_fit_inputs(contig2size, windowSize, c2dists, limit, contigs)
+    if not x:
+        x, yn = dists, np.array([np.median(c) for c in contacts])
+    params, pcov = curve_fit(contact_func, x[skipfirst:], yn[skipfirst:], maxfev=1000)
+    return params
