@@ -50,6 +50,35 @@ class FastaIndex(object):
         for seqid in self.id2stats:
             yield seqid
 
+    _RC = str.maketrans("ACGTacgt", "TGCAtgca")
+
+    def _scan_offsets(self):
+        """byte range of every record's sequence lines (one pass over the FASTA, cached)"""
+        self._seq_range = {}
+        name, begin, pos = None, 0, 0
+        with open(self.fasta, "rb") as f:
+            for line in f:
+                if line.startswith(b">"):
+                    if name is not None:
+                        self._seq_range[name] = (begin, pos)
+                    name, begin = line[1:].split()[0].decode(), pos + len(line)
+                pos += len(line)
+        if name is not None:
+            self._seq_range[name] = (begin, pos)
+
+    def get_sequence(self, contig, reverse=False):
+        """Return sequence of given contig, reverse-complemented if ``reverse`` -- FastaIndex.py:204-220
+        (A/C/G/T in both cases are complemented, every other symbol is kept)."""
+        if contig not in self.id2stats:
+            raise KeyError(contig)
+        if not hasattr(self, "_seq_range"):
+            self._scan_offsets()
+        begin, end = self._seq_range[contig]
+        with open(self.fasta, "rb") as f:
+            f.seek(begin)
+            seq = b"".join(f.read(end - begin).split()).decode()
+        return seq.translate(self._RC)[::-1] if reverse else seq
+
     def get_N_and_L(self, genomeFrac=0.5, return_L=False, genomeSize=None):
         """FastaIndex.py:304-325."""
         if not genomeSize:

@@ -57,6 +57,7 @@ SIGNATURES = {
     "hc_merges_to_linkage": (C.c_int, [_i32, C.c_int, _p, _p, _p, _p, C.c_double, _p]),
     "hc_segment_mean_2d": (C.c_int, [_p, _i32, _p, _p, _i32, _p, _p, _p]),
     "hc_normalize_rows": (C.c_int, [_p, _i32, _p, _sz, _p]),
+    "hc_block_sums4": (C.c_int, [_p, _i32, _p, _p, _p, _p, _i32, _p, _p]),
     "hc_unpack_pairs16": (C.c_int, [_p, C.c_int64, _p, _p]),
     "hc_bam_open": (C.c_int, [C.c_char_p, _i32, _p, _p, _p]),
     "hc_bam_next": (C.c_int, [_p, _i32, _p, C.c_int64, _p, _p, _p]),

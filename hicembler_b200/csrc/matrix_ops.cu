@@ -641,6 +641,48 @@ extern "C" int hc_segment_mean_2d(const float *A, int32_t n, const int32_t *seg_
     return HC_OK;
 }
 
+// join_scaffolds (bam2scaffolds.py:142-174): the four corner-block sums that decide how two scaffolds are
+// oriented.  One CTA per (job, corner); a job's windows are idx[off .. off+n1) (scaffold 1) followed by
+// idx[off+n1 .. off+n1+n2) (scaffold 2).  Rows: first n1/2 (corners 0,1) or last n1/2 (2,3) windows of
+// scaffold 1; columns: first n2/2 (0,2) or last n2/2 (1,3) windows of scaffold 2.  Sums are taken in double
+// in a fixed order (exact for count matrices).
+__global__ void __launch_bounds__(256) k_block_sums4(const float *A, int32_t n, const int32_t *idx,
+                                                      const int64_t *job_off, const int32_t *job_n1,
+                                                      const int32_t *job_n2, double *out) {
+    __shared__ double sh[8];
+    const int job = blockIdx.x >> 2, q = blockIdx.x & 3;
+    const int32_t n1 = job_n1[job], n2 = job_n2[job];
+    const int32_t *rows = idx + job_off[job], *cols = rows + n1;
+    const int32_t h = n1 / 2, w = n2 / 2;
+    if (q & 2) rows += n1 - h;
+    if (q & 1) cols += n2 - w;
+    double acc = 0.0;
+    const long long cells = (long long)h * w;
+    for (long long i = threadIdx.x; i < cells; i += blockDim.x) {
+        const int32_t r = (int32_t)(i / w), c = (int32_t)(i - (long long)r * w);
+        acc += (double)A[(size_t)rows[r] * n + cols[c]];
+    }
+    for (int o = 16; o; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
+    if ((threadIdx.x & 31) == 0) sh[threadIdx.x >> 5] = acc;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        double t = 0.0;
+        for (int k = 0; k < (int)(blockDim.x >> 5); ++k) t += sh[k];
+        out[blockIdx.x] = t;
+    }
+}
+
+extern "C" int hc_block_sums4(const float *A, int32_t n, const int32_t *idx, const int64_t *job_off,
+                              const int32_t *job_n1, const int32_t *job_n2, int32_t n_jobs, double *out,
+                              void *stream_) {
+    cudaStream_t stream = (cudaStream_t)stream_;
+    HC_REQUIRE(A && idx && job_off && job_n1 && job_n2 && out && n > 0 && n_jobs >= 0, "bad arguments");
+    if (n_jobs == 0) return HC_OK;
+    k_block_sums4<<<4 * n_jobs, 256, 0, stream>>>(A, n, idx, job_off, job_n1, job_n2, out);
+    HC_CHECK_LAUNCH();
+    return HC_OK;
+}
+
 extern "C" int hc_normalize_rows(float *A, int32_t n, void *workspace, size_t workspace_bytes, void *stream_) {
     cudaStream_t stream = (cudaStream_t)stream_;
     HC_REQUIRE(A && workspace && n > 0, "bad arguments");

@@ -437,6 +437,31 @@ def segment_mean_2d(A, seg_begin, seg_end):
     return out
 
 
+def block_sums4(A, jobs):
+    """Corner-block sums of join_scaffolds for a batch of independent joins: ``jobs`` = list of
+    (indices1, indices2) window lists into the symmetric float32 matrix ``A``.  Returns a (len(jobs), 4)
+    float64 numpy array (one launch, one D2H read)."""
+    _dev(A)
+    n = A.shape[0]
+    assert A.dtype == torch.float32 and A.shape == (n, n) and A.is_contiguous()
+    if not jobs:
+        return np.empty((0, 4))
+    n1 = np.array([len(a) for a, b in jobs], dtype=np.int32)
+    n2 = np.array([len(b) for a, b in jobs], dtype=np.int32)
+    tot = n1.astype(np.int64) + n2
+    off = np.concatenate([[0], np.cumsum(tot)[:-1]]).astype(np.int64)
+    flat = np.fromiter((i for a, b in jobs for part in (a, b) for i in part), dtype=np.int32, count=int(tot.sum()))
+    if flat.size and (flat.min() < 0 or flat.max() >= n):
+        raise IndexError("window index out of range")
+    dev = A.device
+    up = lambda a: torch.from_numpy(a).to(dev)
+    out = torch.empty((len(jobs), 4), dtype=torch.float64, device=dev)
+    idx = up(flat) if flat.size else torch.zeros(1, dtype=torch.int32, device=dev)
+    _lib.check(_lib.lib().hc_block_sums4(_ptr(A), n, _ptr(idx), _ptr(up(off)), _ptr(up(n1)), _ptr(up(n2)), len(jobs),
+                                         _ptr(out), _stream()))
+    return out.cpu().numpy()
+
+
 def unpack_pairs16(packed, out=None):
     """int32 [n, 4] CUDA tensor of hc_pair16_t -> int32 [n, 6] hc_pair_t records (csrc/bin_pairs.cu)."""
     _dev(packed)

@@ -263,6 +263,12 @@ int hc_merges_to_linkage(int32_t n, int ward, const int32_t *h_a, const int32_t 
 int hc_segment_mean_2d(const float *A, int32_t n, const int32_t *seg_begin, const int32_t *seg_end,
                        int32_t n_seg, float *tmp, float *out, void *stream);
 int hc_normalize_rows(float *A, int32_t n, void *workspace, size_t workspace_bytes, void *stream);
+/* hc_block_sums4: the corner-block sums of join_scaffolds (bam2scaffolds.py:155-161 = array2scaffolds.py:287-293),
+ *   batched over the independent joins of one tree level.  Job j: scaffold-1 windows idx[job_off[j] ..
+ *   +job_n1[j]), scaffold-2 windows right behind them (job_n2[j]); out[4*j + q], q = 0..3 in the reference's
+ *   order (start-start, start-end, end-start, end-end), float64.  A = symmetric float32 window matrix (n x n). */
+int hc_block_sums4(const float *A, int32_t n, const int32_t *idx, const int64_t *job_off, const int32_t *job_n1,
+                   const int32_t *job_n2, int32_t n_jobs, double *out, void *stream);
 
 /* Alternative normalisations of the symmetric matrix, dtype 0 = float32, 1 = float64.
  * hc_gather_square: out (m x m) = X[keep][:, keep], the zero-diagonal filter of normalize_diagional

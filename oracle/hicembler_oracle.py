@@ -724,3 +724,142 @@ def estimate_distance_parameters(sam=None, mapq=10, contig2size=None, windowSize
         x, yn = dists, np.array([np.median(c) for c in contacts])
     params, pcov = curve_fit(contact_func, x[skipfirst:], yn[skipfirst:], maxfev=1000)
     return params
+
+
+# ---------------------------------------------------------------------------------------------
+# scaffolding stage: bam2scaffolds.py:126-278,305-331 (= array2scaffolds.py:258-334)
+# ---------------------------------------------------------------------------------------------
+def get_reversed(scaffold):
+    """bam2scaffolds.py:126-128."""
+    return [(name, not orientation) for name, orientation in reversed(scaffold)]
+
+
+def get_indices(scaffold, contig2indices):
+    """bam2scaffolds.py:130-140."""
+    indices = []
+    for name, reverse in scaffold:
+        if name not in contig2indices:
+            continue
+        if reverse:
+            indices += reversed(contig2indices[name])
+        else:
+            indices += contig2indices[name]
+    return indices
+
+
+def join_scaffolds(scaffold1, scaffold2, d, contig2indices, minWindows=3):
+    """bam2scaffolds.py:142-174 (Py2 ``/`` on ints is ``//``)."""
+    indices1 = get_indices(scaffold1, contig2indices)
+    indices2 = get_indices(scaffold2, contig2indices)
+    if len(indices1) < len(indices2):
+        scaffold1, indices1, scaffold2, indices2 = scaffold2, indices2, scaffold1, indices1
+    if len(indices2) < minWindows:
+        if len(indices1) < minWindows:
+            return []
+        return scaffold1
+    _d = d[:, indices1 + indices2][indices1 + indices2, :]
+    n1, n2 = len(indices1), len(indices2)
+    i = n2 // 2
+    d1, d2 = _d[:n1 // 2, n1:], _d[n1 - n1 // 2:n1, n1:]
+    orientation = np.argmax(list(map(np.sum, (d1[:, :i], d1[:, -i:], d2[:, :i], d2[:, -i:]))))
+    if orientation == 0:
+        scaffold = get_reversed(scaffold2) + scaffold1
+    elif orientation == 1:
+        scaffold = scaffold2 + scaffold1
+    elif orientation == 2:
+        scaffold = scaffold1 + scaffold2
+    else:
+        scaffold = scaffold1 + get_reversed(scaffold2)
+    return scaffold
+
+
+def get_contig2indices(bin_chr):
+    """bam2scaffolds.py:176-181."""
+    contig2indices = {c: [] for c in np.unique(bin_chr)}
+    for i, c in enumerate(bin_chr):
+        contig2indices[c].append(i)
+    return contig2indices
+
+
+def tree2scaffold(Z, names, d, bin_chr, minWindows):
+    """bam2scaffolds.py:183-200 on the linkage array instead of the ete3 tree: rows of Z are a
+    postorder; ``n.get_children()`` of the tree parsed from getNewick's string (bam2clusters.py:368-370:
+    "(" right "," left ")") is [right, left] = [Z[k, 1], Z[k, 0]]."""
+    contig2indices = get_contig2indices(bin_chr)
+    n = len(names)
+    scaffolds = [[(names[i], 0)] for i in range(n)]
+    for k in range(n - 1):
+        n1, n2 = int(Z[k, 1]), int(Z[k, 0])
+        scaffolds.append(join_scaffolds(scaffolds[n1], scaffolds[n2], d, contig2indices, minWindows))
+    return scaffolds[-1]
+
+
+def scaffold2gaps(d, bin_chr, scaffold, params, contig2size, mingap=100, maxgap=1000000, gapfrac=.33):
+    """bam2scaffolds.py:202-232 (``contig2size[c]/2`` is integer division in Py2)."""
+    contig2indices = get_contig2indices(bin_chr)
+    scaffold_with_gaps = []
+    contigbp = gapbp = 0
+    for i, (c, o) in enumerate(scaffold[:-1]):
+        c2, o2 = scaffold[i + 1]
+        csize = contig2size[c]
+        contacts = d[contig2indices[c][0], contig2indices[c2][0]]
+        with np.errstate(divide="ignore"):
+            distance = distance_func(contacts, *params) * 1000
+        gapSize = distance - contig2size[c] // 2 - contig2size[c2] // 2
+        if gapSize < mingap:
+            gapSize = mingap
+        elif gapSize > gapfrac * (contig2size[c] + contig2size[c2]):
+            gapSize = gapfrac * (contig2size[c] + contig2size[c2])
+        if gapSize > maxgap:
+            gapSize = maxgap
+        gapSize = int(round(gapSize))
+        contigbp += csize
+        gapbp += gapSize
+        scaffold_with_gaps.append((c, o, gapSize))
+    c, o = scaffold[-1]
+    scaffold_with_gaps.append((c, o, 0))
+    return scaffold_with_gaps, contigbp, gapbp
+
+
+def contigs2scaffold(sam, contig_sizes, windowSize, contigs, mapq, minWindows, params):
+    """bam2scaffolds.py:234-278 (``windowSize`` = [kb])."""
+    windowSize, windows, chr2window, base2chr, genomeSize = fasta2windows(
+        contig_sizes, windowSize, skipShorter=1, contigs=set(contigs), filterwindows=0)
+    d = bam2arrays(windows, windowSize, chr2window, sam, mapq, regions=contigs)[0]
+    bin_chr = np.array([c for c, s, e in windows[0]])
+    if not d.shape[0]:
+        return []
+    if len(np.unique(bin_chr)) == 1:
+        return [(bin_chr[0], 0, 0)]
+    d += d.T - np.diag(d.diagonal())
+    red = _average_reduce_2d(d, bin_chr)
+    uniq = np.unique(bin_chr)
+    Z = linkage_fastcluster(condense(distance_func(red + 1, *params)), "ward")
+    scaffold = tree2scaffold(Z, uniq, d, bin_chr, minWindows)
+    scaffold, contigbp, gapbp = scaffold2gaps(red, uniq, scaffold, params, dict(contig_sizes))
+    return scaffold
+
+
+def get_reverse_complement(seq):
+    """bin/FastaIndex/FastaIndex.py get_reverse_complement: complement table over ACGT/acgt (+IUPAC
+    left as is), reversed."""
+    comp = str.maketrans("ACGTacgt", "TGCAtgca")
+    return seq.translate(comp)[::-1]
+
+
+def report_scaffolds(scaffolds, seqs, w=60):
+    """bam2scaffolds.py:305-331: returns (FASTA text, scaffolds.tab text)."""
+    fa, tab = [], []
+    for i, scaffold in enumerate(scaffolds, 1):
+        if not scaffold:
+            continue
+        parts, elements = [], []
+        for c, o, gapSize in scaffold:
+            parts.append(get_reverse_complement(seqs[c]) if o else seqs[c])
+            parts.append('N' * gapSize)
+            elements.append("%s-" % c if o else "%s+" % c)
+        seq = "".join(parts)
+        seq = "\n".join(seq[s:s + w] for s in range(0, len(seq), w))
+        fa.append(">scaffold%s %s bp in %s contigs\n%s\n" % (i, len(seq), len(elements), seq))
+        tab.append("%s\n" % "\t".join(elements))
+    return "".join(fa), "".join(tab)

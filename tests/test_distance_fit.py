@@ -104,7 +104,8 @@ def test_bam2clusters_driver_matches_oracle_flow(cuda, tmp_path):
     import warnings
     from hicembler_b200 import pairs
     from hicembler_b200.bam2clusters import bam2clusters
-    g, rec = small_case(n_contigs=36, n_windows=400, window_bp=5000, n_chrom=4, n_pairs=60000, seed=11)
+    # >= 50 contigs above N95: the fit reads c2dists of the 50 longest contigs of the WHOLE assembly (:305-308)
+    g, rec = small_case(n_contigs=90, n_windows=900, window_bp=5000, n_chrom=4, n_pairs=80000, seed=11)
     fasta = str(tmp_path / "contigs.fa")
     with open(fasta, "w") as out:
         for c, s in zip(g.names, g.sizes):
@@ -119,7 +120,7 @@ def test_bam2clusters_driver_matches_oracle_flow(cuda, tmp_path):
     sizes = [(c, int(s)) for c, s in zip(g.names, g.sizes)]
     minSize, windows, chr2window, contig2size = O.contigs2windows(sizes, minSize=2000)
     K = len(windows)
-    assert K >= 20
+    assert K >= 50
     d, c2d = O.bam2array(windows, contig2size, chr2window, [lines], mapq=10, minSize=minSize, threads=3)
     with warnings.catch_warnings():
         warnings.simplefilter("ignore")
