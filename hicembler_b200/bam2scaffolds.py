@@ -114,10 +114,10 @@ def contigs2tree(bam, fasta, windowSize, contigs, mapq, params, names=None, meth
     (Z, contig names in np.unique order, symmetrised window matrix (CUDA float32), bin_chr)."""
     windowSize, windows, chr2window, base2chr, genomeSize = fasta2windows(
         fasta, windowSize, verbose=0, skipShorter=1, contigs=set(contigs), filterwindows=0)
-    counts, _ = bam2counts(windows, windowSize, chr2window, bam, mapq, regions=list(contigs), names=names)
     bin_chr = np.array([c for c, s, e in windows[0]])
     if not len(bin_chr):
         return None, [], None, bin_chr
+    counts, _ = bam2counts(windows, windowSize, chr2window, bam, mapq, regions=list(contigs), names=names)
     d, _ = ops.fold_counts(counts[0], "sym", inplace=True)
     uniq = np.unique(bin_chr)
     if len(uniq) == 1:

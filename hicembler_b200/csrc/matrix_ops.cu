@@ -644,7 +644,8 @@ extern "C" int hc_segment_mean_2d(const float *A, int32_t n, const int32_t *seg_
 // join_scaffolds (bam2scaffolds.py:142-174): the four corner-block sums that decide how two scaffolds are
 // oriented.  One CTA per (job, corner); a job's windows are idx[off .. off+n1) (scaffold 1) followed by
 // idx[off+n1 .. off+n1+n2) (scaffold 2).  Rows: first n1/2 (corners 0,1) or last n1/2 (2,3) windows of
-// scaffold 1; columns: first n2/2 (0,2) or last n2/2 (1,3) windows of scaffold 2.  Sums are taken in double
+// scaffold 1; columns: first n2/2 (0,2) or last n2/2 (1,3) windows of scaffold 2 (all of them when n2/2 == 0, as the
+// reference's [-0:] slice does).  Sums are taken in double
 // in a fixed order (exact for count matrices).
 __global__ void __launch_bounds__(256) k_block_sums4(const float *A, int32_t n, const int32_t *idx,
                                                       const int64_t *job_off, const int32_t *job_n1,
@@ -653,9 +654,13 @@ __global__ void __launch_bounds__(256) k_block_sums4(const float *A, int32_t n, 
     const int job = blockIdx.x >> 2, q = blockIdx.x & 3;
     const int32_t n1 = job_n1[job], n2 = job_n2[job];
     const int32_t *rows = idx + job_off[job], *cols = rows + n1;
-    const int32_t h = n1 / 2, w = n2 / 2;
+    const int32_t h = n1 / 2;
+    int32_t w = n2 / 2;
     if (q & 2) rows += n1 - h;
-    if (q & 1) cols += n2 - w;
+    if (q & 1) {
+        if (w == 0) w = n2;  // Python's d[:, -0:] is the whole axis (n2 == 1, reachable with minWindows = 1)
+        cols += n2 - w;
+    }
     double acc = 0.0;
     const long long cells = (long long)h * w;
     for (long long i = threadIdx.x; i < cells; i += blockDim.x) {

@@ -457,7 +457,8 @@ def block_sums4(A, jobs):
     up = lambda a: torch.from_numpy(a).to(dev)
     out = torch.empty((len(jobs), 4), dtype=torch.float64, device=dev)
     idx = up(flat) if flat.size else torch.zeros(1, dtype=torch.int32, device=dev)
-    _lib.check(_lib.lib().hc_block_sums4(_ptr(A), n, _ptr(idx), _ptr(up(off)), _ptr(up(n1)), _ptr(up(n2)), len(jobs),
+    d_off, d_n1, d_n2 = up(off), up(n1), up(n2)  # kept alive (and distinct) until the launch is queued
+    _lib.check(_lib.lib().hc_block_sums4(_ptr(A), n, _ptr(idx), _ptr(d_off), _ptr(d_n1), _ptr(d_n2), len(jobs),
                                          _ptr(out), _stream()))
     return out.cpu().numpy()
 

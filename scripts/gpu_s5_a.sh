@@ -1,4 +1,4 @@
 mkdir -p gpurun_out
 P=gpurun_out/s5a
-timeout 1200 python -m pytest tests -m gpu -x -q > ${P}_pytest.log 2>&1; echo "pytest rc=$?"; tail -15 ${P}_pytest.log
+timeout 1200 python -m pytest tests -m gpu -q > ${P}_pytest.log 2>&1; echo "pytest rc=$?"; tail -15 ${P}_pytest.log
 python -c "import __graft_entry__ as g; g.smoke()" > ${P}_smoke.log 2>&1; echo "smoke rc=$?"; tail -2 ${P}_smoke.log

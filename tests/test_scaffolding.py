@@ -116,9 +116,8 @@ def test_block_sums4_against_numpy(cuda):
         _d = d[:, i1 + i2][i1 + i2, :]
         n1, i = len(i1), len(i2) // 2
         d1, d2 = _d[:n1 // 2, n1:], _d[n1 - n1 // 2:n1, n1:]
-        # python's -0 slice is the whole axis; join_scaffolds never gets there (minWindows >= 2)
-        want = [np.sum(d1[:, :i], dtype=np.float64), np.sum(d1[:, len(i2) - i:], dtype=np.float64),
-                np.sum(d2[:, :i], dtype=np.float64), np.sum(d2[:, len(i2) - i:], dtype=np.float64)]
+        # the reference's slices, including [-0:] = the whole axis when n2 == 1
+        want = [np.sum(x, dtype=np.float64) for x in (d1[:, :i], d1[:, -i:], d2[:, :i], d2[:, -i:])]
         assert np.array_equal(row, np.array(want))
     assert ops.block_sums4(A, []).shape == (0, 4)
     with pytest.raises(IndexError):
