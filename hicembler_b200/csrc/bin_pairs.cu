@@ -85,6 +85,36 @@ __device__ __forceinline__ int decode(const BinArgs &a, uint2 q0, uint2 q1, uint
     return ST_OK;
 }
 
+// p / window_bp for p < 2^32 with 32-bit multiplies only: hi64(p * inv) = (p * inv_hi + hi32(p * inv_lo)) >> 32
+__device__ __forceinline__ uint32_t div_bp32(const BinArgs &a, uint32_t p) {
+    if (a.window_bp == 1u) return p;
+    const unsigned long long lo = (unsigned long long)p * (uint32_t)a.inv_bp;
+    return (uint32_t)(((unsigned long long)p * (uint32_t)(a.inv_bp >> 32) + (lo >> 32)) >> 32);
+}
+
+// decode() for the tile kernel: the four table look-ups are issued together and the status is two predicates
+// (filtered, ok); what kind of error a rejected record is gets sorted out by decode_reject() on the rare path.
+__device__ __forceinline__ void decode_lean(const BinArgs &a, uint2 q0, uint2 q1, uint2 q2, int32_t &row,
+                                            int32_t &col, bool &filtered, bool &ok) {
+    const int32_t ref = (int32_t)q0.x, pos = (int32_t)q0.y;
+    const int32_t nref = (int32_t)q1.x, npos = (int32_t)q1.y;
+    const int32_t lseq = (int32_t)q2.x;
+    const uint32_t flag = q2.y & 0xffffu, mapq = (q2.y >> 16) & 0xffu;
+    const bool ref_ok = (uint32_t)ref < (uint32_t)a.n_contigs, nref_ok = (uint32_t)nref < (uint32_t)a.n_contigs;
+    const int32_t m1 = ref_ok ? __ldg(a.member + ref) : -1, m2 = nref_ok ? __ldg(a.member + nref) : -1;
+    const int32_t o1 = ref_ok ? __ldg(a.offsets + ref) : -1, o2 = nref_ok ? __ldg(a.offsets + nref) : -1;
+    filtered = (flag & a.skip_flag) || (int32_t)mapq < a.mapq_min;
+    if (a.region_mask) filtered = filtered || !(ref_ok && a.region_mask[ref]);
+    const int32_t add = 1 + ((lseq > 1 ? lseq : 1) >> 1);  // len("*") == 1; Py2 integer division
+    const long long p1 = (long long)pos + add, p2 = (long long)npos + add;  // < 2^32
+    const uint32_t nw = (uint32_t)a.n_windows;
+    const uint32_t d1 = div_bp32(a, (uint32_t)p1), d2 = div_bp32(a, (uint32_t)p2);
+    const uint32_t w1 = d1 + (uint32_t)o1, w2 = d2 + (uint32_t)o2;  // no wrap when d < nw and o >= 0
+    ok = !filtered && (m1 | m2 | o1 | o2) >= 0 && (p1 | p2) >= 0 && d1 < nw && d2 < nw && w1 < nw && w2 < nw;
+    row = (int32_t)w1;
+    col = (int32_t)w2;
+}
+
 // sampled key of a chunk: window of read 1 of the chunk's first record, -1 if it has none
 __global__ void k_lead(BinArgs a, int32_t *lead) {
     long long c = blockIdx.x * (long long)blockDim.x + threadIdx.x;
@@ -251,17 +281,23 @@ __global__ void __launch_bounds__(CELL16 ? 512 : 1024, CELL16 ? 2 : 1) k_bin_til
                 const long long idx = base + (long long)u * T;
                 const bool live = idx < end;
                 int32_t row = 0, col = 0;
-                const int st = live ? decode(a, q[u][0], q[u][1], q[u][2], row, col) : ST_FILTERED;
+                bool filtered, ok;
+                decode_lean(a, q[u][0], q[u][1], q[u][2], row, col, filtered, ok);
+                filtered = filtered || !live;
+                ok = ok && live;
                 const int32_t lo = clo_[u], hi = chi_[u];
                 const bool owner = live && (lo == r0) && (s == 0);  // this tile accounts for the record
                 if (owner) {
-                    n_lines += st != ST_FILTERED;
-                    n_ok += st == ST_OK;
-                    n_absent += st == ST_ABSENT;
-                    n_range += st == ST_RANGE;
-                    n_key += st == ST_KEY;
+                    n_lines += !filtered;
+                    n_ok += ok;
+                    if (!filtered && !ok) {  // rare: which error the reference would raise / skip
+                        int32_t rr, cc;
+                        const int st = decode(a, q[u][0], q[u][1], q[u][2], rr, cc);
+                        n_absent += st == ST_ABSENT;
+                        n_range += st == ST_RANGE;
+                        n_key += st == ST_KEY;
+                    }
                 }
-                const bool ok = st == ST_OK;
                 const bool mine = ok && row >= r0 && row < r1 && col >= c0 && col < c1;
                 // warp-aggregated shared-memory atomics: one add per distinct cell per warp
                 const uint32_t cell = mine ? (uint32_t)((row - r0) * W + (col - c0)) : 0xffffffffu;
@@ -314,6 +350,16 @@ __global__ void __launch_bounds__(CELL16 ? 512 : 1024, CELL16 ? 2 : 1) k_bin_til
         const int rows = r1 - r0;
         if (CELL16) {  // (the host picks this kernel only when vec_ok, c0 % 4 == 0 and W % 4 == 0)
             const int W4 = W >> 2;
+            if (rows == 1 && !a.accumulate) {  // the N > ~29 000 case: one matrix row per tile
+                uint2 *src = (uint2 *)tile;
+                uint4 *dst = (uint4 *)(a.counts + (size_t)(r0 - a.row0) * a.n_windows + c0);
+#pragma unroll 4
+                for (int i = threadIdx.x; i < W4; i += T) {
+                    const uint2 w = src[i];
+                    src[i] = make_uint2(0, 0);
+                    __stcs(dst + i, make_uint4(w.x & 0xffffu, w.x >> 16, w.y & 0xffffu, w.y >> 16));
+                }
+            } else
             for (int i = threadIdx.x; i < rows * W4; i += T) {
                 const int rr = rows == 1 ? 0 : i / W4, cc = i - rr * W4;
                 uint2 *src = (uint2 *)(tile + rr * (W >> 1)) + cc;  // four 16-bit cells
