@@ -253,46 +253,43 @@ __global__ void __launch_bounds__(CELL16 ? 512 : 1024, CELL16 ? 2 : 1) k_bin_til
         const long long clo = a.tile_clo[g], chi = a.tile_chi[g];
         const long long beg = clo << CHUNK_LOG;
         const long long end = min(chi << CHUNK_LOG, a.n_pairs);
-        // warp-uniform trip count (the ballots / matches below need the whole warp)
-        for (long long wbase = beg + (threadIdx.x - lane_id); wbase < end; wbase += (long long)T * UNROLL) {
-            const long long base = wbase + lane_id;
-            uint2 q[UNROLL][3];
-            int32_t clo_[UNROLL], chi_[UNROLL];
+        // Software-pipelined record stream: each thread keeps two half batches (HB records each) in registers and
+        // loads the next half batch BEFORE it works on the current one, so the record loads of a warp are always
+        // in flight while it decodes / adds (warp-uniform trip counts: the ballots / matches need the whole warp).
+        constexpr int HB = UNROLL / 2;
+        auto fetch = [&](long long wb, uint2 (&q)[HB][3], int32_t (&lo_)[HB], int32_t (&hi_)[HB]) {
 #pragma unroll
-            for (int u = 0; u < UNROLL; ++u) {
-                const long long idx = base + (long long)u * T;
+            for (int u = 0; u < HB; ++u) {
+                const long long idx = wb + lane_id + (long long)u * T;
                 if (idx < end) {
                     const uint2 *p = a.pairs + 3 * idx;
                     q[u][0] = __ldg(p);
                     q[u][1] = __ldg(p + 1);
                     q[u][2] = __ldg(p + 2);
                     const long long c = idx >> CHUNK_LOG;
-                    clo_[u] = __ldg(a.chunk_lo + c);
-                    chi_[u] = __ldg(a.chunk_hi + c);
+                    lo_[u] = __ldg(a.chunk_lo + c);
+                    hi_[u] = __ldg(a.chunk_hi + c);
                 } else {
-                    q[u][2].y = 0xffffu;  // every flag bit set -> filtered
-                    q[u][0] = q[u][1] = make_uint2(0, 0);
-                    q[u][2].x = 0;
-                    clo_[u] = chi_[u] = 0;
+                    q[u][0] = q[u][1] = q[u][2] = make_uint2(0, 0);
+                    lo_[u] = hi_[u] = 0;
                 }
             }
-#pragma unroll
-            for (int u = 0; u < UNROLL; ++u) {
-                const long long idx = base + (long long)u * T;
+        };
+        auto work = [&](long long idx, uint2 q0, uint2 q1, uint2 q2, int32_t lo_in, int32_t hi_in) {
                 const bool live = idx < end;
                 int32_t row = 0, col = 0;
                 bool filtered, ok;
-                decode_lean(a, q[u][0], q[u][1], q[u][2], row, col, filtered, ok);
+                decode_lean(a, q0, q1, q2, row, col, filtered, ok);
                 filtered = filtered || !live;
                 ok = ok && live;
-                const int32_t lo = clo_[u], hi = chi_[u];
+                const int32_t lo = lo_in, hi = hi_in;
                 const bool owner = live && (lo == r0) && (s == 0);  // this tile accounts for the record
                 if (owner) {
                     n_lines += !filtered;
                     n_ok += ok;
                     if (!filtered && !ok) {  // rare: which error the reference would raise / skip
                         int32_t rr, cc;
-                        const int st = decode(a, q[u][0], q[u][1], q[u][2], rr, cc);
+                        const int st = decode(a, q0, q1, q2, rr, cc);
                         n_absent += st == ST_ABSENT;
                         n_range += st == ST_RANGE;
                         n_key += st == ST_KEY;
@@ -343,6 +340,22 @@ __global__ void __launch_bounds__(CELL16 ? 512 : 1024, CELL16 ? 2 : 1) k_bin_til
                         n_over++;
                     }
                 }
+        };
+        auto work_half = [&](long long wb, uint2 (&q)[HB][3], int32_t (&lo_)[HB], int32_t (&hi_)[HB]) {
+#pragma unroll
+            for (int u = 0; u < HB; ++u) work(wb + lane_id + (long long)u * T, q[u][0], q[u][1], q[u][2], lo_[u], hi_[u]);
+        };
+        {
+            const long long step = (long long)T * HB;
+            long long wb = beg + (threadIdx.x - lane_id);
+            uint2 qa[HB][3], qb[HB][3];
+            int32_t la[HB], ha[HB], lb[HB], hb[HB];
+            fetch(wb, qa, la, ha);
+            for (; wb < end; wb += 2 * step) {
+                fetch(wb + step, qb, lb, hb);
+                work_half(wb, qa, la, ha);
+                fetch(wb + 2 * step, qa, la, ha);
+                if (wb + step < end) work_half(wb + step, qb, lb, hb);
             }
         }
         __syncthreads();
