@@ -702,9 +702,9 @@ extern "C" int hc_bin_pairs(const hc_pair_t *pairs, int64_t n_pairs, const int32
         if (const char *e = getenv("HC_BIN_THREADS")) threads = atoi(e);
         if (cell16 && threads > 512) threads = 512;
         if (cell16)
-            HC_CUDA_OK(cudaFuncSetAttribute(k_bin_tiles<4, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_max));
+            HC_CUDA_OK(cudaFuncSetAttribute(k_bin_tiles<2, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_max));
         else
-            HC_CUDA_OK(cudaFuncSetAttribute(k_bin_tiles<4, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_max));
+            HC_CUDA_OK(cudaFuncSetAttribute(k_bin_tiles<2, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_max));
         // persistent: as many CTAs as fit (tiles <= ~110 KB let two CTAs share an SM and overlap
         // one CTA's flush with the other's record stream)
         int per_sm = (int)((size_t)(smem_max + 1024) / (smem + 1024));
@@ -713,8 +713,8 @@ extern "C" int hc_bin_pairs(const hc_pair_t *pairs, int64_t n_pairs, const int32
         if (per_sm < 1) per_sm = 1;
         long long n_tiles = (long long)a.n_groups * a.n_segs;
         int grid = (int)std::min<long long>(n_tiles, (long long)sms * per_sm);
-        if (cell16) k_bin_tiles<4, true><<<grid, threads, smem, stream>>>(a);
-        else k_bin_tiles<4, false><<<grid, threads, smem, stream>>>(a);
+        if (cell16) k_bin_tiles<2, true><<<grid, threads, smem, stream>>>(a);
+        else k_bin_tiles<2, false><<<grid, threads, smem, stream>>>(a);
         HC_CHECK_LAUNCH();
         k_apply_overflow<<<4 * sms, 256, 0, stream>>>(a);
         HC_CHECK_LAUNCH();
