@@ -863,3 +863,58 @@ def report_scaffolds(scaffolds, seqs, w=60):
         fa.append(">scaffold%s %s bp in %s contigs\n%s\n" % (i, len(seq), len(elements), seq))
         tab.append("%s\n" % "\t".join(elements))
     return "".join(fa), "".join(tab)
+
+
+# ---------------------------------------------------------------------------------------------
+# array2scaffolds.py: matrix cache loader (:43-121)
+# ---------------------------------------------------------------------------------------------
+def get_contig2size(bin_chr, bin_position):
+    """array2scaffolds.py:43-49 (get_name = first word of the contig name, :181-182)."""
+    contig2size = {c.split()[0]: 0 for c in np.unique(bin_chr)}
+    for c, (s, e) in zip(bin_chr, bin_position):
+        contig2size[c.split()[0]] += e - s
+    return contig2size
+
+
+def load_matrix(d, windows, chrs=(), remove_shorter=True, scaffolds=()):
+    """array2scaffolds.py:51-121 after the file reads: ``d`` = the cached upper-triangular array,
+    ``windows`` = rows of the .windows.tab.gz.  (:108-109 extend bin_chr by the RUNNING index count per
+    scaffold -- a reference bug that makes bin_chr longer than the matrix for >1 scaffold; restated
+    literally.)"""
+    from collections import Counter
+    if len(scaffolds):
+        remove_shorter = True
+    d = np.array(d)
+    bin_chr = np.array([w[0] for w in windows])
+    bin_position = np.array([[int(w[1]), int(w[2])] for w in windows])
+    contig2size = get_contig2size(bin_chr, bin_position)
+    if remove_shorter:
+        c = Counter(np.diff(bin_position, axis=1)[:, 0].tolist())
+        windowSize, occurencies = c.most_common(1)[0]
+        valid_rowcols = ~(np.diff(bin_position, axis=1)[:, 0] != windowSize)
+        d = d[valid_rowcols, :]
+        d = d[:, valid_rowcols]
+        bin_chr = bin_chr[valid_rowcols]
+        bin_position = bin_position[valid_rowcols, :]
+    if len(chrs):
+        indices = np.any(bin_chr[None].T == list(chrs), 1)
+        d = d[indices, :]
+        d = d[:, indices]
+        bin_chr = bin_chr[indices]
+        bin_position = bin_position[indices, :]
+    if len(scaffolds):
+        contig2indices = get_contig2indices(bin_chr)
+        indices, bin_chr, bin_position = [], [], []
+        for i, scaffold in enumerate(scaffolds, 1):
+            name = "scaffold%s" % i
+            indices += get_indices(scaffold, contig2indices)
+            bin_chr += [name] * len(indices)
+            bin_position += [(s, s + windowSize) for s in range(0, windowSize * len(indices), windowSize)]
+        d = d[:, indices][indices, :]
+        bin_chr = np.array(bin_chr)
+        bin_position = np.array(bin_position)
+        contig2size = get_contig2size(bin_chr, bin_position)
+    d += d.T
+    d -= np.diag(d.diagonal() / 2)
+    d = normalize_rows(d)
+    return d, bin_chr, bin_position, contig2size

@@ -207,3 +207,29 @@ def test_bam2scaffolds_driver_files(cuda, tmp_path):
     assert open(base + ".scaffolds.tab").read() == tab
     assert open(base + ".scaffolds.fa").read() == fa
     assert FastaIndex(base + ".scaffolds.fa").genomeSize > sum(contig2size[c] for cl in want for c, o, gp in cl)
+
+
+@pytest.mark.gpu
+def test_load_matrix_matches_oracle(cuda, tmp_path):
+    """array2scaffolds.py:51-121: cache files in, filtered / reordered / symmetrised / row-normalised matrix out"""
+    import gzip
+    from hicembler_b200.array2scaffolds import load_matrix
+    g, rec = small_case(n_contigs=14, n_windows=150, window_bp=5000, n_pairs=40000, seed=8)
+    wsz, windows, chr2window, _, _ = O.fasta2windows(g.contig_sizes, [5], skipShorter=0, minSize=2000, filterwindows=0)
+    d = O.bam2arrays(windows, wsz, chr2window, [sam_lines(g, rec)], 10)[0]
+    wins = windows[0]
+    assert len({e - s for c, s, e in wins}) > 2          # contig tails: windows shorter than 5 kb get dropped
+    fname = str(tmp_path / "x.5k.npz")
+    np.savez_compressed(fname, d)
+    with gzip.open(fname[:-4] + ".windows.tab.gz", "wt") as out:
+        out.write("\n".join("\t".join(map(str, w)) for w in wins) + "\n")
+    names = g.names
+    sc1 = [(names[3], 0), (names[1], 1), ("absent", 0), (names[7], 0)]
+    sc2 = [(names[0], 1), (names[5], 0)]
+    for kw in (dict(), dict(remove_shorter=False), dict(chrs=[names[2], names[9], names[4]]),
+               dict(scaffolds=[sc1]), dict(scaffolds=[sc1, sc2]), dict(chrs=[names[1], names[3]], scaffolds=[sc1])):
+        wd, wc, wp, ws = O.load_matrix(d.copy(), wins, **kw)
+        gd, gc, gp, gs = load_matrix(fname, **kw)
+        assert gd.dtype == np.float32 and gd.shape == wd.shape and gd.shape[0] > 0
+        assert np.allclose(gd, wd, rtol=3e-7, atol=0)
+        assert list(gc) == list(wc) and np.array_equal(gp, wp) and gs == ws
