@@ -256,7 +256,7 @@ __global__ void __launch_bounds__(CELL16 ? 512 : 1024, CELL16 ? 2 : 1) k_bin_til
         // Software-pipelined record stream: each thread keeps two half batches (HB records each) in registers and
         // loads the next half batch BEFORE it works on the current one, so the record loads of a warp are always
         // in flight while it decodes / adds (warp-uniform trip counts: the ballots / matches need the whole warp).
-        constexpr int HB = UNROLL / 2;
+        constexpr int HB = UNROLL == 3 ? 1 : UNROLL / 2;  // UNROLL 3: three one-record stages
         auto fetch = [&](long long wb, uint2 (&q)[HB][3], int32_t (&lo_)[HB], int32_t (&hi_)[HB]) {
 #pragma unroll
             for (int u = 0; u < HB; ++u) {
@@ -351,6 +351,19 @@ __global__ void __launch_bounds__(CELL16 ? 512 : 1024, CELL16 ? 2 : 1) k_bin_til
             uint2 qa[HB][3], qb[HB][3];
             int32_t la[HB], ha[HB], lb[HB], hb[HB];
             fetch(wb, qa, la, ha);
+            if (UNROLL == 3) {  // loads run two records ahead of the decode
+                uint2 qc[HB][3];
+                int32_t lc[HB], hc_[HB];
+                fetch(wb + step, qb, lb, hb);
+                for (; wb < end; wb += 3 * step) {
+                    fetch(wb + 2 * step, qc, lc, hc_);
+                    work_half(wb, qa, la, ha);
+                    fetch(wb + 3 * step, qa, la, ha);
+                    if (wb + step < end) work_half(wb + step, qb, lb, hb);
+                    fetch(wb + 4 * step, qb, lb, hb);
+                    if (wb + 2 * step < end) work_half(wb + 2 * step, qc, lc, hc_);
+                }
+            } else
             for (; wb < end; wb += 2 * step) {
                 fetch(wb + step, qb, lb, hb);
                 work_half(wb, qa, la, ha);
@@ -702,7 +715,7 @@ extern "C" int hc_bin_pairs(const hc_pair_t *pairs, int64_t n_pairs, const int32
         if (const char *e = getenv("HC_BIN_THREADS")) threads = atoi(e);
         if (cell16 && threads > 512) threads = 512;
         if (cell16)
-            HC_CUDA_OK(cudaFuncSetAttribute(k_bin_tiles<2, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_max));
+            HC_CUDA_OK(cudaFuncSetAttribute(k_bin_tiles<3, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_max));
         else
             HC_CUDA_OK(cudaFuncSetAttribute(k_bin_tiles<2, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_max));
         // persistent: as many CTAs as fit (tiles <= ~110 KB let two CTAs share an SM and overlap
@@ -713,7 +726,7 @@ extern "C" int hc_bin_pairs(const hc_pair_t *pairs, int64_t n_pairs, const int32
         if (per_sm < 1) per_sm = 1;
         long long n_tiles = (long long)a.n_groups * a.n_segs;
         int grid = (int)std::min<long long>(n_tiles, (long long)sms * per_sm);
-        if (cell16) k_bin_tiles<2, true><<<grid, threads, smem, stream>>>(a);
+        if (cell16) k_bin_tiles<3, true><<<grid, threads, smem, stream>>>(a);
         else k_bin_tiles<2, false><<<grid, threads, smem, stream>>>(a);
         HC_CHECK_LAUNCH();
         k_apply_overflow<<<4 * sms, 256, 0, stream>>>(a);
