@@ -84,9 +84,6 @@ def test_fasta_get_sequence_and_report(tmp_path):
     assert tab == "%s+\t%s-\t%s+\n%s-\n" % (n[0], n[3], n[1], n[2])
 
 
-# ------------------------------------------------------------------------------------------
-# device-backed
-# ------------------------------------------------------------------------------------------
 def _random_tree(n, rng):
     """a valid linkage array with random topology (heights irrelevant for the walk)"""
     alive = list(range(n))
@@ -99,6 +96,42 @@ def _random_tree(n, rng):
     return Z
 
 
+@pytest.mark.parametrize("seed,minWindows", [(5, 2), (6, 3), (7, 1)])
+def test_tree2scaffold_host_logic_with_numpy_corner_sums(monkeypatch, seed, minWindows):
+    """the level-batched walk (children order, swap, minWindows rules, orientation table) against the oracle's
+    node-by-node walk; the device corner sums are replaced by a numpy stand-in of hc_block_sums4's contract"""
+    from hicembler_b200 import bam2scaffolds as B
+    rng = np.random.default_rng(seed)
+    K = 25
+    names = np.array(["k%02d" % i for i in range(K)])
+    runs = rng.integers(1, 7, K)
+    bin_chr = np.concatenate([[names[c]] * runs[c] for c in rng.permutation(K)])
+    d = hic_like_counts(len(bin_chr), seed)
+    batches = []
+
+    def sums(A, jobs):
+        batches.append(len(jobs))
+        out = np.zeros((len(jobs), 4))
+        for j, (i1, i2) in enumerate(jobs):
+            h, w = len(i1) // 2, len(i2) // 2
+            w_end = w if w else len(i2)
+            r = (i1[:h], i1[len(i1) - h:])
+            c = (i2[:w], i2[len(i2) - w_end:])
+            for q in range(4):
+                out[j, q] = d[np.ix_(r[q >> 1], c[q & 1])].sum(dtype=np.float64)
+        return out
+
+    monkeypatch.setattr(B.ops, "block_sums4", sums)
+    monkeypatch.setattr(B, "_device_matrix", lambda x: x)
+    Z = _random_tree(K, rng)
+    want = O.tree2scaffold(Z, names, d, bin_chr, minWindows)
+    assert B.tree2scaffold((Z, list(names)), d, bin_chr, None, minWindows) == want
+    assert len(batches) < K - 1 and sum(batches) <= K - 1      # one launch per tree level, not per node
+
+
+# ------------------------------------------------------------------------------------------
+# device-backed
+# ------------------------------------------------------------------------------------------
 @pytest.mark.gpu
 def test_block_sums4_against_numpy(cuda):
     import torch
