@@ -247,7 +247,13 @@ __device__ __forceinline__ double xform(const Xform &t, T raw, int i, int j) {
         // ~3x the FP64 work of exp(e*log(u)); that form is used only while |e*log(u)| < 1, where the error of the
         // exponent is not amplified (<= 3 ulp in all).
         const double e = t.inv_p1, y = v - 1.0;
-        if (y >= 0.0 && y <= 0x1p-10) {
+        if (sizeof(T) == 4 && !t.r) {
+            // float32 matrix without balancing vectors (contigs2scaffold: distance_func on the float32 block means,
+            // bam2scaffolds.py:265): numpy evaluates (1./(a*x))**(1./b) in float32 -- a and 1/b are scalars and do
+            // not promote the array -- so a*x, the division and the power are float32 operations.
+            const float u = __fdiv_rn(1.0f, __fmul_rn((float)t.p0, (float)v));
+            out = (double)powf(u, (float)e);
+        } else if (y >= 0.0 && y <= 0x1p-10 && fabs(e) <= 4.0) {   // |z| <= 2^-8: exp series truncation < 2^-57
             double L = fma(y, -1.0 / 6.0, 0.2);
             L = fma(y, L, -0.25);
             L = fma(y, L, 1.0 / 3.0);

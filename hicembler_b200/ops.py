@@ -302,8 +302,8 @@ def transform_to_working(X, kind=KIND_IDENTITY, p0=0.0, p1=1.0, r=None, c=None, 
 def transform(X, kind, p0=0.0, p1=1.0, out_dtype=None):
     _dev(X)
     X = X.contiguous()
-    if out_dtype is None:
-        out_dtype = X.dtype if kind == KIND_LOGMAX else torch.float64
+    if out_dtype is None:      # numpy keeps a float32 array float32 through log / pow with scalar parameters
+        out_dtype = X.dtype if kind in (KIND_LOGMAX, KIND_POWER, KIND_POWER_RAW) else torch.float64
     out = torch.empty(X.shape, dtype=out_dtype, device=X.device)
     _lib.check(_lib.lib().hc_transform(_ptr(X), _dtype_code(X), X.numel(), kind, float(p0), float(p1),
                                        _ptr(out), _dtype_code(out), _stream()))

@@ -66,7 +66,7 @@ def get_window(chrom, start, length, windowSize, chr2window):
     return window
 
 
-def bam2arrays(windows, windowSize, chr2window, sam, mapq, upto=0, regions=(), verbose=0):
+def bam2arrays(windows, windowSize, chr2window, sam, mapq, upto=0, regions=(), verbose=0, shadow_mapq=True):
     """bam2clusters.py:128-166.  ``sam`` is a list of iterables of SAM text lines (one per
     BAM); each stands for the ``samtools view`` pipe of that BAM *before* -q/-F filtering.
 
@@ -78,13 +78,17 @@ def bam2arrays(windows, windowSize, chr2window, sam, mapq, upto=0, regions=(), v
     i = 1
     regions = set(regions)
     for _sam in sam:
-        stream = samtools_view(_sam, mapq)
+        stream = samtools_view(_sam, int(mapq))
         if regions:
             stream = (l for l in stream if l.split("\t", 3)[2] in regions)
         for i, line in enumerate(stream, i):
             if upto and i > upto:
                 break
+            # :145 unpacks the line's MAPQ field into ``mapq`` itself: the argument is overwritten, and the NEXT
+            # BAM is filtered with ``-q <MAPQ of the last line read>`` (:138).  shadow_mapq=False = the intent.
             ref1, start1, _mapq, cigar, ref2, start2, insertSize, seq = line.split("\t")[2:10]
+            if shadow_mapq:
+                mapq = _mapq
             start1, start2, seqlen = int(start1), int(start2), len(seq)
             if ref2 == "=":
                 ref2 = ref1
@@ -378,7 +382,12 @@ def normalize(d, max_iter=1000, epsilon=0.00001, materialize=True, sk=None):
 
 
 def distance_func(x, a, b, maxv=float("inf")):
-    """bam2clusters.py:248-251."""
+    """bam2clusters.py:248-251.  dtype: under the reference's NumPy (value-based casting) the scalars a and 1./b --
+    np.float64 from curve_fit -- do not promote a float32 array, so a float32 ``x`` is evaluated entirely in
+    float32.  NumPy >= 2 (NEP 50) promotes for np.float64 scalars but not for Python floats; the cast below makes
+    the restatement independent of both the NumPy version and the scalar type."""
+    if isinstance(x, np.ndarray) and x.dtype == np.float32:
+        return (np.float32(1.) / (np.float32(a) * x)) ** np.float32(1. / b)
     return (1. / (a * x)) ** (1. / b)
 
 
@@ -781,17 +790,176 @@ def get_contig2indices(bin_chr):
     return contig2indices
 
 
-def tree2scaffold(Z, names, d, bin_chr, minWindows):
-    """bam2scaffolds.py:183-200 on the linkage array instead of the ete3 tree: rows of Z are a
-    postorder; ``n.get_children()`` of the tree parsed from getNewick's string (bam2clusters.py:368-370:
-    "(" right "," left ")") is [right, left] = [Z[k, 1], Z[k, 0]]."""
+def join_scaffolds_diag(scaffold1, scaffold2, d, contig2indices, minWindows=3):
+    """array2scaffolds.py:274-309: the OTHER join_scaffolds -- orientation from four anti/diagonal sums of the
+    rectangle between the two scaffolds instead of corner-block sums, and no empty result for two short scaffolds
+    (Py2 ``n2/2`` is ``//``).  ``d1[:i]`` / ``d3[-i:]`` with i == 0: ``[:0]`` is empty, ``[-0:]`` is everything."""
+    indices1 = get_indices(scaffold1, contig2indices)
+    indices2 = get_indices(scaffold2, contig2indices)
+    if len(indices1) < len(indices2):
+        scaffold1, indices1, scaffold2, indices2 = scaffold2, indices2, scaffold1, indices1
+    if len(indices2) < minWindows:
+        return scaffold1
+    _d = d[:, indices1 + indices2][indices1 + indices2, :]
+    n1, n2 = len(indices1), len(indices2)
+    i = n2 // 2
+    dflip = np.fliplr(_d[:n1, n2:])
+    d1, d2, d3, d4 = np.diag(_d, k=n1), np.diag(dflip), np.diag(dflip, k=n2 - n1), np.diag(_d, k=n2)
+    orientation = np.argmax(list(map(sum, (d1[:i], d2[:i], d3[-i:], d4[-i:]))))
+    if orientation == 0:
+        scaffold = get_reversed(scaffold2) + scaffold1
+    elif orientation == 1:
+        scaffold = scaffold2 + scaffold1
+    elif orientation == 2:
+        scaffold = scaffold1 + scaffold2
+    else:
+        scaffold = scaffold1 + get_reversed(scaffold2)
+    return scaffold
+
+
+def tree2scaffold(Z, names, d, bin_chr, minWindows, join=None, children="newick"):
+    """bam2scaffolds.py:183-200 (= array2scaffolds.py:319-338) on the linkage array instead of the ete3 tree: rows
+    of Z are a postorder.  ``n.get_children()`` is [right, left] = [Z[k, 1], Z[k, 0]] for the tree parsed from
+    getNewick's string (bam2clusters.py:368-370: "(" right "," left ")"; ``children="newick"``) and
+    [Z[k, 0], Z[k, 1]] for the tree distance_matrix2tree builds (array2scaffolds.py:141-142; ``children="dm2t"``)."""
+    join = join or join_scaffolds
     contig2indices = get_contig2indices(bin_chr)
     n = len(names)
     scaffolds = [[(names[i], 0)] for i in range(n)]
     for k in range(n - 1):
-        n1, n2 = int(Z[k, 1]), int(Z[k, 0])
-        scaffolds.append(join_scaffolds(scaffolds[n1], scaffolds[n2], d, contig2indices, minWindows))
+        n1, n2 = (int(Z[k, 1]), int(Z[k, 0])) if children == "newick" else (int(Z[k, 0]), int(Z[k, 1]))
+        scaffolds.append(join(scaffolds[n1], scaffolds[n2], d, contig2indices, minWindows))
     return scaffolds[-1]
+
+
+# ---------------------------------------------------------------------------------------------
+# array2scaffolds.py: distance_matrix2tree (:123-145) and get_clusters (:199-256) on plain arrays.
+# ete3 semantics used by the reference (third-party, unpinned; documented in oracle/ete3_min.py): a node made by
+# ``ete3.Tree()`` has dist 1.0 and name ""; get_farthest_leaf returns the FIRST leaf in pre-order with the
+# strictly largest path length; get_ancestors lists the parent first; len(tree) / iteration = leaves in pre-order;
+# newick format 0 prints "%0.6g" distances and the support value (1) after every internal ")".
+# ---------------------------------------------------------------------------------------------
+class _DM2Tree(object):
+    def __init__(self, Z, names):
+        n = Z.shape[0] + 1
+        self.n = n
+        nn = 2 * n - 1
+        self.children = [[] for _ in range(nn)]
+        self.up = [-1] * nn
+        self.dist = [1.0] * nn                    # ete3 default branch length (the root keeps it)
+        self.name = [names[i] if i < n else "" for i in range(nn)]
+        for i in range(n - 1):
+            a, b = int(Z[i, 0]), int(Z[i, 1])
+            h = float(Z[i, 2])
+            k = n + i
+            self.dist[a] = h - self.farthest_leaf(a)[1]      # :137-138 dist - child.get_farthest_leaf()[1]
+            self.dist[b] = h - self.farthest_leaf(b)[1]
+            self.children[k] = [a, b]
+            self.up[a] = self.up[b] = k
+        self.root = nn - 1
+
+    def leaves(self, node):
+        out, stack = [], [node]
+        while stack:
+            k = stack.pop()
+            if self.children[k]:
+                stack.extend(reversed(self.children[k]))
+            else:
+                out.append(k)
+        return out
+
+    def farthest_leaf(self, node):
+        """ete3 TreeNode.get_farthest_leaf: a single running distance, += on entering an internal node, -= on
+        leaving it; first leaf with the strictly largest value wins (rounding history included, see ete3_min.py)."""
+        if not self.children[node]:
+            return node, 0.0
+        best, best_d = None, None
+        d = 0.0
+        stack = [(c, False) for c in reversed(self.children[node])]
+        while stack:
+            k, leaving = stack.pop()
+            if leaving:
+                d -= self.dist[k]
+            elif self.children[k]:
+                d += self.dist[k]
+                stack.append((k, True))
+                stack.extend((c, False) for c in reversed(self.children[k]))
+            else:
+                tot = d + self.dist[k]
+                if best_d is None or tot > best_d:
+                    best, best_d = k, tot
+        return best, best_d
+
+    def ancestors(self, node):
+        out, k = [], self.up[node]
+        while k >= 0:
+            out.append(k)
+            k = self.up[k]
+        return out
+
+    def newick(self):
+        out, stack = [], [("n", self.root)]
+        while stack:
+            kind, k = stack.pop()
+            if kind == "t":
+                out.append(k)
+            elif self.children[k]:
+                out.append("(")
+                stack.append(("t", ")" if k == self.root else ")1:%0.6g" % self.dist[k]))
+                ch = self.children[k]
+                for q, c in enumerate(reversed(ch)):
+                    stack.append(("n", c))
+                    if q != len(ch) - 1:
+                        stack.append(("t", ","))
+            else:
+                out.append("%s:%0.6g" % (self.name[k], self.dist[k]))
+        return "".join(out) + ";"
+
+
+def distance_matrix2tree_newick(Z, names):
+    """``distance_matrix2tree(Z, names).write()`` (array2scaffolds.py:123-145,171-172): child branch length =
+    merge height - height of the child's farthest leaf."""
+    return _DM2Tree(Z, names).newick()
+
+
+def get_clusters(Z, names, contig2size, bin_chr):
+    """array2scaffolds.py:199-256 on the tree of distance_matrix2tree(Z, names) (without the file output).
+    Restated quirks: ``clusters`` is sized by the leaf count of the LAST subtree (:232, ``len(subtree)`` instead of
+    ``len(subtrees)``) and indexed with the 1-based subtree number (:241), so cluster k lands in slot k, slot 0 stays
+    empty and an IndexError is raised when a subtree number reaches that leaf count; an IndexError is also raised
+    when the longest branch above the farthest leaf is the root's own default branch (:209-216).  Contigs are
+    visited in np.unique order (Python-3 dict order of :220; hash order under Python 2)."""
+    get_name = lambda c: c.split()[0]
+    T = _DM2Tree(Z, names)
+    subtrees = []
+    while len(T.leaves(T.root)) > 2:
+        n, dist = T.farthest_leaf(T.root)
+        anc = T.ancestors(n)
+        dists = [T.dist[a] for a in anc]
+        ai = dists.index(max(dists))
+        a = anc[ai]
+        if T.name[n]:
+            subtrees.append(a)
+        p = anc[ai + 1]
+        T.children[p].remove(a)
+        T.up[a] = -1
+    contig2cluster = {get_name(c): Counter() for c in np.unique(bin_chr)}
+    subtree = None
+    for i, subtree in enumerate(subtrees, 1):
+        lv = T.leaves(subtree)
+        c = Counter(get_name(T.name[k]) for k in lv if T.name[k])
+        c.most_common(1)[0][1]
+        for k, v in c.items():
+            if not k:
+                continue
+            contig2cluster[get_name(k)][i] += v
+    clusters = [[] for i in range(len(T.leaves(subtree)))]
+    for c, counter in contig2cluster.items():
+        if not counter:
+            continue
+        clusteri, count = counter.most_common(1)[0]
+        clusters[clusteri].append(c)
+    return [x for x in clusters if x]
 
 
 def scaffold2gaps(d, bin_chr, scaffold, params, contig2size, mingap=100, maxgap=1000000, gapfrac=.33):

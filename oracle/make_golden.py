@@ -8,8 +8,9 @@ Sources of truth:
     (``from types import IntType, FloatType`` -> ``IntType, FloatType = int, float``), applied in
     memory; plus ``normalize()`` of bam2clusters.py:36-49 evaluated with that library.
   * linkage_*.npz  : scipy.cluster.hierarchy.linkage, the reference's call at array2scaffolds.py:163.
-  * binning_*.npz  : the literal restatement of bam2arrays (oracle/hicembler_oracle.py) over SAM text --
-    the reference's own loop is Python-2 + samtools and cannot run here ("parity unpinned").
+  * binning.npz, reference_pinned.npz : the reference's OWN functions, executed from /root/reference by
+    oracle/ref_exec.py (source compiled in memory after the documented Py2->Py3 shims; ``samtools view`` replaced
+    by an iterator over SAM text) -- the restatement is asserted equal while the fixtures are written.
 The committed fixtures travel to the GPU box; /root/reference does not.
 """
 import importlib.util
@@ -115,7 +116,9 @@ def main():
                 out["n%d_%s_%s_fc" % (n, tag, m)] = O.linkage_fastcluster(y, m)
     np.savez_compressed(os.path.join(GOLD, "linkage.npz"), **out)
 
-    # --- binning: literal loop over SAM text ------------------------------------------------------
+    # --- binning: the REFERENCE'S OWN bam2arrays (bam2clusters.py:128-166, executed by oracle/ref_exec.py with the
+    # documented Py2 shims) over SAM text; the restatement must reproduce it bit for bit ---------------------------
+    import ref_exec as R
     from hicembler_b200 import synth
     from hicembler_b200.pairs import records_to_sam
     g = synth.make_genome(12, 60, 5000, 3, seed=5)
@@ -124,14 +127,56 @@ def main():
     sam = records_to_sam(rec, g.names)
     ws_kb = [5, 10, 2]
     wsz, windows, chr2window, _, _ = O.fasta2windows(g.contig_sizes, ws_kb, minSize=2000, filterwindows=0)
-    arrays = O.bam2arrays(windows, wsz, chr2window, [sam], 10)
+    ref = R.load("bam2clusters.py", sam_sources={"a.bam": sam})
+    arrays = ref.bam2arrays(windows, wsz, chr2window, ["a.bam"], 10, verbose=0)
+    for a, b in zip(arrays, O.bam2arrays(windows, wsz, chr2window, [sam], 10)):
+        assert np.array_equal(a, b)
     out = dict(records=rec.view(np.int32).reshape(-1, 6), sizes=g.sizes, window_bp=np.array(wsz))
     for ii, a in enumerate(arrays):
         out["array%d" % ii] = a
         out["offsets%d" % ii] = np.array([chr2window[ii].get(c, -1) for c in g.names], dtype=np.int32)
-    arrays_upto = O.bam2arrays(windows[:1], wsz[:1], chr2window[:1], [sam], 10, upto=1500)
+    arrays_upto = ref.bam2arrays(windows[:1], wsz[:1], chr2window[:1], ["a.bam"], 10, upto=1500, verbose=0)
     out["array0_upto1500"] = arrays_upto[0]
     np.savez_compressed(os.path.join(GOLD, "binning.npz"), **out)
+
+    # --- reference-executed outputs of the elementwise / block functions (tests/test_oracle_pinned.py re-checks the
+    # restatement against them where /root/reference does not exist; the GPU parity tests use the same inputs) -----
+    b2c, b2s, a2s = ref, R.load("bam2scaffolds.py"), R.load("array2scaffolds.py")
+    n = 96
+    hic = hic_like_counts(n, 31)
+    hic[[7, 50]] = 0
+    hic[:, [7, 50]] = 0
+    sym = hic + hic.T - np.diag(hic.diagonal())
+    keys = np.array(["ctg%02d" % (k // 8) for k in range(n)])
+    bp = np.array([(0, 5000) if k % 8 else (0, 3100) for k in range(n)])
+    x = np.abs(np.random.default_rng(3).normal(3, 2, (40, 40))) + 0.01
+    out = dict(hic_f32=hic, sym_f32=sym, keys=keys, bin_position=bp, dist_x=x,
+               transform_logmax=a2s.transform(hic.copy()),
+               transform_logmax_f64=a2s.transform(hic.astype(np.float64)),
+               normalize_rows=a2s.normalize_rows(sym.copy()),
+               average_reduce_2d=a2s._average_reduce_2d(sym, keys),
+               distance_func=b2c.distance_func(x, 0.5, 1.1),
+               distance_func_f32=b2c.distance_func(x.astype(np.float32) + np.float32(1), 0.5, 1.1),
+               normalize_diagional=b2c.normalize_diagional(hic.copy(), keys, bp)[0],
+               normalize_window_size=b2s.normalize_window_size(hic.copy(), keys, bp)[0])
+    # contigs2scaffold-shaped case: join_scaffolds (both variants), tree2scaffold, get_clusters, newick
+    rng = np.random.default_rng(3)
+    nwin = rng.integers(1, 7, 9)
+    bin_chr = np.array([("ctg%02d" % c) for c, k in enumerate(nwin) for _ in range(k)])
+    m = len(bin_chr)
+    i, j = np.indices((m, m))
+    d = np.triu(rng.poisson(30.0 / (1.0 + np.abs(i - j)) + 0.2).astype(np.float32))
+    d += d.T - np.diag(d.diagonal())
+    names = list(np.unique(bin_chr))
+    red = a2s._average_reduce_2d(d, bin_chr)
+    import scipy.cluster.hierarchy as sch
+    Z = sch.linkage((a2s.transform(red).astype(np.float64) + rng.random(red.shape) * 1e-9)[np.triu_indices(len(names), 1)], "ward")
+    out.update(sc_d=d, sc_bin_chr=bin_chr, sc_Z=Z, sc_newick=np.array(a2s.distance_matrix2tree(Z, names).write()))
+    for mw in (1, 2, 3):
+        for tag, mod in (("b2s", b2s), ("a2s", a2s)):
+            sc = mod.tree2scaffold(a2s.distance_matrix2tree(Z, names), d, bin_chr, None, mw)
+            out["sc_%s_mw%d" % (tag, mw)] = np.array(["%s%s" % (c, "-" if o else "+") for c, o in sc])
+    np.savez_compressed(os.path.join(GOLD, "reference_pinned.npz"), **out)
     print("golden vectors written to", GOLD)
 
 

@@ -453,6 +453,38 @@ def test_distance_func_and_logmax():
     assert _ulp_diff(transform(d), O.transform_logmax(d)) <= 4
 
 
+@pytest.mark.parametrize("b", [0.05, 0.1, 0.4, 1.21, 7.0])
+def test_distance_func_small_and_large_b(b):
+    """the series fast path must not be taken when |z| = |log1p(y)/b| is not small (b from curve_fit can
+    be anything); checked on near-1 arguments (the fast-path domain) and on ordinary ones."""
+    from hicembler_b200.bam2clusters import distance_func
+    rng = np.random.default_rng(4)
+    x = np.concatenate([1.0 + rng.random(4000) * 2.0 ** -10, 1.0 + rng.random(4000) * 2.0 ** -30, 1.0 + rng.random(4000) * 50])
+    x = x.reshape(120, 100)
+    want, got = O.distance_func(x, 0.37, b), distance_func(x, 0.37, b)
+    assert got.dtype == np.float64 and _ulp_diff(got, want) <= 4
+
+
+def test_distance_func_float32_matches_reference_dtype(golden_dir):
+    """float32 contacts are evaluated in float32 by the reference (contigs2scaffold path)."""
+    from hicembler_b200.bam2clusters import distance_func
+    z = np.load(os.path.join(golden_dir, "reference_pinned.npz"))
+    x32 = z["dist_x"].astype(np.float32) + np.float32(1)
+    want = z["distance_func_f32"]                     # the reference's own distance_func on float32 input
+    assert want.dtype == np.float32 and np.array_equal(O.distance_func(x32, 0.5, 1.1), want)
+    got = distance_func(x32, 0.5, 1.1)
+    assert got.dtype == np.float32
+    assert np.max(np.abs(got.view(np.int32).astype(np.int64) - want.view(np.int32))) <= 4        # CUDA powf: 2 ulp documented
+    # and through the working-matrix kernel (float32 block means -> ward linkage input)
+    from hicembler_b200 import ops
+    n = x32.shape[0]
+    W, _ = ops.transform_to_working(torch.from_numpy(x32).cuda(), ops.KIND_POWER_RAW, 0.5, 1.1)
+    w = W.cpu().numpy()[np.triu_indices(n, 1)]
+    w32 = w.astype(np.float32)
+    assert np.array_equal(w32.astype(np.float64), w)    # float32 values widened
+    assert np.max(np.abs(w32.view(np.int32).astype(np.int64) - want[np.triu_indices(n, 1)].view(np.int32))) <= 4
+
+
 def test_condense_and_working_matrix():
     from hicembler_b200 import ops
     d = np.random.default_rng(8).random((77, 77))
