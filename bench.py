@@ -9,9 +9,11 @@ One "step" = one pass of the hot path over one batch of P synthetic read pairs:
 `value`  : pairs/s with the 24-byte records already resident in HBM.
 `e2e`    : the same through the public call with HOST (pinned) records: H2D copy of the records and
            the linkage array coming back to the host are inside the timed region.
-N > 1    : the single-dendrogram linkage does not shard ("replicas only"): every rank runs
-           an independent job of the same shape (weak scaling, no data-path collective).  The
-           row-sharded Sinkhorn with its NCCL all-reduce is measured by --mode sinkhorn.
+N > 1    : ONE job over N GPUs (strong scaling): matrix build, fold and Sinkhorn-Knopp are sharded by row block
+           (every rank bins the slice of the record stream that falls into its rows; host records cross each rank's
+           own PCIe link), the exchanges are peer-memory reads over NVLink inside the kernels, and the dendrogram --
+           which does not shard ("replicas only") -- is built on rank 0.  --mode replicas runs N
+           independent jobs instead (weak scaling, round-1 behaviour); --mode sinkhorn the row-sharded fit alone.
 Prints ONE JSON line on rank 0.
 """
 import argparse
@@ -133,11 +135,26 @@ def cpu_reference_sample(cfg, seed=1, n_sample_pairs=1_000_000, n_small=4000):
     t0 = time.perf_counter()
     sch.linkage(y, cfg["method"])   # the reference's own library call (array2scaffolds.py:163)
     t_link = time.perf_counter() - t0
+    # the LITERAL normalize() of the reference (O(N^3): two dense GEMMs with diagonal matrices per iteration,
+    # sinkhorn_knopp.py:146-148) at two small sizes, next to the matvec form used for the extrapolation
+    literal = {}
+    for nl in (2000, 4000):
+        if nl > n:
+            continue
+        dl = d[:nl, :nl].copy()
+        t0 = time.perf_counter()
+        skl = O.SinkhornKnopp(max_iter=1000, epsilon=0.00001)
+        O.normalize(dl, sk=skl, materialize=True)
+        literal[str(nl)] = {"seconds": time.perf_counter() - t0, "iterations": skl._iterations}
     f = (N / n) ** 2
     total = t_bin * (P / S) + (t_sk + t_tr + t_link) * f
     return dict(value=P / total, seconds_extrapolated=total,
                 parts=dict(bin_s=t_bin, bin_pairs=S, sinkhorn_s=t_sk, sk_iterations=sk._iterations,
-                           transform_condense_s=t_tr, linkage_s=t_link, n_small=n),
+                           transform_condense_s=t_tr, linkage_s=t_link, n_small=n,
+                           sinkhorn_literal_D1PD2=literal,
+                           sinkhorn_literal_note="O(N^3) per iteration: ~%.0f h per fit at N=%d by the N^3 law; not used in the extrapolation"
+                                                 % ((literal.get("4000", literal.get("2000", {"seconds": 0}))["seconds"]
+                                                     * (N / (4000.0 if "4000" in literal else 2000.0)) ** 3) / 3600.0, N)),
                 sample=("%d-pair prefix binned by the literal bam2arrays loop (single process, as the reference), "
                         "linear in P; Sinkhorn (matvec form), distance_func+condense and scipy %s linkage on a "
                         "%d-window matrix, scaled by (N/n)^2 = %.0f" % (S, cfg["method"], n, f)))
@@ -160,7 +177,11 @@ def run_reference(args, cfg, rank, world):
             "cpu_baseline": {"value": res["value"], "unit": UNIT, "cores": cores, "kind": "port",
                              "sample": res["sample"], "parts": res["parts"]},
             "e2e": {"value": res["value"], "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
-            "sample_wall_s": t_all}
+            "extrapolated": True,
+            "extrapolation": "value and ms_per_step are EXTRAPOLATED from the bounded sample described in cpu_baseline.sample "
+                             "(linear in pairs for the binning loop, (N/n)^2 for the matrix stages); measured_wall_s is what the "
+                             "sample itself took",
+            "measured_wall_s": t_all, "sample_wall_s": t_all}
     print(json.dumps(line), flush=True)
 
 
@@ -288,24 +309,26 @@ def run_ours(args, cfg, rank, world, local_rank):
                                              "sinkhorn": "k_colpass+k_rowpass", "transform": "k_transform_tile64",
                                              "linkage": "kr_light+kr_heavy" if lst.get("engine") == "rounds" else "k_nnchain"}[dominant],
                      peak_source=peak_src)
-    if dominant == "linkage" and lst.get("engine") == "rounds" and kernel_us and kernel_us.get("heavy"):
-        # dominant KERNEL = kr_heavy (merged-row builds + exact rescans + the initial scan) with kb_rebuild, the same
-        # work done as one merge+compact pass in the bulk rounds: all their launches of one
-        # step; achieved = algorithmic bytes of those launches / their summed CUDA-event durations
-        heavy_ms = (kernel_us["heavy"] + kernel_us["initial_scan"]) * 1e-3
-        b = 8.0 * lst["rescan_cols"] + 24.0 * lst["build_cols"]
-        a_ = b / (heavy_ms * 1e-3) / 1e9
-        launches = lst["rounds"] + 1
-        ncu = NCU_TRAFFIC.get(args.config, {}).get("kr_heavy")
+    if dominant == "linkage" and lst.get("engine") == "rounds" and kernel_us and kernel_us.get("rebuild"):
+        # dominant KERNEL of the dominant stage = kb_rebuild (the bulk rounds: merge + compact in one pass over the
+        # matrix): all its launches of one step; achieved = algorithmic bytes of those launches (8 B per live column
+        # of a free row, 24 B per live column of a merged row -- counted by the kernel's own retire step) / their summed
+        # CUDA-event durations.  The chain phase (kr_chain) is latency-bound by construction and reported next to it.
+        rb_ms = kernel_us["rebuild"] * 1e-3
+        b = 8.0 * lst["bulk_rescan_cols"] + 24.0 * lst["bulk_build_cols"]
+        a_ = b / (rb_ms * 1e-3) / 1e9
+        launches = max(1, lst["bulk_rounds"])
+        ncu = NCU_TRAFFIC.get(args.config, {}).get("kb_rebuild")
         main_roof = {"bound": "hbm", "achieved": a_, "peak": peak, "unit": "GB/s", "frac": a_ / peak,
                      "traffic": (ncu["dram_bytes"] / ncu["launches"]) if ncu else None,
-                     "kernel": "kr_heavy+kb_rebuild", "launches_per_step": launches, "ms": heavy_ms,
-                     "avg_launch_us": heavy_ms * 1e3 / launches, "algorithmic_bytes": b,
-                     "algorithmic_bytes_per_launch": b / launches, "share_of_step": heavy_ms / (ms_dev / K),
-                     "peak_source": peak_src,
-                     "kernel_us_per_step": kernel_us,
-                     "note": "latency-bound in the %d rounds of the chain phase (1-4 merges per round); the bulk rounds "
-                             "and the initial scan move most of the bytes, see profiles/" % lst["rounds"]}
+                     "kernel": "kb_rebuild", "launches_per_step": launches, "ms": rb_ms,
+                     "avg_launch_us": rb_ms * 1e3 / launches, "algorithmic_bytes": b,
+                     "algorithmic_bytes_per_launch": b / launches, "share_of_step": rb_ms / (ms_dev / K),
+                     "peak_source": peak_src, "kernel_us_per_step": kernel_us,
+                     "chain_phase": {"kernel": "kr_chain (persistent, cooperative)", "ms": kernel_us.get("chain", 0) * 1e-3,
+                                     "rounds": lst["rounds"], "us_per_round": kernel_us.get("chain", 0) / max(1, lst["rounds"] - lst["bulk_rounds"]),
+                                     "note": "1-4 merges per round: three grid barriers per round, latency-bound"},
+                     "linkage_stage_bytes": 8.0 * lst["rescan_cols"] + 24.0 * lst["build_cols"] + 24.0 * lst["light_updates"]}
     # launches per step: bin 8, fold 1, sinkhorn (colpass+finish)=2/pass ... counted from the call graph
     sk_launches = 0 if args.no_balance else res["sk_launches"]      # counted by ops._CudaSinkhornPasses
     link_launches = lst["launches"] if lst.get("engine") == "rounds" else 1     # counted by hc_linkage_rounds
@@ -315,6 +338,39 @@ def run_ours(args, cfg, rank, world, local_rank):
         c = cpu_reference_sample(cfg)
         cpu = {"value": c["value"], "unit": UNIT, "cores": os.cpu_count(), "kind": "port", "sample": c["sample"],
                "parts": c["parts"]}
+    extra, bam = None, None
+    if world == 1 and not args.no_extra_cases:
+        # what the headline does not show: workloads with exact distance ties, where the round-parallel engine cannot
+        # certify fastcluster's merge order and the exact serial engine takes over (one timed step each)
+        extra = {}
+        del host_wire, staging
+        torch.cuda.empty_cache()
+
+        def one_case(rec, off, **kw):
+            pairs_to_dendrogram(rec, off, ws, N, mapq=10, params=PARAMS, method=cfg["method"], workspace=workspace,
+                                engine=args.engine, **kw)
+            torch.cuda.synchronize()
+            c0, c1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            c0.record()
+            tm = StageTimer(True)
+            r_ = pairs_to_dendrogram(rec, off, ws, N, mapq=10, params=PARAMS, method=cfg["method"], workspace=workspace,
+                                     engine=args.engine, timer=tm, **kw)
+            c1.record()
+            torch.cuda.synchronize()
+            ls = r_["linkage_stats"]
+            return {"ms_per_step": c0.elapsed_time(c1), "linkage_engine": ls.get("engine"), "stage_ms": tm.result_ms(),
+                    "fallback_reason": (ls.get("fallback_from_rounds") or {}).get("reason"),
+                    "certified_merges_before_fallback": (ls.get("fallback_from_rounds") or {}).get("merges")}
+        extra["no_balance"] = dict(one_case(records, offsets, balance=False),
+                                   what="normalize() off = the reference at HEAD (bam2clusters.py:512): count-derived distances")
+        g1 = synth.make_genome(cfg["n_contigs"], N, ws, cfg["n_chrom"], seed=1, min_tail=1)
+        rec1 = synth.make_pairs(g1, P, seed=1, device=dev)
+        off1 = torch.from_numpy(g1.window_offsets().astype(np.int32)).to(dev)
+        extra["min_tail_1"] = dict(one_case(rec1, off1, balance=not args.no_balance),
+                                   what="contigs with trailing windows too short to receive a read midpoint: identical empty rows")
+        del rec1
+        torch.cuda.empty_cache()
+        bam = bam_leg(cfg, offsets, ws, N, min(args.bam_records, P), dev, workspace, args.engine)
     total_pairs = float(P) * world * K
     line = {
         "metric": METRIC, "value": total_pairs / (ms_dev * 1e-3), "unit": UNIT, "n_gpus": world, "steps": K,
@@ -341,10 +397,189 @@ def run_ours(args, cfg, rank, world, local_rank):
         "linkage": lst,
         "bin_stats": res["stats"],
         "cpu_baseline": cpu,
+        "tie_heavy_cases": extra,
+        "e2e_bam": bam,
     }
     print(json.dumps(line), flush=True)
     if world > 1:
         dist.destroy_process_group()
+
+
+def run_sharded(args, cfg, rank, world, local_rank):
+    """--gpus N > 1: ONE pairs -> Z job over N GPUs.  Matrix build, fold and Sinkhorn-Knopp are row-sharded
+    (pipeline.sharded_pairs_to_dendrogram), the dendrogram is built on rank 0.  Total work is fixed: strong scaling."""
+    import torch
+    import torch.distributed as dist
+    from hicembler_b200 import ops, synth
+    from hicembler_b200.pairs import pack_pairs16
+    from hicembler_b200.parallel import ProcessGroup, RowShard
+    from hicembler_b200.pipeline import StageTimer, shard_plan, sharded_pairs_to_dendrogram
+
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    dist.init_process_group("nccl", device_id=dev)
+    N, P, ws = cfg["n_windows"], cfg["n_pairs"], cfg["window_bp"]
+    # every rank generates the same synthetic stream (same seed) and keeps only its slice of it
+    g = synth.make_genome(cfg["n_contigs"], N, ws, cfg["n_chrom"], seed=1, min_tail=cfg.get("min_tail", 1))
+    records = synth.make_pairs(g, P, seed=1, device=dev)
+    offsets = torch.from_numpy(g.window_offsets().astype(np.int32)).to(dev)
+    pg = ProcessGroup()
+    plan = shard_plan(records, g.window_offsets(), ws, N, world)       # the job of the BAM index (.bai)
+    a, b = plan[rank]
+    local = records[a:b].clone()
+    del records
+    torch.cuda.synchronize()
+    torch.cuda.empty_cache()
+    shard = RowShard(N, pg, dev)
+    workspace = torch.empty(int(ops._lib.lib().hc_bin_pairs_workspace_bytes(b - a, max(shard.nrows, 1))), dtype=torch.uint8, device=dev)
+    balance = not args.no_balance
+
+    def step(rec, timer=None):
+        return sharded_pairs_to_dendrogram(shard, rec, offsets, ws, mapq=10, params=PARAMS, method=cfg["method"], balance=balance,
+                                           plan=plan, timer=timer, engine=args.engine, workspace=workspace, local_slice=True)
+
+    def barrier():
+        torch.cuda.synchronize()
+        dist.barrier()
+        torch.cuda.synchronize()
+
+    for _ in range(args.warmup):
+        res = step(local)
+    barrier()
+    sampler = ClockSampler(local_rank) if rank == 0 else None
+    stage_ms = {}
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(args.steps):
+        timer = StageTimer(True)
+        res = step(local, timer)
+        for k, v in timer.result_ms().items():
+            stage_ms[k] = stage_ms.get(k, 0.0) + v
+    e1.record()
+    barrier()
+    ms_dev = e0.elapsed_time(e1)
+    # end to end: every rank copies ITS slice of the 16-byte wire records from pinned host memory over its own PCIe link
+    packed = pack_pairs16(local) if args.wire == 16 else local
+    host_wire = torch.empty(packed.shape, dtype=torch.int32, pin_memory=True)
+    host_wire.copy_(packed)
+    del packed
+    staging = {}
+    torch.cuda.synchronize()
+
+    def step_e2e():
+        return sharded_pairs_to_dendrogram(shard, host_wire, offsets, ws, mapq=10, params=PARAMS, method=cfg["method"],
+                                           balance=balance, plan=plan, engine=args.engine, workspace=workspace,
+                                           local_slice=True, staging=staging)
+    for _ in range(min(args.warmup, 1)):
+        step_e2e()
+    barrier()
+    e2, e3 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e2.record()
+    for _ in range(args.steps):
+        res_e = step_e2e()
+    e3.record()
+    barrier()
+    ms_e2e = e2.elapsed_time(e3)
+    clocks = sampler.stop() if sampler else None
+    K = args.steps
+    t = torch.tensor([ms_dev, ms_e2e] + [stage_ms.get(k, 0.0) for k in ("h2d", "bin_pairs", "fold", "sinkhorn", "transform", "linkage")],
+                     dtype=torch.float64, device=dev)
+    tmax = t.clone()
+    dist.all_reduce(tmax, op=dist.ReduceOp.MAX)
+    seen = torch.ones(1, device=dev)
+    dist.all_reduce(seen)
+    ms_dev, ms_e2e = tmax[0].item(), tmax[1].item()
+    if rank == 0:
+        peak, peak_src = load_peaks()
+        lst = res["linkage_stats"]
+        stage0 = {k: v / K for k, v in stage_ms.items()}
+        stage_max = {k: tmax[2 + i].item() / K for i, k in enumerate(("h2d", "bin_pairs", "fold", "sinkhorn", "transform", "linkage"))}
+        sk_it = res.get("sk_iterations", 0)
+        front = sum(stage_max[k] for k in ("bin_pairs", "fold", "sinkhorn"))
+        # per-GPU rooflines of the sharded stages: algorithmic bytes of one rank's share / its time
+        rows = shard.nrows
+        by = {"bin_pairs": 24.0 * (b - a) + 4.0 * rows * N, "fold": 12.0 * rows * N,
+              "sinkhorn": res.get("sk_passes", 0) * 4.0 * rows * N,
+              "transform": 4.0 * N * (N - 1) / 2 + 8.0 * N * N}
+        roof = {}
+        for k, bb in by.items():
+            ms = stage0.get(k)
+            if ms and bb:
+                aa = bb / (ms * 1e-3) / 1e9
+                roof[k] = {"bound": "hbm" if k != "transform" else "hbm+nvlink", "achieved": aa, "peak": peak, "unit": "GB/s",
+                           "frac": aa / peak, "traffic": None, "ms": ms, "algorithmic_bytes": bb, "scope": "rank 0"}
+        link_ms = stage0.get("linkage", 0.0)
+        line = {
+            "metric": METRIC, "value": float(P) * K / (ms_dev * 1e-3), "unit": UNIT, "n_gpus": world, "steps": K,
+            "warmup": args.warmup, "ms_per_step": ms_dev / K, "higher_is_better": True, "scaling": "strong",
+            "vs_baseline": None, "dtype": "u32 counts, f32 matrix, f64 Sinkhorn vectors / distances", "data": "synthetic",
+            "config": {"workload": cfg["name"], "n_contigs": cfg["n_contigs"], "n_windows": N, "n_pairs": P, "window_bp": ws,
+                       "method": cfg["method"], "balance": balance,
+                       "l2": "inputs larger than L2 (records %.1f GB, matrix %.1f GB over %d ranks)" % (24e-9 * P, 4e-9 * N * N, world),
+                       "min_tail_bp": cfg.get("min_tail", 1), "linkage_engine": lst.get("engine"),
+                       "parallelism": "row-sharded x%d (bin + fold + Sinkhorn sharded by row block, peer-memory exchanges over "
+                                      "NVLink inside the kernels; linkage on rank 0)" % world,
+                       "rows_per_rank": shard.per},
+            "e2e": {"value": float(P) * K / (ms_e2e * 1e-3), "unit": UNIT, "h2d_bytes_per_step": int(args.wire * P),
+                    "h2d_bytes_per_step_per_rank": int(args.wire * (b - a)), "d2h_bytes_per_step": int((N - 1) * 32 + 128),
+                    "ms_per_step": ms_e2e / K, "host_record_bytes": args.wire,
+                    "api": "hicembler_b200.pipeline.sharded_pairs_to_dendrogram (each rank: its slice of the pinned host "
+                           "records over its own PCIe link -> Z on rank 0's host)"},
+            "gpu_launches": int(K * 2 * (12 + 1 + res.get("sk_launches", 0) + 1 + lst.get("launches", 1))),
+            "clocks": clocks,
+            "roofline": dict(roof.get("sinkhorn" if balance else "bin_pairs", {}), kernel="kb_colpass+kb_rowpass (row-sharded Sinkhorn passes)"
+                             if balance else "k_bin_tiles", peak_source=peak_src,
+                             note="dominant SHARDED kernel; the step is dominated by the single-GPU linkage (see amdahl)"),
+            "stage_rooflines": roof,
+            "stage_ms": stage0, "stage_ms_max_over_ranks": stage_max,
+            "comm_nranks_seen": int(seen.item()),
+            "amdahl": {"linkage_ms_on_one_gpu": link_ms, "sharded_front_end_ms": front,
+                       "note": "the dendrogram of ONE matrix is a serial merge sequence and runs on one GPU: the step can never be "
+                               "faster than linkage + transform-gather, whatever N"},
+            "seconds_pairs_to_dendrogram": ms_dev / K * 1e-3,
+            "sinkhorn": {"iterations": sk_it, "stop": res.get("sk_stop")},
+            "linkage": lst, "bin_stats": res["stats"], "cpu_baseline": None,
+        }
+        print(json.dumps(line), flush=True)
+    shard.close()
+    dist.destroy_process_group()
+
+
+def bam_leg(cfg, offsets, ws, N, n_records, dev, workspace, engine):
+    """e2e_bam: BGZF file -> native multi-threaded decoder (hc_bam_next) -> pinned 16-byte records -> host entry -> Z,
+    on a stated slice of the workload (writing the full 500 M-record file is ~100 GB)."""
+    import torch
+    from hicembler_b200 import synth
+    from hicembler_b200.pairs import read_bam_native, write_bam_fixed
+    from hicembler_b200.pipeline import host_pairs_to_dendrogram
+    g = synth.make_genome(cfg["n_contigs"], N, ws, cfg["n_chrom"], seed=1, min_tail=cfg.get("min_tail", 1))
+    rec = synth.records_numpy(synth.make_pairs(g, n_records, seed=7))
+    path = os.path.join(tempfile.gettempdir(), "hc_bench_%d.bam" % os.getpid())
+    try:
+        raw = write_bam_fixed(path, rec, g.names, g.sizes)
+        size = os.path.getsize(path)
+        read_bam_native(path, wire=16, side_arrays=False, pinned=True)          # warm the page cache
+        t0 = time.perf_counter()
+        _, _, host, _, _ = read_bam_native(path, wire=16, side_arrays=False, pinned=True)
+        t_dec = time.perf_counter() - t0
+        staging = {}
+        kw = dict(staging=staging, mapq=10, params=PARAMS, method=cfg["method"], balance=True, workspace=workspace, engine=engine)
+        host_pairs_to_dendrogram(host, offsets, ws, N, **kw)
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        _, _, host, _, _ = read_bam_native(path, wire=16, side_arrays=False, pinned=True)
+        out = host_pairs_to_dendrogram(host, offsets, ws, N, **kw)
+        torch.cuda.synchronize()
+        t_all = time.perf_counter() - t0
+    finally:
+        if os.path.exists(path):
+            os.unlink(path)
+    return {"records": int(n_records), "bam_bytes": int(size), "uncompressed_bytes": int(raw), "decode_s": t_dec,
+            "decoder_gb_per_s_uncompressed": raw / t_dec / 1e9, "decoder_records_per_s": n_records / t_dec,
+            "threads": os.cpu_count(), "seconds_bam_to_dendrogram": t_all, "value": n_records / t_all, "unit": UNIT,
+            "linkage_engine": out["linkage_stats"].get("engine"),
+            "note": "BGZF inflate + CRC + record decode on the host cores, then the same host entry as `e2e`; a %d-record slice "
+                    "(%.1f %% of the workload's pairs) of the %d-window job" % (n_records, 100.0 * n_records / cfg["n_pairs"], N)}
 
 
 def run_sinkhorn_mode(args, cfg, rank, world, local_rank):
@@ -413,7 +648,9 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--config", default=os.environ.get("HC_BENCH_CONFIG", "C3"))
-    ap.add_argument("--mode", default="pipeline", choices=["pipeline", "sinkhorn"])
+    ap.add_argument("--mode", default="pipeline", choices=["pipeline", "sinkhorn", "replicas"])
+    ap.add_argument("--no-extra-cases", action="store_true", help="skip the tie-heavy cases and the BAM leg (N = 1 only)")
+    ap.add_argument("--bam-records", type=int, default=5_000_000, help="records of the BGZF file of the e2e_bam leg")
     ap.add_argument("--n", type=int, default=0, help="matrix size for --mode sinkhorn")
     ap.add_argument("--no-balance", action="store_true", help="reference HEAD behaviour: normalize() off")
     ap.add_argument("--no-cpu-baseline", action="store_true")
@@ -438,6 +675,8 @@ def main():
         return run_reference(args, cfg, rank, world)
     if args.mode == "sinkhorn":
         return run_sinkhorn_mode(args, cfg, rank, world, local_rank)
+    if world > 1 and args.mode != "replicas":
+        return run_sharded(args, cfg, rank, world, local_rank)
     run_ours(args, cfg, rank, world, local_rank)
 
 

@@ -26,6 +26,8 @@ SIGNATURES = {
     "hc_bin_pairs_workspace_bytes": (_sz, [_i64, _i64]),
     "hc_bin_pairs": (C.c_int, [_p, _i64, _p, _p, _p, _i32, _u32, _i32, _i32, _u32, _i32, _i32, _p,
                                _p, _sz, C.c_int, _p, _p]),
+    "hc_bin_pairs_stats": (C.c_int, [_p, _p, _p]),
+    "hc_bin_pairs_multi": (C.c_int, [_p, _i64, _i32, _p, _p, _i32, _p, _p, _i32, _u32, _p, C.c_int, _p, _sz, _p, _p]),
     "hc_upto_cutoff": (C.c_int, [_p, _i64, _p, _i32, _i32, _u32, _i64, _p, _sz, _p, _p, _p]),
     "hc_contig_region_filter": (C.c_int, [_p, _i64, _p, _p, _p, _p, _i32, _i32, _i32, _i32, _u32,
                                           _p, _p, _p]),
@@ -45,6 +47,15 @@ SIGNATURES = {
     "hc_sk_apply": (C.c_int, [_p, C.c_int, _i32, _i32, _dbl, _p, _p, _p, C.c_int, _p]),
     "hc_transform_to_working": (C.c_int, [_p, C.c_int, _i32, C.c_int, _dbl, _dbl, _p, _p, _dbl,
                                           C.c_int, _p, _p, _p]),
+    "hc_transform_gather": (C.c_int, [_p, _i32, _i32, C.c_int, _i32, C.c_int, _dbl, _dbl, _p, _p, _dbl, C.c_int, _p, _p, _p]),
+    "hc_shared_alloc": (C.c_int, [_sz, _p, _p]),
+    "hc_shared_free": (C.c_int, [_p]),
+    "hc_shared_open": (C.c_int, [_p, _p]),
+    "hc_shared_close": (C.c_int, [_p]),
+    "hc_fold_block": (C.c_int, [_p, _i32, _i32, _i32, _i32, _flt, _p, _p, _p]),
+    "hc_sk_exchange_bytes": (_sz, [_i32]),
+    "hc_sk_fit_block_workspace_bytes": (_sz, [_i32, _i32]),
+    "hc_sk_fit_block": (C.c_int, [_p, C.c_int, _i32, _i32, _dbl, _dbl, _i32, _i32, _p, _i32, _i32, _p, _p, _sz, _p, _p, _p, _p]),
     "hc_transform": (C.c_int, [_p, C.c_int, _i64, C.c_int, _dbl, _dbl, _p, C.c_int, _p]),
     "hc_condense": (C.c_int, [_p, C.c_int, _i32, _p, _p]),
     "hc_expand_condensed": (C.c_int, [_p, _i32, C.c_int, _p, _p, _p]),
@@ -58,6 +69,8 @@ SIGNATURES = {
     "hc_segment_mean_2d": (C.c_int, [_p, _i32, _p, _p, _i32, _p, _p, _p]),
     "hc_normalize_rows": (C.c_int, [_p, _i32, _p, _sz, _p]),
     "hc_block_sums4": (C.c_int, [_p, _i32, _p, _p, _p, _p, _i32, _p, _p]),
+    "hc_matrix_max": (C.c_int, [_p, C.c_int, _i64, _p, _i32, _p, _p]),
+    "hc_gather_elements": (C.c_int, [_p, _i32, _p, _p, _i64, _p, _p]),
     "hc_unpack_pairs16": (C.c_int, [_p, C.c_int64, _p, _p]),
     "hc_bam_open": (C.c_int, [C.c_char_p, _i32, _p, _p, _p]),
     "hc_bam_next": (C.c_int, [_p, _i32, _p, C.c_int64, _p, _p, _p]),

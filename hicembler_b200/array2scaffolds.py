@@ -7,7 +7,7 @@ import numpy as np
 import torch
 
 from . import ops
-from .bam2clusters import HCTree, array2Z
+from .bam2clusters import HCTree, array2Z, logger
 from .bam2scaffolds import _average_reduce_2d, normalize_rows  # noqa: F401
 
 
@@ -17,7 +17,8 @@ def transform(x):
     X = x if dev_in else torch.from_numpy(np.ascontiguousarray(x)).cuda()
     if X.dtype not in (torch.float32, torch.float64):
         X = X.double()
-    vmax2 = float(X.max().item()) + 1.0 if X.dtype == torch.float64 else float(np.float32(X.max().item()) + np.float32(1))
+    xmax = float(ops.matrix_max(X))            # hc_matrix_max: max(x+1) == max(x)+1 in the matrix dtype
+    vmax2 = xmax + 1.0 if X.dtype == torch.float64 else float(np.float32(xmax) + np.float32(1))
     out = ops.transform(X, ops.KIND_LOGMAX, vmax2)
     return out if dev_in else out.cpu().numpy()
 
@@ -108,3 +109,349 @@ def load_matrix(fname, chrs=[], remove_shorter=True, scaffolds=[], verbose=0, de
         ops.symmetrize_(X)
         ops.normalize_rows_(X)
     return (X if device_out else X.cpu().numpy()), bin_chr, bin_position, contig2size
+
+
+# ---------------------------------------------------------------------------------------------------------------
+# the .npz-driven variant of the pipeline (array2scaffolds.py:123-145, 199-256, 274-334, 356-452)
+# ---------------------------------------------------------------------------------------------------------------
+class LinkageTree:
+    """The tree ``distance_matrix2tree(Z, names)`` builds (array2scaffolds.py:123-145), on plain arrays and without
+    recursion.  Nodes 0..n-1 are the leaves, node n+k is row k of Z with children [Z[k,0], Z[k,1]] (:141-142); a
+    child's branch length is the merge height minus the distance of its farthest leaf (:137-138); the root keeps
+    ete3's default branch length 1.0, internal nodes its default name "".  The methods follow ete3's TreeNode where
+    the reference depends on it (get_farthest_leaf's running-sum arithmetic decides which leaf of an ultrametric tree
+    is "farthest"; see get_clusters)."""
+
+    def __init__(self, Z, names):
+        Z = np.asarray(Z, dtype=np.float64)
+        n = Z.shape[0] + 1
+        nn = 2 * n - 1
+        self.n, self.Z, self.names = n, Z, list(names)
+        self.children = [[] for _ in range(nn)]
+        self.up = [-1] * nn
+        self.dist = [1.0] * nn
+        self.name = [self.names[i] if i < n else "" for i in range(nn)]
+        for i in range(n - 1):
+            a, b, h = int(Z[i, 0]), int(Z[i, 1]), float(Z[i, 2])
+            self.dist[a] = h - self.get_farthest_leaf(a)[1]
+            self.dist[b] = h - self.get_farthest_leaf(b)[1]
+            self.children[n + i] = [a, b]
+            self.up[a] = self.up[b] = n + i
+        self.root = nn - 1
+
+    def leaves(self, node=None):
+        node = self.root if node is None else node
+        out, stack = [], [node]
+        while stack:
+            k = stack.pop()
+            ch = self.children[k]
+            if ch:
+                stack.extend(reversed(ch))
+            else:
+                out.append(k)
+        return out
+
+    def __len__(self):
+        return len(self.leaves())
+
+    def get_farthest_leaf(self, node=None):
+        """(leaf, distance): ete3 keeps ONE running distance, adds a branch on entering an internal node and subtracts
+        it on leaving; the first leaf (pre-order) with the strictly largest value wins."""
+        node = self.root if node is None else node
+        if not self.children[node]:
+            return node, 0.0
+        best, best_d, d = None, None, 0.0
+        stack = [(c, False) for c in reversed(self.children[node])]
+        while stack:
+            k, leaving = stack.pop()
+            if leaving:
+                d -= self.dist[k]
+            elif self.children[k]:
+                d += self.dist[k]
+                stack.append((k, True))
+                stack.extend((c, False) for c in reversed(self.children[k]))
+            else:
+                tot = d + self.dist[k]
+                if best_d is None or tot > best_d:
+                    best, best_d = k, tot
+        return best, best_d
+
+    def get_ancestors(self, node):
+        out, k = [], self.up[node]
+        while k >= 0:
+            out.append(k)
+            k = self.up[k]
+        return out
+
+    def remove_child(self, parent, child):
+        self.children[parent].remove(child)
+        self.up[child] = -1
+
+    def get_leaf_names(self):
+        return [self.name[k] for k in self.leaves()]
+
+    def write(self):
+        """newick as ete3 writes it (format 0): ``name:dist`` leaves, ``)1:dist`` internal nodes, %0.6g numbers"""
+        out, stack = [], [("n", self.root)]
+        while stack:
+            kind, k = stack.pop()
+            if kind == "t":
+                out.append(k)
+            elif self.children[k]:
+                out.append("(")
+                stack.append(("t", ")" if k == self.root else ")1:%0.6g" % self.dist[k]))
+                ch = self.children[k]
+                for q, c in enumerate(reversed(ch)):
+                    stack.append(("n", c))
+                    if q != len(ch) - 1:
+                        stack.append(("t", ","))
+            else:
+                out.append("%s:%0.6g" % (self.name[k], self.dist[k]))
+        return "".join(out) + ";"
+
+
+def distance_matrix2tree(Z, names):
+    """Return tree representation for distance matrix -- array2scaffolds.py:123-145."""
+    return LinkageTree(Z, names)
+
+
+def array2tree_scipy(d, names, outbase="", method="ward"):
+    """array2scaffolds.py's own array2tree (:160-179): linkage of d[np.triu_indices(n,1)] (scipy in the reference: the
+    GPU engines give the same tree whenever heights are distinct) -> distance_matrix2tree; ``.nw`` written."""
+    t = distance_matrix2tree(array2Z(d, method), names)
+    if outbase:
+        with open(outbase + ".nw", "w") as out:
+            out.write(t.write())
+    return t
+
+
+def get_clusters(outbase, t, contig2size, bin_chr):
+    """Return clusters from tree -- array2scaffolds.py:199-256.  The subtree hanging from the longest branch above
+    the farthest leaf is cut off until two leaves are left (:204-216), contigs are assigned to the cluster holding
+    most of their windows (:218-241).  Reference quirks kept: the cluster list is sized by the leaf count of the LAST
+    subtree and indexed by the 1-based subtree number (:232,241: slot 0 stays empty, IndexError when a number reaches
+    that size); IndexError when the longest branch is the root's default branch.  Contigs are visited in np.unique
+    order (the reference's Python-2 dict order is arbitrary).  ``t`` is consumed."""
+    from collections import Counter
+    logger(" Generating clusters from %s windows..." % len(t))
+    subtrees = []
+    while len(t) > 2:
+        n, dist = t.get_farthest_leaf()
+        anc = t.get_ancestors(n)
+        dists = [t.dist[a] for a in anc]
+        ai = dists.index(max(dists))
+        a = anc[ai]
+        if t.name[n]:
+            subtrees.append(a)
+        p = anc[ai + 1]
+        t.remove_child(p, a)
+    logger(" Assigning contigs to %s clusters..." % len(subtrees))
+    total = correct = 0
+    contig2cluster = {get_name(c): Counter() for c in np.unique(bin_chr)}
+    subtree_leaves = []
+    for i, subtree in enumerate(subtrees, 1):
+        subtree_leaves = t.leaves(subtree)
+        c = Counter(get_name(t.name[k]) for k in subtree_leaves if t.name[k])
+        total += len(subtree_leaves)
+        correct += c.most_common(1)[0][1]
+        for k, v in c.items():
+            if not k:
+                continue
+            contig2cluster[get_name(k)][i] += v
+    logger("  %s / %s [%.2f%s]" % (correct, total, 100. * correct / total, '%'))
+    logger(" Weak assignments...")
+    clusters = [[] for i in range(len(subtree_leaves))]
+    withoutCluster, weakCluster = [], []
+    for c, counter in contig2cluster.items():
+        if not counter:
+            withoutCluster.append(c)
+            continue
+        clusteri, count = counter.most_common(1)[0]
+        mfrac = 1. * count / sum(counter.values())
+        clusters[clusteri].append(c)
+        if mfrac < .66:
+            weakCluster.append(c)
+    logger("  %s bp in %s contigs without assignment." % (sum(contig2size[c] for c in withoutCluster), len(withoutCluster)))
+    logger("  %s bp in %s contigs having weak assignment." % (sum(contig2size[c] for c in weakCluster), len(weakCluster)))
+    clusters = [x for x in clusters if x]
+    outfile = outbase + ".clusters.tab"
+    logger(" Reporting clusters to: %s ..." % outfile)
+    totsize = 0
+    with open(outfile, "w") as out:
+        for i, cluster in enumerate(clusters, 1):
+            totsize += sum(contig2size[c] for c in cluster)
+            out.write("\t".join(cluster) + "\n")
+    logger("  %3s bp in %s clusters." % (totsize, len(clusters)))
+    return clusters
+
+
+def _diag_cells(indices1, indices2):
+    """window pairs behind the four sums of array2scaffolds.py:288-291 (d1[:i], d2[:i], d3[-i:], d4[-i:]) of the
+    reordered matrix _d = d[idx][:, idx], idx = indices1 + indices2, as four lists of (row, col) window indices"""
+    idx = list(indices1) + list(indices2)
+    n1, n2 = len(indices1), len(indices2)
+    i = n2 // 2
+    d1 = [(r, n1 + r) for r in range(n2)][:i]                                   # np.diag(_d, k=n1)
+    d2 = [(r, n2 + n1 - 1 - r) for r in range(n1)][:i]                          # np.diag(fliplr(_d[:n1, n2:]))
+    d3 = [(n1 - n2 + q, n2 + n1 - 1 - q) for q in range(n2)][-i:]               # np.diag(dflip, k=n2-n1)
+    d4 = [(r, n2 + r) for r in range(n1)][-i:]                                  # np.diag(_d, k=n2)
+    return [[(idx[r], idx[c]) for r, c in cells] for cells in (d1, d2, d3, d4)]
+
+
+def _plan_join_diag(scaffold1, scaffold2, contig2indices, minWindows):
+    from .bam2scaffolds import get_indices
+    indices1 = get_indices(scaffold1, contig2indices)
+    indices2 = get_indices(scaffold2, contig2indices)
+    if len(indices1) < len(indices2):
+        scaffold1, indices1, scaffold2, indices2 = scaffold2, indices2, scaffold1, indices1
+    if len(indices2) < minWindows:
+        return scaffold1, None, None
+    return scaffold1, scaffold2, _diag_cells(indices1, indices2)
+
+
+def _diag_sums(A, jobs):
+    """the four float32 sums of every job: one gather launch for the whole batch, then Python's ``sum`` over each
+    short list in the reference's order (``map(sum, ...)``, :291)"""
+    cells = [rc for job in jobs for part in job for rc in part]
+    vals = ops.gather_elements(A, [r for r, c in cells], [c for r, c in cells]) if cells else np.empty(0, np.float32)
+    out, pos = [], 0
+    for job in jobs:
+        sums = []
+        for part in job:
+            sums.append(sum(vals[pos:pos + len(part)]))
+            pos += len(part)
+        out.append(sums)
+    return out
+
+
+def join_scaffolds(scaffold1, scaffold2, d, contig2indices, minWindows=3):
+    """Join two adjacent scaffolds -- array2scaffolds.py:274-309 (orientation from the sums along the four
+    (anti)diagonals of the rectangle between the scaffolds; bam2scaffolds.py has the corner-block variant)."""
+    from .bam2scaffolds import _device_matrix, _oriented
+    scaffold1, scaffold2, job = _plan_join_diag(scaffold1, scaffold2, contig2indices, minWindows)
+    if job is None:
+        return scaffold1
+    return _oriented(scaffold1, scaffold2, _diag_sums(_device_matrix(d), [job])[0])
+
+
+def tree2scaffold(t, d, bin_chr, bin_position, minWindows):
+    """Scaffold contigs based on distance matrix and tree -- array2scaffolds.py:319-338, one gather launch per tree
+    level.  ``t``: LinkageTree (children [Z[k,0], Z[k,1]])."""
+    from .bam2scaffolds import _device_matrix, _oriented, get_contig2indices
+    Z, names = t.Z, t.names
+    contig2indices = get_contig2indices(bin_chr)
+    n = len(names)
+    scaffolds = [[(names[i], 0)] for i in range(n)] + [None] * (n - 1)
+    if n == 1:
+        return scaffolds[0]
+    A = _device_matrix(d)
+    left, right = Z[:, 0].astype(np.int64), Z[:, 1].astype(np.int64)
+    level = np.zeros(2 * n - 1, dtype=np.int64)
+    for k in range(n - 1):
+        level[n + k] = 1 + max(level[left[k]], level[right[k]])
+    order = np.argsort(level[n:], kind="stable")
+    bounds = np.flatnonzero(np.diff(level[n:][order])) + 1
+    for nodes in np.split(order, bounds):
+        pending, jobs = [], []
+        for k in nodes:
+            s1, s2, job = _plan_join_diag(scaffolds[left[k]], scaffolds[right[k]], contig2indices, minWindows)
+            if job is None:
+                scaffolds[n + k] = s1
+            else:
+                pending.append((k, s1, s2))
+                jobs.append(job)
+        for (k, s1, s2), sums in zip(pending, _diag_sums(A, jobs)):
+            scaffolds[n + k] = _oriented(s1, s2, sums)
+    return scaffolds[-1]
+
+
+def _contigs2scaffold(args):
+    """Combine contigs into scaffold -- array2scaffolds.py:356-365."""
+    infile, contigs, prev_scaffolds, minWindows = args
+    _d, _bin_chr, _bin_position, contig2size = load_matrix(infile, chrs=contigs, scaffolds=prev_scaffolds, device_out=True)
+    t = array2tree_scipy(transform(_average_reduce_2d(_d, _bin_chr)), np.unique(_bin_chr))
+    return tree2scaffold(t, _d, _bin_chr, _bin_position, minWindows)
+
+
+def clusters2scaffolds(clusters, infile, minWindows, prev_scaffolds, rank=0, world=1):
+    """Process clusters into scaffolds -- array2scaffolds.py:378-389.  The per-cluster trees are independent: with
+    ``world`` > 1 ranks every rank takes clusters rank, rank + world, ... (``None`` stands for the others; the
+    caller gathers) -- the natural multi-GPU use of the linkage."""
+    from .parallel import assign_round_robin
+    mine = set(assign_round_robin(len(clusters), rank, world))
+    scaffolds = []
+    for i, contigs in enumerate(clusters):
+        scaffolds.append(_contigs2scaffold((infile, contigs, prev_scaffolds, minWindows)) if i in mine else None)
+    return scaffolds
+
+
+def clusters2scaffolds_multi(clusters, infile, minWindows, prev_scaffolds, threads):
+    """array2scaffolds.py:367-376: the reference forks a Pool; a CUDA context does not survive fork, so the clusters
+    are processed in this process (and over the ranks of a torch.distributed job when one is initialised)."""
+    rank, world = 0, 1
+    try:
+        import torch.distributed as dist
+        if dist.is_available() and dist.is_initialized():
+            rank, world = dist.get_rank(), dist.get_world_size()
+    except ImportError:
+        pass
+    part = clusters2scaffolds(clusters, infile, minWindows, prev_scaffolds, rank, world)
+    if world == 1:
+        return part
+    import torch.distributed as dist
+    parts = [None] * world
+    dist.all_gather_object(parts, part)
+    return [next(p[i] for p in parts if p[i] is not None) for i in range(len(clusters))]
+
+
+def report_scaffolds(outbase, scaffolds, faidx, w=60):
+    """Save scaffolds -- array2scaffolds.py:391-416 ((contig, orientation) scaffolds without gaps)."""
+    totsize = 0
+    fastafn = outbase + ".scaffolds.fa"
+    with open(fastafn, "w") as out, open(outbase + ".scaffolds.tab", "w") as outscaffolds:
+        for i, scaffold in enumerate(scaffolds, 1):
+            if not scaffold:
+                continue
+            seqs, elements = [], []
+            for c, o in scaffold:
+                seqs.append(faidx.get_sequence(c, reverse=o))
+                elements.append("%s-" % c if o else "%s+" % c)
+            seq = "".join(seqs)
+            seq = "\n".join(seq[s:s + w] for s in range(0, len(seq), w))
+            out.write(">scaffold%s %s bp in %s contigs\n%s\n" % (i, len(seq), len(elements), seq))
+            outscaffolds.write("%s\n" % "\t".join(elements))
+            totsize += len(seq)
+    logger(" %s in %s scaffolds reported to %s" % (totsize, len(scaffolds), fastafn))
+    return fastafn
+
+
+def array2scaffolds(outbase, infile, infile2, fasta, threads, minWindows, scaffolds=[]):
+    """Return scaffolds computed for given matrix -- array2scaffolds.py:418-452.  (The reference's last step calls
+    ``report_scaffolds(outbase, infile, scaffolds, faidx)`` with one argument too many (:450) and cannot finish;
+    the intended call is made here -- DESIGN.md section 8.)"""
+    import sys
+    from .FastaIndex import FastaIndex
+    logger("Loading FastA...")
+    faidx = FastaIndex(fasta)
+    logger(" %s bp in %s contigs" % (faidx.genomeSize, len(faidx)))
+    logger("Loading matrix from %s ..." % infile)
+    d, bin_chr, bin_position, contig2size = load_matrix(infile, scaffolds=scaffolds, verbose=1, device_out=True)
+    logger(" matrix of %s windows for %s contigs summing %s bp" % (d.shape[0], len(contig2size), sum(contig2size.values())))
+    diff = set(contig2size.keys()).difference(faidx)
+    if diff:
+        sys.stderr.write("[ERROR] %s / %s contigs are missing from provided FastA!\n" % (len(diff), len(contig2size)))
+        sys.exit(1)
+    logger("Calculating linkage matrix & tree...")
+    names = ["%s %7sk" % (get_name(c), s // 1000) for c, (s, e) in zip(bin_chr, bin_position)]
+    t = array2tree_scipy(transform(d), names, outbase)
+    del d
+    logger("Assigning contigs to clusters/scaffolds...")
+    clusters = get_clusters(outbase, t, contig2size, bin_chr)
+    logger("Constructing scaffolds...")
+    if threads > 1:
+        scaffolds = clusters2scaffolds_multi(clusters, infile2, minWindows, scaffolds, threads)
+    else:
+        scaffolds = clusters2scaffolds(clusters, infile2, minWindows, scaffolds)
+    logger("Reporting %s scaffolds..." % len(scaffolds))
+    fastafn = report_scaffolds(outbase, scaffolds, faidx)
+    return scaffolds, fastafn

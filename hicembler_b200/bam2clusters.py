@@ -122,7 +122,31 @@ def contigs2windows(fasta, minSize=2000, verbose=0, genomeFrac=0.95, contigs=[])
 # ---------------------------------------------------------------------------------------------
 # K1: binning
 # ---------------------------------------------------------------------------------------------
-def bam2counts(windows, windowSize, chr2window, bam, mapq, upto=0, regions=[], names=None):
+_ONE_PASS_BYTES = 96 << 20      # all matrices of a multi-window-size call fit the 126 MB L2 together
+
+
+def _last_line_mapq(records, mapq, rmask, n_pairs):
+    """MAPQ of the last record among the first n_pairs that passes -q/-F/regions (None if there is none)."""
+    n = int(n_pairs)
+    step = 1 << 16
+    hi = n
+    while hi > 0:
+        lo = max(0, hi - step)
+        blk = records[lo:hi].cpu().numpy()
+        flag, q = blk[:, 5] & 0xffff, (blk[:, 5] >> 16) & 0xff
+        ok = ((flag & SKIP_FLAG) == 0) & (q >= int(mapq))
+        if rmask is not None:
+            m = rmask.cpu().numpy().astype(bool)
+            ref = blk[:, 0]
+            ok &= (ref >= 0) & (ref < len(m)) & m[np.clip(ref, 0, len(m) - 1)]
+        idx = np.flatnonzero(ok)
+        if len(idx):
+            return int(q[idx[-1]])
+        hi = lo
+    return None
+
+
+def bam2counts(windows, windowSize, chr2window, bam, mapq, upto=0, regions=[], names=None, mapq_shadowing=False):
     """Device fast path of bam2arrays: list of u32 count matrices (CUDA int32 tensors, FULL
     orientation: row = window of read 1) plus per-window-size stats.  ``ops.fold_counts`` turns
     them into the reference's arrays or straight into the symmetrised matrix."""
@@ -145,14 +169,33 @@ def bam2counts(windows, windowSize, chr2window, bam, mapq, upto=0, regions=[], n
                 i = i + lines - 1
             n_pairs = n_eff
         member = al.offsets(chr2window[0])
-        for ii in range(nws):
-            off = member if ii == 0 else al.offsets(chr2window[ii])
-            mode = 2 if counts[ii] is not None else 0
-            counts[ii], st = ops.bin_pairs(al.records, off, windowSize[ii], sizes[ii], mapq, member=member,
-                                           region_mask=rmask, n_pairs=n_pairs, out=counts[ii], mode=mode,
-                                           return_stats=True)
+        offs = [member] + [al.offsets(chr2window[ii]) for ii in range(1, nws)]
+
+        def add_stats(ii, st):
             stats[ii] = st if stats[ii] is None else {k: (stats[ii][k] + v if isinstance(v, int) and not isinstance(v, bool) else v)
                                                      for k, v in st.items()}
+        if 1 < nws <= 4 and sum(4 * n * n for n in sizes) <= _ONE_PASS_BYTES:
+            # the reference's inner loop (:154-161): every kept line goes into all window sizes -- one read of the
+            # records, matrices resident in L2 (the per-cluster 5 / 10 / 2 kb matrices of the scaffolding stage)
+            acc = counts[0] is not None
+            outs, st = ops.bin_pairs_multi(al.records, offs, windowSize, sizes, mapq, region_mask=rmask, n_pairs=n_pairs,
+                                           outs=counts, accumulate=acc)
+            for ii in range(nws):
+                counts[ii] = outs[ii]
+                add_stats(ii, st)
+        else:
+            for ii in range(nws):
+                mode = 2 if counts[ii] is not None else 0
+                counts[ii], st = ops.bin_pairs(al.records, offs[ii], windowSize[ii], sizes[ii], mapq, member=member,
+                                               region_mask=rmask, n_pairs=n_pairs, out=counts[ii], mode=mode,
+                                               return_stats=True)
+                add_stats(ii, st)
+        if mapq_shadowing and al.records.shape[0]:
+            # bam2clusters.py:145 unpacks the line's MAPQ into ``mapq`` itself, so the reference filters the NEXT
+            # BAM with -q <MAPQ of the last line it read from this one>
+            last = _last_line_mapq(al.records, mapq, rmask, n_pairs)
+            if last is not None:
+                mapq = last
     for ii in range(nws):
         if counts[ii] is None:
             counts[ii] = torch.zeros((sizes[ii], sizes[ii]), dtype=torch.int32, device="cuda")
@@ -160,12 +203,14 @@ def bam2counts(windows, windowSize, chr2window, bam, mapq, upto=0, regions=[], n
 
 
 def bam2arrays(windows, windowSize, chr2window, bam, mapq, upto=0, regions=[], verbose=1, threads=1,
-               device_out=False, names=None):
+               device_out=False, names=None, mapq_shadowing=False):
     """Return contact matrices based on BAM -- bam2clusters.py:128-166.
 
     One float32 (N_ii, N_ii) upper-triangular (incl. diagonal) array per window size.  Raises
-    IndexError / KeyError where the reference's loop would (:155,161)."""
-    counts, stats = bam2counts(windows, windowSize, chr2window, bam, mapq, upto, regions, names)
+    IndexError / KeyError where the reference's loop would (:155,161).  ``mapq_shadowing=True`` reproduces the
+    reference's accidental re-use of the last line's MAPQ as ``-q`` for every BAM after the first (:145 overwrites the
+    ``mapq`` argument); the default keeps the caller's threshold for all BAMs."""
+    counts, stats = bam2counts(windows, windowSize, chr2window, bam, mapq, upto, regions, names, mapq_shadowing)
     arrays = []
     for cnt in counts:
         a, _ = ops.fold_counts(cnt, "upper", inplace=True)
@@ -453,6 +498,16 @@ def array2tree(d, names, outbase="", method="ward"):
     return t
 
 
+def _dist_rank_world():
+    try:
+        import torch.distributed as dist
+        if dist.is_available() and dist.is_initialized():
+            return dist.get_rank(), dist.get_world_size()
+    except ImportError:
+        pass
+    return 0, 1
+
+
 def cluster_contigs(outbase, d, bin_chr, bin_position, threads=4, frac=0.66, iterations=30, maxnumchr=500,
                     seed=0, dpi=100, minchr=3, nchr=0, selections=None, return_details=False):
     """Estimate number of chromosomes and assign contigs to chromosomes -- bam2clusters.py:406-457.
@@ -470,13 +525,24 @@ def cluster_contigs(outbase, d, bin_chr, bin_position, threads=4, frac=0.66, ite
         subset = int(round(n * frac))
         if subset < maxnumchr:
             maxnumchr = subset - 1
+        # every draw is made on every rank (the global numpy RNG advances as in the reference, :429); the linkages
+        # themselves are independent and are dealt round-robin over the ranks of a torch.distributed job
+        sels = [selections[i] if selections is not None else prng.permutation(n)[:subset] for i in range(iterations)]
+        rank, world = _dist_rank_world()
+        from .parallel import assign_round_robin
+        mine = assign_round_robin(iterations, rank, world)
         Ws = []
-        for i in range(iterations):
-            selection = selections[i] if selections is not None else prng.permutation(n)[:subset]
-            sel = torch.as_tensor(np.asarray(selection), dtype=torch.long, device=D.device)
-            sub = D.index_select(0, sel).index_select(1, sel).contiguous()
+        for i in mine:
+            sel = torch.from_numpy(np.ascontiguousarray(sels[i], dtype=np.int32)).to(D.device)
+            sub = ops.gather_square(D, sel)                                  # d[selection, :][:, selection] (:430)
             Ws.append(ops.transform_to_working(sub, ops.KIND_IDENTITY, square=True)[0])
-        dZ = [np.diff(iZ[:, 2]) for iZ in ops.linkage_batch(Ws, "ward")]
+        part = {i: np.diff(iZ[:, 2]) for i, iZ in zip(mine, ops.linkage_batch(Ws, "ward"))}
+        if world > 1:
+            import torch.distributed as dist
+            parts = [None] * world
+            dist.all_gather_object(parts, part)
+            part = {k: v for p in parts for k, v in p.items()}
+        dZ = [part[i] for i in range(iterations)]
         mean_step_len = np.mean(np.array(dZ), 0)
         nchr = int(np.argmax(mean_step_len[-minchr + 1::-1][:maxnumchr]) + minchr)
     clusters = [[] for _ in range(nchr)]
@@ -489,7 +555,7 @@ def cluster_contigs(outbase, d, bin_chr, bin_position, threads=4, frac=0.66, ite
 
 
 def bam2clusters(bam, fasta, outdir, minSize=2000, mapq=10, threads=4, dpi=100, upto=0, nchr=0,
-                 verbose=1, minchr=3, method="ward", contigs=[], selections=None):
+                 verbose=1, minchr=3, method="ward", contigs=[], selections=None, normalize_matrix=False):
     """Return clusters computed from the contig-level contact matrix -- bam2clusters.py:459-537.
 
     Same files as the reference under ``outdir``: ``auto|chr_N`` + ``.windows.tab.gz``, ``.npz``,
@@ -497,7 +563,8 @@ def bam2clusters(bam, fasta, outdir, minSize=2000, mapq=10, threads=4, dpi=100, 
     matrix stays on the GPU from ``bam2array`` through symmetrisation (:511), the distance transform
     (:516) and the 1 + 30 ward linkages of ``cluster_contigs``; ``selections`` is handed to
     ``cluster_contigs`` (the reference draws from the unseeded global RNG).  Like the reference,
-    ``method`` is accepted and unused (cluster_contigs is ward only, :411)."""
+    ``method`` is accepted and unused (cluster_contigs is ward only, :411).  ``normalize_matrix=True`` switches on
+    the Sinkhorn-Knopp balancing that the reference carries commented out at :512 (default off = HEAD)."""
     logger("=== Clustering ===")
     outbase = os.path.join(outdir, "chr_%s" % nchr if nchr else "auto")
     # link with auto (:466-469)
@@ -533,7 +600,13 @@ def bam2clusters(bam, fasta, outdir, minSize=2000, mapq=10, threads=4, dpi=100, 
         with open(outbase + ".distance.params", "rb") as fh:
             params = pickle.load(fh)
     # make symmetric (:511) and get clusters on the transformed matrix (:516-522), all on the device
-    ops.symmetrize_(D)
+    if normalize_matrix:
+        # the call the reference keeps commented out at :512 (``#d = normalize(d)``): Sinkhorn-Knopp balancing of
+        # the symmetrised matrix before the distance transform.  normalize() symmetrises and adds the pseudo-count
+        # itself (:42-43), so it replaces :511; default off = the reference at HEAD
+        D = normalize(D)
+    else:
+        ops.symmetrize_(D)
     dist = ops.transform(D, ops.KIND_POWER, float(params[0]), float(params[1]))
     clusters = cluster_contigs(outbase, dist, bin_chr, bin_position, dpi=dpi, minchr=minchr, nchr=nchr,
                                selections=selections)

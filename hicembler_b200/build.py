@@ -9,7 +9,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 ROOT = os.path.dirname(HERE)
 CSRC = os.path.join(HERE, "csrc")
 LIB = os.path.join(HERE, "libhicembler_b200.so")
-SOURCES = ["common.cu", "bin_pairs.cu", "matrix_ops.cu", "sinkhorn.cu", "linkage.cu", "linkage_rounds.cu", "dendrogram.cu", "bam_decode.cu"]
+SOURCES = ["common.cu", "bin_pairs.cu", "matrix_ops.cu", "sinkhorn.cu", "sharded.cu", "linkage.cu", "linkage_rounds.cu", "dendrogram.cu", "bam_decode.cu"]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
               "-Xcompiler", "-fPIC", "-fmad=false", "--expt-relaxed-constexpr"]
 

@@ -47,9 +47,12 @@ struct BinArgs {
     long long n_chunks;
     const int32_t *chunk_lo, *chunk_hi;  // group-aligned row bounds advertised by each chunk
     const long long *tile_clo, *tile_chi;  // chunk range per row group
-    uint2 *overflow;
+    uint2 *overflow;                    // stragglers: records whose row their chunk does not advertise
     unsigned long long *overflow_count;
     long long overflow_cap;
+    uint2 *spill;                       // 16-bit tile cells that handed 16 384 counts over (<= n_ok / 16 384 entries)
+    unsigned long long *spill_count;
+    long long spill_cap;
     unsigned long long *stats;
 };
 
@@ -242,7 +245,7 @@ __global__ void __launch_bounds__(CELL16 ? 512 : 1024, CELL16 ? 2 : 1) k_bin_til
     const int max_cells = CELL16 ? (a.R * a.W + 1) / 2 : a.R * a.W;  // shared-memory words
     for (int i = threadIdx.x; i < max_cells; i += T) tile[i] = 0;
     __syncthreads();
-    uint32_t n_lines = 0, n_ok = 0, n_absent = 0, n_range = 0, n_key = 0, n_over = 0;
+    uint32_t n_lines = 0, n_ok = 0, n_absent = 0, n_range = 0, n_key = 0, n_over = 0, n_outside = 0;
     const bool vec_ok = ((a.n_windows & 3) == 0) && ((a.W & 3) == 0) && ((((uintptr_t)a.counts) & 15) == 0);
 
     for (int t = blockIdx.x; t < n_tiles; t += gridDim.x) {
@@ -318,16 +321,18 @@ __global__ void __launch_bounds__(CELL16 ? 512 : 1024, CELL16 ? 2 : 1) k_bin_til
                     if (ms) {
                         const int leader = __ffs(ms) - 1;
                         unsigned long long slot = 0;
-                        if (lane_id == leader) slot = atomicAdd(a.overflow_count, (unsigned long long)__popc(ms));
+                        if (lane_id == leader) slot = atomicAdd(a.spill_count, (unsigned long long)__popc(ms));
                         slot = __shfl_sync(0xffffffffu, slot, leader);
                         if (spill) {
                             slot += __popc(ms & ((1u << lane_id) - 1));
-                            if ((long long)slot < a.overflow_cap) a.overflow[slot] = make_uint2((uint32_t)row | 0x80000000u, col);
+                            if ((long long)slot < a.spill_cap) a.spill[slot] = make_uint2((uint32_t)row, col);
                         }
                     }
                 }
                 // straggler: row not advertised by its chunk -> nobody's tile sees it
-                const bool strag = owner && ok && (row < lo || row >= hi) && row >= a.row0 && row < a.row1;
+                const bool in_block = row >= a.row0 && row < a.row1;
+                n_outside += owner && ok && !in_block;  // binnable, but not a row of this call's block
+                const bool strag = owner && ok && (row < lo || row >= hi) && in_block;
                 const unsigned m = __ballot_sync(0xffffffffu, strag);
                 if (m) {
                     const int leader = __ffs(m) - 1;
@@ -445,27 +450,51 @@ __global__ void __launch_bounds__(CELL16 ? 512 : 1024, CELL16 ? 2 : 1) k_bin_til
         }
         __syncthreads();
     }
-    unsigned long long v[6] = {n_lines, n_ok, n_absent, n_range, n_key, n_over};
+    unsigned long long v[7] = {n_lines, n_ok, n_absent, n_range, n_key, n_over, n_outside};
 #pragma unroll
-    for (int k = 0; k < 6; ++k) {
+    for (int k = 0; k < 7; ++k) {
         unsigned long long t = hc::warp_sum_u64(v[k]);
-        if ((threadIdx.x & 31) == 0 && t) atomicAdd(a.stats + k, t);
+        if ((threadIdx.x & 31) == 0 && t) atomicAdd(a.stats + (k == 6 ? 10 : k), t);
     }
 }
 
+// Spilled 16 384-count blocks are always applied (their list cannot overflow); the straggler list only when it
+// held every straggler -- otherwise k_bin_stragglers re-scans the records.  Both decisions are taken on the device,
+// BEFORE anything a second pass would add again is in `counts` (accumulate mode stays exact).
 __global__ void k_apply_overflow(BinArgs a) {
-    long long n = min((long long)*a.overflow_count, a.overflow_cap);
-    for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n;
-         i += (long long)gridDim.x * blockDim.x) {
-        uint2 e = a.overflow[i];  // top bit of the row: a 16-bit tile cell handed 16 384 counts over
-        const uint32_t w = (e.x & 0x80000000u) ? 0x4000u : 1u;
-        atomicAdd(a.counts + (size_t)((int32_t)(e.x & 0x7fffffffu) - a.row0) * a.n_windows + e.y, w);
+    const long long ns = min((long long)*a.spill_count, a.spill_cap);
+    for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < ns; i += (long long)gridDim.x * blockDim.x) {
+        const uint2 e = a.spill[i];
+        atomicAdd(a.counts + (size_t)((int32_t)e.x - a.row0) * a.n_windows + e.y, 0x4000u);
+    }
+    const long long n = (long long)*a.overflow_count;
+    if (n > a.overflow_cap) return;
+    for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {
+        const uint2 e = a.overflow[i];
+        atomicAdd(a.counts + (size_t)((int32_t)e.x - a.row0) * a.n_windows + e.y, 1u);
+    }
+}
+
+// The straggler list overflowed (input not sorted by read-1 window): every straggler -- a record whose row lies
+// outside the rows [chunk_lo, chunk_hi) its chunk advertises, so that no tile saw it -- is added with a global
+// atomic instead.  The tiles have already been flushed with everything else, each record is counted exactly once.
+__global__ void __launch_bounds__(256) k_bin_stragglers(BinArgs a) {
+    if ((long long)*a.overflow_count <= a.overflow_cap) return;
+    for (long long idx = blockIdx.x * (long long)blockDim.x + threadIdx.x; idx < a.n_pairs;
+         idx += (long long)gridDim.x * blockDim.x) {
+        const uint2 *p = a.pairs + 3 * idx;
+        int32_t row, col;
+        if (decode(a, __ldg(p), __ldg(p + 1), __ldg(p + 2), row, col) != ST_OK) continue;
+        const long long c = idx >> CHUNK_LOG;
+        const int32_t lo = __ldg(a.chunk_lo + c), hi = __ldg(a.chunk_hi + c);
+        if ((row < lo || row >= hi) && row >= a.row0 && row < a.row1)
+            atomicAdd(a.counts + (size_t)(row - a.row0) * a.n_windows + col, 1u);
     }
 }
 
 // Fallback: plain global atomics on a zeroed matrix, any input order.
 __global__ void __launch_bounds__(256) k_bin_atomic(BinArgs a) {
-    unsigned long long n_lines = 0, n_ok = 0, n_absent = 0, n_range = 0, n_key = 0;
+    unsigned long long n_lines = 0, n_ok = 0, n_absent = 0, n_range = 0, n_key = 0, n_outside = 0;
     for (long long idx = blockIdx.x * (long long)blockDim.x + threadIdx.x; idx < a.n_pairs;
          idx += (long long)gridDim.x * blockDim.x) {
         const uint2 *p = a.pairs + 3 * idx;
@@ -478,6 +507,82 @@ __global__ void __launch_bounds__(256) k_bin_atomic(BinArgs a) {
         n_key += st == ST_KEY;
         if (st == ST_OK && row >= a.row0 && row < a.row1)
             atomicAdd(a.counts + (size_t)(row - a.row0) * a.n_windows + col, 1u);
+        n_outside += st == ST_OK && !(row >= a.row0 && row < a.row1);
+    }
+    unsigned long long v[6] = {n_lines, n_ok, n_absent, n_range, n_key, n_outside};
+#pragma unroll
+    for (int k = 0; k < 6; ++k) {
+        unsigned long long t = hc::warp_sum_u64(v[k]);
+        if ((threadIdx.x & 31) == 0 && t) atomicAdd(a.stats + (k == 5 ? 10 : k), t);
+    }
+}
+
+// ---- several window sizes from ONE read of the records ---------------------------------------------------------
+// bam2arrays bins every kept line into all window sizes of the call (inner loop bam2clusters.py:154-161).  The
+// per-cluster matrices of the scaffolding stage (5 / 10 / 2 kb, bam2scaffolds.py:379) are small enough to live in
+// the 126 MB L2 together, so each record is read and filtered once and added to every matrix with a warp-aggregated
+// global atomic (resolved in L2); the privatised-row kernel above stays the path for one big matrix.
+constexpr int MAX_WS = 4;
+struct MultiArgs {
+    const uint2 *pairs;
+    long long n_pairs;
+    const int32_t *offsets[MAX_WS];
+    const uint8_t *region_mask;
+    int32_t n_contigs, n_ws;
+    uint32_t window_bp[MAX_WS];
+    unsigned long long inv_bp[MAX_WS];
+    int32_t n_windows[MAX_WS];
+    int32_t mapq_min;
+    uint32_t skip_flag;
+    uint32_t *counts[MAX_WS];
+    unsigned long long *stats;
+};
+
+__global__ void __launch_bounds__(256) k_bin_multi(MultiArgs a) {
+    unsigned long long n_lines = 0, n_ok = 0, n_absent = 0, n_range = 0, n_key = 0;
+    const int lane = threadIdx.x & 31;
+    const long long total = (a.n_pairs + 31) & ~31ll;   // whole warps take part in the matches
+    for (long long idx = blockIdx.x * (long long)blockDim.x + threadIdx.x; idx < total;
+         idx += (long long)gridDim.x * blockDim.x) {
+        bool live = idx < a.n_pairs;
+        uint2 q0 = make_uint2(0, 0), q1 = q0, q2 = q0;
+        if (live) {
+            const uint2 *p = a.pairs + 3 * idx;
+            q0 = __ldg(p); q1 = __ldg(p + 1); q2 = __ldg(p + 2);
+        }
+        const int32_t ref = (int32_t)q0.x, pos = (int32_t)q0.y, nref = (int32_t)q1.x, npos = (int32_t)q1.y;
+        const int32_t lseq = (int32_t)q2.x;
+        const uint32_t flag = q2.y & 0xffffu, mapq = (q2.y >> 16) & 0xffu;
+        const bool ref_ok = (uint32_t)ref < (uint32_t)a.n_contigs, nref_ok = (uint32_t)nref < (uint32_t)a.n_contigs;
+        live = live && !(flag & a.skip_flag) && (int32_t)mapq >= a.mapq_min;
+        if (a.region_mask) live = live && ref_ok && a.region_mask[ref];
+        n_lines += live;
+        // membership is tested against the first table only (bam2clusters.py:151)
+        const bool member = live && ref_ok && nref_ok && __ldg(a.offsets[0] + ref) >= 0 && __ldg(a.offsets[0] + nref) >= 0;
+        n_absent += live && !member;
+        const int32_t half = (lseq > 1 ? lseq : 1) >> 1;
+        const long long p1 = (long long)pos + 1 + half, p2 = (long long)npos + 1 + half;
+        bool ok_all = member;
+#pragma unroll
+        for (int ii = 0; ii < MAX_WS; ++ii) {
+            if (ii >= a.n_ws) break;
+            uint32_t cell = 0xffffffffu;
+            if (member && ok_all) {
+                const int32_t o1 = __ldg(a.offsets[ii] + ref), o2 = __ldg(a.offsets[ii] + nref);
+                if (o1 < 0 || o2 < 0) { n_key++; ok_all = false; }
+                else if (p1 < 0 || p2 < 0) { n_range++; ok_all = false; }
+                else {
+                    const uint32_t wb = a.window_bp[ii];
+                    const long long w1 = (long long)(wb == 1u ? (uint32_t)p1 : (uint32_t)__umul64hi((unsigned long long)(uint32_t)p1, a.inv_bp[ii])) + o1;
+                    const long long w2 = (long long)(wb == 1u ? (uint32_t)p2 : (uint32_t)__umul64hi((unsigned long long)(uint32_t)p2, a.inv_bp[ii])) + o2;
+                    if (w1 >= a.n_windows[ii] || w2 >= a.n_windows[ii]) { n_range++; ok_all = false; }
+                    else cell = (uint32_t)(w1 * a.n_windows[ii] + w2);   // full orientation, like hc_bin_pairs
+                }
+            }
+            const unsigned peers = __match_any_sync(0xffffffffu, cell);
+            if (cell != 0xffffffffu && (__ffs(peers) - 1) == lane) atomicAdd(a.counts[ii] + cell, (uint32_t)__popc(peers));
+        }
+        n_ok += member && ok_all;
     }
     unsigned long long v[5] = {n_lines, n_ok, n_absent, n_range, n_key};
 #pragma unroll
@@ -604,6 +709,15 @@ __global__ void k_region_filter(const uint2 *pairs, long long n, const int32_t *
     }
 }
 
+// stats[5] = stragglers, stats[6] = 1 when the sorted-input path handled everything (0: forced atomic kernel, or the
+// straggler list overflowed and the records were re-scanned), stats[7] = tile shape
+__global__ void k_bin_finish(unsigned long long *stats, long long overflow_cap, long long shape) {
+    const long long n_over = (long long)stats[8];
+    stats[5] = overflow_cap < 0 ? 0ull : (unsigned long long)n_over;
+    stats[6] = (overflow_cap >= 0 && n_over <= overflow_cap) ? 1ull : 0ull;
+    stats[7] = (unsigned long long)shape;
+}
+
 }  // namespace
 
 extern "C" size_t hc_bin_pairs_workspace_bytes(int64_t n_pairs, int64_t n_rows) {
@@ -613,7 +727,8 @@ extern "C" size_t hc_bin_pairs_workspace_bytes(int64_t n_pairs, int64_t n_rows) 
     bytes += hc::align_up(n_chunks * 4, 256) * 3;        // lead/chunk_lo/chunk_hi
     bytes += hc::align_up(nb * 4, 256);                  // block maxima
     bytes += hc::align_up((size_t)n_rows * 8, 256) * 2;  // tile ranges (<= one group per row)
-    bytes += hc::align_up((size_t)(n_pairs / 16 + 65536) * 8, 256);  // overflow list
+    bytes += hc::align_up((size_t)(n_pairs / 16 + 65536) * 8, 256);  // straggler list
+    bytes += hc::align_up((size_t)(n_pairs / 16384 + 1024) * 8, 256);  // spill list
     return bytes;
 }
 
@@ -626,7 +741,7 @@ extern "C" int hc_bin_pairs(const hc_pair_t *pairs, int64_t n_pairs, const int32
     cudaStream_t stream = (cudaStream_t)stream_;
     HC_REQUIRE(n_pairs >= 0 && n_windows > 0 && window_bp > 0, "bad sizes");
     HC_REQUIRE(row0 >= 0 && row0 < row1 && row1 <= n_windows, "bad row block");
-    HC_REQUIRE(offsets && counts && h_stats && workspace, "null pointer");
+    HC_REQUIRE(offsets && counts && workspace, "null pointer");
     HC_REQUIRE(((uintptr_t)pairs & 7) == 0, "pairs must be 8-byte aligned");
     if (workspace_bytes < hc_bin_pairs_workspace_bytes(n_pairs, row1 - row0)) {
         hc::set_error("hc_bin_pairs: workspace too small");
@@ -687,18 +802,20 @@ extern "C" int hc_bin_pairs(const hc_pair_t *pairs, int64_t n_pairs, const int32
     long long *tile_chi = ws.take<long long>(a.n_groups);
     a.overflow_cap = n_pairs / 16 + 65536;
     a.overflow = ws.take<uint2>(a.overflow_cap);
+    a.spill_cap = n_pairs / 16384 + 1024;
+    a.spill = ws.take<uint2>(a.spill_cap);
     if (!ws.ok()) {
         hc::set_error("hc_bin_pairs: workspace carve overflow");
         return HC_EWORKSPACE;
     }
     a.stats = stats;
     a.overflow_count = stats + 8;
+    a.spill_count = stats + 9;
     a.chunk_lo = chunk_lo;
     a.chunk_hi = chunk_hi;
     a.tile_clo = tile_clo;
     a.tile_chi = tile_chi;
 
-    unsigned long long h[16];
     a.accumulate = (mode & 2) != 0;
     bool fast = ((mode & 1) == 0) && n_pairs > 0;
     if (fast) {
@@ -730,25 +847,30 @@ extern "C" int hc_bin_pairs(const hc_pair_t *pairs, int64_t n_pairs, const int32
         else k_bin_tiles<2, false><<<grid, threads, smem, stream>>>(a);
         HC_CHECK_LAUNCH();
         k_apply_overflow<<<4 * sms, 256, 0, stream>>>(a);
+        k_bin_stragglers<<<16 * sms, 256, 0, stream>>>(a);   // returns at once unless the straggler list overflowed
         HC_CHECK_LAUNCH();
-        HC_CUDA_OK(cudaMemcpyAsync(h, stats, sizeof h, cudaMemcpyDeviceToHost, stream));
-        HC_CUDA_OK(cudaStreamSynchronize(stream));
-        if ((long long)h[8] > a.overflow_cap) fast = false;  // unsorted input: redo with atomics
-    }
-    if (!fast) {
+    } else {
         HC_CUDA_OK(cudaMemsetAsync(stats, 0, 16 * sizeof(unsigned long long), stream));
         if (!a.accumulate) HC_CUDA_OK(cudaMemsetAsync(counts, 0, (size_t)rows * n_windows * 4, stream));
         if (n_pairs > 0) {
             k_bin_atomic<<<16 * sms, 256, 0, stream>>>(a);
             HC_CHECK_LAUNCH();
         }
-        HC_CUDA_OK(cudaMemcpyAsync(h, stats, sizeof h, cudaMemcpyDeviceToHost, stream));
-        HC_CUDA_OK(cudaStreamSynchronize(stream));
-        h[5] = 0;
     }
-    for (int k = 0; k < 6; ++k) h_stats[k] = (int64_t)h[k];
-    h_stats[6] = fast ? 1 : 0;
-    h_stats[7] = ((int64_t)a.R << 32) | (uint32_t)a.n_segs;
+    k_bin_finish<<<1, 1, 0, stream>>>(stats, fast ? a.overflow_cap : -1, ((long long)a.R << 32) | (uint32_t)a.n_segs);
+    HC_CHECK_LAUNCH();
+    if (!h_stats) return HC_OK;   // asynchronous call: hc_bin_pairs_stats() reads the device stats later
+    return hc_bin_pairs_stats(workspace, h_stats, stream_);
+}
+
+extern "C" int hc_bin_pairs_stats(const void *workspace, int64_t *h_stats, void *stream_) {
+    cudaStream_t stream = (cudaStream_t)stream_;
+    HC_REQUIRE(workspace && h_stats, "null pointer");
+    unsigned long long h[16];
+    HC_CUDA_OK(cudaMemcpyAsync(h, workspace, sizeof h, cudaMemcpyDeviceToHost, stream));
+    HC_CUDA_OK(cudaStreamSynchronize(stream));
+    for (int k = 0; k < 8; ++k) h_stats[k] = (int64_t)h[k];
+    h_stats[8] = (int64_t)h[10];
     if (h[4]) {
         hc::set_error("contig present in chr2window[0] but absent for this window size (%llu records)", h[4]);
         return HC_EKEY;
@@ -758,6 +880,45 @@ extern "C" int hc_bin_pairs(const hc_pair_t *pairs, int64_t n_pairs, const int32
         return HC_ERANGE;
     }
     return HC_OK;
+}
+
+extern "C" int hc_bin_pairs_multi(const hc_pair_t *pairs, int64_t n_pairs, int32_t n_ws, const int32_t *const *h_offsets,
+                                  const uint8_t *region_mask, int32_t n_contigs, const uint32_t *h_window_bp,
+                                  const int32_t *h_n_windows, int32_t mapq_min, uint32_t skip_flag,
+                                  uint32_t *const *h_counts, int accumulate, void *workspace, size_t workspace_bytes,
+                                  int64_t *h_stats, void *stream_) {
+    cudaStream_t stream = (cudaStream_t)stream_;
+    HC_REQUIRE(n_ws >= 1 && n_ws <= MAX_WS && n_pairs >= 0, "1..4 window sizes per call");
+    HC_REQUIRE(h_offsets && h_window_bp && h_n_windows && h_counts && workspace && workspace_bytes >= 256, "null pointer");
+    HC_REQUIRE(((uintptr_t)pairs & 7) == 0, "pairs must be 8-byte aligned");
+    MultiArgs a;
+    memset(&a, 0, sizeof a);
+    a.pairs = (const uint2 *)pairs;
+    a.n_pairs = n_pairs;
+    a.region_mask = region_mask;
+    a.n_contigs = n_contigs;
+    a.n_ws = n_ws;
+    a.mapq_min = mapq_min;
+    a.skip_flag = skip_flag;
+    a.stats = (unsigned long long *)workspace;
+    for (int ii = 0; ii < n_ws; ++ii) {
+        HC_REQUIRE(h_offsets[ii] && h_counts[ii] && h_window_bp[ii] > 0 && h_n_windows[ii] > 0, "bad window table");
+        HC_REQUIRE((long long)h_n_windows[ii] * h_n_windows[ii] < 0xffffffffll, "matrix too large for the one-pass kernel");
+        a.offsets[ii] = h_offsets[ii];
+        a.window_bp[ii] = h_window_bp[ii];
+        a.inv_bp[ii] = h_window_bp[ii] == 1u ? 0ull : (~0ull) / h_window_bp[ii] + 1ull;
+        a.n_windows[ii] = h_n_windows[ii];
+        a.counts[ii] = h_counts[ii];
+        if (!accumulate)
+            HC_CUDA_OK(cudaMemsetAsync(h_counts[ii], 0, (size_t)h_n_windows[ii] * h_n_windows[ii] * 4, stream));
+    }
+    HC_CUDA_OK(cudaMemsetAsync(workspace, 0, 16 * sizeof(unsigned long long), stream));
+    if (n_pairs > 0) {
+        k_bin_multi<<<8 * hc::sm_count(), 256, 0, stream>>>(a);
+        HC_CHECK_LAUNCH();
+    }
+    if (!h_stats) return HC_OK;
+    return hc_bin_pairs_stats(workspace, h_stats, stream_);
 }
 
 extern "C" int hc_upto_cutoff(const hc_pair_t *pairs, int64_t n_pairs, const uint8_t *region_mask,

@@ -51,8 +51,16 @@ struct __align__(16) Pair {  // 48 bytes; i < j, the merged cluster lives at j
     double m, s1, s2, as, at;
 };
 
+// per-round counters; the persistent kernel alternates between the two sets (round parity) so that the set of the
+// NEXT round can be cleared while the current one is still being read
+struct Ctr {
+    int P, qlen, deferred, pad;
+};
+
 struct RState {
-    int P, qlen, n_done, nactive, ambiguous, stuck, done, deferred, round, blocks_done, last_P, last_q;
+    Ctr ctr[2];
+    int n_done, nactive, ambiguous, stuck, done, round, blocks_done, last_P, last_q, exit_reason;
+    unsigned int bar;  // arrival counter of the persistent kernel's grid barrier (monotone)
     int amb_r, amb_b, amb_sr, amb_sb;
     double amb_v, amb_secr, amb_secb, amb_vb;
     double gaps[16];  // relative gap (second minimum / minimum - 1) of the first near-tie observations
@@ -104,6 +112,19 @@ __device__ __forceinline__ double lw(int method, double a, double b, const Pair 
         return __ddiv_rn(t, __dadd_rn(__dadd_rn(p.s1, p.s2), v));
     }
     }
+}
+
+// Everything another CTA may have written earlier in the same launch (the persistent kernel runs many rounds in one
+// launch) is read through L2: ld.global.cg.  In the one-kernel-per-phase launches these are ordinary L2 hits.
+__device__ __forceinline__ Pair ld_pair(const Pair *p) {
+    const int4 *q = (const int4 *)p;   // 48 bytes, 16-byte aligned: {i, j, m} {s1, s2} {as, at}
+    const int4 a = __ldcg(q), b = __ldcg(q + 1), c = __ldcg(q + 2);
+    Pair r;
+    r.i = a.x; r.j = a.y;
+    r.m = __hiloint2double(a.w, a.z);
+    r.s1 = __hiloint2double(b.y, b.x); r.s2 = __hiloint2double(b.w, b.z);
+    r.as = __hiloint2double(c.y, c.x); r.at = __hiloint2double(c.w, c.z);
+    return r;
 }
 
 __device__ __forceinline__ bool lex_lt(double x, int c, double y, int d) { return x < y || (x == y && c < d); }
@@ -208,109 +229,116 @@ __global__ void kr_init(RArgs a) {
 }
 
 // ---- select: reciprocal nearest neighbours -> certified pair list ----------------------------
-__global__ void __launch_bounds__(256) kr_select(RArgs a) {
+// rows r = r_first, r_first + r_stride, ...: whole warps stay together (r_first differs by lane only)
+__device__ __forceinline__ void select_rows(const RArgs &a, Ctr *ct, int r_first, int r_stride) {
     RState *st = a.st;
-    if (st->done) return;
-    const int r = blockIdx.x * blockDim.x + threadIdx.x, lane = threadIdx.x & 31;
-    bool emit = false;
-    int b = -1;
-    double va = 0;
-    if (r < a.ncols && a.c.role[r] == ROLE_FREE) {
-        b = a.c.cidx[(size_t)r * LC];
-        if (b > r && a.c.cidx[(size_t)b * LC] == r) {
-            va = a.c.cval[(size_t)r * LC];
-            const double vb = a.c.cval[(size_t)b * LC];
-            // second smallest entry of either row: the next candidate (exact) or, with a single candidate left,
-            // the bound of the unlisted entries (exact only straight after a scan)
-            const bool two_r = a.c.cidx[(size_t)r * LC + 1] >= 0, two_b = a.c.cidx[(size_t)b * LC + 1] >= 0;
-            const double sr = a.c.cval[(size_t)r * LC + (two_r ? 1 : KC)], sb = a.c.cval[(size_t)b * LC + (two_b ? 1 : KC)];
-            const bool exact_r = two_r || a.c.fresh[r], exact_b = two_b || a.c.fresh[b];
-            // Margin 0 where both engines compute bit-identical entries: min/max updates commute exactly
-            // (single, complete), and for average/weighted every entry of a row whose cluster is still a
-            // single leaf went only through the OTHER cluster's merge tree, whose operation order is fixed
-            // (ward is excluded: its update uses the merge height, which is interleaving dependent).
-            // Elsewhere the engines interleave two merge trees differently: demand a relative MARGIN.
-            const bool exact_all = a.method == M_SINGLE || a.method == M_COMPLETE;
-            const bool leaf_exact = a.method == M_AVERAGE || a.method == M_WEIGHTED;
-            const double thr = __dadd_rn(va, __dmul_rn(fabs(va), a.margin));
-            const bool ok_r = sr > ((exact_all || (leaf_exact && a.c.size[r] == 1)) ? va : thr);
-            const bool ok_b = sb > ((exact_all || (leaf_exact && a.c.size[b] == 1)) ? va : thr);
-            const bool ok = ok_r && ok_b && vb == va;
-            if (ok) emit = true;
-            else if (exact_r && exact_b) {
-                // Exact second minima and still too close.  A NEAR tie is left pending: the pair stays reciprocal
-                // (reducibility) and is merged in a later round if its rivals move away; all other certified
-                // merges go on (a run whose every merge is strict has a unique tree, whatever the order).  An
-                // EXACT tie (identical rows, e.g. empty windows) practically never resolves: stop at once.
-                st->amb_r = a.c.orig[r]; st->amb_b = a.c.orig[b];
-                st->amb_sr = a.c.size[r]; st->amb_sb = a.c.size[b];
-                st->amb_v = va; st->amb_vb = vb;
-                st->amb_secr = sr; st->amb_secb = sb;
-                const unsigned long long k_obs = atomicAdd(&st->stats[6], 1ull);
-                if (k_obs < 16) st->gaps[k_obs] = (fmin(sr, sb) - va) / fabs(va);
-                if (a.diag) emit = true;  // diagnostics only: merge anyway, the result is NOT certified
-                else if (!(sr > va) || !(sb > va) || vb != va) st->ambiguous = 1;
-            }
-            else {  // the bound of "the rest" is stale: rescan both rows, decide next round
-                a.c.need[r] = 1;
-                a.c.need[b] = 1;
-                atomicAdd(&st->deferred, 1);
+    const int lane = threadIdx.x & 31;
+    const int n_done = __ldcg(&st->n_done);
+    for (int r0 = r_first - lane; r0 < a.ncols; r0 += r_stride) {
+        const int r = r0 + lane;
+        bool emit = false;
+        int b = -1;
+        double va = 0;
+        if (r < a.ncols && __ldcg(a.c.role + r) == ROLE_FREE) {
+            b = __ldcg(a.c.cidx + (size_t)r * LC);
+            if (b > r && __ldcg(a.c.cidx + (size_t)b * LC) == r) {
+                va = __ldcg(a.c.cval + (size_t)r * LC);
+                const double vb = __ldcg(a.c.cval + (size_t)b * LC);
+                // second smallest entry of either row: the next candidate (exact) or, with a single candidate left,
+                // the bound of the unlisted entries (exact only straight after a scan)
+                const bool two_r = __ldcg(a.c.cidx + (size_t)r * LC + 1) >= 0, two_b = __ldcg(a.c.cidx + (size_t)b * LC + 1) >= 0;
+                const double sr = __ldcg(a.c.cval + (size_t)r * LC + (two_r ? 1 : KC)), sb = __ldcg(a.c.cval + (size_t)b * LC + (two_b ? 1 : KC));
+                const bool exact_r = two_r || __ldcg(a.c.fresh + r), exact_b = two_b || __ldcg(a.c.fresh + b);
+                const int size_r = __ldcg(a.c.size + r), size_b = __ldcg(a.c.size + b);
+                // Margin 0 where both engines compute bit-identical entries: min/max updates commute exactly
+                // (single, complete), and for average/weighted every entry of a row whose cluster is still a
+                // single leaf went only through the OTHER cluster's merge tree, whose operation order is fixed
+                // (ward is excluded: its update uses the merge height, which is interleaving dependent).
+                // Elsewhere the engines interleave two merge trees differently: demand a relative MARGIN.
+                const bool exact_all = a.method == M_SINGLE || a.method == M_COMPLETE;
+                const bool leaf_exact = a.method == M_AVERAGE || a.method == M_WEIGHTED;
+                const double thr = __dadd_rn(va, __dmul_rn(fabs(va), a.margin));
+                const bool ok_r = sr > ((exact_all || (leaf_exact && size_r == 1)) ? va : thr);
+                const bool ok_b = sb > ((exact_all || (leaf_exact && size_b == 1)) ? va : thr);
+                const bool ok = ok_r && ok_b && vb == va;
+                if (ok) emit = true;
+                else if (exact_r && exact_b) {
+                    // Exact second minima and still too close.  A NEAR tie is left pending: the pair stays reciprocal
+                    // (reducibility) and is merged in a later round if its rivals move away; all other certified
+                    // merges go on (a run whose every merge is strict has a unique tree, whatever the order).  An
+                    // EXACT tie (identical rows, e.g. empty windows) practically never resolves: stop at once.
+                    st->amb_r = a.c.orig[r]; st->amb_b = a.c.orig[b];
+                    st->amb_sr = size_r; st->amb_sb = size_b;
+                    st->amb_v = va; st->amb_vb = vb;
+                    st->amb_secr = sr; st->amb_secb = sb;
+                    const unsigned long long k_obs = atomicAdd(&st->stats[6], 1ull);
+                    if (k_obs < 16) st->gaps[k_obs] = (fmin(sr, sb) - va) / fabs(va);
+                    if (a.diag) emit = true;  // diagnostics only: merge anyway, the result is NOT certified
+                    else if (!(sr > va) || !(sb > va) || vb != va) st->ambiguous = 1;
+                }
+                else {  // the bound of "the rest" is stale: rescan both rows, decide next round
+                    a.c.need[r] = 1;
+                    a.c.need[b] = 1;
+                    atomicAdd(&ct->deferred, 1);
+                }
             }
         }
+        const unsigned m = __ballot_sync(0xffffffffu, emit);
+        if (!m) continue;
+        int base = 0;
+        const int leader = __ffs(m) - 1;
+        if (lane == leader) base = atomicAdd(&ct->P, __popc(m));
+        base = __shfl_sync(0xffffffffu, base, leader);
+        if (emit) {
+            const int slot = base + __popc(m & ((1u << lane) - 1));
+            Pair p;
+            p.i = r;
+            p.j = b;
+            p.m = va;
+            p.s1 = (double)__ldcg(a.c.size + r);
+            p.s2 = (double)__ldcg(a.c.size + b);
+            const double tot = __dadd_rn(p.s1, p.s2);
+            p.as = __ddiv_rn(p.s1, tot);
+            p.at = __ddiv_rn(p.s2, tot);
+            a.pairs[slot] = p;
+            a.c.role[r] = 2 * slot;
+            a.c.role[b] = 2 * slot + 1;
+            const int k = n_done + slot;
+            a.rec_a[k] = a.c.orig[r];
+            a.rec_b[k] = a.c.orig[b];
+            a.rec_d[k] = va;
+        }
     }
-    const unsigned m = __ballot_sync(0xffffffffu, emit);
-    if (!m) return;
-    int base = 0;
-    const int leader = __ffs(m) - 1;
-    if (lane == leader) base = atomicAdd(&st->P, __popc(m));
-    base = __shfl_sync(0xffffffffu, base, leader);
-    if (emit) {
-        const int slot = base + __popc(m & ((1u << lane) - 1));
-        Pair p;
-        p.i = r;
-        p.j = b;
-        p.m = va;
-        p.s1 = (double)a.c.size[r];
-        p.s2 = (double)a.c.size[b];
-        const double tot = __dadd_rn(p.s1, p.s2);
-        p.as = __ddiv_rn(p.s1, tot);
-        p.at = __ddiv_rn(p.s2, tot);
-        a.pairs[slot] = p;
-        a.c.role[r] = 2 * slot;
-        a.c.role[b] = 2 * slot + 1;
-        const int k = st->n_done + slot;
-        a.rec_a[k] = a.c.orig[r];
-        a.rec_b[k] = a.c.orig[b];
-        a.rec_d[k] = va;
-    }
+}
+
+__global__ void __launch_bounds__(256) kr_select(RArgs a) {
+    if (a.st->done) return;
+    select_rows(a, &a.st->ctr[0], blockIdx.x * blockDim.x + threadIdx.x, gridDim.x * blockDim.x);
 }
 
 // ---- light: every unmerged row updates its own D(k, j_q), keeps its NN cache --------------------
 // A row is owned by a group of G = min(32, pow2ceil(P)) lanes that strides over the pairs, so a round with
 // one pair handles 32 rows per warp and a round with thousands of pairs gives a row a whole warp.
-__global__ void __launch_bounds__(LIGHT_THREADS) kr_light(RArgs a) {
+__device__ __forceinline__ void light_rows(const RArgs &a, Ctr *ct, int P, long long warp0, long long nwarps) {
     RState *st = a.st;
-    if (st->done) return;
-    const int P = st->P, method = a.method, lane = threadIdx.x & 31;
+    const int method = a.method, lane = threadIdx.x & 31;
     int G = 1;
     while (G < 32 && G < P) G <<= 1;
     const int rows_per_warp = 32 / G, g = lane / G, q0 = lane - g * G;
     const unsigned gmask = G == 32 ? 0xffffffffu : (((1u << G) - 1u) << (g * G));
-    const long long warp0 = ((long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
-    const long long nwarps = ((long long)gridDim.x * blockDim.x) >> 5;
     unsigned long long upd = 0;
     for (long long rbase = warp0 * rows_per_warp; rbase < a.ncols; rbase += nwarps * rows_per_warp) {
         const int row = (int)rbase + g;
-        if (row >= a.ncols || a.c.role[row] != ROLE_FREE) continue;
-        const bool need = a.c.need[row] != 0;
+        if (row >= a.ncols || __ldcg(a.c.role + row) != ROLE_FREE) continue;
+        const bool need = __ldcg(a.c.need + row) != 0;
         if (P > 0) {
             double *Wr = a.W + (size_t)row * a.stride;
-            const double v = (double)a.c.size[row];
+            const double v = (double)__ldcg(a.c.size + row);
             for (int q = q0; q < P; q += 2 * G) {  // two pairs per lane in flight
                 const int q2 = q + G;
                 const bool two = q2 < P;
-                const Pair p = a.pairs[q];
-                const Pair p2 = a.pairs[two ? q2 : q];
+                const Pair p = ld_pair(a.pairs + q);
+                const Pair p2 = ld_pair(a.pairs + (two ? q2 : q));
                 const double A = __ldcg(Wr + p.i), B = __ldcg(Wr + p.j);
                 const double A2 = __ldcg(Wr + p2.i), B2 = __ldcg(Wr + p2.j);
                 Wr[p.j] = lw(method, A, B, p, v);
@@ -328,16 +356,16 @@ __global__ void __launch_bounds__(LIGHT_THREADS) kr_light(RArgs a) {
                     double cv[KC];
                     int ci[KC];
 #pragma unroll
-                    for (int k = 0; k < KC; ++k) { cv[k] = a.c.cval[base + k]; ci[k] = a.c.cidx[base + k]; }
-                    const double lb = a.c.cval[base + KC];
+                    for (int k = 0; k < KC; ++k) { cv[k] = __ldcg(a.c.cval + base + k); ci[k] = __ldcg(a.c.cidx + base + k); }
+                    const double lb = __ldcg(a.c.cval + base + KC);
                     bool hit = false;
 #pragma unroll
                     for (int k = 0; k < KC; ++k) {
                         if (ci[k] < 0) continue;
-                        const int r = a.c.role[ci[k]];
+                        const int r = __ldcg(a.c.role + ci[k]);
                         if (r < 0) continue;
                         hit = true;
-                        const int j = a.pairs[r >> 1].j;
+                        const int j = __ldcg(&a.pairs[r >> 1].j);
                         bool dup = false;  // both sides of the pair were listed: keep one
 #pragma unroll
                         for (int t = 0; t < KC; ++t) dup |= (t != k) && (ci[t] == j) && ((r & 1) == 0 || t < k);
@@ -356,14 +384,21 @@ __global__ void __launch_bounds__(LIGHT_THREADS) kr_light(RArgs a) {
                             a.c.cval[base + k] = out.v[k];
                             a.c.cidx[base + k] = out.i[k] == INT_MAX ? -1 : out.i[k];
                         }
-                        if (out.i[0] == INT_MAX) a.rq[atomicAdd(&st->qlen, 1)] = row;
+                        if (out.i[0] == INT_MAX) a.rq[atomicAdd(&ct->qlen, 1)] = row;
                     }
                 }
             }
         }
-        if (need && q0 == 0) a.rq[atomicAdd(&st->qlen, 1)] = row;  // kr_heavy clears the flag
+        if (need && q0 == 0) a.rq[atomicAdd(&ct->qlen, 1)] = row;  // the rescan clears the flag
     }
     if (upd) atomicAdd(&st->stats[4], upd);
+}
+
+__global__ void __launch_bounds__(LIGHT_THREADS) kr_light(RArgs a) {
+    RState *st = a.st;
+    if (st->done) return;
+    light_rows(a, &st->ctr[0], st->ctr[0].P, ((long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5,
+               ((long long)gridDim.x * blockDim.x) >> 5);
 }
 
 // ---- heavy: new rows of merged clusters, exact rescans; the last CTA retires the pairs -----------
@@ -376,7 +411,7 @@ __device__ __forceinline__ void heavy_columns(const RArgs &a, int e, int P, int 
     const int lane = threadIdx.x & 31, method = a.method;  // one warp per (entry, segment)
     constexpr int V = VEC ? 2 : 1, U = 2, UR = 4;  // loads in flight per thread: builds 2 x (A, B), rescans 4 (8 when all live)
     if (e < P) {
-        const Pair p = a.pairs[e];
+        const Pair p = ld_pair(a.pairs + e);
         const double *Wi = a.W + (size_t)p.i * a.stride;
         double *Wj = a.W + (size_t)p.j * a.stride;
         // Phase A: columns of clusters that do not merge this round -- coalesced, no divergent work.
@@ -389,15 +424,15 @@ __device__ __forceinline__ void heavy_columns(const RArgs &a, int e, int P, int 
 #pragma unroll
                 for (int k = 0; k < V; ++k) rc[u][k] = ROLE_DEAD;
                 if (VEC && c + 1 < c_hi) {
-                    const int2 r2 = *(const int2 *)(a.c.role + c), s2 = *(const int2 *)(a.c.size + c);
+                    const int2 r2 = __ldcg((const int2 *)(a.c.role + c)), s2 = __ldcg((const int2 *)(a.c.size + c));
                     const double2 a2 = __ldcg((const double2 *)(Wi + c)), b2 = __ldcg((const double2 *)(Wj + c));
                     rc[u][0] = r2.x; rc[u][V - 1] = r2.y;
                     sz[u][0] = s2.x; sz[u][V - 1] = s2.y;
                     A[u][0] = a2.x; A[u][V - 1] = a2.y;
                     B[u][0] = b2.x; B[u][V - 1] = b2.y;
                 } else if (c < c_hi) {
-                    rc[u][0] = a.c.role[c];
-                    sz[u][0] = a.c.size[c];
+                    rc[u][0] = __ldcg(a.c.role + c);
+                    sz[u][0] = __ldcg(a.c.size + c);
                     A[u][0] = __ldcg(Wi + c);
                     B[u][0] = __ldcg(Wj + c);
                 }
@@ -435,12 +470,12 @@ __device__ __forceinline__ void heavy_columns(const RArgs &a, int e, int P, int 
         };
         for (int q = seg + S * lane; q < P; q += S * 32) {  // (two pairs per lane in flight measured no faster)
             if (q == e) continue;
-            const Pair pq = a.pairs[q];
+            const Pair pq = ld_pair(a.pairs + q);
             const double Ai = __ldcg(Wi + pq.i), Bi = __ldcg(Wj + pq.i), Aj = __ldcg(Wi + pq.j), Bj = __ldcg(Wj + pq.j);
             combine(pq, Ai, Bi, Aj, Bj);
         }
     } else if (all_free) {  // initial scan: every column is a live singleton, no role lookups
-        const int row = a.rq[e - P];
+        const int row = __ldcg(a.rq + e - P);
         const double *Wr = a.W + (size_t)row * a.stride;
         constexpr int UA = 8;
         for (int c0 = c_lo + lane * V; c0 < c_hi; c0 += UA * V * 32) {
@@ -467,7 +502,7 @@ __device__ __forceinline__ void heavy_columns(const RArgs &a, int e, int P, int 
             }
         }
     } else {
-        const int row = a.rq[e - P];
+        const int row = __ldcg(a.rq + e - P);
         const double *Wr = a.W + (size_t)row * a.stride;
         for (int c0 = c_lo + lane * V; c0 < c_hi; c0 += UR * V * 32) {
             double X[UR][V];
@@ -478,12 +513,12 @@ __device__ __forceinline__ void heavy_columns(const RArgs &a, int e, int P, int 
 #pragma unroll
                 for (int k = 0; k < V; ++k) rc[u][k] = ROLE_DEAD;
                 if (VEC && c + 1 < c_hi) {
-                    const int2 r2 = *(const int2 *)(a.c.role + c);
+                    const int2 r2 = __ldcg((const int2 *)(a.c.role + c));
                     const double2 x2 = __ldcg((const double2 *)(Wr + c));
                     rc[u][0] = r2.x; rc[u][V - 1] = r2.y;
                     X[u][0] = x2.x; X[u][V - 1] = x2.y;
                 } else if (c < c_hi) {
-                    rc[u][0] = a.c.role[c];
+                    rc[u][0] = __ldcg(a.c.role + c);
                     X[u][0] = __ldcg(Wr + c);
                 }
             }
@@ -536,17 +571,9 @@ __device__ __forceinline__ void warp_select(unsigned long long k1, int i1, unsig
     obound = r1 < r2 ? r1 : r2;
 }
 
-template <int MINB>
-__global__ void __launch_bounds__(HEAVY_THREADS, MINB) kr_heavy(RArgs a) {
-    __shared__ int s_flag;
-    static_assert(MAX_SEGS <= 32, "one lane per partial list in the final selection");
-    RState *st = a.st;
-    if (st->done) return;
-    const int P = st->P, total = P + st->qlen, tid = threadIdx.x, lane = tid & 31, ncols = a.ncols;
-    const int nwarps = (int)gridDim.x * (HEAVY_THREADS / 32), gwarp = (int)blockIdx.x * (HEAVY_THREADS / 32) + (tid >> 5);
-    // One warp per (entry, column segment): warps never wait for each other, so short rows in the long tail of
-    // small rounds cost one load latency plus one selection.  Segments per entry: enough items for every
-    // resident warp, at least SEG_MIN columns each (even length keeps the 16-byte loads aligned).
+// segments per entry for `total` entries on `nwarps` warps: enough items for every resident warp, at least SEG_MIN
+// columns each (even length keeps the 16-byte loads aligned)
+__device__ __forceinline__ int heavy_segments(const RArgs &a, int P, int total, int nwarps) {
     constexpr int SEG_MIN = 512;
     int S = 1;
     if (total > 0) {
@@ -555,17 +582,27 @@ __global__ void __launch_bounds__(HEAVY_THREADS, MINB) kr_heavy(RArgs a) {
         // cut into many segments only ~100 rows are being built at a time (2 x 8 x ncols bytes each), so the
         // gathers and the second write of a sector find them in the 126 MB L2 instead of going back to HBM.
         if (P >= 64 && S < a.bulk_segs) S = a.bulk_segs;
-        const int smax = (ncols + SEG_MIN - 1) / SEG_MIN;
+        const int smax = (a.ncols + SEG_MIN - 1) / SEG_MIN;
         if (S > smax) S = smax;
         if (S > a.max_segs) S = a.max_segs;
         if (S < 1) S = 1;
     }
+    return S;
+}
+
+// One warp per (entry, column segment), entries [e_lo, e_hi) of the round's list (merged rows first, then the rows
+// to rescan): warps never wait for each other, so short rows in the long tail of small rounds cost one load latency
+// plus one selection.  nactive = live columns (for the byte accounting).
+__device__ __forceinline__ void heavy_items(const RArgs &a, int P, int e_lo, int e_hi, int S, int gwarp, int nwarps,
+                                            bool all_free, int nactive) {
+    RState *st = a.st;
+    const int lane = threadIdx.x & 31, ncols = a.ncols;
     int seg_len = (ncols + S - 1) / S;
     seg_len = (seg_len + 1) & ~1;
-    const bool vec = (a.stride & 1) == 0, all_free = st->round == 0;
-    const long long items = (long long)total * S;
+    const bool vec = (a.stride & 1) == 0;
+    const long long items = (long long)(e_hi - e_lo) * S;
     for (long long w = gwarp; w < items; w += nwarps) {
-        const int e = (int)(w / S), seg = (int)(w - (long long)e * S);
+        const int e = e_lo + (int)(w / S), seg = (int)(w % S);
         const int c_lo = seg * seg_len, c_hi = min(ncols, c_lo + seg_len);
         Min3 mine;
         mine.init();
@@ -616,7 +653,7 @@ __global__ void __launch_bounds__(HEAVY_THREADS, MINB) kr_heavy(RArgs a) {
             }
         }
         if (finish) {
-            const int row = e < P ? a.pairs[e].j : a.rq[e - P];
+            const int row = e < P ? __ldcg(&a.pairs[e].j) : __ldcg(a.rq + e - P);
             const size_t base = (size_t)row * LC;
             // the smallest entry outside the list: the (KC+1)-th candidate or an entry nobody kept
             const unsigned long long last = __shfl_sync(0xffffffffu, key, KC);
@@ -632,10 +669,51 @@ __global__ void __launch_bounds__(HEAVY_THREADS, MINB) kr_heavy(RArgs a) {
                 a.c.need[row] = 0;
                 if (S > 1) a.seg_done[e] = 0;
                 atomicAdd(&st->stats[e < P ? 2 : 0], 1ull);
-                atomicAdd(&st->stats[e < P ? 3 : 1], (unsigned long long)st->nactive);
+                atomicAdd(&st->stats[e < P ? 3 : 1], (unsigned long long)nactive);
             }
         }
     }
+}
+
+// the pairs of a finished round leave the matrix: i retires, j carries the merged cluster
+__device__ __forceinline__ void retire_pairs(const RArgs &a, int P, int tid, int nthreads) {
+    for (int q = tid; q < P; q += nthreads) {
+        const Pair p = ld_pair(a.pairs + q);
+        a.c.role[p.i] = ROLE_DEAD;
+        a.c.role[p.j] = ROLE_FREE;
+        a.c.size[p.j] = (int)(p.s1 + p.s2);
+    }
+}
+
+// one thread: close the round (counters of `cur` are read, the set `next` is cleared for the round after)
+__device__ __forceinline__ void close_round(const RArgs &a, Ctr *cur, Ctr *next, int P, int total) {
+    RState *st = a.st;
+    st->n_done += P;
+    st->nactive -= P;
+    st->stats[5] += cur->deferred;
+    if (st->n_done >= a.n - 1) st->done = 1;
+    else if (st->ambiguous && !a.diag) st->done = 1;
+    else if (P == 0 && cur->deferred == 0 && total == 0) { st->stuck = 1; st->done = 1; }  // only pending near-ties left
+    st->last_P = P;
+    st->last_q = total - P;
+    next->P = 0;
+    next->qlen = 0;
+    next->deferred = 0;
+    st->blocks_done = 0;
+    st->round += 1;
+}
+
+template <int MINB>
+__global__ void __launch_bounds__(HEAVY_THREADS, MINB) kr_heavy(RArgs a) {
+    __shared__ int s_flag;
+    static_assert(MAX_SEGS <= 32, "one lane per partial list in the final selection");
+    RState *st = a.st;
+    if (st->done) return;
+    Ctr *ct = &st->ctr[0];
+    const int P = ct->P, total = P + ct->qlen, tid = threadIdx.x;
+    const int nwarps = (int)gridDim.x * (HEAVY_THREADS / 32), gwarp = (int)blockIdx.x * (HEAVY_THREADS / 32) + (tid >> 5);
+    const int S = heavy_segments(a, P, total, nwarps);
+    heavy_items(a, P, 0, total, S, gwarp, nwarps, st->round == 0, st->nactive);
     // last CTA out retires the pairs of this round and closes it
     __syncthreads();
     if (tid == 0) {
@@ -645,27 +723,85 @@ __global__ void __launch_bounds__(HEAVY_THREADS, MINB) kr_heavy(RArgs a) {
     __syncthreads();
     if (!s_flag) return;
     __threadfence();
-    for (int q = tid; q < P; q += HEAVY_THREADS) {
-        const Pair p = a.pairs[q];
-        a.c.role[p.i] = ROLE_DEAD;
-        a.c.role[p.j] = ROLE_FREE;
-        a.c.size[p.j] = (int)(p.s1 + p.s2);
+    retire_pairs(a, P, tid, HEAVY_THREADS);
+    __syncthreads();
+    if (tid == 0) close_round(a, ct, ct, P, total);
+}
+
+// ---- the chain phase in ONE launch ---------------------------------------------------------------------------------
+// After the bulk rounds a single growing cluster merges one to four pairs per round for hundreds of rounds (C3: rounds
+// 12-545).  Three dependent launches per round (select, light, heavy) plus a host synchronisation every few rounds
+// cost ~45 us per round for ~5 us of work.  kr_chain runs the same three phases for MANY rounds inside one
+// cooperative launch, separated by grid barriers (one CTA per SM):
+//   phase 1  select_rows            -> pairs of the round (counter set `par`)
+//   phase 2  build of the merged rows (heavy_items over the pairs) and light_rows -- they touch disjoint rows
+//   phase 3  exact rescans of the rows whose candidate list ran empty; CTA 0 retires the pairs and closes the round
+// It returns to the host when the run is finished, when half of the columns are dead (the host compacts the matrix)
+// or after max_rounds rounds.
+struct ChainCtl {
+    int max_rounds;
+};
+
+__device__ __forceinline__ void grid_barrier(unsigned int *bar, unsigned int &target) {
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        target += gridDim.x;
+        __threadfence();
+        atomicAdd(bar, 1u);
+        while (*(volatile unsigned int *)bar < target) { }
+        __threadfence();
     }
     __syncthreads();
-    if (tid == 0) {
-        st->n_done += P;
-        st->nactive -= P;
-        st->stats[5] += st->deferred;
-        if (st->n_done >= a.n - 1) st->done = 1;
-        else if (st->ambiguous && !a.diag) st->done = 1;
-        else if (P == 0 && st->deferred == 0 && total == 0) { st->stuck = 1; st->done = 1; }  // only pending near-ties left
-        st->last_P = P;
-        st->last_q = total - P;
-        st->P = 0;
-        st->qlen = 0;
-        st->deferred = 0;
-        st->blocks_done = 0;
-        st->round += 1;
+}
+
+constexpr int CHAIN_THREADS = 512;
+
+// out-of-line copies for the persistent kernel: three inlined phases do not fit 128 registers together
+__device__ __noinline__ void select_rows_ni(const RArgs &a, Ctr *ct, int r_first, int r_stride) { select_rows(a, ct, r_first, r_stride); }
+__device__ __noinline__ void light_rows_ni(const RArgs &a, Ctr *ct, int P, long long warp0, long long nwarps) { light_rows(a, ct, P, warp0, nwarps); }
+__device__ __noinline__ void heavy_items_ni(const RArgs &a, int P, int e_lo, int e_hi, int S, int gwarp, int nwarps, int nactive) {
+    heavy_items(a, P, e_lo, e_hi, S, gwarp, nwarps, false, nactive);
+}
+
+__global__ void __launch_bounds__(CHAIN_THREADS, 1) kr_chain(RArgs a, ChainCtl ctl) {
+    RState *st = a.st;
+    const int tid = threadIdx.x, wpc = CHAIN_THREADS / 32;
+    const int nwarps = (int)gridDim.x * wpc;
+    // consecutive items go to different SMs
+    const int gwarp = (tid >> 5) * (int)gridDim.x + (int)blockIdx.x;
+    const int gthread = gwarp * 32 + (tid & 31), gthreads = nwarps * 32;
+    if (blockIdx.x == 0 && tid == 0) st->exit_reason = 0;
+    unsigned int target = __ldcg(&st->bar);   // all CTAs start from the same value: the previous launch ended on a barrier
+    target -= target % gridDim.x;
+    for (int it = 0; it < ctl.max_rounds; ++it) {
+        const int round = __ldcg(&st->round), par = round & 1;
+        Ctr *ct = &st->ctr[par], *nx = &st->ctr[par ^ 1];
+        if (__ldcg(&st->done)) break;
+        const int nactive = __ldcg(&st->nactive);
+        if (a.ncols >= 256 && (long long)nactive * 2 <= a.ncols) {   // the host compacts and comes back
+            if (blockIdx.x == 0 && tid == 0) st->exit_reason = 1;
+            break;
+        }
+        select_rows_ni(a, ct, gthread, gthreads);
+        grid_barrier(&st->bar, target);
+        const int P = __ldcg(&ct->P);
+        {
+            const int Sb = heavy_segments(a, P, P, nwarps / 2);
+            heavy_items_ni(a, P, 0, P, Sb, gwarp, nwarps, nactive);
+            light_rows_ni(a, ct, P, gwarp, nwarps);
+        }
+        grid_barrier(&st->bar, target);
+        const int total = P + __ldcg(&ct->qlen);
+        {
+            const int Sr = heavy_segments(a, 0, total - P, nwarps);
+            heavy_items_ni(a, P, P, total, Sr, gwarp, nwarps, nactive);
+            if (blockIdx.x == 0) {
+                retire_pairs(a, P, tid, CHAIN_THREADS);
+                __syncthreads();
+                if (tid == 0) close_round(a, ct, nx, P, total);
+            }
+        }
+        grid_barrier(&st->bar, target);
     }
 }
 
@@ -864,23 +1000,26 @@ __global__ void __launch_bounds__(HEAVY_THREADS, 3) kb_rebuild(RArgs a, Cols d, 
 // closes a bulk round like the last CTA of kr_heavy does
 __global__ void kb_retire(RArgs a, int nnew) {
     RState *st = a.st;
-    const int P = st->P;
+    Ctr *ct = &st->ctr[0];
+    const int P = ct->P;
     const unsigned long long nfree = (unsigned long long)(nnew - P), oldcols = (unsigned long long)st->nactive;
     st->stats[0] += nfree;
     st->stats[1] += nfree * oldcols;
     st->stats[2] += (unsigned long long)P;
     st->stats[3] += (unsigned long long)P * oldcols;
     st->stats[4] += nfree * (unsigned long long)P;
+    st->stats[7] += nfree * oldcols;
+    st->stats[8] += (unsigned long long)P * oldcols;
     st->n_done += P;
     st->nactive -= P;
-    st->stats[5] += st->deferred;
+    st->stats[5] += ct->deferred;
     if (st->n_done >= a.n - 1) st->done = 1;
     else if (st->ambiguous && !a.diag) st->done = 1;
     st->last_P = P;
     st->last_q = nnew - P;
-    st->P = 0;
-    st->qlen = 0;
-    st->deferred = 0;
+    ct->P = 0;
+    ct->qlen = 0;
+    ct->deferred = 0;
     st->round += 1;
 }
 
@@ -943,14 +1082,14 @@ extern "C" size_t hc_linkage_rounds_workspace_bytes(int32_t n) {
 
 // W: n x n float64 full symmetric working matrix (squared distances for ward, +inf diagonal), destroyed.
 // Returns HC_OK with Z filled, or HC_EAMBIGUOUS (W is then garbage: rebuild it and call hc_linkage).
-// h_stats[16]: rounds, merges, rescans, sum of live columns over rescans, sum over merged-row builds,
+// h_stats[24]: rounds, merges, rescans, sum of live columns over rescans, sum over merged-row builds,
 // row x pair light updates, compactions, near-tied sorted heights, near-tied pair observations (pairs left
 // pending for a round), pairs deferred for an exact rescan.
 extern "C" int hc_linkage_rounds(double *W, int32_t n, int method, void *workspace, size_t workspace_bytes,
                                  double *h_Z, int64_t *h_stats, void *stream_) {
     cudaStream_t stream = (cudaStream_t)stream_;
     HC_REQUIRE(W && workspace && h_Z && n >= 1 && method >= 0 && method <= 4, "bad arguments");
-    if (h_stats) memset(h_stats, 0, 16 * sizeof(int64_t));
+    if (h_stats) memset(h_stats, 0, 24 * sizeof(int64_t));
     if (n < 2) return HC_OK;
     Layout L;
     if (workspace_bytes < hc_linkage_rounds_workspace_bytes(n) || !carve(workspace, workspace_bytes, n, L)) {
@@ -998,7 +1137,7 @@ extern "C" int hc_linkage_rounds(double *W, int32_t n, int method, void *workspa
     const bool ktime = getenv("HC_ROUNDS_KTIME") != nullptr && !trace;
     std::vector<cudaEvent_t> kev;   // events of the current batch, in launch order
     std::vector<int> kkind;         // kind of the interval that STARTS at event k (-1: none)
-    double kus[5] = {0, 0, 0, 0, 0};
+    double kus[7] = {0, 0, 0, 0, 0, 0, 0};  // select, light, heavy, compaction, initial scan, kb_rebuild, kr_chain
     size_t kused = 0;
     auto kmark = [&](int kind) {
         if (!ktime) return;
@@ -1097,9 +1236,9 @@ extern "C" int hc_linkage_rounds(double *W, int32_t n, int method, void *workspa
         HC_CHECK_LAUNCH();
         HC_CUDA_OK(cudaMemcpyAsync(&h, L.st, sizeof h, cudaMemcpyDeviceToHost, stream));
         HC_CUDA_OK(cudaStreamSynchronize(stream));
-        const int nnew = h.nactive - h.P;
+        const int nnew = h.nactive - h.ctr[0].P;
         const long long stride_new = (nnew + 1) & ~1;
-        const bool bulk = !h.done && !h.ambiguous && (long long)h.P * 5 >= a.ncols && nnew >= 2 &&
+        const bool bulk = !h.done && !h.ambiguous && (long long)h.ctr[0].P * 5 >= a.ncols && nnew >= 2 &&
                           (in_spare || (size_t)nnew * stride_new <= L.spare_elems);
         if (!bulk) {            // finish this round the ordinary way and go on in batches
             light_heavy();
@@ -1110,7 +1249,7 @@ extern "C" int hc_linkage_rounds(double *W, int32_t n, int method, void *workspa
         kmark(3);
         kc_map<<<1, 1024, 0, stream>>>(a.c.role, a.ncols, L.newidx, L.oldidx, true);
         kb_desc<<<(nnew + 255) / 256, 256, 0, stream>>>(a.c, L.cols[cur ^ 1], a.pairs, L.oldidx, nnew, L.desc, L.colp, n);
-        kmark(2);
+        kmark(5);
         {
             const int rg = sms * 12;  // 3 CTAs per SM (80 registers): 12.4 vs 14.2 ms in the largest round at C3
             const Cols dc = L.cols[cur ^ 1];
@@ -1130,7 +1269,7 @@ extern "C" int hc_linkage_rounds(double *W, int32_t n, int method, void *workspa
             cudaEventSynchronize(ev1);
             float ms = 0;
             cudaEventElapsedTime(&ms, ev0, ev1);
-            fprintf(stderr, "[rounds trace] bulk round pairs %d ncols %d -> %d us %.1f\n", h.P, a.ncols, nnew, ms * 1e3f);
+            fprintf(stderr, "[rounds trace] bulk round pairs %d ncols %d -> %d us %.1f\n", h.ctr[0].P, a.ncols, nnew, ms * 1e3f);
         }
         cur ^= 1;
         in_spare = !in_spare;
@@ -1141,7 +1280,54 @@ extern "C" int hc_linkage_rounds(double *W, int32_t n, int method, void *workspa
         n_launches += 4;
         rebuilds++;
     }
-    for (;;) {
+    // The rest of the run in cooperative launches of the persistent kernel (one CTA per SM, many rounds per launch);
+    // the one-kernel-per-phase path below stays for the per-round trace and HC_ROUNDS_PERSIST=0.
+    bool persist = !trace && getenv("HC_ROUNDS_DIAG") == nullptr;
+    if (const char *e = getenv("HC_ROUNDS_PERSIST")) persist = persist && atoi(e) != 0;
+    int chain_grid = 0;
+    if (persist) {
+        int dev = 0, coop = 0, occ = 0;
+        cudaGetDevice(&dev);
+        cudaDeviceGetAttribute(&coop, cudaDevAttrCooperativeLaunch, dev);
+        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kr_chain, CHAIN_THREADS, 0);
+        chain_grid = sms;
+        if (!coop || occ < 1) persist = false;
+    }
+    while (persist) {
+        ChainCtl ctl;
+        ctl.max_rounds = 1 << 20;
+        if (const char *e = getenv("HC_ROUNDS_CHAIN_MAX")) ctl.max_rounds = atoi(e) > 0 ? atoi(e) : 1;
+        void *kargs[] = {(void *)&a, (void *)&ctl};
+        kmark(6);
+        HC_CUDA_OK(cudaLaunchCooperativeKernel((const void *)kr_chain, dim3(chain_grid), dim3(CHAIN_THREADS), kargs, 0, stream));
+        kmark(-1);
+        n_launches++;
+        HC_CUDA_OK(cudaMemcpyAsync(&h, L.st, sizeof h, cudaMemcpyDeviceToHost, stream));
+        HC_CUDA_OK(cudaStreamSynchronize(stream));
+        kflush();
+        if (h.done) break;
+        if (compact && a.ncols >= 256 && (long long)h.nactive * 2 <= a.ncols) {
+            const int nnew = h.nactive;
+            double *dst = in_spare ? W : L.spare;
+            const long long stride_new = (nnew + 1) & ~1;
+            HC_REQUIRE(in_spare || (size_t)nnew * stride_new <= L.spare_elems, "compaction buffer too small");
+            kmark(3);
+            kc_map<<<1, 1024, 0, stream>>>(a.c.role, a.ncols, L.newidx, L.oldidx, false);
+            kc_gather<<<nnew < sms * 8 ? nnew : sms * 8, 256, 0, stream>>>(a.W, a.stride, dst, stride_new, L.oldidx, nnew);
+            kc_cols<<<(nnew + 255) / 256, 256, 0, stream>>>(a.c, L.cols[cur ^ 1], L.newidx, L.oldidx, nnew);
+            kmark(-1);
+            HC_CHECK_LAUNCH();
+            n_launches += 3;
+            cur ^= 1;
+            in_spare = !in_spare;
+            a.c = L.cols[cur];
+            a.W = dst;
+            a.stride = stride_new;
+            a.ncols = nnew;
+            compactions++;
+        }
+    }
+    for (; !persist;) {
         if (trace) cudaEventRecord(ev0, stream);
         // (instantiating a graph costs ~0.1 ms: only worth it for the long epochs of big problems)
         const bool graph_now = use_graph && a.ncols >= 16384;
@@ -1235,6 +1421,12 @@ extern "C" int hc_linkage_rounds(double *W, int32_t n, int method, void *workspa
         h_stats[9] = (int64_t)h.stats[5];
         for (int k = 0; k < 5; ++k) h_stats[10 + k] = (int64_t)(kus[k] + 0.5);
         h_stats[15] = n_launches;
+        h_stats[16] = (int64_t)(kus[5] + 0.5);
+        h_stats[17] = (int64_t)(kus[6] + 0.5);
+        h_stats[18] = (int64_t)h.stats[7];   // bulk rounds: live columns summed over the free rows of kb_rebuild
+        h_stats[19] = (int64_t)h.stats[8];   // ... and over its merged rows
+        h_stats[20] = rebuilds;
+        h_stats[21] = persist ? 1 : 0;
     }
     if (uncertified) return HC_EAMBIGUOUS;
     if (near) {

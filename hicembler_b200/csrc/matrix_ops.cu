@@ -8,6 +8,8 @@
 // triangle that d[np.triu_indices(n,1)] (bam2clusters.py:385) selects.
 #include <math.h>
 
+#include <algorithm>
+
 #include "common.cuh"
 
 namespace {
@@ -208,6 +210,18 @@ __global__ void __launch_bounds__(256) k_tilepair64(const TIn *C, int n, int T, 
     }
 }
 
+// Row blocks of one matrix living in different buffers (the row-sharded build keeps block k in the HBM of rank k;
+// the linkage rank reads them over NVLink): row i = base[i / per] + (i % per) * n.  One buffer: per >= n.
+struct RowBlocks {
+    const void *base[HC_MAX_RANKS];
+    int per;
+    template <typename T>
+    __device__ __forceinline__ const T *row(int i, int n) const {
+        const int b = i / per;
+        return (const T *)base[b] + (size_t)(i - b * per) * n;
+    }
+};
+
 struct Xform {
     int kind;
     double p0, p1;
@@ -284,7 +298,7 @@ __device__ __forceinline__ double xform(const Xform &t, T raw, int i, int j) {
 }
 
 template <typename T>
-__global__ void __launch_bounds__(256) k_transform_working(const T *X, int n, Xform t, double *W,
+__global__ void __launch_bounds__(256) k_transform_working(RowBlocks X, int n, Xform t, double *W,
                                                             int32_t *flags) {
     const int I = blockIdx.y, J = blockIdx.x;
     if (I > J) return;
@@ -295,7 +309,7 @@ __global__ void __launch_bounds__(256) k_transform_working(const T *X, int n, Xf
         int i = I * TS + r, j = J * TS + tx;
         double v = 0;
         if (i < n && j < n && i < j) {
-            v = xform<T>(t, X[(size_t)i * n + j], i, j);
+            v = xform<T>(t, X.row<T>(i, n)[j], i, j);
             bad |= isnan(v);
         }
         A[r][tx] = v;
@@ -318,7 +332,7 @@ __global__ void __launch_bounds__(256) k_transform_working(const T *X, int n, Xf
 
 // 64 x 64 tile version for the float matrix (n % 4 == 0): one CTA per tile pair of the upper triangle, float4
 // loads, the transformed tile staged once in shared memory as f64, both mirror tiles written with 16-byte stores.
-__global__ void __launch_bounds__(256) k_transform_tile64(const float *X, int n, int T, Xform t, double *W,
+__global__ void __launch_bounds__(256) k_transform_tile64(RowBlocks X, int n, int T, Xform t, double *W,
                                                            int32_t *flags) {
     __shared__ double A[T64][T64 + 1];
     int I, J;
@@ -330,7 +344,7 @@ __global__ void __launch_bounds__(256) k_transform_tile64(const float *X, int n,
         const int r = ty + 16 * p;
         const int i = I * T64 + r, j = J * T64 + tx * 4;
         float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
-        if (i < n && j < n && i < j + 3) v = __ldcs((const float4 *)(X + (size_t)i * n + j));
+        if (i < n && j < n && i < j + 3) v = __ldcs((const float4 *)(X.row<float>(i, n) + j));
         const float *pv = (const float *)&v;
 #pragma unroll
         for (int q = 0; q < 4; ++q) {
@@ -574,23 +588,108 @@ extern "C" int hc_symmetrize(void *d, int32_t n, int dtype, double add, void *d_
     return HC_OK;
 }
 
+static int transform_blocks(const RowBlocks &rb, bool aligned16, int dtype, int32_t n, int kind, double p0, double p1,
+                            const double *r, const double *c, double vmax, int square, double *W, int32_t *d_flags,
+                            cudaStream_t stream) {
+    Xform t = make_xform(kind, p0, p1, r, c, vmax, square);
+    int T = (n + TS - 1) / TS;
+    HC_CUDA_OK(cudaMemsetAsync(d_flags, 0, sizeof(int32_t), stream));
+    if (dtype == 0 && (n & 3) == 0 && aligned16 && (((uintptr_t)W) & 15) == 0 && !getenv("HC_FOLD_TS32")) {
+        const int T6 = (n + T64 - 1) / T64;
+        const long long pairs = (long long)T6 * (T6 + 1) / 2;
+        k_transform_tile64<<<(unsigned)pairs, 256, 0, stream>>>(rb, n, T6, t, W, d_flags);
+    } else if (dtype == 0)
+        k_transform_working<float><<<dim3(T, T), dim3(TS, 8), 0, stream>>>(rb, n, t, W, d_flags);
+    else
+        k_transform_working<double><<<dim3(T, T), dim3(TS, 8), 0, stream>>>(rb, n, t, W, d_flags);
+    HC_CHECK_LAUNCH();
+    return HC_OK;
+}
+
 extern "C" int hc_transform_to_working(const void *X, int dtype, int32_t n, int kind, double p0, double p1,
                                        const double *r, const double *c, double vmax, int square,
                                        double *W, int32_t *d_flags, void *stream_) {
     cudaStream_t stream = (cudaStream_t)stream_;
     HC_REQUIRE(X && W && d_flags && n > 0 && kind >= 0 && kind <= 3 && (dtype == 0 || dtype == 1), "bad arguments");
     HC_REQUIRE((r == nullptr) == (c == nullptr), "r and c must be given together");
-    Xform t = make_xform(kind, p0, p1, r, c, vmax, square);
-    int T = (n + TS - 1) / TS;
-    HC_CUDA_OK(cudaMemsetAsync(d_flags, 0, sizeof(int32_t), stream));
-    if (dtype == 0 && (n & 3) == 0 && (((uintptr_t)X | (uintptr_t)W) & 15) == 0 && !getenv("HC_FOLD_TS32")) {
-        const int T6 = (n + T64 - 1) / T64;
-        const long long pairs = (long long)T6 * (T6 + 1) / 2;
-        k_transform_tile64<<<(unsigned)pairs, 256, 0, stream>>>((const float *)X, n, T6, t, W, d_flags);
-    } else if (dtype == 0)
-        k_transform_working<float><<<dim3(T, T), dim3(TS, 8), 0, stream>>>((const float *)X, n, t, W, d_flags);
-    else
-        k_transform_working<double><<<dim3(T, T), dim3(TS, 8), 0, stream>>>((const double *)X, n, t, W, d_flags);
+    RowBlocks rb;
+    memset(&rb, 0, sizeof rb);
+    rb.base[0] = X;
+    rb.per = n;
+    return transform_blocks(rb, (((uintptr_t)X) & 15) == 0, dtype, n, kind, p0, p1, r, c, vmax, square, W, d_flags, stream);
+}
+
+extern "C" int hc_transform_gather(const void *const *h_blocks, int32_t nblocks, int32_t per, int dtype, int32_t n, int kind,
+                                   double p0, double p1, const double *r, const double *c, double vmax, int square,
+                                   double *W, int32_t *d_flags, void *stream_) {
+    cudaStream_t stream = (cudaStream_t)stream_;
+    HC_REQUIRE(h_blocks && W && d_flags && n > 0 && kind >= 0 && kind <= 3 && (dtype == 0 || dtype == 1), "bad arguments");
+    HC_REQUIRE(nblocks >= 1 && nblocks <= HC_MAX_RANKS && per > 0 && per % T64 == 0 && (long long)per * nblocks >= n,
+               "rows per block must be a multiple of 64 and cover the matrix");
+    HC_REQUIRE((r == nullptr) == (c == nullptr), "r and c must be given together");
+    RowBlocks rb;
+    memset(&rb, 0, sizeof rb);
+    bool aligned = true;
+    for (int k = 0; k < nblocks; ++k) {
+        HC_REQUIRE(h_blocks[k] || (long long)per * k >= n, "null block pointer");
+        rb.base[k] = h_blocks[k];
+        aligned = aligned && (((uintptr_t)h_blocks[k]) & 15) == 0;
+    }
+    rb.per = per;
+    return transform_blocks(rb, aligned, dtype, n, kind, p0, p1, r, c, vmax, square, W, d_flags, stream);
+}
+
+// max over a flat array (np.max of array2scaffolds.py:31 / bam2clusters.py:45): block maxima, then one block
+template <typename T>
+__global__ void __launch_bounds__(256) k_max_partial(const T *X, long long count, T *part) {
+    __shared__ T sh[8];
+    T m = -INFINITY;
+    bool nan = false;
+    for (long long k = blockIdx.x * (long long)blockDim.x + threadIdx.x; k < count; k += (long long)gridDim.x * blockDim.x) {
+        const T v = X[k];
+        nan |= v != v;
+        m = v > m ? v : m;
+    }
+    if (nan) m = (T)NAN;   // numpy's max propagates NaN
+    for (int o = 16; o; o >>= 1) {
+        const T w = __shfl_xor_sync(0xffffffffu, m, o);
+        m = (m != m || w != w) ? (T)NAN : (w > m ? w : m);
+    }
+    if ((threadIdx.x & 31) == 0) sh[threadIdx.x >> 5] = m;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        for (int k = 1; k < 8; ++k) m = (m != m || sh[k] != sh[k]) ? (T)NAN : (sh[k] > m ? sh[k] : m);
+        part[blockIdx.x] = m;
+    }
+}
+
+extern "C" int hc_matrix_max(const void *X, int dtype, int64_t count, void *d_partial, int32_t n_partial, void *d_max,
+                             void *stream_) {
+    cudaStream_t stream = (cudaStream_t)stream_;
+    HC_REQUIRE(X && d_partial && d_max && count > 0 && n_partial >= 1 && (dtype == 0 || dtype == 1), "bad arguments");
+    const int grid = (int)std::min<long long>(n_partial, (count + 255) / 256);
+    if (dtype == 0) {
+        k_max_partial<float><<<grid, 256, 0, stream>>>((const float *)X, count, (float *)d_partial);
+        k_max_partial<float><<<1, 256, 0, stream>>>((const float *)d_partial, grid, (float *)d_max);
+    } else {
+        k_max_partial<double><<<grid, 256, 0, stream>>>((const double *)X, count, (double *)d_partial);
+        k_max_partial<double><<<1, 256, 0, stream>>>((const double *)d_partial, grid, (double *)d_max);
+    }
+    HC_CHECK_LAUNCH();
+    return HC_OK;
+}
+
+__global__ void k_gather_elements(const float *A, int n, const int32_t *rows, const int32_t *cols, long long m, float *out) {
+    for (long long k = blockIdx.x * (long long)blockDim.x + threadIdx.x; k < m; k += (long long)gridDim.x * blockDim.x)
+        out[k] = A[(size_t)rows[k] * n + cols[k]];
+}
+
+extern "C" int hc_gather_elements(const float *A, int32_t n, const int32_t *rows, const int32_t *cols, int64_t m,
+                                  float *out, void *stream_) {
+    cudaStream_t stream = (cudaStream_t)stream_;
+    HC_REQUIRE(A && n > 0 && m >= 0 && (m == 0 || (rows && cols && out)), "bad arguments");
+    if (m == 0) return HC_OK;
+    k_gather_elements<<<(int)std::min<long long>((m + 255) / 256, 4096), 256, 0, stream>>>(A, n, rows, cols, m, out);
     HC_CHECK_LAUNCH();
     return HC_OK;
 }

@@ -81,14 +81,44 @@ def upto_cutoff(records, mapq, upto, region_mask=None, skip_flag=SKIP_FLAG):
     return n_eff.value, lines.value
 
 
+def _bin_stats_dict(stats):
+    return dict(lines=stats[0], binned=stats[1], skipped_absent=stats[2], out_of_range=stats[3],
+                key_errors=stats[4], overflow=stats[5], fast_path=bool(stats[6]),
+                tile_rows=stats[7] >> 32, col_segments=stats[7] & 0xFFFFFFFF, outside_rows=stats[8])
+
+
+class DeferredBinStats:
+    """Stats of an asynchronous hc_bin_pairs call: nothing was copied to the host and the stream was not synchronised;
+    ``read()`` does both (and raises IndexError / KeyError if the call met the reference's error cases)."""
+
+    def __init__(self, workspace, stream):
+        self.workspace, self.stream, self._st = workspace, stream, None
+
+    def snapshot(self):
+        """keep the 128 stats bytes in a buffer of their own, so that the workspace can serve the next call"""
+        keep = torch.empty(128, dtype=torch.uint8, device=self.workspace.device)
+        keep.copy_(self.workspace[:128], non_blocking=True)
+        self.workspace = keep
+        return self
+
+    def read(self):
+        if self._st is None:
+            stats = (C.c_int64 * 16)()
+            rc = _lib.lib().hc_bin_pairs_stats(_ptr(self.workspace), stats, self.stream)
+            self._st = _bin_stats_dict(stats)
+            _lib.check(rc)
+        return self._st
+
+
 def bin_pairs(records, offsets, window_bp, n_windows, mapq, member=None, region_mask=None,
               n_pairs=None, rows=None, skip_flag=SKIP_FLAG, mode=0, out=None, workspace=None,
-              return_stats=False):
+              return_stats=False, defer_stats=False):
     """Scatter-add read pairs into the full-orientation u32 count matrix (K1).
 
     offsets/member: int32 CUDA tensors indexed by refID (-1 = absent).  ``window_bp=None`` bins
     one window per contig (contig-level matrix).  Returns int32-typed tensor holding u32 counts of
-    shape (rows, n_windows)."""
+    shape (rows, n_windows).  ``defer_stats=True``: asynchronous call (no host synchronisation); returns
+    (out, DeferredBinStats) -- the workspace must stay untouched until the stats have been read."""
     _dev(records)
     dev = records.device
     n = records.shape[0] if n_pairs is None else int(n_pairs)
@@ -98,17 +128,42 @@ def bin_pairs(records, offsets, window_bp, n_windows, mapq, member=None, region_
     need = _lib.lib().hc_bin_pairs_workspace_bytes(n, row1 - row0)
     if workspace is None or workspace.numel() < need:
         workspace = torch.empty(need, dtype=torch.uint8, device=dev)
-    stats = (C.c_int64 * 8)()
+    stats = (C.c_int64 * 16)()
     wbp = _UINT32_MAX if window_bp is None else int(window_bp)
+    stream = _stream()
     rc = _lib.lib().hc_bin_pairs(_ptr(records), n, _ptr(offsets), _ptr(member), _ptr(region_mask),
                                  offsets.numel(), wbp, int(n_windows), int(mapq), skip_flag,
                                  row0, row1, _ptr(out), _ptr(workspace), workspace.numel(), mode,
-                                 stats, _stream())
+                                 None if defer_stats else stats, stream)
     _lib.check(rc)
-    st = dict(lines=stats[0], binned=stats[1], skipped_absent=stats[2], out_of_range=stats[3],
-              key_errors=stats[4], overflow=stats[5], fast_path=bool(stats[6]),
-              tile_rows=stats[7] >> 32, col_segments=stats[7] & 0xFFFFFFFF)
+    if defer_stats:
+        return out, DeferredBinStats(workspace, stream)
+    st = _bin_stats_dict(stats)
     return (out, st) if return_stats else out
+
+
+def bin_pairs_multi(records, offsets_list, window_bps, n_windows_list, mapq, region_mask=None, n_pairs=None,
+                    skip_flag=SKIP_FLAG, outs=None, accumulate=False):
+    """All window sizes of one bam2arrays call from ONE read of the records (hc_bin_pairs_multi; <= 4 sizes).
+    offsets_list[0] is also the membership table (bam2clusters.py:151).  Returns (list of count tensors, stats)."""
+    _dev(records)
+    dev = records.device
+    k = len(window_bps)
+    n = records.shape[0] if n_pairs is None else int(n_pairs)
+    if outs is None:
+        outs = [None] * k
+    outs = [o if o is not None else torch.empty((nw, nw), dtype=torch.int32, device=dev) for o, nw in zip(outs, n_windows_list)]
+    ws = torch.empty(256, dtype=torch.uint8, device=dev)
+    stats = (C.c_int64 * 16)()
+    offs = (C.c_void_p * k)(*[o.data_ptr() for o in offsets_list])
+    cnts = (C.c_void_p * k)(*[o.data_ptr() for o in outs])
+    wbp = (C.c_uint32 * k)(*[int(w) for w in window_bps])
+    nws = (C.c_int32 * k)(*[int(w) for w in n_windows_list])
+    rc = _lib.lib().hc_bin_pairs_multi(_ptr(records), n, k, offs, _ptr(region_mask), offsets_list[0].numel(), wbp, nws,
+                                       int(mapq), skip_flag, cnts, int(bool(accumulate)), _ptr(ws), ws.numel(), stats,
+                                       _stream())
+    _lib.check(rc)
+    return outs, _bin_stats_dict(stats)
 
 
 def contig_region_filter(records, tlen, ref_span, contig_size, member, min_size, nth, mapq,
@@ -357,14 +412,15 @@ def linkage_rounds(W, method="ward", nan_flags=None, workspace=None):
     ws = workspace if workspace is not None and workspace.numel() >= need else \
         torch.empty(need, dtype=torch.uint8, device=W.device)
     Z = np.empty((max(n - 1, 0), 4), dtype=np.float64)
-    stats = (C.c_int64 * 16)()
+    stats = (C.c_int64 * 24)()
     rc = L.hc_linkage_rounds(_ptr(W), n, METHODS[method], _ptr(ws), ws.numel(),
                              Z.ctypes.data_as(C.c_void_p), stats, _stream())
     st = dict(engine="rounds", rounds=stats[0], merges=stats[1], rescans=stats[2], rescan_cols=stats[3],
               build_cols=stats[4], light_updates=stats[5], compactions=stats[6], near_tied_heights=stats[7],
               pending_near_ties=stats[8], deferred_rescans=stats[9],
               kernel_us=dict(select=stats[10], light=stats[11], heavy=stats[12], compaction=stats[13],
-                             initial_scan=stats[14]), launches=stats[15],
+                             initial_scan=stats[14], rebuild=stats[16], chain=stats[17]), launches=stats[15],
+              bulk_rescan_cols=stats[18], bulk_build_cols=stats[19], bulk_rounds=stats[20], persistent=bool(stats[21]),
               certified=(rc == _lib.HC_OK))
     if rc == _lib.HC_EAMBIGUOUS:
         st["reason"] = _lib.last_error()
@@ -460,6 +516,34 @@ def block_sums4(A, jobs):
     d_off, d_n1, d_n2 = up(off), up(n1), up(n2)  # kept alive (and distinct) until the launch is queued
     _lib.check(_lib.lib().hc_block_sums4(_ptr(A), n, _ptr(idx), _ptr(d_off), _ptr(d_n1), _ptr(d_n2), len(jobs),
                                          _ptr(out), _stream()))
+    return out.cpu().numpy()
+
+
+def matrix_max(X):
+    """np.max(X) for a float32 / float64 CUDA tensor (hc_matrix_max); returns a Python float."""
+    _dev(X)
+    X = X.contiguous()
+    part = torch.empty(1024, dtype=X.dtype, device=X.device)
+    out = torch.empty(1, dtype=X.dtype, device=X.device)
+    _lib.check(_lib.lib().hc_matrix_max(_ptr(X), _dtype_code(X), X.numel(), _ptr(part), 1024, _ptr(out), _stream()))
+    return float(out.item())
+
+
+def gather_elements(A, rows, cols):
+    """A[rows[k], cols[k]] for int32 index arrays (numpy) -> float32 numpy array (one launch, one read-back)."""
+    _dev(A)
+    n = A.shape[0]
+    assert A.dtype == torch.float32 and A.shape == (n, n) and A.is_contiguous()
+    rows = np.ascontiguousarray(rows, dtype=np.int32)
+    cols = np.ascontiguousarray(cols, dtype=np.int32)
+    m = len(rows)
+    if m == 0:
+        return np.empty(0, dtype=np.float32)
+    if rows.min() < 0 or rows.max() >= n or cols.min() < 0 or cols.max() >= n:
+        raise IndexError("window index out of range")
+    d_r, d_c = torch.from_numpy(rows).to(A.device), torch.from_numpy(cols).to(A.device)
+    out = torch.empty(m, dtype=torch.float32, device=A.device)
+    _lib.check(_lib.lib().hc_gather_elements(_ptr(A), n, _ptr(d_r), _ptr(d_c), m, _ptr(out), _stream()))
     return out.cpu().numpy()
 
 

@@ -181,6 +181,54 @@ def write_bam(path, rec, names, sizes, tlen=None):
         out.write(_BGZF_EOF)
 
 
+def write_bam_fixed(path, rec, names, sizes, level=1):
+    """Vectorised BAM writer for synthetic benchmarks: every record has a 2-byte read name, one CIGAR operation
+    (l_seq M), l_seq bases and qualities -- all records must share one l_seq, so that a record is a fixed-size
+    struct (192 bytes at l_seq = 100) built with numpy; BGZF blocks of 0xFF00 bytes, zlib ``level``."""
+    rec = np.ascontiguousarray(rec)
+    L = int(rec["l_seq"][0]) if len(rec) else 0
+    if len(rec) and not np.all(rec["l_seq"] == L):
+        raise ValueError("write_bam_fixed needs one common l_seq")
+    nseq, ncig = (L + 1) // 2, (1 if L else 0)
+    body = 32 + 2 + 4 * ncig + nseq + L
+    dt = np.dtype([("block_size", "<i4"), ("refID", "<i4"), ("pos", "<i4"), ("l_read_name", "u1"), ("mapq", "u1"),
+                   ("bin", "<u2"), ("n_cigar", "<u2"), ("flag", "<u2"), ("l_seq", "<i4"), ("next_refID", "<i4"),
+                   ("next_pos", "<i4"), ("tlen", "<i4"), ("name", "S2"), ("cigar", "<u4", (ncig,)),
+                   ("seq", "u1", (nseq,)), ("qual", "u1", (L,))])
+    assert dt.itemsize == 4 + body
+    out = np.zeros(len(rec), dtype=dt)
+    out["block_size"] = body
+    for k in ("refID", "pos", "mapq", "flag", "l_seq", "next_refID", "next_pos"):
+        out[k] = rec[k]
+    out["l_read_name"] = 2
+    out["name"] = b"r"
+    out["n_cigar"] = ncig
+    if ncig:
+        out["cigar"] = (L << 4)
+    out["seq"] = 0x11
+    out["qual"] = 0xFF
+    out["bin"] = 4680                    # (unused by the decoder; samtools recomputes it when indexing)
+    text = "@HD\tVN:1.0\tSO:coordinate\n" + "".join("@SQ\tSN:%s\tLN:%d\n" % (n, s) for n, s in zip(names, sizes))
+    head = io.BytesIO()
+    head.write(b"BAM\x01" + struct.pack("<i", len(text)) + text.encode())
+    head.write(struct.pack("<i", len(names)))
+    for n, s in zip(names, sizes):
+        nb = n.encode() + b"\0"
+        head.write(struct.pack("<i", len(nb)) + nb + struct.pack("<i", s))
+    raw = memoryview(head.getvalue() + out.tobytes())
+
+    def block(data):
+        comp = zlib.compressobj(level, zlib.DEFLATED, -15)
+        cdata = comp.compress(data) + comp.flush()
+        hdr = struct.pack("<BBBBIBBHBBHH", 0x1F, 0x8B, 8, 4, 0, 0, 0xFF, 6, 66, 67, 2, len(cdata) + 25)
+        return hdr + cdata + struct.pack("<II", zlib.crc32(data) & 0xFFFFFFFF, len(data))
+    with open(path, "wb") as fh:
+        for s in range(0, len(raw), 0xFF00):
+            fh.write(block(raw[s:s + 0xFF00]))
+        fh.write(_BGZF_EOF)
+    return len(raw)
+
+
 def _reg2bin(beg, end):
     end -= 1
     if beg >> 14 == end >> 14: return ((1 << 15) - 1) // 7 + (beg >> 14)

@@ -187,28 +187,178 @@ def host_pairs_to_dendrogram(host_records, offsets, window_bp, n_windows, stagin
             events.append(ev)
     counts = torch.zeros((n_windows, n_windows), dtype=torch.int32, device=dev)
     mapq = kw.get("mapq", 10)
-    total, ok = None, True
+    pending = []
     for (a, b, c_lo, c_hi, r0, r1), ev in zip(plan, events):
         cur.wait_event(ev)
         if width == 4:
             ops.unpack_pairs16(wire[a:b], out=rec[a:b])
-        if not ok or r1 <= r0:
+        if r1 <= r0:
             continue
-        # guard: every record of the piece belongs to its contig range (the input really is sorted by contig)
-        lo_, hi_ = torch.aminmax(rec[a:b, 0].to(torch.int64) & 0xffffffff)
-        if int(lo_) < c_lo or (c_hi != _NO_REF and int(hi_) > c_hi):
-            ok = False
-            continue
-        _, st = ops.bin_pairs(rec[a:b], offsets, window_bp, n_windows, mapq, rows=(r0, r1), mode=2,
-                              out=counts[r0:r1], workspace=kw.get("workspace"), return_stats=True)
+        # asynchronous calls: no host synchronisation between the pieces.  A record of the piece that can be binned
+        # but whose row lies outside the piece's row range is counted by the kernel (outside_rows): the guard that
+        # the input really is sorted by contig
+        _, later = ops.bin_pairs(rec[a:b], offsets, window_bp, n_windows, mapq, rows=(r0, r1), mode=2,
+                                 out=counts[r0:r1], workspace=kw.get("workspace"), defer_stats=True)
+        pending.append(later.snapshot())
+    total = None
+    for later in pending:
+        st = later.read()
         if total is None:
             total = dict(st)
         else:
-            for k_ in ("lines", "binned", "skipped_absent", "out_of_range", "key_errors", "overflow"):
+            for k_ in ("lines", "binned", "skipped_absent", "out_of_range", "key_errors", "overflow", "outside_rows"):
                 total[k_] += st[k_]
             total["fast_path"] = total["fast_path"] and st["fast_path"]
-    if not ok or total is None:               # not sorted by contig after all: bin in one piece
+    if total is None or total["outside_rows"]:    # not sorted by contig after all: bin in one piece
         del counts
         return pairs_to_dendrogram(rec, offsets, window_bp, n_windows, **kw)
     total["chunks"] = len(plan)
     return pairs_to_dendrogram(rec, offsets, window_bp, n_windows, counts_stats=(counts, total), **kw)
+
+
+# ------------------------------------------------------------------------------------------------------------
+# one job over the GPUs of a node: row-sharded matrix build + Sinkhorn, linkage on one rank
+# ------------------------------------------------------------------------------------------------------------
+def window_of_records(rec_np, offsets_np, window_bp):
+    """read-1 window of host records (numpy int32 [k, 6] hc_pair_t or [k, 4] hc_pair16_t rows), -1 when the contig is
+    absent: the key the coordinate-sorted stream is cut by (get_window, bam2clusters.py:119-126)."""
+    import numpy as np
+    rec_np = np.atleast_2d(rec_np)
+    if rec_np.shape[1] == 6:
+        ref = rec_np[:, 0].astype(np.int64)
+        lseq = np.maximum(rec_np[:, 4].astype(np.int64), 1)
+        p1 = rec_np[:, 1].astype(np.int64) + 1 + lseq // 2
+    else:
+        v = rec_np[:, 2].astype(np.int64) & 0xfffff
+        ref = np.where(v == 0xfffff, -1, v)
+        p1 = (rec_np[:, 0].astype(np.int64) & 0xffffffff) + 1
+    ok = (ref >= 0) & (ref < len(offsets_np))
+    off = np.where(ok, np.asarray(offsets_np, dtype=np.int64)[np.clip(ref, 0, len(offsets_np) - 1)], -1)
+    return np.where(off >= 0, p1 // int(window_bp) + off, -1)
+
+
+def shard_plan(records, offsets_np, window_bp, n_windows, world):
+    """Record slice [a, b) of every rank's row block -- the job the BAM index (.bai) does for ``samtools view bam
+    <regions>`` (bam2clusters.py:108-117): a property of the input, computed once per record buffer.  ``records``:
+    host or device int32 tensor [P, 4|6] sorted by (contig, position).  Unmapped / absent contigs sort by their
+    neighbours (a monotone fill), and the result is verified by the binning kernels themselves (outside_rows)."""
+    import numpy as np
+    from .parallel import row_block
+    P = records.shape[0]
+    step = max(1, P // 65536)
+    idx = torch.arange(0, P, step, device=records.device)
+    samp = records[idx].cpu().numpy()
+    w = window_of_records(samp, offsets_np, window_bp)
+    w = np.maximum.accumulate(np.where(w < 0, 0, w))          # monotone fill
+    idx = idx.cpu().numpy()
+    plan = []
+    for k in range(world):
+        r0, r1 = row_block(n_windows, k, world)
+        cut = []
+        for row in (r0, r1):
+            if row >= n_windows and row == r1:
+                cut.append(P)
+                continue
+            s = int(np.searchsorted(w, row, side="left"))      # first sample with window >= row
+            lo = int(idx[s - 1]) if s > 0 else 0
+            hi = int(idx[s]) if s < len(idx) else P
+            if hi > lo:
+                blk = window_of_records(records[lo:hi].cpu().numpy(), offsets_np, window_bp)
+                blk = np.maximum.accumulate(np.where(blk < 0, 0, blk))
+                lo += int(np.searchsorted(blk, row, side="left"))
+            cut.append(lo)
+        plan.append((cut[0], max(cut[0], cut[1])))
+    plan[0] = (0, plan[0][1])
+    plan[-1] = (plan[-1][0], P)
+    for k in range(1, world):                                  # slices partition the stream
+        plan[k] = (plan[k - 1][1], max(plan[k - 1][1], plan[k][1]))
+    return plan
+
+
+def sharded_pairs_to_dendrogram(shard, records, offsets, window_bp, mapq=10, params=(0.5, 1.1), method="ward",
+                                balance=True, max_iter=1000, epsilon=0.00001, plan=None, timer=None, engine="auto",
+                                staging=None, root=0, workspace=None, local_slice=False):
+    """pairs -> Z as ONE job over the ranks of ``shard`` (a parallel.RowShard): every rank bins the slice of the
+    record stream that falls into its row block (host records: only that slice crosses the rank's own PCIe link),
+    the fold / Sinkhorn / transform exchanges read peer memory over NVLink, the dendrogram is built on ``root``.
+    Same result as pairs_to_dendrogram on one GPU: counts bit-exact, r / c to rounding (the column sums are added in a
+    different order), identical merge order.  Returns the pairs_to_dendrogram dict on ``root``, {"stats": ...}
+    elsewhere.  ``records``: the FULL stream, int32 [P, 6] on the device or [P, 4|6] (pinned) on the host -- or, with
+    ``local_slice=True`` and a ``plan``, only this rank's slice of it (what a rank keeps in its own pinned buffer)."""
+    import numpy as np
+    n = shard.n
+    g = shard.g
+    t = timer or StageTimer(False)
+    t.mark("start")
+    staging = {} if staging is None else staging
+    if plan is None:
+        if local_slice:
+            raise ValueError("local_slice=True needs the plan the slices were cut by")
+        key = ("plan", records.data_ptr(), records.shape[0], g.world)
+        if staging.get("plan_key") != key:
+            staging["plan_key"] = key
+            staging["plan"] = shard_plan(records, offsets.cpu().numpy(), window_bp, n, g.world)
+        plan = staging["plan"]
+    a, b = plan[shard.rank]
+    if local_slice:                                            # ``records`` already is this rank's slice [a, b)
+        lo, hi = 0, b - a
+    else:
+        lo, hi = a, b
+    dev = shard.device
+    if records.is_cuda:
+        rec = records[lo:hi]
+    else:                                                      # this rank's slice over this rank's PCIe link
+        width = records.shape[1]
+        need = max(b - a, 1)
+
+        def buf(name, wdt):
+            x = staging.get(name)
+            if x is None or x.shape[0] < need:
+                x = staging[name] = torch.empty((need, wdt), dtype=torch.int32, device=dev)
+            return x[:b - a]
+        rec = buf("rec24", 6)
+        if width == 6:
+            rec.copy_(records[lo:hi], non_blocking=True)
+        else:
+            wire = buf("rec16", 4)
+            wire.copy_(records[lo:hi], non_blocking=True)
+            ops.unpack_pairs16(wire, out=rec)
+    t.mark("h2d")
+    st = None
+    if shard.active:
+        _, later = ops.bin_pairs(rec, offsets, window_bp, n, mapq, rows=(shard.row0, shard.row1), out=shard.counts,
+                                 workspace=workspace, defer_stats=True)
+        st = later.read()
+    t.mark("bin_pairs")
+    # certificate of the slicing: no binnable record of any slice belongs to another rank's rows
+    flag = torch.tensor([float(st["outside_rows"]) if st else 0.0], dtype=torch.float32, device=dev)
+    if float(g.allreduce_max_float(flag).item()) > 0:
+        raise ValueError("records are not sorted by read-1 window: a row-sharded build needs coordinate-sorted input "
+                         "(or bin every rank's row block from the full stream with ops.bin_pairs(rows=...))")
+    out = {"stats": st, "slice": (a, b)}
+    vmax = shard.fold(add=1.0 if balance else 0.0)
+    t.mark("fold")
+    a_, b_ = params
+    r = c = None
+    if balance:
+        res = shard.sinkhorn_fit(vmax, max_iter, epsilon)
+        r, c = res.r, res.c
+        out.update(r=r, c=c, sk_iterations=res.iterations, sk_stop=res.stopping_condition, vmax=vmax,
+                   sk_passes=res.matrix_passes, sk_launches=res.launches)
+    t.mark("sinkhorn")
+    r_full = shard.prepare_transform(r)
+    if shard.rank == root:
+        made = []
+
+        def make_working():                                    # local: repeatable after an uncertified rounds run
+            Wf = shard.build_working(ops.KIND_POWER, a_, b_, r_full, c, vmax if balance else 1.0,
+                                     square=(method == "ward"))
+            if not made:
+                t.mark("transform")
+            made.append(1)
+            return Wf
+        Z, lst = ops.linkage_auto(make_working, method, engine=engine, return_stats=True)
+        out["Z"], out["linkage_stats"] = Z, lst
+    t.mark("linkage")
+    g.barrier()                                                # peers' blocks stay alive until the root is done
+    return out

@@ -2,7 +2,9 @@
 the passes run.  ``passes`` supplies the per-rank matrix passes over its row block (CUDA kernels in
 ops._CudaSinkhornPasses; a numpy stand-in in the gloo tests); ``allreduce`` sums a tensor over the
 ranks of a row-sharded fit (the NCCL all-reduce of the column-sum vector).  Every rank takes the same
-decisions because every decision is taken on all-reduced data."""
+decisions because every decision -- the flags for the AssertionError / UserWarning included -- is taken on
+all-reduced data.  (On an NVLink node the product path is hc_sk_fit_block, which keeps this loop on the device;
+this driver serves the symmetric single-GPU fit and process groups without peer memory.)"""
 from __future__ import annotations
 
 import warnings
@@ -27,6 +29,13 @@ def sinkhorn_driver(passes, max_iter, iterations0=0, allreduce=None):
     # r = 1 / (P c)                                                                  (:130-134)
     passes.rowpass()
     fl = passes.read_flags()
+    if allreduce is not None:
+        # the flags are rank-local (a negative entry or an empty row sits in ONE row block): all ranks must raise /
+        # warn together, or the others would wait in the next all-reduce for ever
+        ft = passes.y.new_tensor([float(fl["negative"]), float(fl["zero_col"]), float(fl["zero_row"])])
+        allreduce(ft)
+        neg, zc, zr = (bool(v) for v in ft.tolist())
+        fl = dict(negative=neg, zero_col=zc, zero_row=zr)
     if fl["negative"]:
         raise AssertionError("P must be non-negative (sinkhorn_knopp.py:110)")
     warned = False

@@ -21,7 +21,8 @@
 extern "C" {
 #endif
 
-#define HC_VERSION 100
+#define HC_VERSION 200
+#define HC_MAX_RANKS 8   /* GPUs of one NVLink / NVSwitch node that share a row-sharded matrix */
 
 typedef enum {
     HC_OK = 0,
@@ -75,11 +76,13 @@ int hc_device_info(int *h_sm_count, size_t *h_total_mem, int *h_cc_major, int *h
  * member[c]   = chr2window[0][contig c]   (membership test of :151; NULL = same as offsets)
  * region_mask = per-contig 0/1 for ``samtools view bam <contig>...`` (NULL = no regions)
  * n_pairs     = records to read (apply hc_upto_cutoff first for ``upto``)
- * h_stats[8]  = {lines kept by -q/-F/regions, pairs binned, skipped (contig absent),
- *               out-of-range, key errors, records routed through the overflow list,
- *               fast path used (1) or atomic fallback (0), reserved}
- * mode: bit 0 clear = auto (row-privatised shared-memory tiles; falls back to global atomics when
- *       the input is not sorted), bit 0 set = force the global-atomic kernel;
+ * h_stats[9]  = {lines kept by -q/-F/regions, pairs binned, skipped (contig absent),
+ *               out-of-range, key errors, stragglers (records whose row their chunk does not advertise),
+ *               1 = the sorted-input path handled everything / 0 = forced atomic kernel or the straggler
+ *               list overflowed and the stragglers were re-scanned, tile shape,
+ *               binnable records whose row lies outside [row0,row1) (left to the call that owns that block)}
+ * mode: bit 0 clear = auto (row-privatised shared-memory tiles; records of unsorted input that no tile sees are
+ *       added with global atomics afterwards, decided on the device), bit 0 set = force the global-atomic kernel;
  *       bit 1 set = accumulate into counts (several BAM files, bam2clusters.py:133) instead of
  *       overwriting it.
  */
@@ -90,6 +93,21 @@ int hc_bin_pairs(const hc_pair_t *pairs, int64_t n_pairs,
                  int32_t mapq_min, uint32_t skip_flag, int32_t row0, int32_t row1,
                  uint32_t *counts, void *workspace, size_t workspace_bytes,
                  int mode, int64_t *h_stats, void *stream);
+
+/* h_stats may be NULL: the call is then asynchronous (no device-to-host copy, no stream synchronisation; every
+ * fast-path / fallback decision is taken on the device) and the stats, which live in the first 128 bytes of
+ * `workspace`, are read later with hc_bin_pairs_stats, which also returns HC_EKEY / HC_ERANGE for the call. */
+int hc_bin_pairs_stats(const void *workspace, int64_t *h_stats, void *stream);
+/* All window sizes of one bam2arrays call from ONE read of the records (inner loop bam2clusters.py:154-161): each
+ * kept line is added to counts[ii] for every ii < n_ws (<= 4) with warp-aggregated global atomics -- meant for the
+ * small per-cluster matrices of the scaffolding stage (windowSize 5 / 10 / 2 kb, bam2scaffolds.py:379), which stay
+ * resident in L2 together.  h_offsets / h_counts: HOST arrays of n_ws DEVICE pointers; h_window_bp / h_n_windows:
+ * host arrays.  Membership is tested against h_offsets[0] (:151); a contig absent from a later table is HC_EKEY
+ * (:155), a window past the matrix HC_ERANGE (:161).  workspace >= 256 bytes; h_stats[9] as hc_bin_pairs. */
+int hc_bin_pairs_multi(const hc_pair_t *pairs, int64_t n_pairs, int32_t n_ws, const int32_t *const *h_offsets,
+                       const uint8_t *region_mask, int32_t n_contigs, const uint32_t *h_window_bp,
+                       const int32_t *h_n_windows, int32_t mapq_min, uint32_t skip_flag, uint32_t *const *h_counts,
+                       int accumulate, void *workspace, size_t workspace_bytes, int64_t *h_stats, void *stream);
 
 int hc_unpack_pairs16(const hc_pair16_t *packed, int64_t n_pairs, hc_pair_t *pairs, void *stream);
 
@@ -183,6 +201,41 @@ int hc_sk_apply(const void *X, int dtype, int32_t nrows, int32_t n, double vmax,
                 const double *c, void *out, int out_dtype, void *stream);
 
 /* ---------------------------------------------------------------------------------------
+ * Row-sharded build of one matrix over the GPUs of a node (csrc/sharded.cu).  The reference's analogue is
+ * the split of the contigs over Pool workers and the reduction in the parent (bam2clusters.py:224-230,
+ * bam2plot.py:138-161).  Rank k owns rows [k*per, (k+1)*per), per % 64 == 0.
+ *
+ * hc_shared_alloc / _open / _close / _free: device memory that peers can map (cudaMalloc + cudaIpc handle, zeroed).
+ *   The 64-byte handle travels through the caller's process group; hc_shared_open maps a PEER's buffer (a process
+ *   cannot open its own handle).
+ * hc_fold_block: d += d.T - diag(d) (+add) for the row block of `rank` (bam2clusters.py:42,511):
+ *   out[i-row0][j] = C[i][j] + C[j][i]; C[j][i] is read from the counts block of the rank that owns row j
+ *   (h_counts_blocks: HOST array of nranks device pointers, peer-mapped), so the transposition is the kernel's own
+ *   NVLink read and not a separate collective.  out: float32 rows x n, must not alias a counts block; d_vmax
+ *   (device float, zeroed by the caller) receives the block maximum -- all-reduce(max) it over the ranks.
+ * hc_sk_fit_block: SinkhornKnopp.fit (sinkhorn_knopp.py:114-163) on the row block X of P = X / vmax, whole fit in one
+ *   call.  The column-sum vector of every pass is all-reduced by a one-shot exchange through peer memory fused with
+ *   the column-chunk reduction and the c = 1/y update / stopping test; the loop condition lives on the device
+ *   (kernels of iterations past convergence return at once), the host reads it once per 4 queued iterations.
+ *   h_exchange: HOST array of nranks device pointers to the ranks' exchange regions (hc_sk_exchange_bytes(n) bytes
+ *   each, from hc_shared_alloc, peer-mapped; NULL when nranks == 1).  *h_epoch: exchange counter, starts at 0 and is
+ *   carried from call to call (all ranks make the same calls).  r (nrows) and c (n): float64 device outputs.
+ *   h_result[8] = {iterations (iterations0 carried in, :150-152), stop (0 epsilon / 1 max_iter), negative-or-NaN
+ *   entry, zero column sum, zero row sum -- the three flags all-reduced so every rank raises / warns alike --,
+ *   matrix passes executed, kernels launched, loop iterations queued}. */
+int hc_shared_alloc(size_t bytes, void **h_dptr, void *h_handle64);
+int hc_shared_free(void *dptr);
+int hc_shared_open(const void *h_handle64, void **h_dptr);
+int hc_shared_close(void *dptr);
+int hc_fold_block(const uint32_t *const *h_counts_blocks, int32_t nranks, int32_t rank, int32_t per, int32_t n,
+                  float add, float *out, float *d_vmax, void *stream);
+size_t hc_sk_exchange_bytes(int32_t n);
+size_t hc_sk_fit_block_workspace_bytes(int32_t nrows, int32_t n);
+int hc_sk_fit_block(const void *X, int dtype, int32_t nrows, int32_t n, double vmax, double eps, int32_t max_iter,
+                    int32_t iterations0, void *const *h_exchange, int32_t nranks, int32_t rank, int32_t *h_epoch,
+                    void *workspace, size_t workspace_bytes, double *r, double *c, int32_t *h_result, void *stream);
+
+/* ---------------------------------------------------------------------------------------
  * K6  contacts -> distances, written straight into the linkage working matrix.
  * Reads the UPPER triangle of X (n x n, dtype 0/1) -- the part d[np.triu_indices(n,1)]
  * selects (bam2clusters.py:385,411; array2scaffolds.py:163) -- and writes the full symmetric
@@ -196,6 +249,12 @@ int hc_sk_apply(const void *X, int dtype, int32_t nrows, int32_t n, double vmax,
 int hc_transform_to_working(const void *X, int dtype, int32_t n, int kind, double p0, double p1,
                             const double *r, const double *c, double vmax, int square, double *W,
                             int32_t *d_flags, void *stream);
+/* The same from a ROW-SHARDED matrix: block k = rows [k*per, (k+1)*per) lives in h_blocks[k] (a HOST array of device
+ * pointers -- on a multi-GPU node the peer-mapped row blocks of the other ranks, read over NVLink while the tile is
+ * transformed: gather and transform are one kernel).  per % 64 == 0; r has all n rows. */
+int hc_transform_gather(const void *const *h_blocks, int32_t nblocks, int32_t per, int dtype, int32_t n, int kind,
+                        double p0, double p1, const double *r, const double *c, double vmax, int square,
+                        double *W, int32_t *d_flags, void *stream);
 /* elementwise transform of a full matrix (same kinds), out dtype = in dtype (kind 2) or f64 */
 int hc_transform(const void *X, int dtype, int64_t count, int kind, double p0, double p1,
                  void *out, int out_dtype, void *stream);
@@ -234,12 +293,15 @@ int hc_linkage_finish(int32_t n, int method, void *workspace, size_t workspace_b
  * hc_linkage's and Z[:,2] agrees to rounding (same Lance-Williams operations, different interleaving).
  * A NEAR tie only leaves its pair pending (it is merged in a later round once it is strict); the call
  * gives up on an EXACT tie or when only near-tied pairs are left.
- * h_stats[16]: rounds, merges, rescans, sum live columns over rescans, sum live columns over merged-row
+ * h_stats[24]: rounds, merges, rescans, sum live columns over rescans, sum live columns over merged-row
  * builds, row x pair updates, compactions, near-tied heights, pending near-tie observations, pairs
  * deferred for an exact rescan; [10..14] microseconds per kernel (select, light, heavy, compaction, initial
- * scan; a bulk round's merge+compact pass counts as heavy) when HC_ROUNDS_KTIME is set, else 0; [15] kernels
- * launched.  Bulk rounds (a fifth or more of the columns merge) are done as one merge+compact pass over the
- * matrix and count as a compaction; HC_ROUNDS_REBUILD=0 switches that path off. */
+ * scan) when HC_ROUNDS_KTIME is set, else 0; [15] kernels launched; [16] microseconds in kb_rebuild (bulk rounds:
+ * a fifth or more of the columns merge, done as one merge+compact pass over the matrix; HC_ROUNDS_REBUILD=0 switches
+ * that path off), [17] microseconds in kr_chain (the persistent kernel that runs all later rounds, many per
+ * cooperative launch; HC_ROUNDS_PERSIST=0 switches it off), [18] / [19] live columns summed over the free / merged
+ * rows of the bulk rounds (the algorithmic bytes of kb_rebuild are 8 x [18] + 24 x [19]), [20] bulk rounds,
+ * [21] 1 when the persistent kernel ran. */
 size_t hc_linkage_rounds_workspace_bytes(int32_t n);
 int hc_linkage_rounds(double *W, int32_t n, int method, void *workspace, size_t workspace_bytes,
                       double *h_Z, int64_t *h_stats, void *stream);
@@ -269,6 +331,15 @@ int hc_normalize_rows(float *A, int32_t n, void *workspace, size_t workspace_byt
  *   order (start-start, start-end, end-start, end-end), float64.  A = symmetric float32 window matrix (n x n). */
 int hc_block_sums4(const float *A, int32_t n, const int32_t *idx, const int64_t *job_off, const int32_t *job_n1,
                    const int32_t *job_n2, int32_t n_jobs, double *out, void *stream);
+
+/* hc_matrix_max: np.max over `count` elements (dtype 0 float32 / 1 float64; NaN propagates) into *d_max (same dtype);
+ *   d_partial: n_partial scratch elements of the same dtype (array2scaffolds.py:31 ``np.max(x+1)``). */
+int hc_matrix_max(const void *X, int dtype, int64_t count, void *d_partial, int32_t n_partial, void *d_max, void *stream);
+/* hc_gather_elements: out[k] = A[rows[k]][cols[k]] -- the (anti)diagonal entries the other join_scaffolds
+ *   (array2scaffolds.py:274-309: np.diag of the rectangle between two scaffolds, :288-291) compares, batched over the
+ *   independent joins of one tree level; the four short float32 sums are then added up in numpy's order on the host. */
+int hc_gather_elements(const float *A, int32_t n, const int32_t *rows, const int32_t *cols, int64_t m, float *out,
+                       void *stream);
 
 /* Alternative normalisations of the symmetric matrix, dtype 0 = float32, 1 = float64.
  * hc_gather_square: out (m x m) = X[keep][:, keep], the zero-diagonal filter of normalize_diagional

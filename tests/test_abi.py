@@ -29,7 +29,7 @@ def test_library_exports_every_declared_symbol():
 
 def test_version_and_error_buffer():
     L = _lib.lib()
-    assert L.hc_version() == 100
+    assert L.hc_version() == 200
     buf = ctypes.create_string_buffer(64)
     assert L.hc_last_error(buf, 64) == 0
 

@@ -113,6 +113,83 @@ def test_unsorted_input_falls_back_and_stays_exact():
     assert np.array_equal(up.cpu().numpy(), O.bin_records(rec, g.window_bp, g.window_offsets(), 1000, 10))
 
 
+def test_unsorted_input_accumulate_mode_counts_once():
+    """when the straggler list overflows in accumulate mode nothing may be added twice.  Unsorted
+    records are accumulated onto a non-zero matrix: the result must be exactly matrix + counts."""
+    from hicembler_b200 import ops
+    g, rec = small_case(n_contigs=40, n_windows=1000, window_bp=5000, n_chrom=4, n_pairs=400000, seed=3, sort=False)
+    off = torch.from_numpy(g.window_offsets().astype(np.int32)).cuda()
+    dev = ops.to_device_records(rec)
+    cnt, st = ops.bin_pairs(dev, off, g.window_bp, 1000, 10, return_stats=True)
+    assert not st["fast_path"] and st["overflow"] > len(rec) // 16 + 65536      # the list did overflow
+    once = cnt.cpu().numpy().astype(np.int64)
+    cnt2, st2 = ops.bin_pairs(dev, off, g.window_bp, 1000, 10, mode=2, out=cnt, return_stats=True)
+    assert not st2["fast_path"] and st2["binned"] == st["binned"]
+    assert np.array_equal(cnt2.cpu().numpy().astype(np.int64), 2 * once)
+    up, _ = ops.fold_counts(cnt2, "upper")
+    assert np.array_equal(up.cpu().numpy(), 2 * O.bin_records(rec, g.window_bp, g.window_offsets(), 1000, 10))
+
+
+def test_bam2arrays_two_unsorted_bams_and_mapq_shadowing():
+    """two name-sorted (here: shuffled) BAMs through the drop-in; and the reference's re-use of the last line's MAPQ
+    as -q for the second BAM (bam2clusters.py:145), opt-in on the product side, default in the oracle"""
+    from hicembler_b200.bam2clusters import bam2arrays
+    g, rec = small_case(n_contigs=30, n_windows=400, window_bp=5000, n_chrom=3, n_pairs=150000, seed=6, sort=False)
+    rec = rec.copy()
+    hi = np.flatnonzero(rec["mapq"] >= 10)
+    rec["mapq"][hi[::3]] = 30
+    rec["mapq"][hi[-1]] = 45
+    wsz, windows, chr2window, _, _ = _tables(g, (5,))
+    lines = sam_lines(g, rec)
+    want_intent = O.bam2arrays(windows, wsz, chr2window, [lines, lines], 10, shadow_mapq=False)[0]
+    want_ref = O.bam2arrays(windows, wsz, chr2window, [lines, lines], 10)[0]
+    assert want_ref.sum() < want_intent.sum()
+    got = bam2arrays(windows, wsz, chr2window, [_bam(g, rec), _bam(g, rec)], 10, verbose=0)[0]
+    assert np.array_equal(got, want_intent)
+    got = bam2arrays(windows, wsz, chr2window, [_bam(g, rec), _bam(g, rec)], 10, verbose=0, mapq_shadowing=True)[0]
+    assert np.array_equal(got, want_ref)
+
+
+def test_bin_pairs_multi_one_pass_equals_per_size_calls(golden_dir):
+    """all window sizes of a call from one read of the records (bam2clusters.py:154-161) == one call per size ==
+    the reference-executed golden arrays"""
+    from hicembler_b200 import ops
+    gld = np.load(os.path.join(golden_dir, "binning.npz"))
+    dev = torch.from_numpy(gld["records"]).cuda()
+    offs = [torch.from_numpy(gld["offsets%d" % ii]).cuda() for ii in range(3)]
+    wbp = [int(w) for w in gld["window_bp"]]
+    nws = [gld["array%d" % ii].shape[0] for ii in range(3)]
+    outs, st = ops.bin_pairs_multi(dev, offs, wbp, nws, 10)
+    for ii in range(3):
+        one = ops.bin_pairs(dev, offs[ii], wbp[ii], nws[ii], 10, member=offs[0])
+        assert torch.equal(outs[ii], one)
+        up, _ = ops.fold_counts(outs[ii], "upper")
+        assert np.array_equal(up.cpu().numpy(), gld["array%d" % ii])
+    assert st["binned"] == int(gld["array0"].sum())
+    outs2, _ = ops.bin_pairs_multi(dev, offs, wbp, nws, 10, outs=[o.clone() for o in outs], accumulate=True)
+    assert all(torch.equal(b, 2 * a) for a, b in zip(outs, outs2))
+    # a contig of table 0 missing from table 2 -> KeyError like the reference (:155); a short matrix -> IndexError (:161)
+    bad = offs[2].clone()
+    bad[int(torch.nonzero(offs[2] >= 0)[-1])] = -1
+    with pytest.raises(KeyError):
+        ops.bin_pairs_multi(dev, [offs[0], offs[1], bad], wbp, nws, 10)
+    with pytest.raises(IndexError):
+        ops.bin_pairs_multi(dev, offs, wbp, [nws[0], nws[1] - 3, nws[2]], 10)
+
+
+def test_bin_pairs_deferred_stats():
+    from hicembler_b200 import ops
+    g, rec = small_case(n_contigs=40, n_windows=1000, window_bp=5000, n_chrom=4, n_pairs=100000, seed=2)
+    off = torch.from_numpy(g.window_offsets().astype(np.int32)).cuda()
+    dev = ops.to_device_records(rec)
+    cnt, st = ops.bin_pairs(dev, off, g.window_bp, 1000, 10, return_stats=True)
+    cnt2, later = ops.bin_pairs(dev, off, g.window_bp, 1000, 10, defer_stats=True)
+    assert later.read() == st and torch.equal(cnt, cnt2)
+    _, later = ops.bin_pairs(dev, off, g.window_bp, 990, 10, defer_stats=True)      # windows past the matrix
+    with pytest.raises(IndexError):
+        later.read()
+
+
 def test_nearly_sorted_input_uses_overflow_list():
     from hicembler_b200 import ops
     g, rec = small_case(n_contigs=40, n_windows=1000, window_bp=5000, n_chrom=4, n_pairs=300000, seed=4)
@@ -815,9 +892,12 @@ def test_contigs2tree_sequence():
         red = O._average_reduce_2d(d, keys)
         Z, uniq, dsym, bin_chr = contigs2tree([_bam(g, rec)], FI(g.contig_sizes), [ws], cluster, 10, params)
         assert np.array_equal(dsym.cpu().numpy(), d) and list(uniq) == list(np.unique(keys))
-        # feed the oracle linkage the float64 distances of the float32 block means (NEP 50 promotion)
-        want = O.linkage_fastcluster(O.condense(O.distance_func(red + 1, np.float64(0.5), np.float64(1.1))), "ward")
-        _same_tree(Z, want, rtol=1e-9)
+        # the reference evaluates distance_func on the float32 block means in float32 (value-based casting); CUDA
+        # powf and glibc powf differ by float32 ulps, so heights agree to float32 precision, merge order exactly
+        dist32 = O.distance_func(red + 1, 0.5, 1.1)
+        assert dist32.dtype == np.float32
+        want = O.linkage_fastcluster(O.condense(dist32).astype(np.float64), "ward")
+        _same_tree(Z, want, rtol=1e-5)
 
 
 def test_pairs_to_dendrogram_c1_end_to_end():

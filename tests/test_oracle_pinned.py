@@ -372,6 +372,58 @@ def test_get_clusters_and_tree_match_reference(tmp_path, seed):
 
 
 # ------------------------------------------------------------------------------------------------------------
+# the product's HOST-side tree code (no GPU involved) against the reference executed here
+# ------------------------------------------------------------------------------------------------------------
+@live
+@pytest.mark.parametrize("seed", [1, 2, 3, 4])
+def test_product_linkage_tree_and_get_clusters_match_reference(tmp_path, seed):
+    from hicembler_b200.array2scaffolds import distance_matrix2tree, get_clusters
+    a2s = R.load("array2scaffolds.py")
+    rng = np.random.default_rng(seed)
+    n_contigs, per = 9, 4
+    bin_chr = np.array(["ctg%02d" % c for c in range(n_contigs) for _ in range(per)])
+    n = len(bin_chr)
+    d = rng.poisson(2.0, (n, n)).astype(np.float32)
+    for b in range(0, n, 3 * per):
+        d[b:b + 3 * per, b:b + 3 * per] += rng.poisson(40, (3 * per, 3 * per))
+    d = np.triu(d)
+    d += d.T - np.diag(d.diagonal())
+    names = ["%s %7sk" % (c, k) for k, c in enumerate(bin_chr)]
+    Z = O.linkage_scipy(O.condense(O.transform_logmax(d).astype(np.float64) + rng.random((n, n)) * 1e-9), "ward")
+    contig2size = {c: per * 5000 for c in np.unique(bin_chr)}
+    t_ref, t = a2s.distance_matrix2tree(Z, names), distance_matrix2tree(Z, names)
+    assert t.write() == t_ref.write() and len(t) == len(t_ref)
+    assert [t.name[k] for k in t.leaves()] == [x.name for x in t_ref]
+    try:
+        want = a2s.get_clusters(str(tmp_path / "w"), t_ref, contig2size, bin_chr)
+    except IndexError:
+        with pytest.raises(IndexError):
+            get_clusters(str(tmp_path / "g"), t, contig2size, bin_chr)
+        return
+    got = get_clusters(str(tmp_path / "g"), t, contig2size, bin_chr)
+    assert want == got
+    assert open(str(tmp_path / "w.clusters.tab")).read() == open(str(tmp_path / "g.clusters.tab")).read()
+
+
+@live
+def test_product_diag_cells_match_reference_slices():
+    """the window pairs the product gathers for array2scaffolds.join_scaffolds are exactly the np.diag slices of the
+    reference (:286-291), including i == 0 (``[-0:]`` = everything) and n1 == n2"""
+    from hicembler_b200.array2scaffolds import _diag_cells
+    rng = np.random.default_rng(0)
+    for n1, n2 in [(5, 3), (4, 4), (7, 1), (2, 2), (9, 6), (3, 2)]:
+        idx = list(rng.permutation(40)[:n1 + n2])
+        d = rng.random((40, 40)).astype(np.float32)
+        _d = d[:, idx][idx, :]
+        i = n2 // 2
+        dflip = np.fliplr(_d[:n1, n2:])
+        want = (np.diag(_d, k=n1)[:i], np.diag(dflip)[:i], np.diag(dflip, k=n2 - n1)[-i:], np.diag(_d, k=n2)[-i:])
+        got = _diag_cells(idx[:n1], idx[n1:])
+        for w, cells in zip(want, got):
+            assert np.array_equal(w, np.array([d[r, c] for r, c in cells], dtype=np.float32))
+
+
+# ------------------------------------------------------------------------------------------------------------
 # committed reference outputs (run anywhere): oracle/make_golden.py wrote them by EXECUTING the reference
 # ------------------------------------------------------------------------------------------------------------
 def test_reference_pinned_golden():

@@ -82,9 +82,12 @@ def _worker(rank, world, port, P, eps, max_iter, out_dir):
     os.environ["MASTER_PORT"] = str(port)
     dist.init_process_group("gloo", rank=rank, world_size=world)
     try:
-        r0, r1 = row_block(P.shape[0], rank, world)
+        r0, r1 = row_block(P.shape[0], rank, world, align=8)
         passes = NumpyPasses(P[r0:r1], eps)
-        it, stop, warned = sinkhorn_driver(passes, max_iter, 0, make_allreduce())
+        try:
+            it, stop, warned = sinkhorn_driver(passes, max_iter, 0, make_allreduce())
+        except AssertionError:
+            it, stop = -1, "assert"
         np.savez(os.path.join(out_dir, "rank%d.npz" % rank), r=passes.r, c=passes.c, it=it, stop=stop, r0=r0, r1=r1)
     finally:
         dist.destroy_process_group()
@@ -118,3 +121,16 @@ def test_round_robin_assignment_covers_all_units():
         rows = [row_block(50_000, r, world) for r in range(world)]
         assert rows[0][0] == 0 and rows[-1][1] == 50_000
         assert all(a[1] == b[0] for a, b in zip(rows[:-1], rows[1:]))
+
+
+def test_negative_entry_on_one_rank_raises_on_every_rank(tmp_path):
+    """the AssertionError of sinkhorn_knopp.py:110 must reach all ranks (no rank may go on to the next
+    all-reduce alone)"""
+    n = 64
+    d = hic_like_counts(n, seed=3)
+    d = d + d.T - np.diag(d.diagonal()) + 1
+    P = (d / d.max()).astype(np.float64)
+    P[50, 3] = -0.5                                  # second rank's block only
+    mp.spawn(_worker, args=(2, _free_port(), P, 1e-5, 100, str(tmp_path)), nprocs=2, join=True)
+    res = [np.load(os.path.join(str(tmp_path), "rank%d.npz" % k)) for k in range(2)]
+    assert str(res[0]["stop"]) == str(res[1]["stop"]) == "assert"
