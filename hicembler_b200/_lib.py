@@ -48,6 +48,7 @@ SIGNATURES = {
     "hc_transform_to_working": (C.c_int, [_p, C.c_int, _i32, C.c_int, _dbl, _dbl, _p, _p, _dbl,
                                           C.c_int, _p, _p, _p]),
     "hc_transform_gather": (C.c_int, [_p, _i32, _i32, C.c_int, _i32, C.c_int, _dbl, _dbl, _p, _p, _dbl, C.c_int, _p, _p, _p]),
+    "hc_sharded_preload": (C.c_int, []),
     "hc_shared_alloc": (C.c_int, [_sz, _p, _p]),
     "hc_shared_free": (C.c_int, [_p]),
     "hc_shared_open": (C.c_int, [_p, _p]),

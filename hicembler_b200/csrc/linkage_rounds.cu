@@ -739,7 +739,7 @@ __global__ void __launch_bounds__(HEAVY_THREADS, MINB) kr_heavy(RArgs a) {
 // It returns to the host when the run is finished, when half of the columns are dead (the host compacts the matrix)
 // or after max_rounds rounds.
 struct ChainCtl {
-    int max_rounds;
+    int max_rounds, compact;
 };
 
 __device__ __forceinline__ void grid_barrier(unsigned int *bar, unsigned int &target) {
@@ -778,7 +778,7 @@ __global__ void __launch_bounds__(CHAIN_THREADS, 1) kr_chain(RArgs a, ChainCtl c
         Ctr *ct = &st->ctr[par], *nx = &st->ctr[par ^ 1];
         if (__ldcg(&st->done)) break;
         const int nactive = __ldcg(&st->nactive);
-        if (a.ncols >= 256 && (long long)nactive * 2 <= a.ncols) {   // the host compacts and comes back
+        if (ctl.compact && a.ncols >= 256 && (long long)nactive * 2 <= a.ncols) {   // the host compacts and comes back
             if (blockIdx.x == 0 && tid == 0) st->exit_reason = 1;
             break;
         }
@@ -1296,6 +1296,7 @@ extern "C" int hc_linkage_rounds(double *W, int32_t n, int method, void *workspa
     while (persist) {
         ChainCtl ctl;
         ctl.max_rounds = 1 << 20;
+        ctl.compact = compact ? 1 : 0;
         if (const char *e = getenv("HC_ROUNDS_CHAIN_MAX")) ctl.max_rounds = atoi(e) > 0 ? atoi(e) : 1;
         void *kargs[] = {(void *)&a, (void *)&ctl};
         kmark(6);

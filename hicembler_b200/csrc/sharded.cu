@@ -355,6 +355,27 @@ bool carve_fit(void *ws, size_t bytes, int nrows, int n, FitLayout &L) {
 
 }  // namespace
 
+// Loads every kernel of this file into the context now.  With CUDA's lazy module loading the FIRST launch of a kernel
+// may wait for running kernels to finish; a rank that enters the exchange kernel spins until its peers have launched
+// theirs, so with several (emulated) ranks on one device that first launch must not happen inside the fit.
+extern "C" int hc_sharded_preload(void) {
+    cudaFuncAttributes at;
+    HC_CUDA_OK(cudaFuncGetAttributes(&at, k_fold_block));
+    HC_CUDA_OK(cudaFuncGetAttributes(&at, kb_colpass<float, true>));
+    HC_CUDA_OK(cudaFuncGetAttributes(&at, kb_colpass<float, false>));
+    HC_CUDA_OK(cudaFuncGetAttributes(&at, kb_colpass<double, true>));
+    HC_CUDA_OK(cudaFuncGetAttributes(&at, kb_colpass<double, false>));
+    HC_CUDA_OK(cudaFuncGetAttributes(&at, kb_rowpass<float, true>));
+    HC_CUDA_OK(cudaFuncGetAttributes(&at, kb_rowpass<float, false>));
+    HC_CUDA_OK(cudaFuncGetAttributes(&at, kb_rowpass<double, true>));
+    HC_CUDA_OK(cudaFuncGetAttributes(&at, kb_rowpass<double, false>));
+    HC_CUDA_OK(cudaFuncGetAttributes(&at, kb_exchange));
+    HC_CUDA_OK(cudaFuncGetAttributes(&at, kb_advance));
+    HC_CUDA_OK(cudaFuncGetAttributes(&at, kb_post_row));
+    HC_CUDA_OK(cudaFuncGetAttributes(&at, kb_init_state));
+    return HC_OK;
+}
+
 extern "C" int hc_shared_alloc(size_t bytes, void **h_dptr, void *h_handle64) {
     HC_REQUIRE(h_dptr && h_handle64 && bytes > 0, "bad arguments");
     static_assert(sizeof(cudaIpcMemHandle_t) == 64, "IPC handle is 64 bytes");

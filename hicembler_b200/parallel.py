@@ -159,6 +159,11 @@ class ProcessGroup:
         self.dist.broadcast_object_list(box, src=src, group=self.group)
         return box[0]
 
+    def broadcast_tensor(self, t, src=0):
+        self.dist.broadcast(t, src=self.dist.get_global_rank(self.group, src) if self.group is not None else src,
+                            group=self.group)
+        return t
+
 
 class LocalGroup:
     """several emulated ranks in one process on one device (tests): ``run(fn)`` calls ``fn(member)`` on one thread and
@@ -190,6 +195,13 @@ class LocalGroup:
 
         def broadcast_object(self, obj, src=0):
             return self.parent._exchange(self.rank, obj)[src]
+
+        def broadcast_tensor(self, t, src=0):
+            torch.cuda.current_stream().synchronize()
+            t.copy_(self.parent._exchange(self.rank, t)[src])
+            torch.cuda.current_stream().synchronize()
+            self.parent._barrier.wait()
+            return t
 
     def __init__(self, world, device="cuda:0"):
         self.world, self.device = world, torch.device(device)
@@ -246,6 +258,8 @@ class RowShard:
         if self.world > MAX_RANKS:
             raise ValueError("at most %d ranks share a matrix" % MAX_RANKS)
         L = _lib.lib()
+        _lib.check(L.hc_set_device(self.device.index))
+        _lib.check(L.hc_sharded_preload())                    # before the collective calls below: see csrc/sharded.cu
         nb = max(self.nrows, 1) * self.n * 4
         self.counts_buf = SharedBuffer(nb, self.device)       # u32 counts block, read by peers in the fold
         self.sym_buf = SharedBuffer(nb, self.device)          # float32 symmetrised block, read by the linkage rank
@@ -307,6 +321,7 @@ class RowShard:
         out = list(out)
         if self.world < self.g.world:                        # ranks without rows learn the outcome from rank 0
             out = self.g.broadcast_object(out if self.active else None, src=0)
+            self.g.broadcast_tensor(res.c, src=0)
         res.iterations, res.stopping_condition = out[0], ("max_iter" if out[1] else "epsilon")
         res.matrix_passes, res.launches = out[5], out[6]
         res.warned = False

@@ -223,6 +223,7 @@ int hc_sk_apply(const void *X, int dtype, int32_t nrows, int32_t n, double vmax,
  *   h_result[8] = {iterations (iterations0 carried in, :150-152), stop (0 epsilon / 1 max_iter), negative-or-NaN
  *   entry, zero column sum, zero row sum -- the three flags all-reduced so every rank raises / warns alike --,
  *   matrix passes executed, kernels launched, loop iterations queued}. */
+int hc_sharded_preload(void);   /* load the kernels of the row-sharded path now (no lazy load inside an exchange) */
 int hc_shared_alloc(size_t bytes, void **h_dptr, void *h_handle64);
 int hc_shared_free(void *dptr);
 int hc_shared_open(const void *h_handle64, void **h_dptr);

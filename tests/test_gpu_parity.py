@@ -700,7 +700,8 @@ def test_linkage_rounds_hic_balanced_matrix(method):
 
 @pytest.mark.parametrize("env", [{}, {"HC_ROUNDS_NOCOMPACT": "1"}, {"HC_ROUNDS_BATCH": "1"}, {"HC_ROUNDS_BULK_SEGS": "32"},
                                  {"HC_ROUNDS_KTIME": "1"}, {"HC_ROUNDS_TRACE": "1"}, {"HC_ROUNDS_REBUILD": "16"},
-                                 {"HC_ROUNDS_REBUILD": "0"}])
+                                 {"HC_ROUNDS_REBUILD": "0"}, {"HC_ROUNDS_PERSIST": "0"}, {"HC_ROUNDS_CHAIN_MAX": "3"},
+                                 {"HC_ROUNDS_PERSIST": "0", "HC_ROUNDS_KTIME": "1"}])
 def test_linkage_rounds_compaction_and_batching_do_not_change_results(env, monkeypatch):
     from hicembler_b200 import ops
     n = 1200
@@ -712,7 +713,8 @@ def test_linkage_rounds_compaction_and_batching_do_not_change_results(env, monke
     Z, st = ops.linkage_rounds(W, "average", nan_flags=flags)
     assert Z is not None
     _same_tree(Z, want, rtol=1e-12)
-    assert (st["kernel_us"]["heavy"] > 0) == ("HC_ROUNDS_KTIME" in env)
+    assert (sum(st["kernel_us"].values()) > 0) == ("HC_ROUNDS_KTIME" in env)
+    assert st["persistent"] == (env.get("HC_ROUNDS_PERSIST") != "0" and "HC_ROUNDS_TRACE" not in env)
     ref = getattr(test_linkage_rounds_compaction_and_batching_do_not_change_results, "_ref", None)
     if ref is None:
         test_linkage_rounds_compaction_and_batching_do_not_change_results._ref = Z
