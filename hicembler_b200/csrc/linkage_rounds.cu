@@ -61,6 +61,7 @@ struct RState {
     Ctr ctr[2];
     int n_done, nactive, ambiguous, stuck, done, round, blocks_done, last_P, last_q, exit_reason;
     unsigned int bar;  // arrival counter of the persistent kernel's grid barrier (monotone)
+    unsigned long long phase_ns[8];  // persistent kernel, CTA 0: time spent in select / build+light / rescan+retire (incl. barrier)
     int amb_r, amb_b, amb_sr, amb_sb;
     double amb_v, amb_secr, amb_secb, amb_vb;
     double gaps[16];  // relative gap (second minimum / minimum - 1) of the first near-tie observations
@@ -98,6 +99,7 @@ struct RArgs {
     int *rq, *rec_a, *rec_b;
     double *rec_d;
     RState *st;
+    unsigned int *bar;   // arrival counter of the persistent kernel's grid barrier, alone in its 256-byte line
 };
 
 __device__ __forceinline__ double lw(int method, double a, double b, const Pair &p, double v) {
@@ -742,13 +744,20 @@ struct ChainCtl {
     int max_rounds, compact;
 };
 
+__device__ __forceinline__ unsigned long long globaltimer_ns() {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
+    return t;
+}
+
 __device__ __forceinline__ void grid_barrier(unsigned int *bar, unsigned int &target) {
     __syncthreads();
     if (threadIdx.x == 0) {
         target += gridDim.x;
         __threadfence();
         atomicAdd(bar, 1u);
-        while (*(volatile unsigned int *)bar < target) { }
+        // poll with a pause: 148 CTAs spinning flat out on one L2 sector slow down every access to that slice
+        while (*(volatile unsigned int *)bar < target) __nanosleep(64);
         __threadfence();
     }
     __syncthreads();
@@ -771,7 +780,7 @@ __global__ void __launch_bounds__(CHAIN_THREADS, 1) kr_chain(RArgs a, ChainCtl c
     const int gwarp = (tid >> 5) * (int)gridDim.x + (int)blockIdx.x;
     const int gthread = gwarp * 32 + (tid & 31), gthreads = nwarps * 32;
     if (blockIdx.x == 0 && tid == 0) st->exit_reason = 0;
-    unsigned int target = __ldcg(&st->bar);   // all CTAs start from the same value: the previous launch ended on a barrier
+    unsigned int target = __ldcg(a.bar);   // all CTAs start from the same value: the previous launch ended on a barrier
     target -= target % gridDim.x;
     for (int it = 0; it < ctl.max_rounds; ++it) {
         const int round = __ldcg(&st->round), par = round & 1;
@@ -782,26 +791,34 @@ __global__ void __launch_bounds__(CHAIN_THREADS, 1) kr_chain(RArgs a, ChainCtl c
             if (blockIdx.x == 0 && tid == 0) st->exit_reason = 1;
             break;
         }
+        const bool timing = blockIdx.x == 0 && tid == 0;
+        unsigned long long t0 = timing ? globaltimer_ns() : 0ull;
         select_rows_ni(a, ct, gthread, gthreads);
-        grid_barrier(&st->bar, target);
+        grid_barrier(a.bar, target);
+        if (timing) { const unsigned long long t1 = globaltimer_ns(); st->phase_ns[0] += t1 - t0; t0 = t1; }
         const int P = __ldcg(&ct->P);
         {
             const int Sb = heavy_segments(a, P, P, nwarps / 2);
             heavy_items_ni(a, P, 0, P, Sb, gwarp, nwarps, nactive);
+            unsigned long long tb = timing ? globaltimer_ns() : 0ull;
             light_rows_ni(a, ct, P, gwarp, nwarps);
+            if (timing) { const unsigned long long tl = globaltimer_ns(); st->phase_ns[3] += tb - t0; st->phase_ns[4] += tl - tb; }
         }
-        grid_barrier(&st->bar, target);
+        grid_barrier(a.bar, target);
+        if (timing) { const unsigned long long t1 = globaltimer_ns(); st->phase_ns[1] += t1 - t0; t0 = t1; }
         const int total = P + __ldcg(&ct->qlen);
         {
             const int Sr = heavy_segments(a, 0, total - P, nwarps);
             heavy_items_ni(a, P, P, total, Sr, gwarp, nwarps, nactive);
+            if (timing) st->phase_ns[5] += globaltimer_ns() - t0;
             if (blockIdx.x == 0) {
                 retire_pairs(a, P, tid, CHAIN_THREADS);
                 __syncthreads();
                 if (tid == 0) close_round(a, ct, nx, P, total);
             }
         }
-        grid_barrier(&st->bar, target);
+        grid_barrier(a.bar, target);
+        if (timing) { const unsigned long long t1 = globaltimer_ns(); st->phase_ns[2] += t1 - t0; }
     }
 }
 
@@ -1025,6 +1042,7 @@ __global__ void kb_retire(RArgs a, int nnew) {
 
 struct Layout {
     RState *st;
+    unsigned int *bar;
     Pair *pairs;
     int *rq, *rec_a, *rec_b, *newidx, *oldidx;
     double *rec_d;
@@ -1046,6 +1064,7 @@ size_t spare_elems_for(int n) {
 bool carve(void *workspace, size_t bytes, int n, Layout &L) {
     hc::Carver ws(workspace, bytes);
     L.st = ws.take<RState>(1);
+    L.bar = ws.take<unsigned int>(64);
     L.pairs = ws.take<Pair>((size_t)n / 2 + 1);
     L.rq = ws.take<int>(n);
     L.rec_a = ws.take<int>(n);
@@ -1111,6 +1130,7 @@ extern "C" int hc_linkage_rounds(double *W, int32_t n, int method, void *workspa
     a.rec_b = L.rec_b;
     a.rec_d = L.rec_d;
     a.st = L.st;
+    a.bar = L.bar;
     a.parts = L.parts;
     a.seg_done = L.seg_done;
     a.max_segs = MAX_SEGS;
@@ -1209,6 +1229,7 @@ extern "C" int hc_linkage_rounds(double *W, int32_t n, int method, void *workspa
         return true;
     };
     HC_CUDA_OK(cudaMemsetAsync(L.seg_done, 0, (size_t)n * sizeof(int), stream));
+    HC_CUDA_OK(cudaMemsetAsync(L.bar, 0, 256, stream));
     kr_init<<<(n + 255) / 256, 256, 0, stream>>>(a);
     if (trace) cudaEventRecord(ev0, stream);
     light_heavy();  // initial nearest neighbour of every row ("first linkage pass")
@@ -1379,6 +1400,11 @@ extern "C" int hc_linkage_rounds(double *W, int32_t n, int method, void *workspa
             compactions++;
         }
     }
+    if (getenv("HC_ROUNDS_PHASES"))
+        fprintf(stderr, "[rounds phases] persistent kernel, CTA 0: select %.1f us, build+light %.1f us (own build %.1f, own light %.1f), "
+                        "rescan+retire %.1f us (own rescan %.1f) over %d rounds\n",
+                h.phase_ns[0] * 1e-3, h.phase_ns[1] * 1e-3, h.phase_ns[3] * 1e-3, h.phase_ns[4] * 1e-3, h.phase_ns[2] * 1e-3,
+                h.phase_ns[5] * 1e-3, h.round);
     if (trace) { cudaEventDestroy(ev0); cudaEventDestroy(ev1); }
     for (cudaEvent_t e : kev) cudaEventDestroy(e);
     drop_graph();

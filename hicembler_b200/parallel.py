@@ -244,7 +244,7 @@ class LocalGroup:
 class RowShard:
     """Per-rank state of a row-sharded N x N build: the rank's row block and the peer-visible buffers."""
 
-    def __init__(self, n, group, device=None):
+    def __init__(self, n, group, device=None, with_counts=True):
         self.n, self.g = int(n), group
         self.rank = group.rank
         self.world = effective_world(self.n, group.world)     # ranks that own rows
@@ -261,10 +261,11 @@ class RowShard:
         _lib.check(L.hc_set_device(self.device.index))
         _lib.check(L.hc_sharded_preload())                    # before the collective calls below: see csrc/sharded.cu
         nb = max(self.nrows, 1) * self.n * 4
-        self.counts_buf = SharedBuffer(nb, self.device)       # u32 counts block, read by peers in the fold
+        # u32 counts block, read by peers in the fold (with_counts=False: a Sinkhorn-only job on a given matrix)
+        self.counts_buf = SharedBuffer(nb if with_counts else 256, self.device)
         self.sym_buf = SharedBuffer(nb, self.device)          # float32 symmetrised block, read by the linkage rank
         self.exch_buf = SharedBuffer(L.hc_sk_exchange_bytes(self.n), self.device)
-        self.counts = self.counts_buf.tensor(torch.int32, (max(self.nrows, 1), self.n))[:self.nrows]
+        self.counts = self.counts_buf.tensor(torch.int32, (max(self.nrows, 1), self.n))[:self.nrows] if with_counts else None
         self.sym = self.sym_buf.tensor(torch.float32, (max(self.nrows, 1), self.n))[:self.nrows]
         self.counts_map = group.peer_map(self.counts_buf)
         self.sym_map = group.peer_map(self.sym_buf)
