@@ -653,7 +653,7 @@ def main():
     ap.add_argument("--mode", default="pipeline", choices=["pipeline", "sinkhorn", "replicas"])
     ap.add_argument("--no-extra-cases", action="store_true", help="skip the tie-heavy cases and the BAM leg (N = 1 only)")
     ap.add_argument("--bam-records", type=int, default=5_000_000, help="records of the BGZF file of the e2e_bam leg")
-    ap.add_argument("--n", type=int, default=0, help="matrix size for --mode sinkhorn")
+    ap.add_argument("--matrix-n", dest="n", type=int, default=0, help="matrix size for --mode sinkhorn")
     ap.add_argument("--no-balance", action="store_true", help="reference HEAD behaviour: normalize() off")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--wire", type=int, default=16, choices=[16, 24],

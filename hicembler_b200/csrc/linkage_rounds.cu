@@ -61,7 +61,8 @@ struct RState {
     Ctr ctr[2];
     int n_done, nactive, ambiguous, stuck, done, round, blocks_done, last_P, last_q, exit_reason;
     unsigned int bar;  // arrival counter of the persistent kernel's grid barrier (monotone)
-    unsigned long long phase_ns[8];  // persistent kernel, CTA 0: time spent in select / build+light / rescan+retire (incl. barrier)
+    unsigned long long dbgmax[4];     // latest finishing times (globaltimer) of build / light / rescan items over all warps
+    unsigned long long phase_ns[16];  // persistent kernel, CTA 0: time spent in select / build+light / rescan+retire (incl. barrier)
     int amb_r, amb_b, amb_sr, amb_sb;
     double amb_v, amb_secr, amb_secb, amb_vb;
     double gaps[16];  // relative gap (second minimum / minimum - 1) of the first near-tie observations
@@ -127,6 +128,20 @@ __device__ __forceinline__ Pair ld_pair(const Pair *p) {
     r.s1 = __hiloint2double(b.y, b.x); r.s2 = __hiloint2double(b.w, b.z);
     r.as = __hiloint2double(c.y, c.x); r.at = __hiloint2double(c.w, c.z);
     return r;
+}
+
+__device__ __forceinline__ unsigned long long globaltimer_ns() {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
+    return t;
+}
+
+// one instruction asks the TMA unit to bring a whole row segment into L2 (cp.async.bulk.prefetch): the register loop
+// that follows then runs on L2 hits instead of paying one DRAM (+TLB) round trip per dependent iteration
+__device__ __forceinline__ void bulk_prefetch_l2(const void *p, size_t bytes) {
+    const size_t a = ((size_t)p + 15) & ~(size_t)15;
+    const size_t e = ((size_t)p + bytes) & ~(size_t)15;
+    if (e > a) asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(a), "r"((unsigned)(e - a)) : "memory");
 }
 
 __device__ __forceinline__ bool lex_lt(double x, int c, double y, int d) { return x < y || (x == y && c < d); }
@@ -328,7 +343,6 @@ __device__ __forceinline__ void light_rows(const RArgs &a, Ctr *ct, int P, long 
     while (G < 32 && G < P) G <<= 1;
     const int rows_per_warp = 32 / G, g = lane / G, q0 = lane - g * G;
     const unsigned gmask = G == 32 ? 0xffffffffu : (((1u << G) - 1u) << (g * G));
-    unsigned long long upd = 0;
     for (long long rbase = warp0 * rows_per_warp; rbase < a.ncols; rbase += nwarps * rows_per_warp) {
         const int row = (int)rbase + g;
         if (row >= a.ncols || __ldcg(a.c.role + row) != ROLE_FREE) continue;
@@ -349,7 +363,6 @@ __device__ __forceinline__ void light_rows(const RArgs &a, Ctr *ct, int P, long 
             __syncwarp(gmask);  // the new entries of this row (written by the lanes of its group) are visible below
             if (q0 == 0) {
                 a.c.fresh[row] = 0;  // the bound is no longer the exact next entry
-                upd += P;
                 if (!need) {
                     // Candidates that were merged this round follow their cluster to column j with the new value.
                     // Unlisted entries only move up (reducibility), so the bound stays valid; a candidate that rose
@@ -393,14 +406,93 @@ __device__ __forceinline__ void light_rows(const RArgs &a, Ctr *ct, int P, long 
         }
         if (need && q0 == 0) a.rq[atomicAdd(&ct->qlen, 1)] = row;  // the rescan clears the flag
     }
-    if (upd) atomicAdd(&st->stats[4], upd);
+}
+
+// Thin rounds (<= 4 pairs, the chain phase): one lane per row and a dependency chain of TWO memory levels instead of
+// six -- everything indexed by the row (role, size, candidate list) and the row's old entries of the merging columns
+// are requested together, the roles of the candidates right behind them, and the new entries are taken from registers
+// when the list is repaired.  Same arithmetic, same list, same queue as light_rows.
+template <typename Tv>
+__device__ __forceinline__ Tv pick4(const Tv (&v)[4], int k) {
+    return k == 0 ? v[0] : (k == 1 ? v[1] : (k == 2 ? v[2] : v[3]));
+}
+
+__device__ __forceinline__ void light_rows_thin(const RArgs &a, Ctr *ct, int P, int t_first, int t_stride) {
+    RState *st = a.st;
+    const int method = a.method;
+    Pair pr[4];
+#pragma unroll
+    for (int q = 0; q < 4; ++q) pr[q] = ld_pair(a.pairs + (q < P ? q : 0));
+    for (int row = t_first; row < a.ncols; row += t_stride) {
+        const size_t base = (size_t)row * LC;
+        double *Wr = a.W + (size_t)row * a.stride;
+        const int role = __ldcg(a.c.role + row);
+        const bool need = __ldcg(a.c.need + row) != 0;
+        const double v = (double)__ldcg(a.c.size + row);
+        double cv[KC], A[4], B[4];
+        int ci[KC], rci[KC];
+#pragma unroll
+        for (int k = 0; k < KC; ++k) { cv[k] = __ldcg(a.c.cval + base + k); ci[k] = __ldcg(a.c.cidx + base + k); }
+        const double lb = __ldcg(a.c.cval + base + KC);
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+            A[q] = __ldcg(Wr + pr[q].i);
+            B[q] = __ldcg(Wr + pr[q].j);
+        }
+#pragma unroll
+        for (int k = 0; k < KC; ++k) rci[k] = ci[k] >= 0 ? __ldcg(a.c.role + ci[k]) : -1;
+        if (role != ROLE_FREE) continue;
+        double nv[4];
+        int nj[4];
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+            nv[q] = lw(method, A[q], B[q], pr[q], v);
+            nj[q] = pr[q].j;
+            if (q < P) Wr[pr[q].j] = nv[q];
+        }
+        a.c.fresh[row] = 0;  // the bound is no longer the exact next entry
+        if (!need) {
+            bool hit = false;
+#pragma unroll
+            for (int k = 0; k < KC; ++k) {
+                if (ci[k] < 0) continue;
+                const int r = rci[k];
+                if (r < 0) continue;
+                hit = true;
+                const int j = pick4(nj, r >> 1);
+                bool dup = false;  // both sides of the pair were listed: keep one
+#pragma unroll
+                for (int t = 0; t < KC; ++t) dup |= (t != k) && (ci[t] == j) && ((r & 1) == 0 || t < k);
+                if (dup && (r & 1) == 0) { ci[k] = -1; continue; }
+                ci[k] = j;
+                cv[k] = pick4(nv, r >> 1);
+            }
+            if (hit) {
+                TopL out;
+                out.init();
+#pragma unroll
+                for (int k = 0; k < KC; ++k)
+                    if (ci[k] >= 0 && cv[k] <= lb) out.insert(cv[k], ci[k]);
+#pragma unroll
+                for (int k = 0; k < KC; ++k) {
+                    a.c.cval[base + k] = out.v[k];
+                    a.c.cidx[base + k] = out.i[k] == INT_MAX ? -1 : out.i[k];
+                }
+                if (out.i[0] == INT_MAX) a.rq[atomicAdd(&ct->qlen, 1)] = row;
+            }
+        } else {
+            a.rq[atomicAdd(&ct->qlen, 1)] = row;  // the rescan clears the flag
+        }
+    }
 }
 
 __global__ void __launch_bounds__(LIGHT_THREADS) kr_light(RArgs a) {
     RState *st = a.st;
     if (st->done) return;
-    light_rows(a, &st->ctr[0], st->ctr[0].P, ((long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5,
-               ((long long)gridDim.x * blockDim.x) >> 5);
+    const int P = st->ctr[0].P;
+    if (P >= 1 && P <= 4) light_rows_thin(a, &st->ctr[0], P, blockIdx.x * blockDim.x + threadIdx.x, gridDim.x * blockDim.x);
+    else light_rows(a, &st->ctr[0], P, ((long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5,
+                    ((long long)gridDim.x * blockDim.x) >> 5);
 }
 
 // ---- heavy: new rows of merged clusters, exact rescans; the last CTA retires the pairs -----------
@@ -411,11 +503,15 @@ template <bool VEC>
 __device__ __forceinline__ void heavy_columns(const RArgs &a, int e, int P, int seg, int S, int c_lo, int c_hi,
                                               bool all_free, Min3 &best) {
     const int lane = threadIdx.x & 31, method = a.method;  // one warp per (entry, segment)
-    constexpr int V = VEC ? 2 : 1, U = 2, UR = 4;  // loads in flight per thread: builds 2 x (A, B), rescans 4 (8 when all live)
+    constexpr int V = VEC ? 2 : 1, U = 2, UR = 4;  // loads in flight per thread: builds 2 x (A, B), rescans 4
     if (e < P) {
         const Pair p = ld_pair(a.pairs + e);
         const double *Wi = a.W + (size_t)p.i * a.stride;
         double *Wj = a.W + (size_t)p.j * a.stride;
+        if (lane == 0 && c_hi - c_lo <= 4096) {   // (short segments = the latency-bound rounds; big rounds stream anyway)
+            bulk_prefetch_l2(Wi + c_lo, (size_t)(c_hi - c_lo) * 8);
+            bulk_prefetch_l2(Wj + c_lo, (size_t)(c_hi - c_lo) * 8);
+        }
         // Phase A: columns of clusters that do not merge this round -- coalesced, no divergent work.
         for (int c0 = c_lo + lane * V; c0 < c_hi; c0 += U * V * 32) {
             double A[U][V], B[U][V];
@@ -506,6 +602,7 @@ __device__ __forceinline__ void heavy_columns(const RArgs &a, int e, int P, int 
     } else {
         const int row = __ldcg(a.rq + e - P);
         const double *Wr = a.W + (size_t)row * a.stride;
+        if (lane == 0 && c_hi - c_lo <= 4096) bulk_prefetch_l2(Wr + c_lo, (size_t)(c_hi - c_lo) * 8);
         for (int c0 = c_lo + lane * V; c0 < c_hi; c0 += UR * V * 32) {
             double X[UR][V];
             int rc[UR][V];
@@ -579,7 +676,7 @@ __device__ __forceinline__ int heavy_segments(const RArgs &a, int P, int total, 
     constexpr int SEG_MIN = 512;
     int S = 1;
     if (total > 0) {
-        if (total < nwarps / 2) S = (nwarps / 2 + total - 1) / total;
+        if (total < nwarps / 2) S = (2 * nwarps + total - 1) / total;   // up to two items per warp: short dependent chains
         // Big rounds: the pair x pair gathers of a merged row (phase B) re-read the two old rows.  With every row
         // cut into many segments only ~100 rows are being built at a time (2 x 8 x ncols bytes each), so the
         // gathers and the second write of a sector find them in the 126 MB L2 instead of going back to HBM.
@@ -670,8 +767,6 @@ __device__ __forceinline__ void heavy_items(const RArgs &a, int P, int e_lo, int
                 a.c.fresh[row] = 1;
                 a.c.need[row] = 0;
                 if (S > 1) a.seg_done[e] = 0;
-                atomicAdd(&st->stats[e < P ? 2 : 0], 1ull);
-                atomicAdd(&st->stats[e < P ? 3 : 1], (unsigned long long)nactive);
             }
         }
     }
@@ -690,6 +785,14 @@ __device__ __forceinline__ void retire_pairs(const RArgs &a, int P, int tid, int
 // one thread: close the round (counters of `cur` are read, the set `next` is cleared for the round after)
 __device__ __forceinline__ void close_round(const RArgs &a, Ctr *cur, Ctr *next, int P, int total) {
     RState *st = a.st;
+    // work counters of the round, derived instead of counted: one atomicAdd per updated row on ONE address (14 000
+    // per round in the chain phase) serialised in L2 for ~20 us, longer than the round's real work
+    const unsigned long long nact = (unsigned long long)st->nactive, np = (unsigned long long)P, nq = (unsigned long long)(total - P);
+    st->stats[0] += nq;                    // rescans
+    st->stats[1] += nq * nact;             // ... live columns
+    st->stats[2] += np;                    // merged-row builds
+    st->stats[3] += np * nact;
+    st->stats[4] += (nact - 2 * np) * np;  // row x pair updates of the free rows
     st->n_done += P;
     st->nactive -= P;
     st->stats[5] += cur->deferred;
@@ -741,14 +844,8 @@ __global__ void __launch_bounds__(HEAVY_THREADS, MINB) kr_heavy(RArgs a) {
 // It returns to the host when the run is finished, when half of the columns are dead (the host compacts the matrix)
 // or after max_rounds rounds.
 struct ChainCtl {
-    int max_rounds, compact;
+    int max_rounds, compact, diag;
 };
-
-__device__ __forceinline__ unsigned long long globaltimer_ns() {
-    unsigned long long t;
-    asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
-    return t;
-}
 
 __device__ __forceinline__ void grid_barrier(unsigned int *bar, unsigned int &target) {
     __syncthreads();
@@ -767,7 +864,10 @@ constexpr int CHAIN_THREADS = 512;
 
 // out-of-line copies for the persistent kernel: three inlined phases do not fit 128 registers together
 __device__ __noinline__ void select_rows_ni(const RArgs &a, Ctr *ct, int r_first, int r_stride) { select_rows(a, ct, r_first, r_stride); }
-__device__ __noinline__ void light_rows_ni(const RArgs &a, Ctr *ct, int P, long long warp0, long long nwarps) { light_rows(a, ct, P, warp0, nwarps); }
+__device__ __noinline__ void light_rows_ni(const RArgs &a, Ctr *ct, int P, long long warp0, long long nwarps) {
+    if (P >= 1 && P <= 4) light_rows_thin(a, ct, P, (int)warp0 * 32 + (threadIdx.x & 31), (int)nwarps * 32);
+    else light_rows(a, ct, P, warp0, nwarps);
+}
 __device__ __noinline__ void heavy_items_ni(const RArgs &a, int P, int e_lo, int e_hi, int S, int gwarp, int nwarps, int nactive) {
     heavy_items(a, P, e_lo, e_hi, S, gwarp, nwarps, false, nactive);
 }
@@ -795,22 +895,35 @@ __global__ void __launch_bounds__(CHAIN_THREADS, 1) kr_chain(RArgs a, ChainCtl c
         unsigned long long t0 = timing ? globaltimer_ns() : 0ull;
         select_rows_ni(a, ct, gthread, gthreads);
         grid_barrier(a.bar, target);
-        if (timing) { const unsigned long long t1 = globaltimer_ns(); st->phase_ns[0] += t1 - t0; t0 = t1; }
         const int P = __ldcg(&ct->P);
+        const int tk = P <= 8 ? 0 : 3;   // thin rounds (the chain phase) and thick rounds are timed apart
+        if (timing) { const unsigned long long t1 = globaltimer_ns(); st->phase_ns[tk] += t1 - t0; t0 = t1; st->phase_ns[6 + (tk ? 1 : 0)] += 1; }
         {
+            // the merged rows are built by the LAST warps of the grid, the light rows start at the first: in a thin
+            // round no warp does both, so the two run side by side
             const int Sb = heavy_segments(a, P, P, nwarps / 2);
-            heavy_items_ni(a, P, 0, P, Sb, gwarp, nwarps, nactive);
-            unsigned long long tb = timing ? globaltimer_ns() : 0ull;
+            const int bwarp = nwarps - 1 - gwarp;
+            heavy_items_ni(a, P, 0, P, Sb, bwarp, nwarps, nactive);
+            if (ctl.diag && (tid & 31) == 0 && bwarp < P * Sb) atomicMax(&st->dbgmax[0], globaltimer_ns());
             light_rows_ni(a, ct, P, gwarp, nwarps);
-            if (timing) { const unsigned long long tl = globaltimer_ns(); st->phase_ns[3] += tb - t0; st->phase_ns[4] += tl - tb; }
+            if (ctl.diag && (tid & 31) == 0) atomicMax(&st->dbgmax[1], globaltimer_ns());
         }
         grid_barrier(a.bar, target);
-        if (timing) { const unsigned long long t1 = globaltimer_ns(); st->phase_ns[1] += t1 - t0; t0 = t1; }
+        if (timing) {
+            const unsigned long long t1 = globaltimer_ns();
+            st->phase_ns[tk + 1] += t1 - t0;
+            if (ctl.diag && tk == 0) {
+                const unsigned long long b = __ldcg(&st->dbgmax[0]), l = __ldcg(&st->dbgmax[1]);
+                if (b > t0) st->phase_ns[8] += b - t0;
+                if (l > t0) st->phase_ns[9] += l - t0;
+            }
+            t0 = t1;
+        }
         const int total = P + __ldcg(&ct->qlen);
         {
             const int Sr = heavy_segments(a, 0, total - P, nwarps);
             heavy_items_ni(a, P, P, total, Sr, gwarp, nwarps, nactive);
-            if (timing) st->phase_ns[5] += globaltimer_ns() - t0;
+            if (ctl.diag && (tid & 31) == 0 && gwarp < (total - P) * Sr) atomicMax(&st->dbgmax[2], globaltimer_ns());
             if (blockIdx.x == 0) {
                 retire_pairs(a, P, tid, CHAIN_THREADS);
                 __syncthreads();
@@ -818,7 +931,15 @@ __global__ void __launch_bounds__(CHAIN_THREADS, 1) kr_chain(RArgs a, ChainCtl c
             }
         }
         grid_barrier(a.bar, target);
-        if (timing) { const unsigned long long t1 = globaltimer_ns(); st->phase_ns[2] += t1 - t0; }
+        if (timing) {
+            const unsigned long long t1 = globaltimer_ns();
+            st->phase_ns[tk + 2] += t1 - t0;
+            if (ctl.diag && tk == 0) {
+                const unsigned long long r = __ldcg(&st->dbgmax[2]);
+                if (r > t0) st->phase_ns[10] += r - t0;
+                st->phase_ns[11] += total - P;
+            }
+        }
     }
 }
 
@@ -1318,6 +1439,7 @@ extern "C" int hc_linkage_rounds(double *W, int32_t n, int method, void *workspa
         ChainCtl ctl;
         ctl.max_rounds = 1 << 20;
         ctl.compact = compact ? 1 : 0;
+        ctl.diag = getenv("HC_ROUNDS_PHASES") != nullptr;
         if (const char *e = getenv("HC_ROUNDS_CHAIN_MAX")) ctl.max_rounds = atoi(e) > 0 ? atoi(e) : 1;
         void *kargs[] = {(void *)&a, (void *)&ctl};
         kmark(6);
@@ -1401,10 +1523,13 @@ extern "C" int hc_linkage_rounds(double *W, int32_t n, int method, void *workspa
         }
     }
     if (getenv("HC_ROUNDS_PHASES"))
-        fprintf(stderr, "[rounds phases] persistent kernel, CTA 0: select %.1f us, build+light %.1f us (own build %.1f, own light %.1f), "
-                        "rescan+retire %.1f us (own rescan %.1f) over %d rounds\n",
-                h.phase_ns[0] * 1e-3, h.phase_ns[1] * 1e-3, h.phase_ns[3] * 1e-3, h.phase_ns[4] * 1e-3, h.phase_ns[2] * 1e-3,
-                h.phase_ns[5] * 1e-3, h.round);
+        fprintf(stderr, "[rounds phases] persistent kernel (CTA 0 clock, barriers included): %llu thin rounds (<= 8 pairs): select %.1f "
+                        "build+light %.1f rescan+retire %.1f us; %llu thick rounds: select %.1f build+light %.1f rescan+retire %.1f us\n",
+                h.phase_ns[6], h.phase_ns[0] * 1e-3, h.phase_ns[1] * 1e-3, h.phase_ns[2] * 1e-3,
+                h.phase_ns[7], h.phase_ns[3] * 1e-3, h.phase_ns[4] * 1e-3, h.phase_ns[5] * 1e-3);
+    if (getenv("HC_ROUNDS_PHASES"))
+        fprintf(stderr, "[rounds phases] thin rounds, last warp to finish after the phase started: build items %.1f, light rows %.1f, "
+                        "rescan items %.1f us (%llu rescans)\n", h.phase_ns[8] * 1e-3, h.phase_ns[9] * 1e-3, h.phase_ns[10] * 1e-3, h.phase_ns[11]);
     if (trace) { cudaEventDestroy(ev0); cudaEventDestroy(ev1); }
     for (cudaEvent_t e : kev) cudaEventDestroy(e);
     drop_graph();

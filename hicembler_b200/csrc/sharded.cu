@@ -505,7 +505,7 @@ extern "C" int hc_sk_fit_block(const void *X, int dtype, int32_t nrows, int32_t 
     int queued = 0, mode = 1;
     for (;;) {
         // one loop iteration: y = P^T r -> all-reduce -> test / c = 1/y -> r = 1/(P c) -> iterations += 1
-        const int batch = 4;
+        const int batch = 3;
         for (int b = 0; b < batch; ++b) {
             colpass(r, false, 1);
             exchange(mode);

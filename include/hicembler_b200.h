@@ -216,7 +216,7 @@ int hc_sk_apply(const void *X, int dtype, int32_t nrows, int32_t n, double vmax,
  * hc_sk_fit_block: SinkhornKnopp.fit (sinkhorn_knopp.py:114-163) on the row block X of P = X / vmax, whole fit in one
  *   call.  The column-sum vector of every pass is all-reduced by a one-shot exchange through peer memory fused with
  *   the column-chunk reduction and the c = 1/y update / stopping test; the loop condition lives on the device
- *   (kernels of iterations past convergence return at once), the host reads it once per 4 queued iterations.
+ *   (kernels of iterations past convergence return at once), the host reads it once per 3 queued iterations.
  *   h_exchange: HOST array of nranks device pointers to the ranks' exchange regions (hc_sk_exchange_bytes(n) bytes
  *   each, from hc_shared_alloc, peer-mapped; NULL when nranks == 1).  *h_epoch: exchange counter, starts at 0 and is
  *   carried from call to call (all ranks make the same calls).  r (nrows) and c (n): float64 device outputs.

@@ -16,3 +16,8 @@ try:
 except Exception as e:
     print("no bench line:", e)
 PY
+if [ -n "$HC_SK_SIZES" ]; then
+  for n in $HC_SK_SIZES; do
+    timeout -s KILL 400 python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29513 bench.py --gpus $N --mode sinkhorn --matrix-n $n --steps 5 --warmup 2 > ${P}_sk_$n.json 2> ${P}_sk_$n.err; echo "sinkhorn n=$n rc=$?"; grep "^{" ${P}_sk_$n.json | tail -1; tail -2 ${P}_sk_$n.err
+  done
+fi
