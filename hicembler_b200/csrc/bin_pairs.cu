@@ -97,6 +97,7 @@ __device__ __forceinline__ uint32_t div_bp32(const BinArgs &a, uint32_t p) {
 
 // decode() for the tile kernel: the four table look-ups are issued together and the status is two predicates
 // (filtered, ok); what kind of error a rejected record is gets sorted out by decode_reject() on the rare path.
+template <bool SAME_MEMBER = false>
 __device__ __forceinline__ void decode_lean(const BinArgs &a, uint2 q0, uint2 q1, uint2 q2, int32_t &row,
                                             int32_t &col, bool &filtered, bool &ok) {
     const int32_t ref = (int32_t)q0.x, pos = (int32_t)q0.y;
@@ -104,8 +105,9 @@ __device__ __forceinline__ void decode_lean(const BinArgs &a, uint2 q0, uint2 q1
     const int32_t lseq = (int32_t)q2.x;
     const uint32_t flag = q2.y & 0xffffu, mapq = (q2.y >> 16) & 0xffu;
     const bool ref_ok = (uint32_t)ref < (uint32_t)a.n_contigs, nref_ok = (uint32_t)nref < (uint32_t)a.n_contigs;
-    const int32_t m1 = ref_ok ? __ldg(a.member + ref) : -1, m2 = nref_ok ? __ldg(a.member + nref) : -1;
     const int32_t o1 = ref_ok ? __ldg(a.offsets + ref) : -1, o2 = nref_ok ? __ldg(a.offsets + nref) : -1;
+    // (the membership table of bam2clusters.py:151 is the window table itself unless several window sizes are binned)
+    const int32_t m1 = SAME_MEMBER ? o1 : (ref_ok ? __ldg(a.member + ref) : -1), m2 = SAME_MEMBER ? o2 : (nref_ok ? __ldg(a.member + nref) : -1);
     filtered = (flag & a.skip_flag) || (int32_t)mapq < a.mapq_min;
     if (a.region_mask) filtered = filtered || !(ref_ok && a.region_mask[ref]);
     const int32_t add = 1 + ((lseq > 1 ? lseq : 1) >> 1);  // len("*") == 1; Py2 integer division
@@ -458,6 +460,244 @@ __global__ void __launch_bounds__(CELL16 ? 512 : 1024, CELL16 ? 2 : 1) k_bin_til
     }
 }
 
+// ---- band kernel: one matrix row per tile, records staged by TMA --------------------------------------------------
+// For matrices too wide for two u32 rows per SM (n_windows > ~29 000) the row tile above needs 16-bit cells and
+// leaves no shared memory for staging the record stream: its loads live in registers and the kernel stalls on them
+// (ncu: 29 % of the stall samples on the first use of the record loads, 46 % issue slots busy).
+// Hi-C pairs are near-diagonal: at C3 ~80 % of the records of a row fall within +-1024 windows of it.  This kernel
+// keeps only that BAND of the row in shared memory (u32 cells, 8 KB) and
+//   * zeroes the rest of the row in global memory itself (plain 16-byte stores: the row's 200 KB stay in the 126 MB
+//     L2 while the ~300 resident CTAs work on ~300 rows = 60 MB),
+//   * adds the far hits (trans contacts, long-range cis) with global reductions (RED.ADD), resolved in L2 on the
+//     lines it has just written, so DRAM still sees every matrix cell once,
+//   * streams the records through a ring of shared-memory stages filled by the TMA unit (cp.async.bulk + mbarrier):
+//     1024 records per stage, BAND_STAGES stages, one elected thread issues the copies -- across tile boundaries, so the
+//     first records of the next tile arrive while the band of the current one is flushed.
+// Counts, statistics, straggler handling and accumulate mode are those of k_bin_tiles.
+constexpr int BAND_THREADS = 512;
+constexpr int BAND_RPT = 2;         // records per thread and stage
+constexpr int BAND_STAGE = BAND_THREADS * BAND_RPT;   // records per stage (two 256-record chunks per record slot)
+constexpr int BAND_STAGES = 4;      // 4 x 24 KB ring
+
+__device__ __forceinline__ uint32_t smem_u32(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(unsigned long long *b, int count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(b)), "r"(count));
+}
+__device__ __forceinline__ void mbar_expect_tx(unsigned long long *b, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(b)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(unsigned long long *b) {
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(b)) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(unsigned long long *b, uint32_t parity) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "W_%=:\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n\t"
+        "@!p bra W_%=;\n\t}"
+        ::"r"(smem_u32(b)), "r"(parity) : "memory");
+}
+__device__ __forceinline__ void tma_load_1d(void *dst, const void *src, uint32_t bytes, unsigned long long *bar) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                 ::"r"(smem_u32(dst)), "l"(src), "r"(bytes), "r"(smem_u32(bar)) : "memory");
+}
+
+// the CTA's tiles t = blockIdx.x, blockIdx.x + gridDim.x, ... as one stream of stages; every thread walks it alike
+struct BandCursor {
+    int t;               // tile (row group) of the stage
+    long long idx, end;  // first record of the stage, end of the tile's slice
+    bool valid;
+    __device__ __forceinline__ void open(const BinArgs &a, int tile) {
+        t = tile;
+        valid = t < a.n_groups;
+        if (valid) {
+            idx = a.tile_clo[t] << CHUNK_LOG;
+            end = min(a.tile_chi[t] << CHUNK_LOG, a.n_pairs);
+            if (idx > end) idx = end;                          // (an empty slice still gets one, empty, stage)
+        } else idx = end = 0;
+    }
+    __device__ __forceinline__ void next(const BinArgs &a) {   // after a stage [idx, idx + BAND_STAGE)
+        idx += BAND_STAGE;
+        if (idx >= end) open(a, t + (int)gridDim.x);
+    }
+    __device__ __forceinline__ bool last_of_tile() const { return idx + BAND_STAGE >= end; }
+};
+
+template <bool SAME_MEMBER>
+__global__ void __launch_bounds__(BAND_THREADS, 2) k_bin_band(BinArgs a, int half_band) {
+    extern __shared__ __align__(128) unsigned char smem_raw[];
+    uint2 *ring = (uint2 *)smem_raw;                                      // [BAND_STAGES][BAND_STAGE * 3]
+    uint32_t *band = (uint32_t *)(smem_raw + (size_t)BAND_STAGES * BAND_STAGE * 24);
+    __shared__ unsigned long long full[BAND_STAGES], empty[BAND_STAGES];
+    __shared__ int4 sbound[BAND_STAGES][BAND_RPT];   // row bounds advertised by the 256-record chunks of a stage
+    const int tid = threadIdx.x, lane_id = tid & 31;
+    const int band_cap = 2 * half_band + 8;
+    for (int i = tid; i < band_cap; i += BAND_THREADS) band[i] = 0;
+    if (tid == 0) {
+        for (int s = 0; s < BAND_STAGES; ++s) { mbar_init(&full[s], 1); mbar_init(&empty[s], BAND_THREADS / 32); }
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    __syncthreads();
+    uint32_t n_lines = 0, n_ok = 0, n_absent = 0, n_range = 0, n_key = 0, n_over = 0, n_outside = 0;
+    const int nw = a.n_windows;
+
+    // producer state (thread 0): the stage stream runs BAND_STAGES - 1 ahead of the consumers
+    BandCursor prod, cons;
+    prod.open(a, blockIdx.x);
+    cons.open(a, blockIdx.x);
+    int issued = 0;
+    // chunk bounds of the stage that will be issued next: requested one issue ahead, so that the producer never waits
+    // for them (the consumers read them from shared memory with their records)
+    int4 nb[BAND_RPT];
+    auto fetch_bounds = [&]() {
+        if (!prod.valid) return;
+        const long long c = prod.idx >> CHUNK_LOG;
+#pragma unroll
+        for (int k = 0; k < BAND_RPT; ++k) {
+            const long long c0 = min(c + 2 * k, a.n_chunks - 1), c1 = min(c + 2 * k + 1, a.n_chunks - 1);
+            nb[k] = make_int4(__ldg(a.chunk_lo + c0), __ldg(a.chunk_hi + c0), __ldg(a.chunk_lo + c1), __ldg(a.chunk_hi + c1));
+        }
+    };
+    if (tid == 0) fetch_bounds();
+    auto issue = [&]() {      // thread 0 only
+        if (!prod.valid) return;
+        const int slot = issued % BAND_STAGES;
+        if (issued >= BAND_STAGES) mbar_wait(&empty[slot], (uint32_t)(((issued / BAND_STAGES) - 1) & 1));
+#pragma unroll
+        for (int k = 0; k < BAND_RPT; ++k) sbound[slot][k] = nb[k];
+        const long long cnt = min((long long)BAND_STAGE, prod.end - prod.idx);
+        if (cnt > 0) {
+            // multiple of 8, TMA wants 16: round up inside the record array, down at its very end (the thread that
+            // holds the array's last record then fetches its last 8 bytes itself)
+            const uint32_t bytes = (uint32_t)(cnt * 24);
+            const uint32_t b16 = (prod.idx + cnt == a.n_pairs) ? (bytes & ~15u) : ((bytes + 15u) & ~15u);
+            mbar_expect_tx(&full[slot], b16);
+            tma_load_1d(ring + (size_t)slot * BAND_STAGE * 3, a.pairs + 3 * prod.idx, b16, &full[slot]);
+        } else {
+            mbar_arrive(&full[slot]);                       // empty slice: complete the phase without a copy
+        }
+        ++issued;
+        prod.next(a);
+        fetch_bounds();
+    };
+    if (tid == 0)
+        for (int k = 0; k < BAND_STAGES - 1; ++k) issue();
+
+    int32_t r0 = 0, b0 = 0, b1 = 0;
+    // the part of a tile's row outside the band is zeroed before its first reduction can arrive: by the CTA itself, at
+    // the end of the previous tile (the stores drain under the flush), with one fence + barrier for both
+    auto zero_row = [&](int t) {
+        const int32_t r = a.row0 + t;
+        const int32_t z0 = max(0, (r - half_band) & ~3), z1 = min(nw, (r + half_band + 4) & ~3);
+        uint4 *dst = (uint4 *)(a.counts + (size_t)(r - a.row0) * nw);
+        const int n4 = nw >> 2, s0 = z0 >> 2, s1 = z1 >> 2;
+        const uint4 z = make_uint4(0, 0, 0, 0);
+        for (int i = tid; i < n4; i += BAND_THREADS)
+            if (i < s0 || i >= s1) dst[i] = z;
+    };
+    auto open_tile = [&](int t) {
+        r0 = a.row0 + t;
+        b0 = max(0, (r0 - half_band) & ~3);
+        b1 = min(nw, (r0 + half_band + 4) & ~3);
+    };
+    if (cons.valid) {
+        if (!a.accumulate) { zero_row(cons.t); __threadfence(); }
+        __syncthreads();
+        open_tile(cons.t);
+    }
+    int consumed = 0;
+    while (cons.valid) {
+        if (tid == 0) issue();
+        const int slot = consumed % BAND_STAGES;
+        mbar_wait(&full[slot], (uint32_t)((consumed / BAND_STAGES) & 1));
+        const uint2 *rp = ring + (size_t)slot * BAND_STAGE * 3;
+        uint2 q[BAND_RPT][3];
+        int4 bd[BAND_RPT];
+#pragma unroll
+        for (int k = 0; k < BAND_RPT; ++k) {
+            const uint2 *p = rp + 3 * (tid + k * BAND_THREADS);
+            q[k][0] = p[0]; q[k][1] = p[1]; q[k][2] = p[2];
+            bd[k] = sbound[slot][k];
+        }
+        __syncwarp();
+        if (lane_id == 0) mbar_arrive(&empty[slot]);         // this warp holds its records in registers
+#pragma unroll
+        for (int k = 0; k < BAND_RPT; ++k) {
+            const long long idx = cons.idx + tid + k * BAND_THREADS;
+            const bool live = idx < cons.end;
+            if (idx == a.n_pairs - 1) q[k][2] = __ldg(a.pairs + 3 * idx + 2);
+            const int32_t lo = tid < CHUNK ? bd[k].x : bd[k].z, hi = tid < CHUNK ? bd[k].y : bd[k].w;
+            if (!live) q[k][0] = q[k][1] = q[k][2] = make_uint2(0, 0);
+            int32_t row = 0, col = 0;
+            bool filtered, ok;
+            decode_lean<SAME_MEMBER>(a, q[k][0], q[k][1], q[k][2], row, col, filtered, ok);
+            filtered = filtered || !live;
+            ok = ok && live;
+            const bool owner = live && lo == r0;             // this tile accounts for the record
+            if (owner) {
+                n_lines += !filtered;
+                n_ok += ok;
+                if (!filtered && !ok) {
+                    int32_t rr, cc;
+                    const int st = decode(a, q[k][0], q[k][1], q[k][2], rr, cc);
+                    n_absent += st == ST_ABSENT;
+                    n_range += st == ST_RANGE;
+                    n_key += st == ST_KEY;
+                }
+            }
+            const bool mine = ok && row == r0;
+            const bool near = mine && col >= b0 && col < b1;
+            const uint32_t cell = near ? (uint32_t)(col - b0) : 0xffffffffu;
+            const unsigned peers = __match_any_sync(0xffffffffu, cell);
+            if (near && (__ffs(peers) - 1) == lane_id) atomicAdd(&band[cell], (uint32_t)__popc(peers));
+            if (mine && !near)    // far hit: a reduction resolved in L2, nothing comes back (the warp does not wait for it)
+                asm volatile("red.relaxed.gpu.global.add.u32 [%0], %1;" ::"l"(a.counts + (size_t)(r0 - a.row0) * nw + col), "r"(1u) : "memory");
+            const bool in_block = row >= a.row0 && row < a.row1;
+            n_outside += owner && ok && !in_block;
+            const bool strag = owner && ok && (row < lo || row >= hi) && in_block;
+            const unsigned m = __ballot_sync(0xffffffffu, strag);
+            if (m) {
+                const int leader = __ffs(m) - 1;
+                unsigned long long sl = 0;
+                if (lane_id == leader) sl = atomicAdd(a.overflow_count, (unsigned long long)__popc(m));
+                sl = __shfl_sync(0xffffffffu, sl, leader);
+                if (strag) {
+                    sl += __popc(m & ((1u << lane_id) - 1));
+                    if ((long long)sl < a.overflow_cap) a.overflow[sl] = make_uint2(row, col);
+                    n_over++;
+                }
+            }
+        }
+        const bool last = cons.last_of_tile();
+        ++consumed;
+        cons.next(a);
+        if (last) {           // flush the band (every band cell is written exactly once) and prepare the next row
+            __syncthreads();
+            uint32_t *dst = a.counts + (size_t)(r0 - a.row0) * nw + b0;
+            for (int i = tid * 4; i < b1 - b0; i += BAND_THREADS * 4) {
+                uint4 v = *(uint4 *)(band + i);
+                if (a.accumulate) {
+                    const uint4 o = *(uint4 *)(dst + i);
+                    v.x += o.x; v.y += o.y; v.z += o.z; v.w += o.w;
+                }
+                *(uint4 *)(dst + i) = v;
+                *(uint4 *)(band + i) = make_uint4(0, 0, 0, 0);
+            }
+            if (cons.valid) {
+                if (!a.accumulate) { zero_row(cons.t); __threadfence(); }
+                open_tile(cons.t);
+            }
+            __syncthreads();
+        }
+    }
+    unsigned long long v[7] = {n_lines, n_ok, n_absent, n_range, n_key, n_over, n_outside};
+#pragma unroll
+    for (int k = 0; k < 7; ++k) {
+        unsigned long long t = hc::warp_sum_u64(v[k]);
+        if ((threadIdx.x & 31) == 0 && t) atomicAdd(a.stats + (k == 6 ? 10 : k), t);
+    }
+}
+
 // Spilled 16 384-count blocks are always applied (their list cannot overflow); the straggler list only when it
 // held every straggler -- otherwise k_bin_stragglers re-scans the records.  Both decisions are taken on the device,
 // BEFORE anything a second pass would add again is in `counts` (accumulate mode stays exact).
@@ -776,6 +1016,15 @@ extern "C" int hc_bin_pairs(const hc_pair_t *pairs, int64_t n_pairs, const int32
     const bool vec_host = (n_windows & 3) == 0 && (((uintptr_t)counts) & 15) == 0;
     bool cell16 = vec_host && (long long)n_windows * 4 > (smem_max - 1024) / 2;
     if (const char *e = getenv("HC_BIN_CELL16")) cell16 = vec_host && atoi(e) != 0;
+    // one-row tiles (n_windows > ~29 000): the band kernel (TMA-staged record ring, far hits as L2 reductions);
+    // HC_BIN_BAND=0/1 overrides, HC_BIN_BAND_B sets the half width of the band in windows
+    bool band = cell16 && (((uintptr_t)pairs) & 15) == 0 && n_windows >= 4096;
+    if (const char *e = getenv("HC_BIN_BAND")) band = atoi(e) != 0 && vec_host && (((uintptr_t)pairs) & 15) == 0;
+    int half_band = 1024;
+    if (const char *e = getenv("HC_BIN_BAND_B")) half_band = atoi(e);
+    if (half_band < 4) half_band = 4;
+    if (half_band > 8192) half_band = 8192;
+    half_band &= ~3;
     long long max_cells = (smem_max - 1024) / (cell16 ? 2 : 4);
     if (const char *e = getenv("HC_BIN_MAX_CELLS")) max_cells = atoll(e);
     a.n_segs = (int)((n_windows + max_cells - 1) / max_cells);
@@ -788,6 +1037,7 @@ extern "C" int hc_bin_pairs(const hc_pair_t *pairs, int64_t n_pairs, const int32
     int Rwant = (rows + 4 * sms - 1) / (4 * sms);  // aim for >= 4 tiles per SM
     a.R = Rwant < 1 ? 1 : (Rwant > Rmax ? Rmax : Rwant);
     if (const char *e = getenv("HC_BIN_ROWS")) a.R = atoi(e) < 1 ? 1 : (atoi(e) > Rmax ? Rmax : atoi(e));
+    if (band) { a.R = 1; a.n_segs = 1; a.W = n_windows; }
     if (cell16 && (a.W & 3) != 0) cell16 = false;  // (cannot happen: W = n_windows or a multiple of 4)
     a.n_groups = (rows + a.R - 1) / a.R;
 
@@ -843,7 +1093,17 @@ extern "C" int hc_bin_pairs(const hc_pair_t *pairs, int64_t n_pairs, const int32
         if (per_sm < 1) per_sm = 1;
         long long n_tiles = (long long)a.n_groups * a.n_segs;
         int grid = (int)std::min<long long>(n_tiles, (long long)sms * per_sm);
-        if (cell16) k_bin_tiles<3, true><<<grid, threads, smem, stream>>>(a);
+        if (band) {
+            const size_t bsmem = (size_t)BAND_STAGES * BAND_STAGE * 24 + (size_t)(2 * half_band + 8) * 4;
+            const int bgrid = (int)std::min<long long>(a.n_groups, (long long)sms * 2);
+            if (a.member == a.offsets) {
+                HC_CUDA_OK(cudaFuncSetAttribute(k_bin_band<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bsmem));
+                k_bin_band<true><<<bgrid, BAND_THREADS, bsmem, stream>>>(a, half_band);
+            } else {
+                HC_CUDA_OK(cudaFuncSetAttribute(k_bin_band<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bsmem));
+                k_bin_band<false><<<bgrid, BAND_THREADS, bsmem, stream>>>(a, half_band);
+            }
+        } else if (cell16) k_bin_tiles<3, true><<<grid, threads, smem, stream>>>(a);
         else k_bin_tiles<2, false><<<grid, threads, smem, stream>>>(a);
         HC_CHECK_LAUNCH();
         k_apply_overflow<<<4 * sms, 256, 0, stream>>>(a);

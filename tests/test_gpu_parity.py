@@ -52,7 +52,8 @@ def test_bam2arrays_multi_window_bit_exact(kw):
 @pytest.mark.parametrize("mode", [0, 1])
 @pytest.mark.parametrize("env", [dict(), dict(HC_BIN_MAX_CELLS="700", HC_BIN_ROWS="3"), dict(HC_BIN_CELL16="1"),
                                  dict(HC_BIN_CELL16="1", HC_BIN_MAX_CELLS="1200", HC_BIN_ROWS="3"),
-                                 dict(HC_BIN_CELL16="0")])
+                                 dict(HC_BIN_CELL16="0"), dict(HC_BIN_BAND="1"), dict(HC_BIN_BAND="1", HC_BIN_BAND_B="8"),
+                                 dict(HC_BIN_BAND="1", HC_BIN_BAND_B="200")])
 def test_bin_pairs_paths_agree(mode, env, monkeypatch):
     """shared-memory tile path (also with several column segments / odd tile heights) and the
     global-atomic path give the same full-orientation counts"""
@@ -188,6 +189,37 @@ def test_bin_pairs_deferred_stats():
     _, later = ops.bin_pairs(dev, off, g.window_bp, 990, 10, defer_stats=True)      # windows past the matrix
     with pytest.raises(IndexError):
         later.read()
+
+
+@pytest.mark.parametrize("half_band", ["4", "64", "1024"])
+def test_bin_band_kernel_edge_cases(half_band, monkeypatch):
+    """the TMA-staged band kernel (one row per tile, far hits as global reductions): odd record counts (the 8-byte tail
+    of the last TMA copy), rows without records, accumulate mode, unsorted input, a row block of a sharded build"""
+    from hicembler_b200 import ops
+    monkeypatch.setenv("HC_BIN_BAND", "1")
+    monkeypatch.setenv("HC_BIN_BAND_B", half_band)
+    g, rec = small_case(n_contigs=40, n_windows=1200, window_bp=5000, n_chrom=4, n_pairs=200001, seed=13)
+    off = torch.from_numpy(g.window_offsets().astype(np.int32)).cuda()
+    want = O.bin_records(rec, g.window_bp, g.window_offsets(), 1200, 10).astype(np.int64)
+
+    def upper(c):
+        full = c.cpu().numpy().astype(np.int64)
+        return np.triu(full + full.T - np.diag(full.diagonal()))
+    for n in (200001, 200000, 511, 513, 1):
+        cnt, st = ops.bin_pairs(ops.to_device_records(rec[:n]), off, g.window_bp, 1200, 10, return_stats=True)
+        assert np.array_equal(upper(cnt), O.bin_records(rec[:n], g.window_bp, g.window_offsets(), 1200, 10).astype(np.int64)), n
+        assert st["fast_path"]
+    dev = ops.to_device_records(rec)
+    cnt = ops.bin_pairs(dev, off, g.window_bp, 1200, 10)
+    cnt2 = ops.bin_pairs(dev, off, g.window_bp, 1200, 10, mode=2, out=cnt.clone())
+    assert torch.equal(cnt2, 2 * cnt)
+    blk = ops.bin_pairs(dev, off, g.window_bp, 1200, 10, rows=(256, 640))          # a rank's row block
+    assert torch.equal(blk, cnt[256:640])
+    g2, rec2 = small_case(n_contigs=40, n_windows=1200, window_bp=5000, n_chrom=4, n_pairs=300000, seed=3, sort=False)
+    cnt3, st3 = ops.bin_pairs(ops.to_device_records(rec2), torch.from_numpy(g2.window_offsets().astype(np.int32)).cuda(),
+                              g2.window_bp, 1200, 10, return_stats=True)
+    assert np.array_equal(upper(cnt3), O.bin_records(rec2, g2.window_bp, g2.window_offsets(), 1200, 10).astype(np.int64))
+    assert not st3["fast_path"]
 
 
 def test_nearly_sorted_input_uses_overflow_list():
