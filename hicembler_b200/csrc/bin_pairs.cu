@@ -474,10 +474,7 @@ __global__ void __launch_bounds__(CELL16 ? 512 : 1024, CELL16 ? 2 : 1) k_bin_til
 //     1024 records per stage, BAND_STAGES stages, one elected thread issues the copies -- across tile boundaries, so the
 //     first records of the next tile arrive while the band of the current one is flushed.
 // Counts, statistics, straggler handling and accumulate mode are those of k_bin_tiles.
-constexpr int BAND_THREADS = 512;
 constexpr int BAND_RPT = 2;         // records per thread and stage
-constexpr int BAND_STAGE = BAND_THREADS * BAND_RPT;   // records per stage (two 256-record chunks per record slot)
-constexpr int BAND_STAGES = 4;      // 4 x 24 KB ring
 
 __device__ __forceinline__ uint32_t smem_u32(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
 __device__ __forceinline__ void mbar_init(unsigned long long *b, int count) {
@@ -503,6 +500,7 @@ __device__ __forceinline__ void tma_load_1d(void *dst, const void *src, uint32_t
 }
 
 // the CTA's tiles t = blockIdx.x, blockIdx.x + gridDim.x, ... as one stream of stages; every thread walks it alike
+template <int BAND_STAGE>
 struct BandCursor {
     int t;               // tile (row group) of the stage
     long long idx, end;  // first record of the stage, end of the tile's slice
@@ -523,8 +521,10 @@ struct BandCursor {
     __device__ __forceinline__ bool last_of_tile() const { return idx + BAND_STAGE >= end; }
 };
 
-template <bool SAME_MEMBER>
-__global__ void __launch_bounds__(BAND_THREADS, 2) k_bin_band(BinArgs a, int half_band) {
+template <bool SAME_MEMBER, int NT, int NSTAGE>
+__global__ void __launch_bounds__(NT, 1024 / NT) k_bin_band(BinArgs a, int half_band) {
+    constexpr int BAND_THREADS = NT, BAND_STAGE = NT * BAND_RPT, BAND_STAGES = NSTAGE, CPS = NT / CHUNK;  // chunks per record slot
+    static_assert(NT == 256 || NT == 512, "a record slot is one or two 256-record chunks");
     extern __shared__ __align__(128) unsigned char smem_raw[];
     uint2 *ring = (uint2 *)smem_raw;                                      // [BAND_STAGES][BAND_STAGE * 3]
     uint32_t *band = (uint32_t *)(smem_raw + (size_t)BAND_STAGES * BAND_STAGE * 24);
@@ -542,7 +542,7 @@ __global__ void __launch_bounds__(BAND_THREADS, 2) k_bin_band(BinArgs a, int hal
     const int nw = a.n_windows;
 
     // producer state (thread 0): the stage stream runs BAND_STAGES - 1 ahead of the consumers
-    BandCursor prod, cons;
+    BandCursor<BAND_STAGE> prod, cons;
     prod.open(a, blockIdx.x);
     cons.open(a, blockIdx.x);
     int issued = 0;
@@ -554,7 +554,7 @@ __global__ void __launch_bounds__(BAND_THREADS, 2) k_bin_band(BinArgs a, int hal
         const long long c = prod.idx >> CHUNK_LOG;
 #pragma unroll
         for (int k = 0; k < BAND_RPT; ++k) {
-            const long long c0 = min(c + 2 * k, a.n_chunks - 1), c1 = min(c + 2 * k + 1, a.n_chunks - 1);
+            const long long c0 = min(c + CPS * k, a.n_chunks - 1), c1 = min(c + CPS * k + (CPS - 1), a.n_chunks - 1);
             nb[k] = make_int4(__ldg(a.chunk_lo + c0), __ldg(a.chunk_hi + c0), __ldg(a.chunk_lo + c1), __ldg(a.chunk_hi + c1));
         }
     };
@@ -621,12 +621,15 @@ __global__ void __launch_bounds__(BAND_THREADS, 2) k_bin_band(BinArgs a, int hal
         }
         __syncwarp();
         if (lane_id == 0) mbar_arrive(&empty[slot]);         // this warp holds its records in registers
+        // (32-bit positions inside the stage: how many records it holds, and where the array's last record sits)
+        const int remain = (int)min((long long)BAND_STAGE, cons.end - cons.idx);
+        const int tail = (cons.idx + remain == a.n_pairs) ? remain - 1 : -1;
 #pragma unroll
         for (int k = 0; k < BAND_RPT; ++k) {
-            const long long idx = cons.idx + tid + k * BAND_THREADS;
-            const bool live = idx < cons.end;
-            if (idx == a.n_pairs - 1) q[k][2] = __ldg(a.pairs + 3 * idx + 2);
-            const int32_t lo = tid < CHUNK ? bd[k].x : bd[k].z, hi = tid < CHUNK ? bd[k].y : bd[k].w;
+            const int rel = tid + k * BAND_THREADS;
+            const bool live = rel < remain;
+            if (rel == tail) q[k][2] = __ldg(a.pairs + 3 * (cons.idx + rel) + 2);
+            const int32_t lo = (CPS == 1 || tid < CHUNK) ? bd[k].x : bd[k].z, hi = (CPS == 1 || tid < CHUNK) ? bd[k].y : bd[k].w;
             if (!live) q[k][0] = q[k][1] = q[k][2] = make_uint2(0, 0);
             int32_t row = 0, col = 0;
             bool filtered, ok;
@@ -647,9 +650,12 @@ __global__ void __launch_bounds__(BAND_THREADS, 2) k_bin_band(BinArgs a, int hal
             }
             const bool mine = ok && row == r0;
             const bool near = mine && col >= b0 && col < b1;
-            const uint32_t cell = near ? (uint32_t)(col - b0) : 0xffffffffu;
-            const unsigned peers = __match_any_sync(0xffffffffu, cell);
-            if (near && (__ffs(peers) - 1) == lane_id) atomicAdd(&band[cell], (uint32_t)__popc(peers));
+            // a third of a row's pairs land on its diagonal cell: those are counted with one ballot per warp; the other
+            // band cells rarely coincide inside a warp and take plain shared-memory atomics
+            const bool diag = mine && col == r0;
+            const unsigned dm = __ballot_sync(0xffffffffu, diag);
+            if (dm && lane_id == (__ffs(dm) - 1)) atomicAdd(&band[r0 - b0], (uint32_t)__popc(dm));
+            if (near && !diag) atomicAdd(&band[col - b0], 1u);
             if (mine && !near)    // far hit: a reduction resolved in L2, nothing comes back (the warp does not wait for it)
                 asm volatile("red.relaxed.gpu.global.add.u32 [%0], %1;" ::"l"(a.counts + (size_t)(r0 - a.row0) * nw + col), "r"(1u) : "memory");
             const bool in_block = row >= a.row0 && row < a.row1;
@@ -1094,15 +1100,22 @@ extern "C" int hc_bin_pairs(const hc_pair_t *pairs, int64_t n_pairs, const int32
         long long n_tiles = (long long)a.n_groups * a.n_segs;
         int grid = (int)std::min<long long>(n_tiles, (long long)sms * per_sm);
         if (band) {
-            const size_t bsmem = (size_t)BAND_STAGES * BAND_STAGE * 24 + (size_t)(2 * half_band + 8) * 4;
-            const int bgrid = (int)std::min<long long>(a.n_groups, (long long)sms * 2);
-            if (a.member == a.offsets) {
-                HC_CUDA_OK(cudaFuncSetAttribute(k_bin_band<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bsmem));
-                k_bin_band<true><<<bgrid, BAND_THREADS, bsmem, stream>>>(a, half_band);
-            } else {
-                HC_CUDA_OK(cudaFuncSetAttribute(k_bin_band<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bsmem));
-                k_bin_band<false><<<bgrid, BAND_THREADS, bsmem, stream>>>(a, half_band);
-            }
+            int nt = 256, nst = 3;   // four CTAs per SM: C3 5.9 ms (512 x 4: 6.2 ms, 256 x 4: 8.0 ms)
+            if (const char *e = getenv("HC_BIN_BAND_THREADS")) nt = atoi(e) == 256 ? 256 : 512;
+            if (const char *e = getenv("HC_BIN_BAND_STAGES")) nst = atoi(e) == 3 ? 3 : 4;
+            const size_t bsmem2 = (size_t)nst * nt * BAND_RPT * 24 + (size_t)(2 * half_band + 8) * 4;
+            const int bgrid = (int)std::min<long long>(a.n_groups, (long long)sms * (1024 / nt));
+            const bool same = a.member == a.offsets;
+#define HC_BAND_LAUNCH(SM_, NT_, NS_)                                                                                       \
+    do {                                                                                                                    \
+        HC_CUDA_OK(cudaFuncSetAttribute(k_bin_band<SM_, NT_, NS_>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bsmem2)); \
+        k_bin_band<SM_, NT_, NS_><<<bgrid, NT_, bsmem2, stream>>>(a, half_band);                                             \
+    } while (0)
+            if (nt == 512 && nst == 4) { if (same) HC_BAND_LAUNCH(true, 512, 4); else HC_BAND_LAUNCH(false, 512, 4); }
+            else if (nt == 512) { if (same) HC_BAND_LAUNCH(true, 512, 3); else HC_BAND_LAUNCH(false, 512, 3); }
+            else if (nst == 4) { if (same) HC_BAND_LAUNCH(true, 256, 4); else HC_BAND_LAUNCH(false, 256, 4); }
+            else { if (same) HC_BAND_LAUNCH(true, 256, 3); else HC_BAND_LAUNCH(false, 256, 3); }
+#undef HC_BAND_LAUNCH
         } else if (cell16) k_bin_tiles<3, true><<<grid, threads, smem, stream>>>(a);
         else k_bin_tiles<2, false><<<grid, threads, smem, stream>>>(a);
         HC_CHECK_LAUNCH();
