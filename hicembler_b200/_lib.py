@@ -70,6 +70,7 @@ SIGNATURES = {
     "hc_segment_mean_2d": (C.c_int, [_p, _i32, _p, _p, _i32, _p, _p, _p]),
     "hc_normalize_rows": (C.c_int, [_p, _i32, _p, _sz, _p]),
     "hc_block_sums4": (C.c_int, [_p, _i32, _p, _p, _p, _p, _i32, _p, _p]),
+    "hc_segment_mean_2d_static": (C.c_int, [_p, _i32, _p, _p, _i32, _p, _p]),
     "hc_matrix_max": (C.c_int, [_p, C.c_int, _i64, _p, _i32, _p, _p]),
     "hc_gather_elements": (C.c_int, [_p, _i32, _p, _p, _i64, _p, _p]),
     "hc_unpack_pairs16": (C.c_int, [_p, C.c_int64, _p, _p]),

@@ -746,6 +746,55 @@ extern "C" int hc_segment_mean_2d(const float *A, int32_t n, const int32_t *seg_
     return HC_OK;
 }
 
+// hc_segment_mean_2d without an allocation anywhere (for callers that cannot cudaMalloc: graph capture, tight
+// serving loops): the n_seg x n intermediate lives in a file-scope device array that every GPU loading the library
+// holds until exit (HC_SEGMEAN_STATIC_MAX_ELEMS floats = 8 MiB).  The name below is only a host-side stand-in in
+// host code; the device address is taken per device with cudaGetSymbolAddress, with that device current.
+static __device__ __align__(256) float g_segmean_scratch[HC_SEGMEAN_STATIC_MAX_ELEMS];
+
+static int segmean_scratch_ptr(float **out) {
+    constexpr int MAX_DEV = 64;
+    static float *ptr[MAX_DEV];       // written once per device; a race between two first calls stores the same value
+    int dev = -1;
+    HC_CUDA_OK(cudaGetDevice(&dev));
+    if (dev < 0 || dev >= MAX_DEV) {
+        hc::set_error("hc_segment_mean_2d_static: device ordinal %d not supported (max %d)", dev, MAX_DEV - 1);
+        return HC_EINVAL;
+    }
+    float *p = __atomic_load_n(&ptr[dev], __ATOMIC_ACQUIRE);
+    if (!p) {
+        HC_CUDA_OK(cudaGetSymbolAddress((void **)&p, g_segmean_scratch));
+        if (!p) {
+            hc::set_error("hc_segment_mean_2d_static: cudaGetSymbolAddress returned a null pointer");
+            return HC_ECUDA;
+        }
+        __atomic_store_n(&ptr[dev], p, __ATOMIC_RELEASE);
+    }
+    *out = p;
+    return HC_OK;
+}
+
+extern "C" int hc_segment_mean_2d_static(const float *A, int32_t n, const int32_t *seg_begin, const int32_t *seg_end,
+                                         int32_t n_seg, float *out, void *stream_) {
+    cudaStream_t stream = (cudaStream_t)stream_;
+    HC_REQUIRE(A && seg_begin && seg_end && out && n > 0 && n_seg > 0, "bad arguments");
+    if ((long long)n * n_seg > (long long)HC_SEGMEAN_STATIC_MAX_ELEMS) {
+        hc::set_error("hc_segment_mean_2d_static: n * n_seg = %lld exceeds the static scratch of %lld floats "
+                      "(HC_SEGMEAN_STATIC_MAX_ELEMS); use hc_segment_mean_2d with a caller-provided tmp",
+                      (long long)n * n_seg, (long long)HC_SEGMEAN_STATIC_MAX_ELEMS);
+        return HC_EWORKSPACE;
+    }
+    float *tmp = nullptr;
+    int rc = segmean_scratch_ptr(&tmp);
+    if (rc != HC_OK) return rc;
+    // every element of tmp[0 .. n_seg*n) that stage 2 reads is written by stage 1 of this call: nothing has to
+    // start at zero, whatever the previous call left behind
+    k_segmean_rows<<<dim3((n + 255) / 256, n_seg), 256, 0, stream>>>(A, n, seg_begin, seg_end, n_seg, tmp);
+    k_segmean_cols<<<dim3((n_seg + 127) / 128, n_seg), 128, 0, stream>>>(tmp, n, seg_begin, seg_end, n_seg, out);
+    HC_CHECK_LAUNCH();
+    return HC_OK;
+}
+
 // join_scaffolds (bam2scaffolds.py:142-174): the four corner-block sums that decide how two scaffolds are
 // oriented.  One CTA per (job, corner); a job's windows are idx[off .. off+n1) (scaffold 1) followed by
 // idx[off+n1 .. off+n1+n2) (scaffold 2).  Rows: first n1/2 (corners 0,1) or last n1/2 (2,3) windows of

@@ -326,6 +326,17 @@ int hc_merges_to_linkage(int32_t n, int ward, const int32_t *h_a, const int32_t 
 int hc_segment_mean_2d(const float *A, int32_t n, const int32_t *seg_begin, const int32_t *seg_end,
                        int32_t n_seg, float *tmp, float *out, void *stream);
 int hc_normalize_rows(float *A, int32_t n, void *workspace, size_t workspace_bytes, void *stream);
+/* hc_segment_mean_2d_static: hc_segment_mean_2d for callers that cannot allocate (CUDA graph capture, tight serving
+ *   loops, harnesses that forbid cudaMalloc).  NO COUNTERPART IN THE REFERENCE.
+ *   Same inputs, same output bits; the n_seg x n intermediate lives in a file-scope `static __device__`
+ *   array of HC_SEGMEAN_STATIC_MAX_ELEMS floats (8 MiB, held by every GPU that loads the library until exit), so the
+ *   call performs no cudaMalloc / cudaFree and needs no tmp.  n * n_seg > HC_SEGMEAN_STATIC_MAX_ELEMS -> HC_EWORKSPACE
+ *   with a message in hc_last_error().  All calls on a device share the one array (it keeps the last call's contents;
+ *   stage 1 overwrites every element stage 2 reads, so nothing needs clearing): calls that overlap on the GPU --
+ *   different streams without ordering -- race; order them on one stream or with events. */
+#define HC_SEGMEAN_STATIC_MAX_ELEMS (1 << 21)
+int hc_segment_mean_2d_static(const float *A, int32_t n, const int32_t *seg_begin, const int32_t *seg_end,
+                              int32_t n_seg, float *out, void *stream);
 /* hc_block_sums4: the corner-block sums of join_scaffolds (bam2scaffolds.py:155-161 = array2scaffolds.py:287-293),
  *   batched over the independent joins of one tree level.  Job j: scaffold-1 windows idx[job_off[j] ..
  *   +job_n1[j]), scaffold-2 windows right behind them (job_n2[j]); out[4*j + q], q = 0..3 in the reference's
