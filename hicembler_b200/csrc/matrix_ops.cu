@@ -385,6 +385,150 @@ __global__ void __launch_bounds__(256) k_transform_tile64(RowBlocks X, int n, in
     if (bad) atomicOr(flags, 1);
 }
 
+// ---- the hot case of K6: float matrix, Sinkhorn vectors given, power law (bam2clusters.py:516 on the balanced matrix) ----
+// k_transform_tile64 inlines the general xform() sixteen times (every kind, pow/log/exp fall-backs: 13 600 SASS lines,
+// ~120 instructions per cell, 4-way shared-memory bank conflicts from its float4 thread layout) and ran at 42 % of the
+// HBM peak, issue-bound.  Here: one lane per COLUMN (a warp reads / writes 128 / 256 contiguous bytes per instruction and
+// walks shared memory conflict-free in both orientations, row stride 65 doubles), all 16 loads of a thread in flight
+// before the first use, d/vmax by the exact reciprocal form (ScaledDivF), the two short series straight-line, and the
+// rare cell outside the series range in ONE out-of-line call.  Same arithmetic as xform(): identical bits.
+__device__ __noinline__ double power_outside_series(double v, double e, double p0) {
+    const double u = 1.0 / (p0 * v);
+    const double lg = log(u), z = __dmul_rn(e, lg), zl = fma(e, lg, -z);  // z + zl = e*lg exactly
+    if (fabs(z) < 1.0) {
+        const double out = exp(z);
+        return fma(out, zl, out);
+    }
+    return pow(u, e);
+}
+
+// INTERIOR: a tile strictly above the diagonal with all 64 x 64 cells inside the matrix (all but ~2/T of the tiles):
+// no guards, pointer increments only.
+template <bool SQUARE, bool INTERIOR>
+__device__ __forceinline__ void transform_bal64_tile(const RowBlocks &X, int n, int I, int J, const Xform &t,
+                                                     double *__restrict__ W, int32_t *flags, double (*A)[T64 + 1]) {
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const hc::ScaledDivF dv((float)t.vmax);
+    const double e = t.inv_p1, K = t.K;
+    const bool series_ok = fabs(e) <= 4.0;
+    const int j0 = J * T64 + lane, j1 = j0 + 32;
+    const double cj[2] = {INTERIOR || j0 < n ? __ldg(t.c + j0) : 0.0, INTERIOR || j1 < n ? __ldg(t.c + j1) : 0.0};
+    float x[16], pq[16];
+    double ri[8];
+    // all rows of a tile live in the same row block (blocks are multiples of 64 rows, or one block holds everything)
+    const int i_base = I * T64, blk = i_base / X.per;
+    const float *Xb = (const float *)X.base[blk] + (size_t)(i_base - blk * X.per + warp) * n;
+    unsigned valid = INTERIOR ? 0xffffu : 0u;
+#pragma unroll
+    for (int p = 0; p < 8; ++p) {
+        const int i = i_base + warp + 8 * p;
+        const float *row = Xb + (size_t)(8 * p) * n;
+        if (INTERIOR) {
+            ri[p] = __ldg(t.r + i);
+            x[2 * p] = __ldcs(row + j0);
+            x[2 * p + 1] = __ldcs(row + j1);
+        } else {
+            x[2 * p] = x[2 * p + 1] = 1.0f;   // masked cells: a harmless operand for the grouped division
+            ri[p] = 0.0;
+            if (i < n) {
+                ri[p] = __ldg(t.r + i);
+                if (j0 < n && i < j0) { x[2 * p] = __ldcs(row + j0); valid |= 1u << (2 * p); }
+                if (j1 < n && i < j1) { x[2 * p + 1] = __ldcs(row + j1); valid |= 2u << (2 * p); }
+            }
+        }
+    }
+    dv.apply(x, pq);                      // d/vmax in the matrix dtype (bam2clusters.py:46)
+    // sixteen independent straight-line chains (the series of xform()); cells outside the series range are redone below
+    double o[16];
+    unsigned slow = 0;
+#pragma unroll
+    for (int k = 0; k < 16; ++k) {
+        const double v = __dadd_rn(__dmul_rn(__dmul_rn(ri[k >> 1], (double)pq[k]), cj[k & 1]), 1.0);  // (D1.P).D2 + 1
+        const double y = __dsub_rn(v, 1.0);
+        if (!(y >= 0.0 && y <= 0x1p-10)) slow |= 1u << k;
+        double L = fma(y, -1.0 / 6.0, 0.2);
+        L = fma(y, L, -0.25);
+        L = fma(y, L, 1.0 / 3.0);
+        L = fma(y, L, -0.5);
+        L = fma(y, L, 1.0);
+        const double z = -__dmul_rn(e, __dmul_rn(y, L));
+        double E = fma(z, 1.0 / 120.0, 1.0 / 24.0);
+        E = fma(z, E, 1.0 / 6.0);
+        E = fma(z, E, 0.5);
+        E = fma(z, E, 1.0);
+        o[k] = fma(K, __dmul_rn(z, E), K);
+    }
+    if (!series_ok) slow = 0xffffu;
+    slow &= valid;
+    if (slow) {
+#pragma unroll
+        for (int k = 0; k < 16; ++k)
+            if (slow >> k & 1) {
+                const double v = __dadd_rn(__dmul_rn(__dmul_rn(ri[k >> 1], (double)pq[k]), cj[k & 1]), 1.0);
+                o[k] = power_outside_series(v, e, t.p0);
+            }
+    }
+    bool bad = false;
+    double *As = &A[warp][lane];
+#pragma unroll
+    for (int k = 0; k < 16; ++k) {
+        double q = o[k];
+        if (INTERIOR || (valid >> k & 1)) bad |= q != q;
+        if (SQUARE) q = __dmul_rn(q, q);
+        As[(k >> 1) * 8 * (T64 + 1) + (k & 1) * 32] = (INTERIOR || (valid >> k & 1)) ? q : 0.0;
+    }
+    __syncthreads();
+    if (INTERIOR) {
+        double *d1 = W + (size_t)(i_base + warp) * n + j0;            // W[i][j]
+        double *d2 = W + (size_t)(J * T64 + warp) * n + i_base + lane;  // mirror tile: W[j][i] = the same value
+        const double *a2 = &A[lane][warp];
+#pragma unroll
+        for (int p = 0; p < 8; ++p) {
+            const size_t g = (size_t)(8 * p) * n;
+            d1[g] = As[8 * p * (T64 + 1)];
+            d1[g + 32] = As[8 * p * (T64 + 1) + 32];
+            d2[g] = a2[8 * p];
+            d2[g + 32] = a2[32 * (T64 + 1) + 8 * p];
+        }
+    } else {
+        const double inf = __longlong_as_double(0x7ff0000000000000LL);
+#pragma unroll
+        for (int p = 0; p < 8; ++p) {
+            const int r = warp + 8 * p, i = I * T64 + r;
+            if (i < n) {
+                double *dst = W + (size_t)i * n;
+#pragma unroll
+                for (int h = 0; h < 2; ++h) {
+                    const int c = lane + 32 * h, j = J * T64 + c;
+                    if (j < n) dst[j] = (I != J || i < j) ? A[r][c] : (i == j ? inf : A[c][r]);
+                }
+            }
+            if (I != J) {
+                const int i2 = J * T64 + r;   // mirror tile: W[i2][j2] = f(X[j2][i2])
+                if (i2 < n) {
+                    double *dst = W + (size_t)i2 * n;
+#pragma unroll
+                    for (int h = 0; h < 2; ++h) {
+                        const int c = lane + 32 * h, j2 = I * T64 + c;
+                        if (j2 < n) dst[j2] = A[c][r];
+                    }
+                }
+            }
+        }
+    }
+    if (bad) atomicOr(flags, 1);
+}
+
+template <bool SQUARE>
+__global__ void __launch_bounds__(256, 3) k_transform_bal64(RowBlocks X, int n, int T, Xform t, double *__restrict__ W,
+                                                             int32_t *flags) {
+    __shared__ double A[T64][T64 + 1];
+    int I, J;
+    tile_pair_from_linear(blockIdx.x, T, I, J);
+    if (I != J && (J + 1) * T64 <= n) transform_bal64_tile<SQUARE, true>(X, n, I, J, t, W, flags, A);
+    else transform_bal64_tile<SQUARE, false>(X, n, I, J, t, W, flags, A);
+}
+
 template <typename TI, typename TO>
 __global__ void k_transform_flat(const TI *X, long long count, Xform t, TO *out) {
     for (long long k = blockIdx.x * (long long)blockDim.x + threadIdx.x; k < count;
@@ -594,7 +738,12 @@ static int transform_blocks(const RowBlocks &rb, bool aligned16, int dtype, int3
     Xform t = make_xform(kind, p0, p1, r, c, vmax, square);
     int T = (n + TS - 1) / TS;
     HC_CUDA_OK(cudaMemsetAsync(d_flags, 0, sizeof(int32_t), stream));
-    if (dtype == 0 && (n & 3) == 0 && aligned16 && (((uintptr_t)W) & 15) == 0 && !getenv("HC_FOLD_TS32")) {
+    if (dtype == 0 && kind == 1 && r && !getenv("HC_TRANSFORM_GENERIC")) {   // the balanced power-law case: any n, any alignment
+        const int T6 = (n + T64 - 1) / T64;
+        const long long pairs = (long long)T6 * (T6 + 1) / 2;
+        if (square) k_transform_bal64<true><<<(unsigned)pairs, 256, 0, stream>>>(rb, n, T6, t, W, d_flags);
+        else k_transform_bal64<false><<<(unsigned)pairs, 256, 0, stream>>>(rb, n, T6, t, W, d_flags);
+    } else if (dtype == 0 && (n & 3) == 0 && aligned16 && (((uintptr_t)W) & 15) == 0 && !getenv("HC_FOLD_TS32")) {
         const int T6 = (n + T64 - 1) / T64;
         const long long pairs = (long long)T6 * (T6 + 1) / 2;
         k_transform_tile64<<<(unsigned)pairs, 256, 0, stream>>>(rb, n, T6, t, W, d_flags);
