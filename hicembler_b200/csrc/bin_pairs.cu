@@ -54,6 +54,7 @@ struct BinArgs {
     unsigned long long *spill_count;
     long long spill_cap;
     unsigned long long *stats;
+    int stream_evict_first;  // band kernel: the record stream is read once -- keep it from evicting the rows resident in L2
 };
 
 enum { ST_FILTERED = 0, ST_OK = 1, ST_ABSENT = 2, ST_RANGE = 3, ST_KEY = 4 };
@@ -499,6 +500,18 @@ __device__ __forceinline__ void tma_load_1d(void *dst, const void *src, uint32_t
                  ::"r"(smem_u32(dst)), "l"(src), "r"(bytes), "r"(smem_u32(bar)) : "memory");
 }
 
+// the same copy with an L2 eviction-priority hint (createpolicy): data read exactly once should leave L2 first
+__device__ __forceinline__ unsigned long long l2_policy_evict_first() {
+    unsigned long long pol;
+    asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(pol));
+    return pol;
+}
+__device__ __forceinline__ void tma_load_1d_hint(void *dst, const void *src, uint32_t bytes, unsigned long long *bar,
+                                                 unsigned long long pol) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes.L2::cache_hint [%0], [%1], %2, [%3], %4;"
+                 ::"r"(smem_u32(dst)), "l"(src), "r"(bytes), "r"(smem_u32(bar)), "l"(pol) : "memory");
+}
+
 // the CTA's tiles t = blockIdx.x, blockIdx.x + gridDim.x, ... as one stream of stages; every thread walks it alike
 template <int BAND_STAGE>
 struct BandCursor {
@@ -559,6 +572,7 @@ __global__ void __launch_bounds__(NT, 1024 / NT) k_bin_band(BinArgs a, int half_
         }
     };
     if (tid == 0) fetch_bounds();
+    const unsigned long long pol_stream = l2_policy_evict_first();
     auto issue = [&]() {      // thread 0 only
         if (!prod.valid) return;
         const int slot = issued % BAND_STAGES;
@@ -572,7 +586,8 @@ __global__ void __launch_bounds__(NT, 1024 / NT) k_bin_band(BinArgs a, int half_
             const uint32_t bytes = (uint32_t)(cnt * 24);
             const uint32_t b16 = (prod.idx + cnt == a.n_pairs) ? (bytes & ~15u) : ((bytes + 15u) & ~15u);
             mbar_expect_tx(&full[slot], b16);
-            tma_load_1d(ring + (size_t)slot * BAND_STAGE * 3, a.pairs + 3 * prod.idx, b16, &full[slot]);
+            if (a.stream_evict_first) tma_load_1d_hint(ring + (size_t)slot * BAND_STAGE * 3, a.pairs + 3 * prod.idx, b16, &full[slot], pol_stream);
+            else tma_load_1d(ring + (size_t)slot * BAND_STAGE * 3, a.pairs + 3 * prod.idx, b16, &full[slot]);
         } else {
             mbar_arrive(&full[slot]);                       // empty slice: complete the phase without a copy
         }
@@ -1030,6 +1045,8 @@ extern "C" int hc_bin_pairs(const hc_pair_t *pairs, int64_t n_pairs, const int32
     if (const char *e = getenv("HC_BIN_BAND_B")) half_band = atoi(e);
     if (half_band < 4) half_band = 4;
     if (half_band > 8192) half_band = 8192;
+    a.stream_evict_first = 1;
+    if (const char *e = getenv("HC_BIN_EVICT_FIRST")) a.stream_evict_first = atoi(e) != 0;
     half_band &= ~3;
     long long max_cells = (smem_max - 1024) / (cell16 ? 2 : 4);
     if (const char *e = getenv("HC_BIN_MAX_CELLS")) max_cells = atoll(e);

@@ -1135,6 +1135,275 @@ __global__ void __launch_bounds__(HEAVY_THREADS, 3) kb_rebuild(RArgs a, Cols d, 
     }
 }
 
+// ---- kb_rebuild2: the same pass with the old rows STAGED BY THE TMA UNIT ------------------------------------------------
+// kb_rebuild gathers every old entry with an 8-byte load behind an index load: ~170 instructions per new cell, two
+// (rows) x two (unroll) loads in flight per lane, 2.0-2.5 TB/s.  Here a CTA builds RB_WARPS new rows in lockstep, one per
+// consumer warp, chunk by chunk of RB_CH OLD columns, out of a two-stage shared-memory ring that a producer warp fills
+// with cp.async.bulk copies (full / empty mbarriers): per stage the chunk of both old rows of every new row, the chunk's
+// column descriptors and the per-column pair data -- metadata is read from L2 once per CTA and chunk instead of once per
+// row, and no consumer instruction waits for global memory.
+//   * the new columns of a chunk are contiguous (the compaction preserves order): pass 1 takes the FREE columns (copy, or
+//     one Lance-Williams step for a merged row) and queues the chunk's PAIR columns, pass 2 works the queue with all lanes
+//     on the same code path (one step for a free row, the three "lower j first" steps for a merged row) -- the gather
+//     kernel ran both paths for every warp iteration;
+//   * both sides of a column pair come out of shared memory (the i side sits a few columns before the j side for Hi-C
+//     shaped input; an i side before the chunk start is a plain global load);
+//   * the new row segment is assembled in shared memory and leaves in whole 256-byte warp stores.
+// Merged rows come first in the row list (they cost about twice a free row), groups of RB_WARPS rows are dealt round
+// robin.  Same operands and operation order as kb_rebuild, so the matrix and the merge records are bit-identical.
+// (A first version with a private two-stage ring per warp and the descriptors read through L1 measured 1.6x SLOWER than
+// the gather kernel: every chunk paid two exposed L2 latencies for its metadata.)
+constexpr int RB_CH = 256, RB_WARPS = 8, RB_STAGES = 2;
+struct __align__(16) RbStage {
+    int4 sD[RB_CH];                    // descriptors of the chunk's new columns
+    double sP[3][RB_CH + 2];           // pair data of those columns: m, s1, s2 (ward) / as, at (average)
+    double rows[RB_WARPS][2][RB_CH];   // old row chunk: [0] the row itself / j side, [1] the i side (merged rows)
+};
+struct __align__(16) RbWarp {
+    double sOut[RB_CH];
+    unsigned short q[RB_CH];
+};
+constexpr size_t RB_SMEM = RB_STAGES * sizeof(RbStage) + RB_WARPS * sizeof(RbWarp) + 2 * RB_STAGES * sizeof(unsigned long long);
+
+__device__ __forceinline__ uint32_t smem_u32(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(unsigned long long *b, int count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(b)), "r"(count));
+}
+__device__ __forceinline__ void mbar_expect_tx(unsigned long long *b, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(b)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(unsigned long long *b) {
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(b)) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(unsigned long long *b, uint32_t parity) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "W_%=:\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n\t"
+        "@!p bra W_%=;\n\t}"
+        ::"r"(smem_u32(b)), "r"(parity) : "memory");
+}
+__device__ __forceinline__ void tma_load_1d(void *dst, const void *src, uint32_t bytes, unsigned long long *bar) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                 ::"r"(smem_u32(dst)), "l"(src), "r"(bytes), "r"(smem_u32(bar)) : "memory");
+}
+
+// block 0: chunk0[k] = number of surviving columns whose OLD index is below k * RB_CH (oldidx is ascending)
+// block 1: rowlist = the new rows of merged clusters (ascending), then the free rows (ascending); P = pairs of the round
+__global__ void __launch_bounds__(1024) kb_chunks(const int *oldidx, const int4 *desc, int nnew, int nch, int P, int *chunk0,
+                                                   int *rowlist) {
+    if (blockIdx.x == 0) {
+        for (int k = threadIdx.x; k <= nch; k += blockDim.x) {
+            const int key = k * RB_CH;
+            int lo = 0, hi = nnew;
+            while (lo < hi) {
+                const int mid = (lo + hi) >> 1;
+                if (oldidx[mid] < key) lo = mid + 1; else hi = mid;
+            }
+            chunk0[k] = lo;
+        }
+        return;
+    }
+    __shared__ int s_warp[32];
+    __shared__ int s_base;
+    if (threadIdx.x == 0) s_base = 0;
+    __syncthreads();
+    for (int c0 = 0; c0 < nnew; c0 += 1024) {
+        const int c = c0 + threadIdx.x;
+        const bool pr = c < nnew && desc[c].y >= 0;
+        const unsigned m = __ballot_sync(0xffffffffu, pr);
+        if ((threadIdx.x & 31) == 0) s_warp[threadIdx.x >> 5] = __popc(m);
+        __syncthreads();
+        int before = s_base;
+        for (int w = 0; w < (int)(threadIdx.x >> 5); ++w) before += s_warp[w];
+        const int k = before + __popc(m & ((1u << (threadIdx.x & 31)) - 1));   // merged rows before c
+        if (c < nnew) rowlist[pr ? k : P + (c - k)] = c;
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            int t = 0;
+            for (int w = 0; w < 32; ++w) t += s_warp[w];
+            s_base += t;
+        }
+        __syncthreads();
+    }
+}
+
+template <int METHOD>
+__global__ void __launch_bounds__((RB_WARPS + 1) * 32, 2) kb_rebuild2(RArgs a, Cols d, const int4 *__restrict__ desc,
+                                                                       const double *__restrict__ colp, long long cstride,
+                                                                       const int *__restrict__ chunk0, int nch,
+                                                                       const int *__restrict__ rowlist,
+                                                                       double *__restrict__ Wn, long long stride_n, int nnew) {
+    extern __shared__ __align__(128) unsigned char rb_smem[];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    RbStage *stages = (RbStage *)rb_smem;
+    RbWarp *wsm = (RbWarp *)(rb_smem + RB_STAGES * sizeof(RbStage));
+    unsigned long long *full = (unsigned long long *)(rb_smem + RB_STAGES * sizeof(RbStage) + RB_WARPS * sizeof(RbWarp));
+    unsigned long long *empty = full + RB_STAGES;
+    if (threadIdx.x == 0) {
+        for (int s = 0; s < RB_STAGES; ++s) { mbar_init(&full[s], 1); mbar_init(&empty[s], RB_WARPS); }
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    __syncthreads();
+    constexpr bool NEED_S = METHOD == M_WARD, NEED_A = METHOD == M_AVERAGE;
+    constexpr int NP = NEED_S ? 3 : (NEED_A ? 2 : 0), PBASE = NEED_A ? 3 : 0;   // pair-data arrays staged per chunk
+    const int ncols = a.ncols, ngroups = (nnew + RB_WARPS - 1) / RB_WARPS;
+    unsigned it = 0;   // stage sequence number: slot = it % RB_STAGES, phase = it / RB_STAGES
+
+    if (warp == RB_WARPS) {   // ---- producer warp: lane l < RB_WARPS feeds row l of the group, the next lanes the metadata
+        for (int g = blockIdx.x; g < ngroups; g += gridDim.x) {
+            const double *Wj = nullptr, *Wi = nullptr;
+            bool have = false, prow = false;
+            if (lane < RB_WARPS && g * RB_WARPS + lane < nnew) {
+                const int4 dr = __ldg(desc + __ldg(rowlist + g * RB_WARPS + lane));
+                have = true;
+                prow = dr.y >= 0;
+                Wj = a.W + (size_t)dr.x * a.stride;
+                Wi = a.W + (size_t)dr.w * a.stride;
+            }
+            for (int k = 0; k < nch; ++k, ++it) {
+                const int slot = it % RB_STAGES;
+                if (it >= RB_STAGES) mbar_wait(&empty[slot], ((it / RB_STAGES) - 1) & 1u);
+                RbStage *st = stages + slot;
+                const int o0 = k * RB_CH, cnt = min(RB_CH, ncols - o0);
+                const uint32_t rbytes = (uint32_t)((cnt + 1) & ~1) * 8u;   // (stride is even: the pad element belongs to the row)
+                const int n0 = __ldg(chunk0 + k), cn = __ldg(chunk0 + k + 1) - n0;
+                const uint32_t pbytes = (uint32_t)(((n0 & 1) + cn + 1) & ~1) * 8u;
+                uint32_t mine = 0;
+                if (have) mine = prow ? 2u * rbytes : rbytes;
+                else if (lane == RB_WARPS && cn > 0) mine = (uint32_t)cn * 16u;
+                else if (lane > RB_WARPS && lane <= RB_WARPS + NP && cn > 0) mine = pbytes;
+                const uint32_t total = __reduce_add_sync(0xffffffffu, mine);
+                if (lane == 0) mbar_expect_tx(&full[slot], total);
+                __syncwarp();
+                if (have) {
+                    tma_load_1d(st->rows[lane][0], Wj + o0, rbytes, &full[slot]);
+                    if (prow) tma_load_1d(st->rows[lane][1], Wi + o0, rbytes, &full[slot]);
+                } else if (lane == RB_WARPS && cn > 0) {
+                    tma_load_1d(st->sD, desc + n0, (uint32_t)cn * 16u, &full[slot]);
+                } else if (lane > RB_WARPS && lane <= RB_WARPS + NP && cn > 0) {
+                    const int pa = lane - RB_WARPS - 1;
+                    tma_load_1d(st->sP[pa], colp + (size_t)(PBASE + pa) * cstride + (n0 & ~1), pbytes, &full[slot]);
+                }
+            }
+        }
+        return;
+    }
+
+    // ---- consumer warps: one new row each
+    RbWarp *ws = wsm + warp;
+    const double INF = __longlong_as_double(0x7ff0000000000000LL);
+    const unsigned lt_mask = (1u << lane) - 1u;
+    for (int g = blockIdx.x; g < ngroups; g += gridDim.x) {
+        const bool have = g * RB_WARPS + warp < nnew;
+        const int rn = have ? __ldg(rowlist + g * RB_WARPS + warp) : -1;
+        int4 dr = make_int4(0, ROLE_FREE, 1, 0);
+        if (have) dr = __ldg(desc + rn);
+        const bool prow = dr.y >= 0;
+        Pair p;
+        p.i = dr.w;
+        p.j = dr.x;
+        p.m = p.s1 = p.s2 = p.as = p.at = 0.0;
+        if (prow) {
+            p.m = __ldg(colp + rn); p.s1 = __ldg(colp + cstride + rn); p.s2 = __ldg(colp + 2 * cstride + rn);
+            p.as = __ldg(colp + 3 * cstride + rn); p.at = __ldg(colp + 4 * cstride + rn);
+        }
+        const double *Wj = a.W + (size_t)dr.x * a.stride, *Wi = a.W + (size_t)dr.w * a.stride;   // (i sides before a chunk)
+        const double vR = (double)dr.z, ps = __dadd_rn(p.s1, p.s2);
+        double *dst = Wn + (size_t)(have ? rn : 0) * stride_n;
+        Min3 best;
+        best.init();
+        for (int k = 0; k < nch; ++k, ++it) {
+            const int slot = it % RB_STAGES;
+            const RbStage *st = stages + slot;
+            const int o0 = k * RB_CH, n0 = __ldg(chunk0 + k), cn = __ldg(chunk0 + k + 1) - n0;
+            mbar_wait(&full[slot], (it / RB_STAGES) & 1u);
+            if (have) {
+                const double *sJ = st->rows[warp][0], *sI = st->rows[warp][1];
+                const int podd = n0 & 1;
+                // pass 1: free columns; pair columns are queued
+                int nq = 0;
+                for (int t0 = 0; t0 < cn; t0 += 32) {
+                    const int t = t0 + lane, c = n0 + t;
+                    const bool in = t < cn;
+                    int4 dc = make_int4(0, ROLE_FREE, 1, 0);
+                    if (in) dc = st->sD[t];
+                    const bool pc = in && dc.y >= 0;
+                    if (in && !pc) {
+                        const int off = dc.x - o0;
+                        const double B = sJ[off];
+                        double x = B;
+                        if (prow) x = lw(METHOD, sI[off], B, p, (double)dc.z);
+                        if (c == rn) x = INF;
+                        else best.push(x, c);
+                        ws->sOut[t] = x;
+                    }
+                    const unsigned m = __ballot_sync(0xffffffffu, pc);
+                    if (pc) ws->q[nq + __popc(m & lt_mask)] = (unsigned short)t;
+                    nq += __popc(m);
+                }
+                __syncwarp();
+                // pass 2: the surviving (j side) columns of the round's pairs
+                for (int u0 = 0; u0 < nq; u0 += 32) {
+                    const int u = u0 + lane;
+                    if (u < nq) {
+                        const int t = ws->q[u], c = n0 + t;
+                        const int4 dc = st->sD[t];
+                        const int off = dc.x - o0, ioff = dc.w - o0;
+                        Pair pq;
+                        pq.i = dc.w; pq.j = dc.x;
+                        pq.m = pq.s1 = pq.s2 = pq.as = pq.at = 0.0;
+                        if (NEED_S) { pq.m = st->sP[0][podd + t]; pq.s1 = st->sP[1][podd + t]; pq.s2 = st->sP[2][podd + t]; }
+                        if (NEED_A) { pq.as = st->sP[0][podd + t]; pq.at = st->sP[1][podd + t]; }
+                        const double Bj = sJ[off], Bi = ioff >= 0 ? sJ[ioff] : __ldg(Wj + dc.w);
+                        double x;
+                        if (!prow) x = lw(METHOD, Bi, Bj, pq, vR);                 // as kr_light
+                        else {                                                     // as phase B of kr_heavy
+                            const double Aj = sI[off], Ai = ioff >= 0 ? sI[ioff] : __ldg(Wi + dc.w);
+                            const bool pf = p.j < pq.j;  // p merges first
+                            Pair F, Sd;
+                            F.m = pf ? p.m : pq.m; F.s1 = pf ? p.s1 : pq.s1; F.s2 = pf ? p.s2 : pq.s2; F.as = pf ? p.as : pq.as; F.at = pf ? p.at : pq.at;
+                            Sd.m = pf ? pq.m : p.m; Sd.s1 = pf ? pq.s1 : p.s1; Sd.s2 = pf ? pq.s2 : p.s2; Sd.as = pf ? pq.as : p.as; Sd.at = pf ? pq.at : p.at;
+                            F.i = F.j = Sd.i = Sd.j = 0;
+                            const double t1 = lw(METHOD, Ai, pf ? Bi : Aj, F, pf ? pq.s1 : p.s1);
+                            const double t2 = lw(METHOD, pf ? Aj : Bi, Bj, F, pf ? pq.s2 : p.s2);
+                            x = lw(METHOD, t1, t2, Sd, pf ? ps : __dadd_rn(pq.s1, pq.s2));
+                        }
+                        if (c == rn) x = INF;
+                        else best.push(x, c);
+                        ws->sOut[t] = x;
+                    }
+                }
+            }
+            __syncwarp();                                   // the stage has been read by every lane
+            if (lane == 0) mbar_arrive(&empty[slot]);
+            if (have)
+                for (int t = lane; t < cn; t += 32) dst[n0 + t] = ws->sOut[t];
+            __syncwarp();                                   // the queue and sOut are free again
+        }
+        if (!have) continue;
+        unsigned long long key, bound;
+        int idx;
+        warp_select(dkey(best.m1), best.i1, dkey(best.m2), best.i2, dkey(best.m3), key, idx, bound);
+        const size_t base = (size_t)rn * LC;
+        const unsigned long long last = __shfl_sync(0xffffffffu, key, KC);
+        const unsigned long long lb = bound < last ? bound : last;
+        if (lane < KC) {
+            const bool keep = idx != INT_MAX && key <= lb;
+            d.cval[base + lane] = keep ? dunkey(key) : INF;
+            d.cidx[base + lane] = keep ? idx : -1;
+        }
+        if (lane == KC) {
+            d.cval[base + KC] = dunkey(lb);
+            d.cidx[base + KC] = -1;
+        }
+        if (lane == 0) {
+            d.fresh[rn] = 1;
+            d.need[rn] = 0;
+        }
+    }
+}
+
 // closes a bulk round like the last CTA of kr_heavy does
 __global__ void kb_retire(RArgs a, int nnew) {
     RState *st = a.st;
@@ -1174,6 +1443,9 @@ struct Layout {
     int *seg_done;
     int4 *desc;
     double *colp;   // [5][n]: m, s1, s2, as, at of the pair behind a new column
+    int *chunk0;    // [n / RB_CH + 2]: first new column of every chunk of old columns (kb_rebuild2)
+    int *rowlist;   // [n]: new rows in the order kb_rebuild2 builds them (merged rows first)
+    long long cstride;  // elements between the five arrays of colp (even: every array 16-byte aligned for the bulk copies)
 };
 
 // second matrix buffer: a compaction halves the columns, a bulk round (>= 1/5 of the columns merge) keeps <= 4/5
@@ -1205,7 +1477,10 @@ bool carve(void *workspace, size_t bytes, int n, Layout &L) {
     L.parts = ws.take<Part>((size_t)n * MAX_SEGS);
     L.seg_done = ws.take<int>(n);
     L.desc = ws.take<int4>(n);
-    L.colp = ws.take<double>((size_t)n * 5);
+    L.cstride = ((long long)n + 1) & ~1LL;
+    L.colp = ws.take<double>((size_t)L.cstride * 5);
+    L.chunk0 = ws.take<int>((size_t)n / RB_CH + 2);
+    L.rowlist = ws.take<int>(n);
     L.spare_elems = spare_elems_for(n);
     L.spare = ws.take<double>(L.spare_elems);
     return ws.ok();
@@ -1217,7 +1492,7 @@ extern "C" size_t hc_linkage_rounds_workspace_bytes(int32_t n) {
     if (n < 1) n = 1;
     size_t per_col = 4 * 5 + 8 + 2 * (4 * 3 + 12 * LC + 2);
     return 8192 + (size_t)n * per_col + ((size_t)n / 2 + 1) * sizeof(Pair) + 40 * 256 + spare_elems_for(n) * 8 +
-           (size_t)n * (MAX_SEGS * sizeof(Part) + 4 + 16 + 40) + 1024;
+           (size_t)n * (MAX_SEGS * sizeof(Part) + 4 + 16 + 40) + 1024 + ((size_t)n / RB_CH + 2) * 4 + (size_t)n * 4 + 1024;
 }
 
 // W: n x n float64 full symmetric working matrix (squared distances for ward, +inf diagonal), destroyed.
@@ -1369,6 +1644,21 @@ extern "C" int hc_linkage_rounds(double *W, int32_t n, int method, void *workspa
     int rebuild_min = 2048;  // columns: below this a round is launch latency, not traffic
     if (const char *e = getenv("HC_ROUNDS_REBUILD")) rebuild_min = atoi(e) > 0 ? atoi(e) : INT_MAX;
     long long rebuilds = 0;
+    int rebuild_v = 2;
+    if (const char *e = getenv("HC_ROUNDS_REBUILD_V")) rebuild_v = atoi(e);
+    if (rebuild_v == 2) {
+        static bool attr_set[64] = {false};   // per device, once: the kernel needs more than 48 KB of shared memory
+        int dev = 0;
+        cudaGetDevice(&dev);
+        if (dev >= 0 && dev < 64 && !attr_set[dev]) {
+            HC_CUDA_OK(cudaFuncSetAttribute(kb_rebuild2<M_SINGLE>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)RB_SMEM));
+            HC_CUDA_OK(cudaFuncSetAttribute(kb_rebuild2<M_COMPLETE>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)RB_SMEM));
+            HC_CUDA_OK(cudaFuncSetAttribute(kb_rebuild2<M_AVERAGE>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)RB_SMEM));
+            HC_CUDA_OK(cudaFuncSetAttribute(kb_rebuild2<M_WEIGHTED>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)RB_SMEM));
+            HC_CUDA_OK(cudaFuncSetAttribute(kb_rebuild2<M_WARD>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)RB_SMEM));
+            attr_set[dev] = true;
+        }
+    }
     while (a.ncols >= rebuild_min) {
         if (trace) cudaEventRecord(ev0, stream);
         kmark(0);
@@ -1390,18 +1680,29 @@ extern "C" int hc_linkage_rounds(double *W, int32_t n, int method, void *workspa
         double *dst = in_spare ? W : L.spare;
         kmark(3);
         kc_map<<<1, 1024, 0, stream>>>(a.c.role, a.ncols, L.newidx, L.oldidx, true);
-        kb_desc<<<(nnew + 255) / 256, 256, 0, stream>>>(a.c, L.cols[cur ^ 1], a.pairs, L.oldidx, nnew, L.desc, L.colp, n);
+        kb_desc<<<(nnew + 255) / 256, 256, 0, stream>>>(a.c, L.cols[cur ^ 1], a.pairs, L.oldidx, nnew, L.desc, L.colp, L.cstride);
+        // TMA-staged pass where the rows can be bulk-copied (16-byte aligned rows: even stride); HC_ROUNDS_REBUILD_V=1
+        // keeps the gather kernel
+        const bool tma_ok = (a.stride & 1) == 0 && (((uintptr_t)a.W) & 15) == 0 && rebuild_v == 2;
+        const int nch = (a.ncols + RB_CH - 1) / RB_CH;
+        if (tma_ok) kb_chunks<<<2, 1024, 0, stream>>>(L.oldidx, L.desc, nnew, nch, h.ctr[0].P, L.chunk0, L.rowlist);
         kmark(5);
         {
             const int rg = sms * 12;  // 3 CTAs per SM (80 registers): 12.4 vs 14.2 ms in the largest round at C3
+            const int rg2 = sms * 2;
             const Cols dc = L.cols[cur ^ 1];
+#define HC_REBUILD_CASE(M)                                                                                                      \
+    if (tma_ok) kb_rebuild2<M><<<rg2, (RB_WARPS + 1) * 32, RB_SMEM, stream>>>(a, dc, L.desc, L.colp, L.cstride, L.chunk0, nch, L.rowlist, dst, stride_new, nnew); \
+    else kb_rebuild<M><<<rg, HEAVY_THREADS, 0, stream>>>(a, dc, L.desc, L.colp, L.cstride, dst, stride_new, nnew);                \
+    break;
             switch (method) {
-            case M_SINGLE: kb_rebuild<M_SINGLE><<<rg, HEAVY_THREADS, 0, stream>>>(a, dc, L.desc, L.colp, n, dst, stride_new, nnew); break;
-            case M_COMPLETE: kb_rebuild<M_COMPLETE><<<rg, HEAVY_THREADS, 0, stream>>>(a, dc, L.desc, L.colp, n, dst, stride_new, nnew); break;
-            case M_AVERAGE: kb_rebuild<M_AVERAGE><<<rg, HEAVY_THREADS, 0, stream>>>(a, dc, L.desc, L.colp, n, dst, stride_new, nnew); break;
-            case M_WEIGHTED: kb_rebuild<M_WEIGHTED><<<rg, HEAVY_THREADS, 0, stream>>>(a, dc, L.desc, L.colp, n, dst, stride_new, nnew); break;
-            default: kb_rebuild<M_WARD><<<rg, HEAVY_THREADS, 0, stream>>>(a, dc, L.desc, L.colp, n, dst, stride_new, nnew); break;
+            case M_SINGLE: HC_REBUILD_CASE(M_SINGLE)
+            case M_COMPLETE: HC_REBUILD_CASE(M_COMPLETE)
+            case M_AVERAGE: HC_REBUILD_CASE(M_AVERAGE)
+            case M_WEIGHTED: HC_REBUILD_CASE(M_WEIGHTED)
+            default: HC_REBUILD_CASE(M_WARD)
             }
+#undef HC_REBUILD_CASE
         }
         kmark(-1);
         kb_retire<<<1, 1, 0, stream>>>(a, nnew);
@@ -1419,7 +1720,7 @@ extern "C" int hc_linkage_rounds(double *W, int32_t n, int method, void *workspa
         a.W = dst;
         a.stride = stride_new;
         a.ncols = nnew;
-        n_launches += 4;
+        n_launches += tma_ok ? 5 : 4;
         rebuilds++;
     }
     // The rest of the run in cooperative launches of the persistent kernel (one CTA per SM, many rounds per launch);

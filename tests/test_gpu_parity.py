@@ -732,6 +732,7 @@ def test_linkage_rounds_hic_balanced_matrix(method):
 
 @pytest.mark.parametrize("env", [{}, {"HC_ROUNDS_NOCOMPACT": "1"}, {"HC_ROUNDS_BATCH": "1"}, {"HC_ROUNDS_BULK_SEGS": "32"},
                                  {"HC_ROUNDS_KTIME": "1"}, {"HC_ROUNDS_TRACE": "1"}, {"HC_ROUNDS_REBUILD": "16"},
+                                 {"HC_ROUNDS_REBUILD": "16", "HC_ROUNDS_REBUILD_V": "1"},
                                  {"HC_ROUNDS_REBUILD": "0"}, {"HC_ROUNDS_PERSIST": "0"}, {"HC_ROUNDS_CHAIN_MAX": "3"},
                                  {"HC_ROUNDS_PERSIST": "0", "HC_ROUNDS_KTIME": "1"}])
 def test_linkage_rounds_compaction_and_batching_do_not_change_results(env, monkeypatch):
@@ -762,13 +763,15 @@ def test_linkage_rounds_bulk_rebuild(n, method, monkeypatch):
     from hicembler_b200 import ops
     y = np.random.default_rng(2000 + n).random(n * (n - 1) // 2) + 0.05
     out = {}
-    for flag in ("0", "16"):
+    for flag, version in (("0", "2"), ("16", "2"), ("16", "1")):   # version 2 = TMA-staged kb_rebuild2, 1 = gather kernel
         monkeypatch.setenv("HC_ROUNDS_REBUILD", flag)
+        monkeypatch.setenv("HC_ROUNDS_REBUILD_V", version)
         W, flags = ops.expand_condensed(torch.from_numpy(y).cuda(), n, square=(method == "ward"))
         Z, st = ops.linkage_rounds(W, method, nan_flags=flags)
         assert Z is not None and st["certified"], st
-        out[flag] = (Z, st)
-    assert np.array_equal(out["0"][0], out["16"][0])
+        out[flag + version] = (Z, st)
+    assert np.array_equal(out["02"][0], out["162"][0]) and np.array_equal(out["02"][0], out["161"][0])
+    out = {"0": out["02"], "16": out["162"]}
     assert out["16"][1]["rounds"] == out["0"][1]["rounds"] and out["16"][1]["compactions"] >= 1
     _same_tree(out["16"][0], O.linkage_fastcluster(y, method), rtol=1e-12)
 
