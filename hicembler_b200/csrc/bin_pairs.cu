@@ -55,6 +55,7 @@ struct BinArgs {
     long long spill_cap;
     unsigned long long *stats;
     int stream_evict_first;  // band kernel: the record stream is read once -- keep it from evicting the rows resident in L2
+    int row_evict_last;      // band kernel: zero stores and far-hit reductions of a row carry the evict_last L2 priority
 };
 
 enum { ST_FILTERED = 0, ST_OK = 1, ST_ABSENT = 2, ST_RANGE = 3, ST_KEY = 4 };
@@ -506,6 +507,11 @@ __device__ __forceinline__ unsigned long long l2_policy_evict_first() {
     asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(pol));
     return pol;
 }
+__device__ __forceinline__ unsigned long long l2_policy_evict_last() {
+    unsigned long long pol;
+    asm volatile("createpolicy.fractional.L2::evict_last.b64 %0, 1.0;" : "=l"(pol));
+    return pol;
+}
 __device__ __forceinline__ void tma_load_1d_hint(void *dst, const void *src, uint32_t bytes, unsigned long long *bar,
                                                  unsigned long long pol) {
     asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes.L2::cache_hint [%0], [%1], %2, [%3], %4;"
@@ -572,7 +578,7 @@ __global__ void __launch_bounds__(NT, 1024 / NT) k_bin_band(BinArgs a, int half_
         }
     };
     if (tid == 0) fetch_bounds();
-    const unsigned long long pol_stream = l2_policy_evict_first();
+    const unsigned long long pol_stream = l2_policy_evict_first(), pol_row = l2_policy_evict_last();
     auto issue = [&]() {      // thread 0 only
         if (!prod.valid) return;
         const int slot = issued % BAND_STAGES;
@@ -607,8 +613,14 @@ __global__ void __launch_bounds__(NT, 1024 / NT) k_bin_band(BinArgs a, int half_
         uint4 *dst = (uint4 *)(a.counts + (size_t)(r - a.row0) * nw);
         const int n4 = nw >> 2, s0 = z0 >> 2, s1 = z1 >> 2;
         const uint4 z = make_uint4(0, 0, 0, 0);
-        for (int i = tid; i < n4; i += BAND_THREADS)
-            if (i < s0 || i >= s1) dst[i] = z;
+        if (a.row_evict_last) {
+            for (int i = tid; i < n4; i += BAND_THREADS)
+                if (i < s0 || i >= s1)
+                    asm volatile("st.global.L2::cache_hint.v4.u32 [%0], {%1, %1, %1, %1}, %2;" ::"l"(dst + i), "r"(0u), "l"(pol_row) : "memory");
+        } else {
+            for (int i = tid; i < n4; i += BAND_THREADS)
+                if (i < s0 || i >= s1) dst[i] = z;
+        }
     };
     auto open_tile = [&](int t) {
         r0 = a.row0 + t;
@@ -639,18 +651,31 @@ __global__ void __launch_bounds__(NT, 1024 / NT) k_bin_band(BinArgs a, int half_
         // (32-bit positions inside the stage: how many records it holds, and where the array's last record sits)
         const int remain = (int)min((long long)BAND_STAGE, cons.end - cons.idx);
         const int tail = (cons.idx + remain == a.n_pairs) ? remain - 1 : -1;
+        // decode all records of the thread first (their table look-ups go out together), count afterwards: the
+        // reduction below is a volatile asm with a memory clobber, no load of the next record moves above it
+        if (tail >= 0) {   // (only the stage that holds the array's very last record)
+#pragma unroll
+            for (int k = 0; k < BAND_RPT; ++k)
+                if (tid + k * BAND_THREADS == tail) q[k][2] = __ldg(a.pairs + 3 * (cons.idx + tail) + 2);
+        }
+        int32_t rows[BAND_RPT], cols[BAND_RPT];
+        bool filt[BAND_RPT], oks[BAND_RPT];
+#pragma unroll
+        for (int k = 0; k < BAND_RPT; ++k) {
+            const bool live = tid + k * BAND_THREADS < remain;
+            if (!live) q[k][0] = q[k][1] = q[k][2] = make_uint2(0, 0);
+            rows[k] = cols[k] = 0;
+            decode_lean<SAME_MEMBER>(a, q[k][0], q[k][1], q[k][2], rows[k], cols[k], filt[k], oks[k]);
+            filt[k] = filt[k] || !live;
+            oks[k] = oks[k] && live;
+        }
 #pragma unroll
         for (int k = 0; k < BAND_RPT; ++k) {
             const int rel = tid + k * BAND_THREADS;
             const bool live = rel < remain;
-            if (rel == tail) q[k][2] = __ldg(a.pairs + 3 * (cons.idx + rel) + 2);
             const int32_t lo = (CPS == 1 || tid < CHUNK) ? bd[k].x : bd[k].z, hi = (CPS == 1 || tid < CHUNK) ? bd[k].y : bd[k].w;
-            if (!live) q[k][0] = q[k][1] = q[k][2] = make_uint2(0, 0);
-            int32_t row = 0, col = 0;
-            bool filtered, ok;
-            decode_lean<SAME_MEMBER>(a, q[k][0], q[k][1], q[k][2], row, col, filtered, ok);
-            filtered = filtered || !live;
-            ok = ok && live;
+            const int32_t row = rows[k], col = cols[k];
+            const bool filtered = filt[k], ok = oks[k];
             const bool owner = live && lo == r0;             // this tile accounts for the record
             if (owner) {
                 n_lines += !filtered;
@@ -671,8 +696,12 @@ __global__ void __launch_bounds__(NT, 1024 / NT) k_bin_band(BinArgs a, int half_
             const unsigned dm = __ballot_sync(0xffffffffu, diag);
             if (dm && lane_id == (__ffs(dm) - 1)) atomicAdd(&band[r0 - b0], (uint32_t)__popc(dm));
             if (near && !diag) atomicAdd(&band[col - b0], 1u);
-            if (mine && !near)    // far hit: a reduction resolved in L2, nothing comes back (the warp does not wait for it)
-                asm volatile("red.relaxed.gpu.global.add.u32 [%0], %1;" ::"l"(a.counts + (size_t)(r0 - a.row0) * nw + col), "r"(1u) : "memory");
+            if (mine && !near) {  // far hit: a reduction resolved in L2, nothing comes back (the warp does not wait for it)
+                if (a.row_evict_last)
+                    asm volatile("red.relaxed.gpu.global.add.L2::cache_hint.u32 [%0], %1, %2;" ::"l"(a.counts + (size_t)(r0 - a.row0) * nw + col), "r"(1u), "l"(pol_row) : "memory");
+                else
+                    asm volatile("red.relaxed.gpu.global.add.u32 [%0], %1;" ::"l"(a.counts + (size_t)(r0 - a.row0) * nw + col), "r"(1u) : "memory");
+            }
             const bool in_block = row >= a.row0 && row < a.row1;
             n_outside += owner && ok && !in_block;
             const bool strag = owner && ok && (row < lo || row >= hi) && in_block;
@@ -1047,6 +1076,8 @@ extern "C" int hc_bin_pairs(const hc_pair_t *pairs, int64_t n_pairs, const int32
     if (half_band > 8192) half_band = 8192;
     a.stream_evict_first = 1;
     if (const char *e = getenv("HC_BIN_EVICT_FIRST")) a.stream_evict_first = atoi(e) != 0;
+    a.row_evict_last = 1;   // measured at C3: 5.83 -> 5.75 ms, 0.5 GB less DRAM write traffic
+    if (const char *e = getenv("HC_BIN_ROW_EVICT_LAST")) a.row_evict_last = atoi(e) != 0;
     half_band &= ~3;
     long long max_cells = (smem_max - 1024) / (cell16 ? 2 : 4);
     if (const char *e = getenv("HC_BIN_MAX_CELLS")) max_cells = atoll(e);

@@ -33,7 +33,7 @@ void records_to_Z(int n, bool ward, const int *ra, const int *rb, double *rd, do
     const int m = n - 1;
     if (ward)
         for (int k = 0; k < m; ++k) rd[k] = sqrt(rd[k]);
-    // stable sort by height: LSD radix sort of order-preserving 64-bit keys (4 passes of 16 bits), ~10x faster
+    // stable sort by height: LSD radix sort of order-preserving 64-bit keys (6 digits of 11 bits), ~10x faster
     // than std::stable_sort with an indirect comparison at m = 50 000
     std::vector<int> order(m), tmp_o(m);
     std::vector<unsigned long long> key(m), tmp_k(m);
@@ -45,16 +45,22 @@ void records_to_Z(int n, bool ward, const int *ra, const int *rb, double *rd, do
         order[k] = k;
     }
     {
-        std::vector<unsigned> cnt(65536);
-        for (int pass = 0; pass < 4; ++pass) {
-            const int sh = 16 * pass;
-            std::fill(cnt.begin(), cnt.end(), 0u);
-            for (int k = 0; k < m; ++k) cnt[(key[k] >> sh) & 0xffff]++;
-            if (cnt[(key[0] >> sh) & 0xffff] == (unsigned)m) continue;  // all keys share this digit
+        // six 11-bit digits; all histograms in ONE pass over the keys (2048-bin tables stay in L1), then one scatter
+        // pass per digit that actually varies
+        constexpr int BITS = 11, NPASS = 6, BINS = 1 << BITS;
+        std::vector<unsigned> cnt((size_t)NPASS * BINS, 0u);
+        for (int k = 0; k < m; ++k) {
+            const unsigned long long v = key[k];
+            for (int pass = 0; pass < NPASS; ++pass) cnt[(size_t)pass * BINS + ((v >> (BITS * pass)) & (BINS - 1))]++;
+        }
+        for (int pass = 0; pass < NPASS; ++pass) {
+            const int sh = BITS * pass;
+            unsigned *c = cnt.data() + (size_t)pass * BINS;
+            if (m > 0 && c[(key[0] >> sh) & (BINS - 1)] == (unsigned)m) continue;  // all keys share this digit
             unsigned run = 0;
-            for (int d = 0; d < 65536; ++d) { const unsigned c = cnt[d]; cnt[d] = run; run += c; }
+            for (int d = 0; d < BINS; ++d) { const unsigned t = c[d]; c[d] = run; run += t; }
             for (int k = 0; k < m; ++k) {
-                const unsigned pos = cnt[(key[k] >> sh) & 0xffff]++;
+                const unsigned pos = c[(key[k] >> sh) & (BINS - 1)]++;
                 tmp_k[pos] = key[k];
                 tmp_o[pos] = order[k];
             }

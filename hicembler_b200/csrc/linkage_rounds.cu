@@ -1153,17 +1153,23 @@ __global__ void __launch_bounds__(HEAVY_THREADS, 3) kb_rebuild(RArgs a, Cols d, 
 // robin.  Same operands and operation order as kb_rebuild, so the matrix and the merge records are bit-identical.
 // (A first version with a private two-stage ring per warp and the descriptors read through L1 measured 1.6x SLOWER than
 // the gather kernel: every chunk paid two exposed L2 latencies for its metadata.)
-constexpr int RB_CH = 256, RB_WARPS = 8, RB_STAGES = 2;
+constexpr int RB_CH = 128;           // unit of the chunk table (chunk0): a kernel chunk is RB_CH or 2 * RB_CH old columns
+constexpr int RB_WARPS = 8;
+template <int CH>
 struct __align__(16) RbStage {
-    int4 sD[RB_CH];                    // descriptors of the chunk's new columns
-    double sP[3][RB_CH + 2];           // pair data of those columns: m, s1, s2 (ward) / as, at (average)
-    double rows[RB_WARPS][2][RB_CH];   // old row chunk: [0] the row itself / j side, [1] the i side (merged rows)
+    int4 sD[CH];                    // descriptors of the chunk's new columns
+    double sP[3][CH + 2];           // pair data of those columns: m, s1, s2 (ward) / as, at (average)
+    double rows[RB_WARPS][2][CH];   // old row chunk: [0] the row itself / j side, [1] the i side (merged rows)
 };
+template <int CH>
 struct __align__(16) RbWarp {
-    double sOut[RB_CH];
-    unsigned short q[RB_CH];
+    double sOut[CH];
+    unsigned short q[CH];
 };
-constexpr size_t RB_SMEM = RB_STAGES * sizeof(RbStage) + RB_WARPS * sizeof(RbWarp) + 2 * RB_STAGES * sizeof(unsigned long long);
+template <int CH, int NST>
+constexpr size_t rb_smem_bytes() {
+    return NST * sizeof(RbStage<CH>) + RB_WARPS * sizeof(RbWarp<CH>) + 2 * NST * sizeof(unsigned long long);
+}
 
 __device__ __forceinline__ uint32_t smem_u32(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
 __device__ __forceinline__ void mbar_init(unsigned long long *b, int count) {
@@ -1175,13 +1181,14 @@ __device__ __forceinline__ void mbar_expect_tx(unsigned long long *b, uint32_t b
 __device__ __forceinline__ void mbar_arrive(unsigned long long *b) {
     asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(b)) : "memory");
 }
+// (the suspend-time hint lets the hardware park the warp instead of spinning through the issue slots of the working warps)
 __device__ __forceinline__ void mbar_wait(unsigned long long *b, uint32_t parity) {
     asm volatile(
         "{\n\t.reg .pred p;\n\t"
         "W_%=:\n\t"
-        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1, %2;\n\t"
         "@!p bra W_%=;\n\t}"
-        ::"r"(smem_u32(b)), "r"(parity) : "memory");
+        ::"r"(smem_u32(b)), "r"(parity), "r"(20000u) : "memory");
 }
 __device__ __forceinline__ void tma_load_1d(void *dst, const void *src, uint32_t bytes, unsigned long long *bar) {
     asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
@@ -1228,17 +1235,20 @@ __global__ void __launch_bounds__(1024) kb_chunks(const int *oldidx, const int4 
     }
 }
 
-template <int METHOD>
+template <int METHOD, int CH, int NST>
 __global__ void __launch_bounds__((RB_WARPS + 1) * 32, 2) kb_rebuild2(RArgs a, Cols d, const int4 *__restrict__ desc,
                                                                        const double *__restrict__ colp, long long cstride,
-                                                                       const int *__restrict__ chunk0, int nch,
+                                                                       const int *__restrict__ chunk0, int nch_units,
                                                                        const int *__restrict__ rowlist,
                                                                        double *__restrict__ Wn, long long stride_n, int nnew) {
     extern __shared__ __align__(128) unsigned char rb_smem[];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    RbStage *stages = (RbStage *)rb_smem;
-    RbWarp *wsm = (RbWarp *)(rb_smem + RB_STAGES * sizeof(RbStage));
-    unsigned long long *full = (unsigned long long *)(rb_smem + RB_STAGES * sizeof(RbStage) + RB_WARPS * sizeof(RbWarp));
+    typedef RbStage<CH> Stage;
+    typedef RbWarp<CH> WarpMem;
+    constexpr int RB_STAGES = NST, CPU = CH / RB_CH;   // chunk-table units per kernel chunk
+    Stage *stages = (Stage *)rb_smem;
+    WarpMem *wsm = (WarpMem *)(rb_smem + RB_STAGES * sizeof(Stage));
+    unsigned long long *full = (unsigned long long *)(rb_smem + RB_STAGES * sizeof(Stage) + RB_WARPS * sizeof(WarpMem));
     unsigned long long *empty = full + RB_STAGES;
     if (threadIdx.x == 0) {
         for (int s = 0; s < RB_STAGES; ++s) { mbar_init(&full[s], 1); mbar_init(&empty[s], RB_WARPS); }
@@ -1247,7 +1257,7 @@ __global__ void __launch_bounds__((RB_WARPS + 1) * 32, 2) kb_rebuild2(RArgs a, C
     __syncthreads();
     constexpr bool NEED_S = METHOD == M_WARD, NEED_A = METHOD == M_AVERAGE;
     constexpr int NP = NEED_S ? 3 : (NEED_A ? 2 : 0), PBASE = NEED_A ? 3 : 0;   // pair-data arrays staged per chunk
-    const int ncols = a.ncols, ngroups = (nnew + RB_WARPS - 1) / RB_WARPS;
+    const int ncols = a.ncols, ngroups = (nnew + RB_WARPS - 1) / RB_WARPS, nch = (ncols + CH - 1) / CH;
     unsigned it = 0;   // stage sequence number: slot = it % RB_STAGES, phase = it / RB_STAGES
 
     if (warp == RB_WARPS) {   // ---- producer warp: lane l < RB_WARPS feeds row l of the group, the next lanes the metadata
@@ -1264,10 +1274,10 @@ __global__ void __launch_bounds__((RB_WARPS + 1) * 32, 2) kb_rebuild2(RArgs a, C
             for (int k = 0; k < nch; ++k, ++it) {
                 const int slot = it % RB_STAGES;
                 if (it >= RB_STAGES) mbar_wait(&empty[slot], ((it / RB_STAGES) - 1) & 1u);
-                RbStage *st = stages + slot;
-                const int o0 = k * RB_CH, cnt = min(RB_CH, ncols - o0);
+                Stage *st = stages + slot;
+                const int o0 = k * CH, cnt = min(CH, ncols - o0);
                 const uint32_t rbytes = (uint32_t)((cnt + 1) & ~1) * 8u;   // (stride is even: the pad element belongs to the row)
-                const int n0 = __ldg(chunk0 + k), cn = __ldg(chunk0 + k + 1) - n0;
+                const int n0 = __ldg(chunk0 + k * CPU), cn = __ldg(chunk0 + min((k + 1) * CPU, nch_units)) - n0;
                 const uint32_t pbytes = (uint32_t)(((n0 & 1) + cn + 1) & ~1) * 8u;
                 uint32_t mine = 0;
                 if (have) mine = prow ? 2u * rbytes : rbytes;
@@ -1291,7 +1301,7 @@ __global__ void __launch_bounds__((RB_WARPS + 1) * 32, 2) kb_rebuild2(RArgs a, C
     }
 
     // ---- consumer warps: one new row each
-    RbWarp *ws = wsm + warp;
+    WarpMem *ws = wsm + warp;
     const double INF = __longlong_as_double(0x7ff0000000000000LL);
     const unsigned lt_mask = (1u << lane) - 1u;
     for (int g = blockIdx.x; g < ngroups; g += gridDim.x) {
@@ -1315,14 +1325,15 @@ __global__ void __launch_bounds__((RB_WARPS + 1) * 32, 2) kb_rebuild2(RArgs a, C
         best.init();
         for (int k = 0; k < nch; ++k, ++it) {
             const int slot = it % RB_STAGES;
-            const RbStage *st = stages + slot;
-            const int o0 = k * RB_CH, n0 = __ldg(chunk0 + k), cn = __ldg(chunk0 + k + 1) - n0;
+            const Stage *st = stages + slot;
+            const int o0 = k * CH, n0 = __ldg(chunk0 + k * CPU), cn = __ldg(chunk0 + min((k + 1) * CPU, nch_units)) - n0;
             mbar_wait(&full[slot], (it / RB_STAGES) & 1u);
             if (have) {
                 const double *sJ = st->rows[warp][0], *sI = st->rows[warp][1];
                 const int podd = n0 & 1;
                 // pass 1: free columns; pair columns are queued
                 int nq = 0;
+#pragma unroll 2
                 for (int t0 = 0; t0 < cn; t0 += 32) {
                     const int t = t0 + lane, c = n0 + t;
                     const bool in = t < cn;
@@ -1377,8 +1388,13 @@ __global__ void __launch_bounds__((RB_WARPS + 1) * 32, 2) kb_rebuild2(RArgs a, C
             }
             __syncwarp();                                   // the stage has been read by every lane
             if (lane == 0) mbar_arrive(&empty[slot]);
-            if (have)
-                for (int t = lane; t < cn; t += 32) dst[n0 + t] = ws->sOut[t];
+            if (have) {
+                double *o = dst + n0 + lane;
+                const double *si = ws->sOut + lane;
+#pragma unroll
+                for (int u = 0; u < CH / 32; ++u)
+                    if (lane + 32 * u < cn) o[32 * u] = si[32 * u];
+            }
             __syncwarp();                                   // the queue and sOut are free again
         }
         if (!have) continue;
@@ -1644,18 +1660,19 @@ extern "C" int hc_linkage_rounds(double *W, int32_t n, int method, void *workspa
     int rebuild_min = 2048;  // columns: below this a round is launch latency, not traffic
     if (const char *e = getenv("HC_ROUNDS_REBUILD")) rebuild_min = atoi(e) > 0 ? atoi(e) : INT_MAX;
     long long rebuilds = 0;
-    int rebuild_v = 2;
+    int rebuild_v = 2, rb_cfg = 0;   // rb_cfg: 0 = chunks of 256 old columns, 2 stages; 1 = 128 columns, 4 stages
     if (const char *e = getenv("HC_ROUNDS_REBUILD_V")) rebuild_v = atoi(e);
+    if (const char *e = getenv("HC_ROUNDS_RB_CFG")) rb_cfg = atoi(e);
     if (rebuild_v == 2) {
         static bool attr_set[64] = {false};   // per device, once: the kernel needs more than 48 KB of shared memory
         int dev = 0;
         cudaGetDevice(&dev);
         if (dev >= 0 && dev < 64 && !attr_set[dev]) {
-            HC_CUDA_OK(cudaFuncSetAttribute(kb_rebuild2<M_SINGLE>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)RB_SMEM));
-            HC_CUDA_OK(cudaFuncSetAttribute(kb_rebuild2<M_COMPLETE>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)RB_SMEM));
-            HC_CUDA_OK(cudaFuncSetAttribute(kb_rebuild2<M_AVERAGE>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)RB_SMEM));
-            HC_CUDA_OK(cudaFuncSetAttribute(kb_rebuild2<M_WEIGHTED>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)RB_SMEM));
-            HC_CUDA_OK(cudaFuncSetAttribute(kb_rebuild2<M_WARD>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)RB_SMEM));
+#define HC_RB_ATTR(M)                                                                                                              \
+    HC_CUDA_OK(cudaFuncSetAttribute(kb_rebuild2<M, 256, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)rb_smem_bytes<256, 2>())); \
+    HC_CUDA_OK(cudaFuncSetAttribute(kb_rebuild2<M, 128, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)rb_smem_bytes<128, 4>()));
+            HC_RB_ATTR(M_SINGLE) HC_RB_ATTR(M_COMPLETE) HC_RB_ATTR(M_AVERAGE) HC_RB_ATTR(M_WEIGHTED) HC_RB_ATTR(M_WARD)
+#undef HC_RB_ATTR
             attr_set[dev] = true;
         }
     }
@@ -1692,7 +1709,8 @@ extern "C" int hc_linkage_rounds(double *W, int32_t n, int method, void *workspa
             const int rg2 = sms * 2;
             const Cols dc = L.cols[cur ^ 1];
 #define HC_REBUILD_CASE(M)                                                                                                      \
-    if (tma_ok) kb_rebuild2<M><<<rg2, (RB_WARPS + 1) * 32, RB_SMEM, stream>>>(a, dc, L.desc, L.colp, L.cstride, L.chunk0, nch, L.rowlist, dst, stride_new, nnew); \
+    if (tma_ok && rb_cfg == 1) kb_rebuild2<M, 128, 4><<<rg2, (RB_WARPS + 1) * 32, rb_smem_bytes<128, 4>(), stream>>>(a, dc, L.desc, L.colp, L.cstride, L.chunk0, nch, L.rowlist, dst, stride_new, nnew); \
+    else if (tma_ok) kb_rebuild2<M, 256, 2><<<rg2, (RB_WARPS + 1) * 32, rb_smem_bytes<256, 2>(), stream>>>(a, dc, L.desc, L.colp, L.cstride, L.chunk0, nch, L.rowlist, dst, stride_new, nnew); \
     else kb_rebuild<M><<<rg, HEAVY_THREADS, 0, stream>>>(a, dc, L.desc, L.colp, L.cstride, dst, stride_new, nnew);                \
     break;
             switch (method) {
