@@ -144,6 +144,31 @@ __device__ __forceinline__ void bulk_prefetch_l2(const void *p, size_t bytes) {
     if (e > a) asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(a), "r"((unsigned)(e - a)) : "memory");
 }
 
+// ---- TMA (cp.async.bulk) + mbarrier helpers ----
+__device__ __forceinline__ uint32_t smem_u32(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(unsigned long long *b, int count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(b)), "r"(count));
+}
+__device__ __forceinline__ void mbar_expect_tx(unsigned long long *b, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(b)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(unsigned long long *b) {
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(b)) : "memory");
+}
+// (the suspend-time hint lets the hardware park the warp instead of spinning through the issue slots of the working warps)
+__device__ __forceinline__ void mbar_wait(unsigned long long *b, uint32_t parity) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "W_%=:\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1, %2;\n\t"
+        "@!p bra W_%=;\n\t}"
+        ::"r"(smem_u32(b)), "r"(parity), "r"(20000u) : "memory");
+}
+__device__ __forceinline__ void tma_load_1d(void *dst, const void *src, uint32_t bytes, unsigned long long *bar) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                 ::"r"(smem_u32(dst)), "l"(src), "r"(bytes), "r"(smem_u32(bar)) : "memory");
+}
+
 __device__ __forceinline__ bool lex_lt(double x, int c, double y, int d) { return x < y || (x == y && c < d); }
 
 // running LC smallest entries of a row in ascending (value, index) order, all in registers (static indexing only)
@@ -670,6 +695,50 @@ __device__ __forceinline__ void warp_select(unsigned long long k1, int i1, unsig
     obound = r1 < r2 ? r1 : r2;
 }
 
+// one warp: lane l holds the sorted partial list of segment l (KEY_INF padded) and its bound kb; out: lane s < LC holds
+// the s-th smallest candidate of all segments, bound (all lanes) = smallest value not selected
+__device__ __forceinline__ void combine_partials(unsigned long long (&pk)[LC], int (&pi)[LC], unsigned long long kb,
+                                                 unsigned long long &key, int &idx, unsigned long long &bound) {
+    const int lane = threadIdx.x & 31;
+    key = KEY_INF;
+    idx = INT_MAX;
+#pragma unroll
+    for (int sel = 0; sel < LC; ++sel) {
+        const unsigned long long m = warp_min_u64(pk[0]);
+        const int wl = __ffs(__ballot_sync(0xffffffffu, pk[0] == m)) - 1;
+        const int wi = __shfl_sync(0xffffffffu, pi[0], wl);
+        if (lane == sel) { key = m; idx = wi; }
+        if (lane == wl) {
+#pragma unroll
+            for (int t = 0; t + 1 < LC; ++t) { pk[t] = pk[t + 1]; pi[t] = pi[t + 1]; }
+            pk[LC - 1] = KEY_INF;
+            pi[LC - 1] = INT_MAX;
+        }
+    }
+    const unsigned long long r1 = warp_min_u64(kb), r2 = warp_min_u64(pk[0]);
+    bound = r1 < r2 ? r1 : r2;
+}
+
+// one warp: the candidate list of `row` from a finished scan (lane s < LC: s-th smallest entry; bound: smallest entry
+// that was not selected)
+__device__ __forceinline__ void store_list(const RArgs &a, int row, unsigned long long key, int idx, unsigned long long bound) {
+    const int lane = threadIdx.x & 31;
+    const size_t base = (size_t)row * LC;
+    // the smallest entry outside the list: the (KC+1)-th candidate or an entry nobody kept
+    const unsigned long long last = __shfl_sync(0xffffffffu, key, KC);
+    const unsigned long long lb = bound < last ? bound : last;
+    if (lane < KC) {
+        const bool keep = idx != INT_MAX && key <= lb;
+        a.c.cval[base + lane] = keep ? dunkey(key) : __longlong_as_double(0x7ff0000000000000LL);
+        a.c.cidx[base + lane] = keep ? idx : -1;
+    }
+    if (lane == KC) a.c.cval[base + KC] = dunkey(lb);
+    if (lane == 0) {
+        a.c.fresh[row] = 1;
+        a.c.need[row] = 0;
+    }
+}
+
 // segments per entry for `total` entries on `nwarps` warps: enough items for every resident warp, at least SEG_MIN
 // columns each (even length keeps the 16-byte loads aligned)
 __device__ __forceinline__ int heavy_segments(const RArgs &a, int P, int total, int nwarps) {
@@ -732,42 +801,13 @@ __device__ __forceinline__ void heavy_items(const RArgs &a, int P, int e_lo, int
                     pi[t] = lane < S ? __ldcg(&pp->i[t]) : INT_MAX;
                 }
                 if (lane < S) kb = __ldcg(&pp->bound);
-                key = KEY_INF;
-                idx = INT_MAX;
-#pragma unroll
-                for (int sel = 0; sel < LC; ++sel) {
-                    const unsigned long long m = warp_min_u64(pk[0]);
-                    const int wl = __ffs(__ballot_sync(0xffffffffu, pk[0] == m)) - 1;
-                    const int wi = __shfl_sync(0xffffffffu, pi[0], wl);
-                    if (lane == sel) { key = m; idx = wi; }
-                    if (lane == wl) {
-#pragma unroll
-                        for (int t = 0; t + 1 < LC; ++t) { pk[t] = pk[t + 1]; pi[t] = pi[t + 1]; }
-                        pk[LC - 1] = KEY_INF;
-                        pi[LC - 1] = INT_MAX;
-                    }
-                }
-                const unsigned long long r1 = warp_min_u64(kb), r2 = warp_min_u64(pk[0]);
-                bound = r1 < r2 ? r1 : r2;
+                combine_partials(pk, pi, kb, key, idx, bound);
             }
         }
         if (finish) {
             const int row = e < P ? __ldcg(&a.pairs[e].j) : __ldcg(a.rq + e - P);
-            const size_t base = (size_t)row * LC;
-            // the smallest entry outside the list: the (KC+1)-th candidate or an entry nobody kept
-            const unsigned long long last = __shfl_sync(0xffffffffu, key, KC);
-            const unsigned long long lb = bound < last ? bound : last;
-            if (lane < KC) {
-                const bool keep = idx != INT_MAX && key <= lb;
-                a.c.cval[base + lane] = keep ? dunkey(key) : __longlong_as_double(0x7ff0000000000000LL);
-                a.c.cidx[base + lane] = keep ? idx : -1;
-            }
-            if (lane == KC) a.c.cval[base + KC] = dunkey(lb);
-            if (lane == 0) {
-                a.c.fresh[row] = 1;
-                a.c.need[row] = 0;
-                if (S > 1) a.seg_done[e] = 0;
-            }
+            store_list(a, row, key, idx, bound);
+            if (lane == 0 && S > 1) a.seg_done[e] = 0;
         }
     }
 }
@@ -845,6 +885,8 @@ __global__ void __launch_bounds__(HEAVY_THREADS, MINB) kr_heavy(RArgs a) {
 // or after max_rounds rounds.
 struct ChainCtl {
     int max_rounds, compact, diag;
+    int thin;   // > 0: thin rounds through the shared-memory staged builds / rescans (rows can be bulk-copied); rows per CTA
+    int cnum, cden;   // compact when nactive * cden <= ncols * cnum (live fraction at or below cnum / cden)
 };
 
 __device__ __forceinline__ void grid_barrier(unsigned int *bar, unsigned int &target) {
@@ -860,7 +902,7 @@ __device__ __forceinline__ void grid_barrier(unsigned int *bar, unsigned int &ta
     __syncthreads();
 }
 
-constexpr int CHAIN_THREADS = 512;
+constexpr int CHAIN_THREADS = 512, CHAIN_THREADS_C = CHAIN_THREADS;
 
 // out-of-line copies for the persistent kernel: three inlined phases do not fit 128 registers together
 __device__ __noinline__ void select_rows_ni(const RArgs &a, Ctr *ct, int r_first, int r_stride) { select_rows(a, ct, r_first, r_stride); }
@@ -872,13 +914,180 @@ __device__ __noinline__ void heavy_items_ni(const RArgs &a, int P, int e_lo, int
     heavy_items(a, P, e_lo, e_hi, S, gwarp, nwarps, false, nactive);
 }
 
+
+// ---- thin rounds (1-4 pairs, the chain phase): latency-optimised builds and rescans ---------------------------------
+// A thin round is a handful of rows: its time is the length of the chain of DEPENDENT memory round trips, not bytes.
+// heavy_items (index load -> four sequential load iterations per segment -> selection -> publish -> fence -> atomic ->
+// last arriver re-reads the partials -> list) is ~10 round trips per row, 22-26 us per phase measured.  Here:
+//   * every warp takes ONE segment and brings it (values, roles, sizes) into shared memory with cp.async.bulk -- one
+//     round trip whatever the segment length, no registers held -- and works it from there;
+//   * a row to rescan belongs to one CTA: its 16 warps combine their partial lists through shared memory behind a
+//     __syncthreads (no fence, no atomic, no second trip to L2);
+//   * a merged row is built by two CTAs (32 segments); their partial lists go to global memory and are combined one
+//     grid barrier later, at the start of the rescan phase, by a single warp (the lists are not needed before select).
+// Same arithmetic, same list semantics (the KC smallest live entries + a lower bound of the rest).
+#ifndef HC_THIN_SEG
+#define HC_THIN_SEG 512
+#endif
+constexpr int THIN_RESCAN_SEG = HC_THIN_SEG, THIN_BUILD_SEG = HC_THIN_SEG / 2;
+constexpr int THIN_WARP_BYTES = THIN_RESCAN_SEG * 12;   // per warp: SEG doubles + SEG ints (rescan) = 2 x SEG/2 doubles + 2 x SEG/2 ints (build)
+struct __align__(16) SPart {
+    unsigned long long k[LC];
+    int i[LC];
+    unsigned long long bound;
+};
+constexpr size_t CHAIN_SMEM = 16 * (size_t)THIN_WARP_BYTES + 16 * sizeof(unsigned long long) + 16 * sizeof(SPart);
+
+// all 16 warps of the CTA: exact rescan of `row` (call with CTA-uniform arguments; ends on a __syncthreads)
+__device__ __noinline__ void rescan_row_cta(const RArgs &a, int row, unsigned char *wbuf, unsigned long long *bar, unsigned &par,
+                                            SPart *sp) {
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, ncols = a.ncols;
+    constexpr int NW = CHAIN_THREADS_C / 32;
+    const double *Wr = a.W + (size_t)row * a.stride;
+    double *vals = (double *)wbuf;
+    int *roles = (int *)(wbuf + THIN_RESCAN_SEG * 8);
+    Min3 best;
+    best.init();
+    for (int base = 0; base < ncols; base += NW * THIN_RESCAN_SEG) {
+        const int span = min(NW * THIN_RESCAN_SEG, ncols - base);
+        const int seg_len = ((span + NW - 1) / NW + 3) & ~3;
+        const int c_lo = base + warp * seg_len, cnt = min(base + span, c_lo + seg_len) - c_lo;
+        if (cnt > 0) {   // warp-uniform
+            if (lane == 0) {
+                const uint32_t vb = (uint32_t)((cnt + 1) & ~1) * 8u, rb = (uint32_t)((cnt + 3) & ~3) * 4u;
+                mbar_expect_tx(bar, vb + rb);
+                tma_load_1d(vals, Wr + c_lo, vb, bar);
+                tma_load_1d(roles, a.c.role + c_lo, rb, bar);
+            }
+            mbar_wait(bar, par & 1u);
+            par ^= 1u;
+            for (int t = lane; t < cnt; t += 32) {
+                const int r = roles[t], c = c_lo + t;
+                if (r == ROLE_DEAD || (r >= 0 && !(r & 1)) || c == row) continue;
+                best.push(vals[t], c);
+            }
+            __syncwarp();   // the buffer has been read: the next bulk copy may overwrite it
+        }
+    }
+    unsigned long long key, bound;
+    int idx;
+    warp_select(dkey(best.m1), best.i1, dkey(best.m2), best.i2, dkey(best.m3), key, idx, bound);
+    if (lane < LC) { sp[warp].k[lane] = key; sp[warp].i[lane] = idx; }
+    if (lane == 0) sp[warp].bound = bound;
+    __syncthreads();
+    if (warp == 0) {
+        unsigned long long pk[LC], kb = KEY_INF;
+        int pi[LC];
+#pragma unroll
+        for (int t = 0; t < LC; ++t) {
+            pk[t] = lane < NW ? sp[lane].k[t] : KEY_INF;
+            pi[t] = lane < NW ? sp[lane].i[t] : INT_MAX;
+        }
+        if (lane < NW) kb = sp[lane].bound;
+        combine_partials(pk, pi, kb, key, idx, bound);
+        store_list(a, row, key, idx, bound);
+    }
+    __syncthreads();
+}
+
+// one warp: segment `seg` of 32 of the merged row of pair e (phase A of heavy_columns out of shared memory; the warp of
+// segment 0 also takes the pair x pair entries, phase B); its partial list goes to parts[e][seg]
+__device__ __noinline__ void build_thin_warp(const RArgs &a, int P, int e, int seg, unsigned char *wbuf, unsigned long long *bar,
+                                             unsigned &par) {
+    const int lane = threadIdx.x & 31, ncols = a.ncols, method = a.method;
+    const Pair p = ld_pair(a.pairs + e);
+    const double *Wi = a.W + (size_t)p.i * a.stride;
+    double *Wj = a.W + (size_t)p.j * a.stride;
+    // phase B operands (the other pairs of the round): requested first, used last
+    const bool doB = seg == 0 && lane < P && lane != e;
+    Pair pq = p;
+    double Ai = 0, Bi = 0, Aj = 0, Bj = 0;
+    if (doB) {
+        pq = ld_pair(a.pairs + lane);
+        Ai = __ldcg(Wi + pq.i); Bi = __ldcg(Wj + pq.i); Aj = __ldcg(Wi + pq.j); Bj = __ldcg(Wj + pq.j);
+    }
+    double *bA = (double *)wbuf, *bB = (double *)(wbuf + THIN_BUILD_SEG * 8);
+    int *bR = (int *)(wbuf + THIN_BUILD_SEG * 16), *bS = (int *)(wbuf + THIN_BUILD_SEG * 20);
+    Min3 best;
+    best.init();
+    for (int base = 0; base < ncols; base += 32 * THIN_BUILD_SEG) {
+        const int span = min(32 * THIN_BUILD_SEG, ncols - base);
+        const int seg_len = ((span + 31) / 32 + 3) & ~3;
+        const int c_lo = base + seg * seg_len, cnt = min(base + span, c_lo + seg_len) - c_lo;
+        if (cnt > 0) {   // warp-uniform
+            if (lane == 0) {
+                const uint32_t vb = (uint32_t)((cnt + 1) & ~1) * 8u, rb = (uint32_t)((cnt + 3) & ~3) * 4u;
+                mbar_expect_tx(bar, 2u * vb + 2u * rb);
+                tma_load_1d(bA, Wi + c_lo, vb, bar);
+                tma_load_1d(bB, Wj + c_lo, vb, bar);
+                tma_load_1d(bR, a.c.role + c_lo, rb, bar);
+                tma_load_1d(bS, a.c.size + c_lo, rb, bar);
+            }
+            mbar_wait(bar, par & 1u);
+            par ^= 1u;
+            for (int t = lane; t < cnt; t += 32) {
+                if (bR[t] != ROLE_FREE) continue;   // dead, or a side of some pair (phase B)
+                const double x = lw(method, bA[t], bB[t], p, (double)bS[t]);
+                Wj[c_lo + t] = x;
+                best.push(x, c_lo + t);
+            }
+            __syncwarp();
+        }
+    }
+    if (doB) {   // as the combine lambda of heavy_columns: "lower j first", both mirror entries bit-identical
+        const double ps = __dadd_rn(p.s1, p.s2);
+        const bool pf = p.j < pq.j;  // p merges first
+        Pair F, Sd;
+        F.m = pf ? p.m : pq.m; F.s1 = pf ? p.s1 : pq.s1; F.s2 = pf ? p.s2 : pq.s2; F.as = pf ? p.as : pq.as; F.at = pf ? p.at : pq.at;
+        Sd.m = pf ? pq.m : p.m; Sd.s1 = pf ? pq.s1 : p.s1; Sd.s2 = pf ? pq.s2 : p.s2; Sd.as = pf ? pq.as : p.as; Sd.at = pf ? pq.at : p.at;
+        F.i = F.j = Sd.i = Sd.j = 0;
+        const double t1 = lw(method, Ai, pf ? Bi : Aj, F, pf ? pq.s1 : p.s1);
+        const double t2 = lw(method, pf ? Aj : Bi, Bj, F, pf ? pq.s2 : p.s2);
+        const double x = lw(method, t1, t2, Sd, pf ? ps : __dadd_rn(pq.s1, pq.s2));
+        Wj[pq.j] = x;
+        best.push(x, pq.j);
+    }
+    unsigned long long key, bound;
+    int idx;
+    warp_select(dkey(best.m1), best.i1, dkey(best.m2), best.i2, dkey(best.m3), key, idx, bound);
+    Part *pt = &a.parts[(size_t)e * a.max_segs + seg];
+    if (lane < LC) { pt->k[lane] = key; pt->i[lane] = idx; }
+    if (lane == 0) pt->bound = bound;
+}
+
+// one warp, one grid barrier after build_thin_warp: the 32 partial lists of pair e -> candidate list of its merged row
+__device__ __noinline__ void build_thin_finish(const RArgs &a, int e) {
+    const int lane = threadIdx.x & 31;
+    const Part *pp = &a.parts[(size_t)e * a.max_segs + lane];
+    unsigned long long pk[LC], kb, key, bound;
+    int pi[LC], idx;
+#pragma unroll
+    for (int t = 0; t < LC; ++t) { pk[t] = __ldcg(&pp->k[t]); pi[t] = __ldcg(&pp->i[t]); }
+    kb = __ldcg(&pp->bound);
+    combine_partials(pk, pi, kb, key, idx, bound);
+    store_list(a, __ldcg(&a.pairs[e].j), key, idx, bound);
+}
+
 __global__ void __launch_bounds__(CHAIN_THREADS, 1) kr_chain(RArgs a, ChainCtl ctl) {
+    extern __shared__ __align__(128) unsigned char chain_smem[];
     RState *st = a.st;
-    const int tid = threadIdx.x, wpc = CHAIN_THREADS / 32;
+    const int tid = threadIdx.x, wpc = CHAIN_THREADS / 32, warp = tid >> 5;
     const int nwarps = (int)gridDim.x * wpc;
     // consecutive items go to different SMs
-    const int gwarp = (tid >> 5) * (int)gridDim.x + (int)blockIdx.x;
+    const int gwarp = warp * (int)gridDim.x + (int)blockIdx.x;
     const int gthread = gwarp * 32 + (tid & 31), gthreads = nwarps * 32;
+    // thin-round staging (ctl.thin): 12 KB and one mbarrier per warp, 16 partial lists per CTA
+    unsigned char *wbuf = chain_smem + (size_t)warp * THIN_WARP_BYTES;
+    unsigned long long *wbar = (unsigned long long *)(chain_smem + (size_t)wpc * THIN_WARP_BYTES) + warp;
+    SPart *sparts = (SPart *)(chain_smem + (size_t)wpc * THIN_WARP_BYTES + wpc * sizeof(unsigned long long));
+    unsigned wpar = 0;
+    if (ctl.thin) {
+        if ((tid & 31) == 0) {
+            mbar_init(wbar, 1);
+            asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+        }
+        __syncwarp();
+    }
     if (blockIdx.x == 0 && tid == 0) st->exit_reason = 0;
     unsigned int target = __ldcg(a.bar);   // all CTAs start from the same value: the previous launch ended on a barrier
     target -= target % gridDim.x;
@@ -887,7 +1096,7 @@ __global__ void __launch_bounds__(CHAIN_THREADS, 1) kr_chain(RArgs a, ChainCtl c
         Ctr *ct = &st->ctr[par], *nx = &st->ctr[par ^ 1];
         if (__ldcg(&st->done)) break;
         const int nactive = __ldcg(&st->nactive);
-        if (ctl.compact && a.ncols >= 256 && (long long)nactive * 2 <= a.ncols) {   // the host compacts and comes back
+        if (ctl.compact && a.ncols >= 256 && (long long)nactive * ctl.cden <= (long long)a.ncols * ctl.cnum) {   // the host compacts and comes back
             if (blockIdx.x == 0 && tid == 0) st->exit_reason = 1;
             break;
         }
@@ -898,7 +1107,15 @@ __global__ void __launch_bounds__(CHAIN_THREADS, 1) kr_chain(RArgs a, ChainCtl c
         const int P = __ldcg(&ct->P);
         const int tk = P <= 8 ? 0 : 3;   // thin rounds (the chain phase) and thick rounds are timed apart
         if (timing) { const unsigned long long t1 = globaltimer_ns(); st->phase_ns[tk] += t1 - t0; t0 = t1; st->phase_ns[6 + (tk ? 1 : 0)] += 1; }
-        {
+        // thin round: the merged rows are built by two whole CTAs each (the last ones of the grid), out of shared memory
+        const bool thin_build = ctl.thin && P >= 1 && P <= 4 && (int)gridDim.x >= 4 * P;
+        if (thin_build) {
+            const int rb = (int)gridDim.x - 1 - (int)blockIdx.x;
+            if (rb < 2 * P) build_thin_warp(a, P, rb >> 1, (rb & 1) * wpc + warp, wbuf, wbar, wpar);
+            if (ctl.diag && (tid & 31) == 0 && rb < 2 * P) atomicMax(&st->dbgmax[0], globaltimer_ns());
+            light_rows_ni(a, ct, P, gwarp, nwarps);
+            if (ctl.diag && (tid & 31) == 0 && gwarp * 32 < a.ncols) atomicMax(&st->dbgmax[1], globaltimer_ns());
+        } else {
             // the merged rows are built by the LAST warps of the grid, the light rows start at the first: in a thin
             // round no warp does both, so the two run side by side
             const int Sb = heavy_segments(a, P, P, nwarps / 2);
@@ -921,9 +1138,17 @@ __global__ void __launch_bounds__(CHAIN_THREADS, 1) kr_chain(RArgs a, ChainCtl c
         }
         const int total = P + __ldcg(&ct->qlen);
         {
-            const int Sr = heavy_segments(a, 0, total - P, nwarps);
-            heavy_items_ni(a, P, P, total, Sr, gwarp, nwarps, nactive);
-            if (ctl.diag && (tid & 31) == 0 && gwarp < (total - P) * Sr) atomicMax(&st->dbgmax[2], globaltimer_ns());
+            // the partial lists of the thin builds are complete (one barrier later): one warp per pair finishes them
+            if (thin_build && blockIdx.x == gridDim.x - 1 && warp < P) build_thin_finish(a, warp);
+            const int R = total - P;
+            if (ctl.thin && R <= ctl.thin * (int)gridDim.x) {   // few rows: one CTA per row, everything behind one memory round trip
+                for (int k = blockIdx.x; k < R; k += gridDim.x) rescan_row_cta(a, __ldcg(a.rq + k), wbuf, wbar, wpar, sparts);
+                if (ctl.diag && (tid & 31) == 0 && (int)blockIdx.x < R) atomicMax(&st->dbgmax[2], globaltimer_ns());
+            } else {
+                const int Sr = heavy_segments(a, 0, R, nwarps);
+                heavy_items_ni(a, P, P, total, Sr, gwarp, nwarps, nactive);
+                if (ctl.diag && (tid & 31) == 0 && gwarp < R * Sr) atomicMax(&st->dbgmax[2], globaltimer_ns());
+            }
             if (blockIdx.x == 0) {
                 retire_pairs(a, P, tid, CHAIN_THREADS);
                 __syncthreads();
@@ -1169,30 +1394,6 @@ struct __align__(16) RbWarp {
 template <int CH, int NST>
 constexpr size_t rb_smem_bytes() {
     return NST * sizeof(RbStage<CH>) + RB_WARPS * sizeof(RbWarp<CH>) + 2 * NST * sizeof(unsigned long long);
-}
-
-__device__ __forceinline__ uint32_t smem_u32(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
-__device__ __forceinline__ void mbar_init(unsigned long long *b, int count) {
-    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(b)), "r"(count));
-}
-__device__ __forceinline__ void mbar_expect_tx(unsigned long long *b, uint32_t bytes) {
-    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(b)), "r"(bytes) : "memory");
-}
-__device__ __forceinline__ void mbar_arrive(unsigned long long *b) {
-    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(b)) : "memory");
-}
-// (the suspend-time hint lets the hardware park the warp instead of spinning through the issue slots of the working warps)
-__device__ __forceinline__ void mbar_wait(unsigned long long *b, uint32_t parity) {
-    asm volatile(
-        "{\n\t.reg .pred p;\n\t"
-        "W_%=:\n\t"
-        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1, %2;\n\t"
-        "@!p bra W_%=;\n\t}"
-        ::"r"(smem_u32(b)), "r"(parity), "r"(20000u) : "memory");
-}
-__device__ __forceinline__ void tma_load_1d(void *dst, const void *src, uint32_t bytes, unsigned long long *bar) {
-    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
-                 ::"r"(smem_u32(dst)), "l"(src), "r"(bytes), "r"(smem_u32(bar)) : "memory");
 }
 
 // block 0: chunk0[k] = number of surviving columns whose OLD index is below k * RB_CH (oldidx is ascending)
@@ -1556,6 +1757,12 @@ extern "C" int hc_linkage_rounds(double *W, int32_t n, int method, void *workspa
     int cur = 0;          // which Cols set is live
     bool in_spare = false;  // whether the live matrix is in the spare buffer
     const bool compact = getenv("HC_ROUNDS_NOCOMPACT") == nullptr;
+    int cnum = 3, cden = 4;   // (measured at C3, chain phase + compactions: 1/2 44.0, 2/3 41.9, 3/4 40.5, 7/8 42.1 ms)
+    // compaction threshold: live columns / stored columns <= cnum / cden (HC_ROUNDS_COMPACT=num/den)
+    if (const char *e = getenv("HC_ROUNDS_COMPACT")) {
+        int x = 0, y = 0;
+        if (sscanf(e, "%d/%d", &x, &y) == 2 && x > 0 && y > x) { cnum = x; cden = y; }
+    }
     int batch = 8;  // rounds per host synchronisation (a round after the last merge is three empty launches)
     if (const char *e = getenv("HC_ROUNDS_BATCH")) batch = atoi(e) > 0 ? atoi(e) : 8;
     long long compactions = 0;
@@ -1746,11 +1953,14 @@ extern "C" int hc_linkage_rounds(double *W, int32_t n, int method, void *workspa
     bool persist = !trace && getenv("HC_ROUNDS_DIAG") == nullptr;
     if (const char *e = getenv("HC_ROUNDS_PERSIST")) persist = persist && atoi(e) != 0;
     int chain_grid = 0;
+    int thin_on = 3;   // rescans of a round go one row per CTA while there are at most thin_on rows per CTA
+    if (const char *e = getenv("HC_ROUNDS_THIN")) thin_on = atoi(e);
     if (persist) {
         int dev = 0, coop = 0, occ = 0;
         cudaGetDevice(&dev);
         cudaDeviceGetAttribute(&coop, cudaDevAttrCooperativeLaunch, dev);
-        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kr_chain, CHAIN_THREADS, 0);
+        if (cudaFuncSetAttribute(kr_chain, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)CHAIN_SMEM) != cudaSuccess) cudaGetLastError();
+        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kr_chain, CHAIN_THREADS, CHAIN_SMEM);
         chain_grid = sms;
         if (!coop || occ < 1) persist = false;
     }
@@ -1758,18 +1968,22 @@ extern "C" int hc_linkage_rounds(double *W, int32_t n, int method, void *workspa
         ChainCtl ctl;
         ctl.max_rounds = 1 << 20;
         ctl.compact = compact ? 1 : 0;
+        ctl.cnum = cnum;
+        ctl.cden = cden;
         ctl.diag = getenv("HC_ROUNDS_PHASES") != nullptr;
+        // bulk copies need 16-byte aligned rows (even stride); HC_ROUNDS_THIN=0 keeps the segment-per-warp path everywhere
+        ctl.thin = ((a.stride & 1) == 0 && (((uintptr_t)a.W) & 15) == 0) ? thin_on : 0;
         if (const char *e = getenv("HC_ROUNDS_CHAIN_MAX")) ctl.max_rounds = atoi(e) > 0 ? atoi(e) : 1;
         void *kargs[] = {(void *)&a, (void *)&ctl};
         kmark(6);
-        HC_CUDA_OK(cudaLaunchCooperativeKernel((const void *)kr_chain, dim3(chain_grid), dim3(CHAIN_THREADS), kargs, 0, stream));
+        HC_CUDA_OK(cudaLaunchCooperativeKernel((const void *)kr_chain, dim3(chain_grid), dim3(CHAIN_THREADS), kargs, CHAIN_SMEM, stream));
         kmark(-1);
         n_launches++;
         HC_CUDA_OK(cudaMemcpyAsync(&h, L.st, sizeof h, cudaMemcpyDeviceToHost, stream));
         HC_CUDA_OK(cudaStreamSynchronize(stream));
         kflush();
         if (h.done) break;
-        if (compact && a.ncols >= 256 && (long long)h.nactive * 2 <= a.ncols) {
+        if (compact && a.ncols >= 256 && (long long)h.nactive * cden <= (long long)a.ncols * cnum) {
             const int nnew = h.nactive;
             double *dst = in_spare ? W : L.spare;
             const long long stride_new = (nnew + 1) & ~1;
@@ -1811,7 +2025,7 @@ extern "C" int hc_linkage_rounds(double *W, int32_t n, int method, void *workspa
                     a.ncols, h.nactive, ms * 1e3f);
         }
         if (h.done) break;
-        if (compact && a.ncols >= 256 && (long long)h.nactive * 2 <= a.ncols) {
+        if (compact && a.ncols >= 256 && (long long)h.nactive * cden <= (long long)a.ncols * cnum) {
             const int nnew = h.nactive;
             double *dst = in_spare ? W : L.spare;
             const long long stride_new = (nnew + 1) & ~1;  // even: rows stay 16-byte aligned for the vector loads

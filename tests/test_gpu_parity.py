@@ -732,7 +732,7 @@ def test_linkage_rounds_hic_balanced_matrix(method):
 
 @pytest.mark.parametrize("env", [{}, {"HC_ROUNDS_NOCOMPACT": "1"}, {"HC_ROUNDS_BATCH": "1"}, {"HC_ROUNDS_BULK_SEGS": "32"},
                                  {"HC_ROUNDS_KTIME": "1"}, {"HC_ROUNDS_TRACE": "1"}, {"HC_ROUNDS_REBUILD": "16"},
-                                 {"HC_ROUNDS_REBUILD": "16", "HC_ROUNDS_REBUILD_V": "1"},
+                                 {"HC_ROUNDS_REBUILD": "16", "HC_ROUNDS_REBUILD_V": "1"}, {"HC_ROUNDS_THIN": "0"}, {"HC_ROUNDS_COMPACT": "1/2"},
                                  {"HC_ROUNDS_REBUILD": "0"}, {"HC_ROUNDS_PERSIST": "0"}, {"HC_ROUNDS_CHAIN_MAX": "3"},
                                  {"HC_ROUNDS_PERSIST": "0", "HC_ROUNDS_KTIME": "1"}])
 def test_linkage_rounds_compaction_and_batching_do_not_change_results(env, monkeypatch):
@@ -772,7 +772,9 @@ def test_linkage_rounds_bulk_rebuild(n, method, monkeypatch):
         out[flag + version] = (Z, st)
     assert np.array_equal(out["02"][0], out["162"][0]) and np.array_equal(out["02"][0], out["161"][0])
     out = {"0": out["02"], "16": out["162"]}
-    assert out["16"][1]["rounds"] == out["0"][1]["rounds"] and out["16"][1]["compactions"] >= 1
+    # (which entries a candidate list keeps depends on how a row was cut into segments, so a pair can be found a round
+    # earlier or later on another path: the records are identical, the round count may differ by one or two)
+    assert abs(out["16"][1]["rounds"] - out["0"][1]["rounds"]) <= 2 and out["16"][1]["compactions"] >= 1
     _same_tree(out["16"][0], O.linkage_fastcluster(y, method), rtol=1e-12)
 
 
