@@ -471,9 +471,12 @@ __device__ __forceinline__ void light_rows_thin(const RArgs &a, Ctr *ct, int P, 
         int nj[4];
 #pragma unroll
         for (int q = 0; q < 4; ++q) {
-            nv[q] = lw(method, A[q], B[q], pr[q], v);
+            nv[q] = 0.0;
             nj[q] = pr[q].j;
-            if (q < P) Wr[pr[q].j] = nv[q];
+            if (q < P) {   // (uniform: a round with one pair does one Lance-Williams step per row, not four)
+                nv[q] = lw(method, A[q], B[q], pr[q], v);
+                Wr[pr[q].j] = nv[q];
+            }
         }
         a.c.fresh[row] = 0;  // the bound is no longer the exact next entry
         if (!need) {
