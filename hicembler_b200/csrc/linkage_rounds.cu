@@ -93,7 +93,7 @@ struct RArgs {
     int max_segs;
     double *W;
     long long stride;
-    int ncols, n, method, diag, bulk_segs;
+    int ncols, n, method, diag, bulk_segs, light8;
     double margin;
     Cols c;
     Pair *pairs;
@@ -514,6 +514,104 @@ __device__ __forceinline__ void light_rows_thin(const RArgs &a, Ctr *ct, int P, 
     }
 }
 
+// The same thin-round update with EIGHT lanes per row (four rows per warp, two rows per group in flight): the one-lane
+// version is a serial chain of ~700 dependent instructions per row (four Lance-Williams steps, a seven-fold insertion
+// sort) with 48 registers of pair data and 220 bytes of spills.  Here lane s of a group holds candidate s of the row's
+// list (lane 7 the bound) and, for s < P, pair s of the round: the steps run side by side, a merged candidate takes
+// its new column and value from the pair's lane by shuffle, and the list is re-sorted by rank (seven shuffles).
+// Same list as light_rows_thin: an i-side candidate is dropped when the j side of its pair is listed too, otherwise it
+// follows the cluster to column j; entries above the bound leave; order = ascending (value, column).
+__device__ __forceinline__ void light_rows_thin8(const RArgs &a, Ctr *ct, int P, int gwarp, int nwarps) {
+    const int lane = threadIdx.x & 31, sub = lane & 7, gbase = lane & ~7, method = a.method;
+    const double INF = __longlong_as_double(0x7ff0000000000000LL);
+    const int ngroups = nwarps * 4;
+    Pair pr = ld_pair(a.pairs + (sub < P ? sub : 0));
+    for (int r0 = gwarp * 4 + (lane >> 3); r0 - (lane >> 3) < a.ncols; r0 += 2 * ngroups) {   // warp-uniform trip count
+        int row[2];
+        bool act[2], need[2];
+        double cv[2], A[2], B[2], v[2];
+        int ci[2], rci[2], role[2];
+#pragma unroll
+        for (int h = 0; h < 2; ++h) {
+            row[h] = r0 + h * ngroups;
+            const bool in = row[h] < a.ncols;
+            const size_t base = (size_t)(in ? row[h] : 0) * LC;
+            const double *Wr = a.W + (size_t)(in ? row[h] : 0) * a.stride;
+            role[h] = in ? __ldcg(a.c.role + row[h]) : ROLE_DEAD;
+            need[h] = in && __ldcg(a.c.need + row[h]) != 0;
+            v[h] = in ? (double)__ldcg(a.c.size + row[h]) : 1.0;
+            cv[h] = in ? __ldcg(a.c.cval + base + sub) : INF;                   // lane 7: the bound of the unlisted entries
+            ci[h] = (in && sub < KC) ? __ldcg(a.c.cidx + base + sub) : -1;
+            A[h] = (in && sub < P) ? __ldcg(Wr + pr.i) : 0.0;
+            B[h] = (in && sub < P) ? __ldcg(Wr + pr.j) : 0.0;
+        }
+#pragma unroll
+        for (int h = 0; h < 2; ++h) rci[h] = ci[h] >= 0 ? __ldcg(a.c.role + ci[h]) : -1;
+        bool push_row[2] = {false, false};
+#pragma unroll
+        for (int h = 0; h < 2; ++h) {
+            act[h] = role[h] == ROLE_FREE;      // group-uniform
+            double nv = 0.0;
+            if (act[h] && sub < P) {
+                nv = lw(method, A[h], B[h], pr, v[h]);
+                a.W[(size_t)row[h] * a.stride + pr.j] = nv;
+            }
+            if (act[h] && sub == 0) a.c.fresh[row[h]] = 0;   // the bound is no longer the exact next entry
+            // candidates whose cluster merges this round follow it to column j with the new value (all lanes shuffle)
+            const bool merging = act[h] && !need[h] && ci[h] >= 0 && rci[h] >= 0;
+            const int src = gbase | (merging ? (rci[h] >> 1) : 0);
+            const int pj = __shfl_sync(0xffffffffu, pr.j, src);
+            const double pv = __shfl_sync(0xffffffffu, nv, src);
+            const unsigned hit_mask = __ballot_sync(0xffffffffu, merging) & (0xffu << gbase);
+            bool jside_listed = false;   // is column pj (the j side) one of the ORIGINAL candidates of the row?
+#pragma unroll
+            for (int t = 0; t < KC; ++t) {
+                const int oc = __shfl_sync(0xffffffffu, ci[h], gbase | t);
+                jside_listed |= (t != sub) && oc == pj;
+            }
+            int nci = ci[h];
+            double ncv = cv[h];
+            if (merging) {
+                if ((rci[h] & 1) == 0 && jside_listed) nci = -1;   // both sides were listed: keep the j side only
+                else { nci = pj; ncv = pv; }
+            }
+            const double lb = __shfl_sync(0xffffffffu, cv[h], gbase | KC);
+            const bool keep = sub < KC && nci >= 0 && ncv <= lb;
+            // rank among the kept entries in (value, column) order; the others fill the tail with (inf, -1)
+            int rank = 0, below_unkept = 0;
+            const unsigned keep_mask = (__ballot_sync(0xffffffffu, keep) >> gbase) & 0x7fu;
+#pragma unroll
+            for (int t = 0; t < KC; ++t) {
+                const double ov = __shfl_sync(0xffffffffu, ncv, gbase | t);
+                const int oi = __shfl_sync(0xffffffffu, nci, gbase | t);
+                const bool ok = (keep_mask >> t) & 1u;
+                if (t != sub && ok && lex_lt(ov, oi, ncv, nci)) rank++;
+                if (t < sub && !ok) below_unkept++;
+            }
+            const int count = __popc(keep_mask);
+            if (act[h] && !need[h] && hit_mask && sub < KC) {
+                const size_t base = (size_t)row[h] * LC;
+                const int slot = keep ? rank : count + below_unkept;
+                a.c.cval[base + slot] = keep ? ncv : INF;
+                a.c.cidx[base + slot] = keep ? nci : -1;
+            }
+            push_row[h] = act[h] && sub == 0 && (need[h] || (hit_mask && count == 0));   // an empty list asks for a rescan
+        }
+        // one queue reservation per warp
+#pragma unroll
+        for (int h = 0; h < 2; ++h) {
+            const unsigned m = __ballot_sync(0xffffffffu, push_row[h]);
+            if (m) {
+                const int leader = __ffs(m) - 1;
+                int slot0 = 0;
+                if (lane == leader) slot0 = atomicAdd(&ct->qlen, __popc(m));
+                slot0 = __shfl_sync(0xffffffffu, slot0, leader);
+                if (push_row[h]) a.rq[slot0 + __popc(m & ((1u << lane) - 1u))] = row[h];
+            }
+        }
+    }
+}
+
 __global__ void __launch_bounds__(LIGHT_THREADS) kr_light(RArgs a) {
     RState *st = a.st;
     if (st->done) return;
@@ -909,8 +1007,10 @@ constexpr int CHAIN_THREADS = 512, CHAIN_THREADS_C = CHAIN_THREADS;
 
 // out-of-line copies for the persistent kernel: three inlined phases do not fit 128 registers together
 __device__ __noinline__ void select_rows_ni(const RArgs &a, Ctr *ct, int r_first, int r_stride) { select_rows(a, ct, r_first, r_stride); }
+__device__ __noinline__ void light_rows_thin8_ni(const RArgs &a, Ctr *ct, int P, int gwarp, int nwarps) { light_rows_thin8(a, ct, P, gwarp, nwarps); }
 __device__ __noinline__ void light_rows_ni(const RArgs &a, Ctr *ct, int P, long long warp0, long long nwarps) {
-    if (P >= 1 && P <= 4) light_rows_thin(a, ct, P, (int)warp0 * 32 + (threadIdx.x & 31), (int)nwarps * 32);
+    if (P >= 1 && P <= 4 && a.light8) light_rows_thin8_ni(a, ct, P, (int)warp0, (int)nwarps);
+    else if (P >= 1 && P <= 4) light_rows_thin(a, ct, P, (int)warp0 * 32 + (threadIdx.x & 31), (int)nwarps * 32);
     else light_rows(a, ct, P, warp0, nwarps);
 }
 __device__ __noinline__ void heavy_items_ni(const RArgs &a, int P, int e_lo, int e_hi, int S, int gwarp, int nwarps, int nactive) {
@@ -925,7 +1025,8 @@ __device__ __noinline__ void heavy_items_ni(const RArgs &a, int P, int e_lo, int
 //   * every warp takes ONE segment and brings it (values, roles, sizes) into shared memory with cp.async.bulk -- one
 //     round trip whatever the segment length, no registers held -- and works it from there;
 //   * a row to rescan belongs to one CTA: its 16 warps combine their partial lists through shared memory behind a
-//     __syncthreads (no fence, no atomic, no second trip to L2);
+//     __syncthreads (no fence, no atomic, no second trip to L2); (a second staging buffer per warp, with the next row's
+//     copy in flight during the scan, measured SLOWER: 35.8 vs 33.6 ms -- the shared memory it takes from L1 costs more)
 //   * a merged row is built by two CTAs (32 segments); their partial lists go to global memory and are combined one
 //     grid barrier later, at the start of the rescan phase, by a single warp (the lists are not needed before select).
 // Same arithmetic, same list semantics (the KC smallest live entries + a lower bound of the rest).
@@ -1752,6 +1853,8 @@ extern "C" int hc_linkage_rounds(double *W, int32_t n, int method, void *workspa
     a.max_segs = MAX_SEGS;
     a.bulk_segs = 1;  // (32 measured slower at C3: 17.8 vs 13.8 ms in the largest round; kept for experiments)
     if (const char *e = getenv("HC_ROUNDS_BULK_SEGS")) a.bulk_segs = atoi(e);
+    a.light8 = 1;   // thin rounds of the persistent kernel: eight lanes per row (HC_ROUNDS_LIGHT8=0: one lane per row)
+    if (const char *e = getenv("HC_ROUNDS_LIGHT8")) a.light8 = atoi(e) != 0;
     a.margin = MARGIN;
     double height_tol = HEIGHT_TOL;
     if (const char *e = getenv("HC_ROUNDS_MARGIN")) a.margin = atof(e);
