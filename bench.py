@@ -311,11 +311,12 @@ def run_ours(args, cfg, rank, world, local_rank):
                      peak_source=peak_src)
     if dominant == "linkage" and lst.get("engine") == "rounds" and kernel_us and kernel_us.get("rebuild"):
         # dominant KERNEL of the dominant stage = kb_rebuild2 (the bulk rounds: merge + compact in one pass over the
-        # matrix): all its launches of one step; achieved = algorithmic bytes of those launches (8 B per live column
-        # of a free row, 24 B per live column of a merged row -- counted by the kernel's own retire step) / their summed
-        # CUDA-event durations.  The chain phase (kr_chain) is latency-bound by construction and reported next to it.
+        # matrix): all its launches of one step; achieved = algorithmic bytes of those launches (counted by the kernel's
+        # own retire step) / their summed CUDA-event durations.  The chain phase (kr_chain) is latency-bound by construction and reported next to it.
         rb_ms = kernel_us["rebuild"] * 1e-3
-        b = 8.0 * lst["bulk_rescan_cols"] + 24.0 * lst["bulk_build_cols"]
+        # algorithmic bytes of the pass = the old rows read once (one row for a free new row, both rows of the pair for a
+        # merged one) + the new matrix written once; 8 B per cell.  The ncu DRAM pass (`traffic`) measures the same number.
+        b = 8.0 * (lst["bulk_rescan_cols"] + 2.0 * lst["bulk_build_cols"] + lst.get("bulk_new_cells", 0))
         a_ = b / (rb_ms * 1e-3) / 1e9
         launches = max(1, lst["bulk_rounds"])
         ncu = NCU_TRAFFIC.get(args.config, {}).get("kb_rebuild2")

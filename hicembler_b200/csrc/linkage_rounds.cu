@@ -1738,6 +1738,7 @@ __global__ void kb_retire(RArgs a, int nnew) {
     st->stats[4] += nfree * (unsigned long long)P;
     st->stats[7] += nfree * oldcols;
     st->stats[8] += (unsigned long long)P * oldcols;
+    st->stats[9] += (unsigned long long)nnew * (unsigned long long)nnew;   // cells of the new matrix written by the pass
     st->n_done += P;
     st->nactive -= P;
     st->stats[5] += ct->deferred;
@@ -1973,6 +1974,8 @@ extern "C" int hc_linkage_rounds(double *W, int32_t n, int method, void *workspa
     int rebuild_min = 2048;  // columns: below this a round is launch latency, not traffic
     if (const char *e = getenv("HC_ROUNDS_REBUILD")) rebuild_min = atoi(e) > 0 ? atoi(e) : INT_MAX;
     long long rebuilds = 0;
+    int bulk_div = 5;   // a round is a bulk round while pairs * bulk_div >= columns (HC_ROUNDS_BULK_DIV)
+    if (const char *e = getenv("HC_ROUNDS_BULK_DIV")) bulk_div = atoi(e) > 0 ? atoi(e) : 5;
     int rebuild_v = 2, rb_cfg = 0;   // rb_cfg: 0 = chunks of 256 old columns, 2 stages; 1 = 128 columns, 4 stages
     if (const char *e = getenv("HC_ROUNDS_REBUILD_V")) rebuild_v = atoi(e);
     if (const char *e = getenv("HC_ROUNDS_RB_CFG")) rb_cfg = atoi(e);
@@ -2000,7 +2003,7 @@ extern "C" int hc_linkage_rounds(double *W, int32_t n, int method, void *workspa
         HC_CUDA_OK(cudaStreamSynchronize(stream));
         const int nnew = h.nactive - h.ctr[0].P;
         const long long stride_new = (nnew + 1) & ~1;
-        const bool bulk = !h.done && !h.ambiguous && (long long)h.ctr[0].P * 5 >= a.ncols && nnew >= 2 &&
+        const bool bulk = !h.done && !h.ambiguous && (long long)h.ctr[0].P * bulk_div >= a.ncols && nnew >= 2 &&
                           (in_spare || (size_t)nnew * stride_new <= L.spare_elems);
         if (!bulk) {            // finish this round the ordinary way and go on in batches
             light_heavy();
@@ -2218,6 +2221,7 @@ extern "C" int hc_linkage_rounds(double *W, int32_t n, int method, void *workspa
         h_stats[19] = (int64_t)h.stats[8];   // ... and over its merged rows
         h_stats[20] = rebuilds;
         h_stats[21] = persist ? 1 : 0;
+        h_stats[22] = (int64_t)h.stats[9];   // bulk rounds: cells of the new matrices written
     }
     if (uncertified) return HC_EAMBIGUOUS;
     if (near) {

@@ -420,7 +420,7 @@ def linkage_rounds(W, method="ward", nan_flags=None, workspace=None):
               pending_near_ties=stats[8], deferred_rescans=stats[9],
               kernel_us=dict(select=stats[10], light=stats[11], heavy=stats[12], compaction=stats[13],
                              initial_scan=stats[14], rebuild=stats[16], chain=stats[17]), launches=stats[15],
-              bulk_rescan_cols=stats[18], bulk_build_cols=stats[19], bulk_rounds=stats[20], persistent=bool(stats[21]),
+              bulk_rescan_cols=stats[18], bulk_build_cols=stats[19], bulk_rounds=stats[20], persistent=bool(stats[21]), bulk_new_cells=stats[22],
               certified=(rc == _lib.HC_OK))
     if rc == _lib.HC_EAMBIGUOUS:
         st["reason"] = _lib.last_error()

@@ -302,7 +302,7 @@ int hc_linkage_finish(int32_t n, int method, void *workspace, size_t workspace_b
  * that path off), [17] microseconds in kr_chain (the persistent kernel that runs all later rounds, many per
  * cooperative launch; HC_ROUNDS_PERSIST=0 switches it off), [18] / [19] live columns summed over the free / merged
  * rows of the bulk rounds (the algorithmic bytes of kb_rebuild are 8 x [18] + 24 x [19]), [20] bulk rounds,
- * [21] 1 when the persistent kernel ran. */
+ * [21] 1 when the persistent kernel ran, [22] cells of the new matrices written by the bulk rounds. */
 size_t hc_linkage_rounds_workspace_bytes(int32_t n);
 int hc_linkage_rounds(double *W, int32_t n, int method, void *workspace, size_t workspace_bytes,
                       double *h_Z, int64_t *h_stats, void *stream);
