@@ -1725,6 +1725,269 @@ __global__ void __launch_bounds__((RB_WARPS + 1) * 32, 2) kb_rebuild2(RArgs a, C
     }
 }
 
+// ---- kb_rebuild3: kb_rebuild2 driven by per-chunk column LISTS ---------------------------------------------------------
+// ncu on kb_rebuild2: 5.3 warp instructions per new cell, 60 % of the issue slots -- every row re-derives, for every chunk, what
+// depends on the chunk alone: the role of each column (descriptor load + test), the queue of its pair columns (ballot, popc,
+// shared-memory append) and the offsets into the staged old rows.  kb_lists does that ONCE per round: for every chunk of 256
+// old columns the list of its free new columns and the list of its pair new columns (offset in the new chunk | offset in the
+// old chunk << 8, cluster size / i-side column, pair data), padded to 8 entries so that every slice can be bulk-copied.  The
+// producer warp stages the chunk's slices next to the old rows; a consumer warp runs two dense loops over them.  Same
+// operands and operation order as kb_rebuild / kb_rebuild2: bit-identical matrix and merge records.
+constexpr int R3_CH = 256, R3_LIST = R3_CH + 8;
+struct __align__(16) R3Stage {
+    unsigned short fTO[R3_LIST], pTO[R3_LIST];   // free / pair columns: t | off << 8
+    int fSize[R3_LIST], pW[R3_LIST];              // cluster size of a free column; old column of the i side of a pair column
+    double pP[3][R3_LIST];                        // pair data of the pair columns: m, s1, s2 (ward) / as, at (average)
+    double rows[RB_WARPS][2][R3_CH];              // old row chunk: [0] the row itself / j side, [1] the i side (merged rows)
+};
+struct __align__(16) R3Warp {
+    double sOut[R3_CH];
+};
+constexpr size_t R3_SMEM = 2 * sizeof(R3Stage) + RB_WARPS * sizeof(R3Warp) + 4 * sizeof(unsigned long long);
+
+struct R3Lists {
+    int4 *ctab;                 // [nch + 1]: {first new column, first free-list entry, free columns, first pair-list entry} of a chunk
+    unsigned short *fTO, *pTO;  // [cap]
+    int *fSize, *pW;            // [cap]
+    double *pP;                 // [5][pstride]: m, s1, s2, as, at per pair-list entry
+    long long pstride;
+};
+
+// one block: chunk table, then the lists (a thread per chunk; chunks of a round: <= ncols / 256)
+__global__ void __launch_bounds__(1024) kb_lists(const int *oldidx, const int4 *desc, const double *colp, long long cstride, int nnew,
+                                                  int ncols, R3Lists L) {
+    __shared__ int s_total[2];
+    const int nch = (ncols + R3_CH - 1) / R3_CH;
+    // first new column of every chunk (oldidx is ascending), free / pair counts
+    for (int k = threadIdx.x; k <= nch; k += blockDim.x) {
+        const int key = k * R3_CH;
+        int lo = 0, hi = nnew;
+        while (lo < hi) {
+            const int mid = (lo + hi) >> 1;
+            if (oldidx[mid] < key) lo = mid + 1; else hi = mid;
+        }
+        L.ctab[k].x = lo;
+    }
+    __syncthreads();
+    for (int k = threadIdx.x; k < nch; k += blockDim.x) {
+        const int n0 = L.ctab[k].x, n1 = L.ctab[k + 1].x;
+        int np = 0;
+        for (int c = n0; c < n1; ++c) np += desc[c].y >= 0;
+        L.ctab[k].z = (n1 - n0) - np;   // free columns
+        L.ctab[k].w = np;               // (pair columns for now; replaced by the list start below)
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) {   // padded starts (multiples of 8 entries: 16-byte aligned slices of the 2-byte lists)
+        int f = 0, q = 0;
+        for (int k = 0; k < nch; ++k) {
+            const int nf = L.ctab[k].z, np = L.ctab[k].w;
+            L.ctab[k].y = f;
+            L.ctab[k].w = q;
+            f += (nf + 7) & ~7;
+            q += (np + 7) & ~7;
+        }
+        L.ctab[nch].y = f; L.ctab[nch].z = 0; L.ctab[nch].w = q;
+        s_total[0] = f; s_total[1] = q;
+    }
+    __syncthreads();
+    for (int k = threadIdx.x; k < nch; k += blockDim.x) {
+        const int4 ct = L.ctab[k];
+        const int n0 = ct.x, n1 = L.ctab[k + 1].x, o0 = k * R3_CH;
+        int f = ct.y, q = ct.w;
+        for (int c = n0; c < n1; ++c) {
+            const int4 d = desc[c];
+            const unsigned short to = (unsigned short)((c - n0) | ((d.x - o0) << 8));
+            if (d.y < 0) {
+                L.fTO[f] = to;
+                L.fSize[f] = d.z;
+                ++f;
+            } else {
+                L.pTO[q] = to;
+                L.pW[q] = d.w;
+                for (int a = 0; a < 5; ++a) L.pP[a * L.pstride + q] = colp[a * cstride + c];
+                ++q;
+            }
+        }
+    }
+}
+
+template <int METHOD>
+__global__ void __launch_bounds__((RB_WARPS + 1) * 32, 2) kb_rebuild3(RArgs a, Cols d, const int4 *__restrict__ desc,
+                                                                       const double *__restrict__ colp, long long cstride,
+                                                                       R3Lists L, const int *__restrict__ rowlist,
+                                                                       double *__restrict__ Wn, long long stride_n, int nnew) {
+    extern __shared__ __align__(128) unsigned char rb_smem[];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    R3Stage *stages = (R3Stage *)rb_smem;
+    R3Warp *wsm = (R3Warp *)(rb_smem + 2 * sizeof(R3Stage));
+    unsigned long long *full = (unsigned long long *)(rb_smem + 2 * sizeof(R3Stage) + RB_WARPS * sizeof(R3Warp));
+    unsigned long long *empty = full + 2;
+    if (threadIdx.x == 0) {
+        for (int s = 0; s < 2; ++s) { mbar_init(&full[s], 1); mbar_init(&empty[s], RB_WARPS); }
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    __syncthreads();
+    constexpr bool NEED_S = METHOD == M_WARD, NEED_A = METHOD == M_AVERAGE;
+    constexpr int NP = NEED_S ? 3 : (NEED_A ? 2 : 0), PBASE = NEED_A ? 3 : 0;   // pair-data arrays staged per chunk
+    const int ncols = a.ncols, ngroups = (nnew + RB_WARPS - 1) / RB_WARPS, nch = (ncols + R3_CH - 1) / R3_CH;
+    unsigned it = 0;   // stage sequence number: slot = it & 1, phase = it >> 1
+
+    if (warp == RB_WARPS) {   // ---- producer warp: lane l < RB_WARPS feeds row l of the group, the next lanes the lists
+        for (int g = blockIdx.x; g < ngroups; g += gridDim.x) {
+            const double *Wj = nullptr, *Wi = nullptr;
+            bool have = false, prow = false;
+            if (lane < RB_WARPS && g * RB_WARPS + lane < nnew) {
+                const int4 dr = __ldg(desc + __ldg(rowlist + g * RB_WARPS + lane));
+                have = true;
+                prow = dr.y >= 0;
+                Wj = a.W + (size_t)dr.x * a.stride;
+                Wi = a.W + (size_t)dr.w * a.stride;
+            }
+            const bool any_prow = __any_sync(0xffffffffu, prow);   // (free rows never read the cluster sizes)
+            for (int k = 0; k < nch; ++k, ++it) {
+                const int slot = it & 1;
+                if (it >= 2) mbar_wait(&empty[slot], ((it >> 1) - 1) & 1u);
+                R3Stage *st = stages + slot;
+                const int o0 = k * R3_CH, cnt = min(R3_CH, ncols - o0);
+                const uint32_t rbytes = (uint32_t)((cnt + 1) & ~1) * 8u;   // (stride is even: the pad element belongs to the row)
+                const int4 ct = __ldg(L.ctab + k);
+                const int nf8 = (ct.z + 7) & ~7, np8 = (((__ldg(&L.ctab[k + 1].x) - ct.x) - ct.z) + 7) & ~7;
+                const int li = lane - RB_WARPS;   // list copies: 0 fTO, 1 fSize, 2 pTO, 3 pW, 4.. pP
+                uint32_t mine = 0;
+                if (have) mine = prow ? 2u * rbytes : rbytes;
+                else if (li == 0) mine = (uint32_t)nf8 * 2u;
+                else if (li == 1 && any_prow) mine = (uint32_t)nf8 * 4u;
+                else if (li == 2) mine = (uint32_t)np8 * 2u;
+                else if (li == 3) mine = (uint32_t)np8 * 4u;
+                else if (li >= 4 && li < 4 + NP) mine = (uint32_t)np8 * 8u;
+                const uint32_t total = __reduce_add_sync(0xffffffffu, mine);
+                if (lane == 0) mbar_expect_tx(&full[slot], total);
+                __syncwarp();
+                if (have) {
+                    tma_load_1d(st->rows[lane][0], Wj + o0, rbytes, &full[slot]);
+                    if (prow) tma_load_1d(st->rows[lane][1], Wi + o0, rbytes, &full[slot]);
+                } else if (mine) {
+                    if (li == 0) tma_load_1d(st->fTO, L.fTO + ct.y, mine, &full[slot]);
+                    else if (li == 1) tma_load_1d(st->fSize, L.fSize + ct.y, mine, &full[slot]);
+                    else if (li == 2) tma_load_1d(st->pTO, L.pTO + ct.w, mine, &full[slot]);
+                    else if (li == 3) tma_load_1d(st->pW, L.pW + ct.w, mine, &full[slot]);
+                    else tma_load_1d(st->pP[li - 4], L.pP + (size_t)(PBASE + li - 4) * L.pstride + ct.w, mine, &full[slot]);
+                }
+            }
+        }
+        return;
+    }
+
+    // ---- consumer warps: one new row each
+    R3Warp *ws = wsm + warp;
+    const double INF = __longlong_as_double(0x7ff0000000000000LL);
+    for (int g = blockIdx.x; g < ngroups; g += gridDim.x) {
+        const bool have = g * RB_WARPS + warp < nnew;
+        const int rn = have ? __ldg(rowlist + g * RB_WARPS + warp) : -1;
+        int4 dr = make_int4(0, ROLE_FREE, 1, 0);
+        if (have) dr = __ldg(desc + rn);
+        const bool prow = dr.y >= 0;
+        Pair p;
+        p.i = dr.w;
+        p.j = dr.x;
+        p.m = p.s1 = p.s2 = p.as = p.at = 0.0;
+        if (prow) {
+            p.m = __ldg(colp + rn); p.s1 = __ldg(colp + cstride + rn); p.s2 = __ldg(colp + 2 * cstride + rn);
+            p.as = __ldg(colp + 3 * cstride + rn); p.at = __ldg(colp + 4 * cstride + rn);
+        }
+        const double *Wj = a.W + (size_t)dr.x * a.stride, *Wi = a.W + (size_t)dr.w * a.stride;   // (i sides before a chunk)
+        const double vR = (double)dr.z, ps = __dadd_rn(p.s1, p.s2);
+        double *dst = Wn + (size_t)(have ? rn : 0) * stride_n;
+        Min3 best;
+        best.init();
+        for (int k = 0; k < nch; ++k, ++it) {
+            const int slot = it & 1;
+            const R3Stage *st = stages + slot;
+            const int4 ct = __ldg(L.ctab + k);
+            const int o0 = k * R3_CH, n0 = ct.x, cn = __ldg(&L.ctab[k + 1].x) - n0, nf = ct.z, np = cn - nf;
+            mbar_wait(&full[slot], (it >> 1) & 1u);
+            if (have) {
+                const double *sJ = st->rows[warp][0], *sI = st->rows[warp][1];
+                // pass 1: free columns (copy, or one Lance-Williams step for a merged row)
+                if (!prow) {
+                    for (int u = lane; u < nf; u += 32) {
+                        const int to = st->fTO[u], t = to & 255, c = n0 + t;
+                        double x = sJ[to >> 8];
+                        if (c == rn) x = INF;
+                        else best.push(x, c);
+                        ws->sOut[t] = x;
+                    }
+                } else {
+                    for (int u = lane; u < nf; u += 32) {
+                        const int to = st->fTO[u], t = to & 255, off = to >> 8, c = n0 + t;
+                        double x = lw(METHOD, sI[off], sJ[off], p, (double)st->fSize[u]);
+                        if (c == rn) x = INF;
+                        else best.push(x, c);
+                        ws->sOut[t] = x;
+                    }
+                }
+                // pass 2: the surviving (j side) columns of the round's pairs
+                for (int u = lane; u < np; u += 32) {
+                    const int to = st->pTO[u], t = to & 255, off = to >> 8, c = n0 + t;
+                    const int wcol = st->pW[u], ioff = wcol - o0;
+                    Pair pq;
+                    pq.i = wcol; pq.j = o0 + off;
+                    pq.m = pq.s1 = pq.s2 = pq.as = pq.at = 0.0;
+                    if (NEED_S) { pq.m = st->pP[0][u]; pq.s1 = st->pP[1][u]; pq.s2 = st->pP[2][u]; }
+                    if (NEED_A) { pq.as = st->pP[0][u]; pq.at = st->pP[1][u]; }
+                    const double Bj = sJ[off], Bi = ioff >= 0 ? sJ[ioff] : __ldg(Wj + wcol);
+                    double x;
+                    if (!prow) x = lw(METHOD, Bi, Bj, pq, vR);                 // as kr_light
+                    else {                                                     // as phase B of kr_heavy
+                        const double Aj = sI[off], Ai = ioff >= 0 ? sI[ioff] : __ldg(Wi + wcol);
+                        const bool pf = p.j < pq.j;  // p merges first
+                        Pair F, Sd;
+                        F.m = pf ? p.m : pq.m; F.s1 = pf ? p.s1 : pq.s1; F.s2 = pf ? p.s2 : pq.s2; F.as = pf ? p.as : pq.as; F.at = pf ? p.at : pq.at;
+                        Sd.m = pf ? pq.m : p.m; Sd.s1 = pf ? pq.s1 : p.s1; Sd.s2 = pf ? pq.s2 : p.s2; Sd.as = pf ? pq.as : p.as; Sd.at = pf ? pq.at : p.at;
+                        F.i = F.j = Sd.i = Sd.j = 0;
+                        const double t1 = lw(METHOD, Ai, pf ? Bi : Aj, F, pf ? pq.s1 : p.s1);
+                        const double t2 = lw(METHOD, pf ? Aj : Bi, Bj, F, pf ? pq.s2 : p.s2);
+                        x = lw(METHOD, t1, t2, Sd, pf ? ps : __dadd_rn(pq.s1, pq.s2));
+                    }
+                    if (c == rn) x = INF;
+                    else best.push(x, c);
+                    ws->sOut[t] = x;
+                }
+            }
+            __syncwarp();                                   // the stage has been read by every lane
+            if (lane == 0) mbar_arrive(&empty[slot]);
+            if (have) {
+                double *o = dst + n0 + lane;
+                const double *si = ws->sOut + lane;
+#pragma unroll
+                for (int u = 0; u < R3_CH / 32; ++u)
+                    if (lane + 32 * u < cn) o[32 * u] = si[32 * u];
+            }
+            __syncwarp();                                   // sOut is free again
+        }
+        if (!have) continue;
+        unsigned long long key, bound;
+        int idx;
+        warp_select(dkey(best.m1), best.i1, dkey(best.m2), best.i2, dkey(best.m3), key, idx, bound);
+        const size_t base = (size_t)rn * LC;
+        const unsigned long long last = __shfl_sync(0xffffffffu, key, KC);
+        const unsigned long long lb = bound < last ? bound : last;
+        if (lane < KC) {
+            const bool keep = idx != INT_MAX && key <= lb;
+            d.cval[base + lane] = keep ? dunkey(key) : INF;
+            d.cidx[base + lane] = keep ? idx : -1;
+        }
+        if (lane == KC) {
+            d.cval[base + KC] = dunkey(lb);
+            d.cidx[base + KC] = -1;
+        }
+        if (lane == 0) {
+            d.fresh[rn] = 1;
+            d.need[rn] = 0;
+        }
+    }
+}
+
 // closes a bulk round like the last CTA of kr_heavy does
 __global__ void kb_retire(RArgs a, int nnew) {
     RState *st = a.st;
@@ -1768,6 +2031,7 @@ struct Layout {
     int *chunk0;    // [n / RB_CH + 2]: first new column of every chunk of old columns (kb_rebuild2)
     int *rowlist;   // [n]: new rows in the order kb_rebuild2 builds them (merged rows first)
     long long cstride;  // elements between the five arrays of colp (even: every array 16-byte aligned for the bulk copies)
+    R3Lists r3;         // per-chunk column lists of kb_rebuild3
 };
 
 // second matrix buffer: a compaction halves the columns, a bulk round (>= 1/5 of the columns merge) keeps <= 4/5
@@ -1775,6 +2039,9 @@ size_t spare_elems_for(int n) {
     const size_t h = (size_t)n * 4 / 5 + 2;
     return h * h;
 }
+
+// entries of a per-chunk list array: every column once + up to 7 padding entries per chunk (multiple of 8: aligned strides)
+size_t r3_list_cap(int n) { return (((size_t)n + 8 * ((size_t)n / R3_CH + 3)) + 7) & ~(size_t)7; }
 
 bool carve(void *workspace, size_t bytes, int n, Layout &L) {
     hc::Carver ws(workspace, bytes);
@@ -1803,6 +2070,16 @@ bool carve(void *workspace, size_t bytes, int n, Layout &L) {
     L.colp = ws.take<double>((size_t)L.cstride * 5);
     L.chunk0 = ws.take<int>((size_t)n / RB_CH + 2);
     L.rowlist = ws.take<int>(n);
+    {
+        const size_t cap = r3_list_cap(n);
+        L.r3.ctab = ws.take<int4>((size_t)n / R3_CH + 3);
+        L.r3.fTO = ws.take<unsigned short>(cap);
+        L.r3.pTO = ws.take<unsigned short>(cap);
+        L.r3.fSize = ws.take<int>(cap);
+        L.r3.pW = ws.take<int>(cap);
+        L.r3.pstride = (long long)cap;
+        L.r3.pP = ws.take<double>(cap * 5);
+    }
     L.spare_elems = spare_elems_for(n);
     L.spare = ws.take<double>(L.spare_elems);
     return ws.ok();
@@ -1814,7 +2091,8 @@ extern "C" size_t hc_linkage_rounds_workspace_bytes(int32_t n) {
     if (n < 1) n = 1;
     size_t per_col = 4 * 5 + 8 + 2 * (4 * 3 + 12 * LC + 2);
     return 8192 + (size_t)n * per_col + ((size_t)n / 2 + 1) * sizeof(Pair) + 40 * 256 + spare_elems_for(n) * 8 +
-           (size_t)n * (MAX_SEGS * sizeof(Part) + 4 + 16 + 40) + 1024 + ((size_t)n / RB_CH + 2) * 4 + (size_t)n * 4 + 1024;
+           (size_t)n * (MAX_SEGS * sizeof(Part) + 4 + 16 + 40) + 1024 + ((size_t)n / RB_CH + 2) * 4 + (size_t)n * 4 + 1024 +
+           ((size_t)n / R3_CH + 3) * 16 + r3_list_cap(n) * (2 + 2 + 4 + 4 + 40) + 8 * 256;
 }
 
 // W: n x n float64 full symmetric working matrix (squared distances for ward, +inf diagonal), destroyed.
@@ -1976,17 +2254,19 @@ extern "C" int hc_linkage_rounds(double *W, int32_t n, int method, void *workspa
     long long rebuilds = 0;
     int bulk_div = 5;   // a round is a bulk round while pairs * bulk_div >= columns (HC_ROUNDS_BULK_DIV)
     if (const char *e = getenv("HC_ROUNDS_BULK_DIV")) bulk_div = atoi(e) > 0 ? atoi(e) : 5;
-    int rebuild_v = 2, rb_cfg = 0;   // rb_cfg: 0 = chunks of 256 old columns, 2 stages; 1 = 128 columns, 4 stages
+    int rebuild_v = 3, rb_cfg = 0;   // 3 = list-driven TMA kernel, 2 = TMA kernel with per-row role tests, 1 = gather kernel;
+    // rb_cfg (version 2 only): 0 = chunks of 256 old columns, 2 stages; 1 = 128 columns, 4 stages
     if (const char *e = getenv("HC_ROUNDS_REBUILD_V")) rebuild_v = atoi(e);
     if (const char *e = getenv("HC_ROUNDS_RB_CFG")) rb_cfg = atoi(e);
-    if (rebuild_v == 2) {
+    if (rebuild_v >= 2) {
         static bool attr_set[64] = {false};   // per device, once: the kernel needs more than 48 KB of shared memory
         int dev = 0;
         cudaGetDevice(&dev);
         if (dev >= 0 && dev < 64 && !attr_set[dev]) {
 #define HC_RB_ATTR(M)                                                                                                              \
     HC_CUDA_OK(cudaFuncSetAttribute(kb_rebuild2<M, 256, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)rb_smem_bytes<256, 2>())); \
-    HC_CUDA_OK(cudaFuncSetAttribute(kb_rebuild2<M, 128, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)rb_smem_bytes<128, 4>()));
+    HC_CUDA_OK(cudaFuncSetAttribute(kb_rebuild2<M, 128, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)rb_smem_bytes<128, 4>())); \
+    HC_CUDA_OK(cudaFuncSetAttribute(kb_rebuild3<M>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)R3_SMEM));
             HC_RB_ATTR(M_SINGLE) HC_RB_ATTR(M_COMPLETE) HC_RB_ATTR(M_AVERAGE) HC_RB_ATTR(M_WEIGHTED) HC_RB_ATTR(M_WARD)
 #undef HC_RB_ATTR
             attr_set[dev] = true;
@@ -2016,16 +2296,18 @@ extern "C" int hc_linkage_rounds(double *W, int32_t n, int method, void *workspa
         kb_desc<<<(nnew + 255) / 256, 256, 0, stream>>>(a.c, L.cols[cur ^ 1], a.pairs, L.oldidx, nnew, L.desc, L.colp, L.cstride);
         // TMA-staged pass where the rows can be bulk-copied (16-byte aligned rows: even stride); HC_ROUNDS_REBUILD_V=1
         // keeps the gather kernel
-        const bool tma_ok = (a.stride & 1) == 0 && (((uintptr_t)a.W) & 15) == 0 && rebuild_v == 2;
+        const bool tma_ok = (a.stride & 1) == 0 && (((uintptr_t)a.W) & 15) == 0 && rebuild_v >= 2;
         const int nch = (a.ncols + RB_CH - 1) / RB_CH;
         if (tma_ok) kb_chunks<<<2, 1024, 0, stream>>>(L.oldidx, L.desc, nnew, nch, h.ctr[0].P, L.chunk0, L.rowlist);
+        if (tma_ok && rebuild_v == 3) kb_lists<<<1, 1024, 0, stream>>>(L.oldidx, L.desc, L.colp, L.cstride, nnew, a.ncols, L.r3);
         kmark(5);
         {
             const int rg = sms * 12;  // 3 CTAs per SM (80 registers): 12.4 vs 14.2 ms in the largest round at C3
             const int rg2 = sms * 2;
             const Cols dc = L.cols[cur ^ 1];
 #define HC_REBUILD_CASE(M)                                                                                                      \
-    if (tma_ok && rb_cfg == 1) kb_rebuild2<M, 128, 4><<<rg2, (RB_WARPS + 1) * 32, rb_smem_bytes<128, 4>(), stream>>>(a, dc, L.desc, L.colp, L.cstride, L.chunk0, nch, L.rowlist, dst, stride_new, nnew); \
+    if (tma_ok && rebuild_v == 3) kb_rebuild3<M><<<rg2, (RB_WARPS + 1) * 32, R3_SMEM, stream>>>(a, dc, L.desc, L.colp, L.cstride, L.r3, L.rowlist, dst, stride_new, nnew); \
+    else if (tma_ok && rb_cfg == 1) kb_rebuild2<M, 128, 4><<<rg2, (RB_WARPS + 1) * 32, rb_smem_bytes<128, 4>(), stream>>>(a, dc, L.desc, L.colp, L.cstride, L.chunk0, nch, L.rowlist, dst, stride_new, nnew); \
     else if (tma_ok) kb_rebuild2<M, 256, 2><<<rg2, (RB_WARPS + 1) * 32, rb_smem_bytes<256, 2>(), stream>>>(a, dc, L.desc, L.colp, L.cstride, L.chunk0, nch, L.rowlist, dst, stride_new, nnew); \
     else kb_rebuild<M><<<rg, HEAVY_THREADS, 0, stream>>>(a, dc, L.desc, L.colp, L.cstride, dst, stride_new, nnew);                \
     break;
@@ -2054,7 +2336,7 @@ extern "C" int hc_linkage_rounds(double *W, int32_t n, int method, void *workspa
         a.W = dst;
         a.stride = stride_new;
         a.ncols = nnew;
-        n_launches += tma_ok ? 5 : 4;
+        n_launches += tma_ok ? (rebuild_v == 3 ? 6 : 5) : 4;
         rebuilds++;
     }
     // The rest of the run in cooperative launches of the persistent kernel (one CTA per SM, many rounds per launch);

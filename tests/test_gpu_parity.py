@@ -732,7 +732,8 @@ def test_linkage_rounds_hic_balanced_matrix(method):
 
 @pytest.mark.parametrize("env", [{}, {"HC_ROUNDS_NOCOMPACT": "1"}, {"HC_ROUNDS_BATCH": "1"}, {"HC_ROUNDS_BULK_SEGS": "32"},
                                  {"HC_ROUNDS_KTIME": "1"}, {"HC_ROUNDS_TRACE": "1"}, {"HC_ROUNDS_REBUILD": "16"},
-                                 {"HC_ROUNDS_REBUILD": "16", "HC_ROUNDS_REBUILD_V": "1"}, {"HC_ROUNDS_THIN": "0"}, {"HC_ROUNDS_COMPACT": "1/2"},
+                                 {"HC_ROUNDS_REBUILD": "16", "HC_ROUNDS_REBUILD_V": "1"}, {"HC_ROUNDS_REBUILD": "16", "HC_ROUNDS_REBUILD_V": "2"},
+                                 {"HC_ROUNDS_THIN": "0"}, {"HC_ROUNDS_COMPACT": "1/2"},
                                  {"HC_ROUNDS_REBUILD": "0"}, {"HC_ROUNDS_PERSIST": "0"}, {"HC_ROUNDS_CHAIN_MAX": "3"},
                                  {"HC_ROUNDS_PERSIST": "0", "HC_ROUNDS_KTIME": "1"}])
 def test_linkage_rounds_compaction_and_batching_do_not_change_results(env, monkeypatch):
@@ -763,7 +764,8 @@ def test_linkage_rounds_bulk_rebuild(n, method, monkeypatch):
     from hicembler_b200 import ops
     y = np.random.default_rng(2000 + n).random(n * (n - 1) // 2) + 0.05
     out = {}
-    for flag, version in (("0", "2"), ("16", "2"), ("16", "1")):   # version 2 = TMA-staged kb_rebuild2, 1 = gather kernel
+    # version 3 = list-driven TMA kernel (default), 2 = TMA kernel with per-row role tests, 1 = gather kernel
+    for flag, version in (("0", "2"), ("16", "2"), ("16", "1"), ("16", "3")):
         monkeypatch.setenv("HC_ROUNDS_REBUILD", flag)
         monkeypatch.setenv("HC_ROUNDS_REBUILD_V", version)
         W, flags = ops.expand_condensed(torch.from_numpy(y).cuda(), n, square=(method == "ward"))
@@ -771,6 +773,7 @@ def test_linkage_rounds_bulk_rebuild(n, method, monkeypatch):
         assert Z is not None and st["certified"], st
         out[flag + version] = (Z, st)
     assert np.array_equal(out["02"][0], out["162"][0]) and np.array_equal(out["02"][0], out["161"][0])
+    assert np.array_equal(out["02"][0], out["163"][0])
     out = {"0": out["02"], "16": out["162"]}
     # (which entries a candidate list keeps depends on how a row was cut into segments, so a pair can be found a round
     # earlier or later on another path: the records are identical, the round count may differ by one or two)
