@@ -310,7 +310,7 @@ def run_ours(args, cfg, rank, world, local_rank):
                                              "linkage": "kr_light+kr_heavy" if lst.get("engine") == "rounds" else "k_nnchain"}[dominant],
                      peak_source=peak_src)
     if dominant == "linkage" and lst.get("engine") == "rounds" and kernel_us and kernel_us.get("rebuild"):
-        # dominant KERNEL of the dominant stage = kb_rebuild2 (the bulk rounds: merge + compact in one pass over the
+        # dominant KERNEL of the dominant stage = kb_rebuild3 (the bulk rounds: merge + compact in one pass over the
         # matrix): all its launches of one step; achieved = algorithmic bytes of those launches (counted by the kernel's
         # own retire step) / their summed CUDA-event durations.  The chain phase (kr_chain) is latency-bound by construction and reported next to it.
         rb_ms = kernel_us["rebuild"] * 1e-3
@@ -319,10 +319,10 @@ def run_ours(args, cfg, rank, world, local_rank):
         b = 8.0 * (lst["bulk_rescan_cols"] + 2.0 * lst["bulk_build_cols"] + lst.get("bulk_new_cells", 0))
         a_ = b / (rb_ms * 1e-3) / 1e9
         launches = max(1, lst["bulk_rounds"])
-        ncu = NCU_TRAFFIC.get(args.config, {}).get("kb_rebuild2")
+        ncu = NCU_TRAFFIC.get(args.config, {}).get("kb_rebuild3")
         main_roof = {"bound": "hbm", "achieved": a_, "peak": peak, "unit": "GB/s", "frac": a_ / peak,
                      "traffic": (ncu["dram_bytes"] / ncu["launches"]) if ncu else None,
-                     "kernel": "kb_rebuild2 (TMA-staged merge + compact pass of the bulk rounds)", "launches_per_step": launches, "ms": rb_ms,
+                     "kernel": "kb_rebuild3 (TMA-staged, list-driven merge + compact pass of the bulk rounds)", "launches_per_step": launches, "ms": rb_ms,
                      "avg_launch_us": rb_ms * 1e3 / launches, "algorithmic_bytes": b,
                      "algorithmic_bytes_per_launch": b / launches, "share_of_step": rb_ms / (ms_dev / K),
                      "peak_source": peak_src, "kernel_us_per_step": kernel_us,

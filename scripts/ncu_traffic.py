@@ -24,7 +24,7 @@ for r in csv.reader(open(path)):
     scale = {"byte": 1.0, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9, "ns": 1.0, "us": 1e3, "ms": 1e6}.get(u, 1.0)
     acc[d["Metric Name"]] += v * scale
     ids.add(d["ID"])
-    k = "kb_rebuild2" if "kb_rebuild2" in name else ("kb_rebuild" if "kb_rebuild" in name else ("kr_chain" if "kr_chain" in name else "kr_heavy"))
+    k = "kb_rebuild3" if "kb_rebuild3" in name else "kb_rebuild2" if "kb_rebuild2" in name else ("kb_rebuild" if "kb_rebuild" in name else ("kr_chain" if "kr_chain" in name else "kr_heavy"))
     per.setdefault(k, {"launches": set(), "dram_bytes": 0.0, "ns": 0.0})
     per[k]["launches"].add(d["ID"])
     if d["Metric Name"].startswith("dram"):
