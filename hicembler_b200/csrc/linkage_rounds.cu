@@ -281,17 +281,33 @@ __device__ __forceinline__ void select_rows(const RArgs &a, Ctr *ct, int r_first
         bool emit = false;
         int b = -1;
         double va = 0;
-        if (r < a.ncols && __ldcg(a.c.role + r) == ROLE_FREE) {
-            b = __ldcg(a.c.cidx + (size_t)r * LC);
-            if (b > r && __ldcg(a.c.cidx + (size_t)b * LC) == r) {
-                va = __ldcg(a.c.cval + (size_t)r * LC);
-                const double vb = __ldcg(a.c.cval + (size_t)b * LC);
+        // two memory levels instead of four: everything indexed by r goes out together, then everything indexed by its
+        // nearest neighbour b (a round of the chain phase is a chain of dependent round trips, not bytes)
+        const bool in = r < a.ncols;
+        const size_t rbase = (size_t)(in ? r : 0) * LC;
+        const int role_r = in ? __ldcg(a.c.role + r) : ROLE_DEAD;
+        const int b0 = in ? __ldcg(a.c.cidx + rbase) : -1, c1r = in ? __ldcg(a.c.cidx + rbase + 1) : -1;
+        const double v0r = __ldcg(a.c.cval + rbase), v1r = __ldcg(a.c.cval + rbase + 1), vKr = __ldcg(a.c.cval + rbase + KC);
+        const int fresh_r = in ? __ldcg(a.c.fresh + r) : 0, size_r = in ? __ldcg(a.c.size + r) : 1;
+        const bool cand = role_r == ROLE_FREE && b0 > r;
+        const size_t bbase = (size_t)(cand ? b0 : 0) * LC;
+        int c0b = -1, c1b = -1, fresh_b = 0, size_b = 1;
+        double v0b = 0, v1b = 0, vKb = 0;
+        if (cand) {
+            c0b = __ldcg(a.c.cidx + bbase); c1b = __ldcg(a.c.cidx + bbase + 1);
+            v0b = __ldcg(a.c.cval + bbase); v1b = __ldcg(a.c.cval + bbase + 1); vKb = __ldcg(a.c.cval + bbase + KC);
+            fresh_b = __ldcg(a.c.fresh + b0); size_b = __ldcg(a.c.size + b0);
+        }
+        if (cand) {
+            b = b0;
+            if (c0b == r) {
+                va = v0r;
+                const double vb = v0b;
                 // second smallest entry of either row: the next candidate (exact) or, with a single candidate left,
                 // the bound of the unlisted entries (exact only straight after a scan)
-                const bool two_r = __ldcg(a.c.cidx + (size_t)r * LC + 1) >= 0, two_b = __ldcg(a.c.cidx + (size_t)b * LC + 1) >= 0;
-                const double sr = __ldcg(a.c.cval + (size_t)r * LC + (two_r ? 1 : KC)), sb = __ldcg(a.c.cval + (size_t)b * LC + (two_b ? 1 : KC));
-                const bool exact_r = two_r || __ldcg(a.c.fresh + r), exact_b = two_b || __ldcg(a.c.fresh + b);
-                const int size_r = __ldcg(a.c.size + r), size_b = __ldcg(a.c.size + b);
+                const bool two_r = c1r >= 0, two_b = c1b >= 0;
+                const double sr = two_r ? v1r : vKr, sb = two_b ? v1b : vKb;
+                const bool exact_r = two_r || fresh_r, exact_b = two_b || fresh_b;
                 // Margin 0 where both engines compute bit-identical entries: min/max updates commute exactly
                 // (single, complete), and for average/weighted every entry of a row whose cluster is still a
                 // single leaf went only through the OTHER cluster's merge tree, whose operation order is fixed
@@ -1753,61 +1769,81 @@ struct R3Lists {
     long long pstride;
 };
 
-// one block: chunk table, then the lists (a thread per chunk; chunks of a round: <= ncols / 256)
-__global__ void __launch_bounds__(1024) kb_lists(const int *oldidx, const int4 *desc, const double *colp, long long cstride, int nnew,
-                                                  int ncols, R3Lists L) {
-    __shared__ int s_total[2];
-    const int nch = (ncols + R3_CH - 1) / R3_CH;
-    // first new column of every chunk (oldidx is ascending), free / pair counts
-    for (int k = threadIdx.x; k <= nch; k += blockDim.x) {
-        const int key = k * R3_CH;
+// kb_lists in three small launches, a WARP per chunk (a first version did everything in one block with a thread per chunk:
+// 0.5 ms per round, more than a tenth of the pass it prepares):
+//   kb_lists_count: first new column of the chunk (oldidx is ascending: binary search), its free / pair column counts
+//   kb_lists_scan : padded list starts (multiples of 8 entries: 16-byte aligned slices of the 2-byte lists)
+//   kb_lists_fill : the lists, order preserving (ballot compaction), coalesced
+__global__ void __launch_bounds__(256) kb_lists_count(const int *oldidx, const int4 *desc, int nnew, int ncols, R3Lists L) {
+    const int nch = (ncols + R3_CH - 1) / R3_CH, lane = threadIdx.x & 31;
+    const int k = (int)((blockIdx.x * blockDim.x + threadIdx.x) >> 5);
+    if (k > nch) return;
+    int bound[2] = {0, 0};   // lanes 0 and 1: first new column of chunk k and of chunk k + 1
+    if (lane < 2) {
+        const int key = (k + lane) * R3_CH;
         int lo = 0, hi = nnew;
         while (lo < hi) {
             const int mid = (lo + hi) >> 1;
             if (oldidx[mid] < key) lo = mid + 1; else hi = mid;
         }
-        L.ctab[k].x = lo;
+        bound[0] = lo;
     }
-    __syncthreads();
-    for (int k = threadIdx.x; k < nch; k += blockDim.x) {
-        const int n0 = L.ctab[k].x, n1 = L.ctab[k + 1].x;
-        int np = 0;
-        for (int c = n0; c < n1; ++c) np += desc[c].y >= 0;
-        L.ctab[k].z = (n1 - n0) - np;   // free columns
-        L.ctab[k].w = np;               // (pair columns for now; replaced by the list start below)
+    const int n0 = __shfl_sync(0xffffffffu, bound[0], 0), n1 = __shfl_sync(0xffffffffu, bound[0], 1);
+    int np = 0;
+    if (k < nch)
+        for (int c = n0 + lane; c < n1; c += 32) np += desc[c].y >= 0;
+    np = (int)hc::warp_sum_u64((unsigned long long)np);
+    if (lane == 0) {
+        L.ctab[k].x = n0;
+        L.ctab[k].z = k < nch ? (n1 - n0) - np : 0;   // free columns
+        L.ctab[k].w = k < nch ? np : 0;               // (pair columns for now; replaced by the list start in kb_lists_scan)
     }
-    __syncthreads();
-    if (threadIdx.x == 0) {   // padded starts (multiples of 8 entries: 16-byte aligned slices of the 2-byte lists)
+}
+
+__global__ void kb_lists_scan(int ncols, R3Lists L) {
+    const int nch = (ncols + R3_CH - 1) / R3_CH;
+    if (threadIdx.x == 0 && blockIdx.x == 0) {
         int f = 0, q = 0;
-        for (int k = 0; k < nch; ++k) {
+        for (int k = 0; k <= nch; ++k) {
             const int nf = L.ctab[k].z, np = L.ctab[k].w;
             L.ctab[k].y = f;
             L.ctab[k].w = q;
             f += (nf + 7) & ~7;
             q += (np + 7) & ~7;
         }
-        L.ctab[nch].y = f; L.ctab[nch].z = 0; L.ctab[nch].w = q;
-        s_total[0] = f; s_total[1] = q;
     }
-    __syncthreads();
-    for (int k = threadIdx.x; k < nch; k += blockDim.x) {
-        const int4 ct = L.ctab[k];
-        const int n0 = ct.x, n1 = L.ctab[k + 1].x, o0 = k * R3_CH;
-        int f = ct.y, q = ct.w;
-        for (int c = n0; c < n1; ++c) {
-            const int4 d = desc[c];
-            const unsigned short to = (unsigned short)((c - n0) | ((d.x - o0) << 8));
-            if (d.y < 0) {
-                L.fTO[f] = to;
-                L.fSize[f] = d.z;
-                ++f;
-            } else {
-                L.pTO[q] = to;
-                L.pW[q] = d.w;
-                for (int a = 0; a < 5; ++a) L.pP[a * L.pstride + q] = colp[a * cstride + c];
-                ++q;
-            }
+}
+
+__global__ void __launch_bounds__(256) kb_lists_fill(const int4 *desc, const double *colp, long long cstride, int ncols, R3Lists L) {
+    const int nch = (ncols + R3_CH - 1) / R3_CH, lane = threadIdx.x & 31;
+    const int k = (int)((blockIdx.x * blockDim.x + threadIdx.x) >> 5);
+    if (k >= nch) return;
+    const int4 ct = L.ctab[k];
+    const int n0 = ct.x, n1 = L.ctab[k + 1].x, o0 = k * R3_CH;
+    int f = ct.y, q = ct.w;
+    for (int c0 = n0; c0 < n1; c0 += 32) {
+        const int c = c0 + lane;
+        const bool in = c < n1;
+        int4 dsc = make_int4(0, ROLE_FREE, 0, 0);
+        if (in) dsc = desc[c];
+        const bool pr = in && dsc.y >= 0, fr = in && dsc.y < 0;
+        const unsigned mp = __ballot_sync(0xffffffffu, pr), mf = __ballot_sync(0xffffffffu, fr);
+        const unsigned below = (1u << lane) - 1u;
+        const unsigned short to = (unsigned short)((c - n0) | ((dsc.x - o0) << 8));
+        if (fr) {
+            const int pos = f + __popc(mf & below);
+            L.fTO[pos] = to;
+            L.fSize[pos] = dsc.z;
         }
+        if (pr) {
+            const int pos = q + __popc(mp & below);
+            L.pTO[pos] = to;
+            L.pW[pos] = dsc.w;
+#pragma unroll
+            for (int a = 0; a < 5; ++a) L.pP[a * L.pstride + pos] = colp[a * cstride + c];
+        }
+        f += __popc(mf);
+        q += __popc(mp);
     }
 }
 
@@ -2299,7 +2335,12 @@ extern "C" int hc_linkage_rounds(double *W, int32_t n, int method, void *workspa
         const bool tma_ok = (a.stride & 1) == 0 && (((uintptr_t)a.W) & 15) == 0 && rebuild_v >= 2;
         const int nch = (a.ncols + RB_CH - 1) / RB_CH;
         if (tma_ok) kb_chunks<<<2, 1024, 0, stream>>>(L.oldidx, L.desc, nnew, nch, h.ctr[0].P, L.chunk0, L.rowlist);
-        if (tma_ok && rebuild_v == 3) kb_lists<<<1, 1024, 0, stream>>>(L.oldidx, L.desc, L.colp, L.cstride, nnew, a.ncols, L.r3);
+        if (tma_ok && rebuild_v == 3) {
+            const int nch3 = (a.ncols + R3_CH - 1) / R3_CH, lg = (nch3 + 1 + 7) / 8;   // a warp per chunk (+ the sentinel), 8 warps per CTA
+            kb_lists_count<<<lg, 256, 0, stream>>>(L.oldidx, L.desc, nnew, a.ncols, L.r3);
+            kb_lists_scan<<<1, 32, 0, stream>>>(a.ncols, L.r3);
+            kb_lists_fill<<<lg, 256, 0, stream>>>(L.desc, L.colp, L.cstride, a.ncols, L.r3);
+        }
         kmark(5);
         {
             const int rg = sms * 12;  // 3 CTAs per SM (80 registers): 12.4 vs 14.2 ms in the largest round at C3
@@ -2336,7 +2377,7 @@ extern "C" int hc_linkage_rounds(double *W, int32_t n, int method, void *workspa
         a.W = dst;
         a.stride = stride_new;
         a.ncols = nnew;
-        n_launches += tma_ok ? (rebuild_v == 3 ? 6 : 5) : 4;
+        n_launches += tma_ok ? (rebuild_v == 3 ? 8 : 5) : 4;
         rebuilds++;
     }
     // The rest of the run in cooperative launches of the persistent kernel (one CTA per SM, many rounds per launch);
