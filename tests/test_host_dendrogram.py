@@ -90,3 +90,26 @@ def test_negative_zero_and_bad_index():
     assert rc == 0 and Z[:, :2].tolist() == [[0.0, 1.0], [2.0, 3.0]]   # -0.0 == 0.0: sequence order kept
     rc, _, _ = _call(3, False, a, np.array([1, 7], np.int32), np.array([1.0, 2.0]))
     assert rc == _lib.HC_EINVAL
+
+
+@pytest.mark.parametrize("case", ["near_equal_reversed", "two_levels_shuffled", "tiny_differences"])
+def test_sort_fallback_paths(case):
+    """heights that agree in their top 33 bits: the insertion pass after the three top radix digits meets many inversions
+    and the full six-digit sort takes over; the result is still numpy's stable order"""
+    n = 6000
+    rng = np.random.default_rng(7)
+    a, b, _ = _random_merges(n, rng, 5)
+    m = n - 1
+    if case == "near_equal_reversed":
+        d = 1.0 + np.arange(m)[::-1] * 1e-13          # all inside one bucket of the top digits, reversed
+    elif case == "two_levels_shuffled":
+        d = np.where(rng.random(m) < 0.5, 2.0, 2.0 + 2e-12) + rng.integers(0, 3, m) * 1e-14
+    else:
+        d = 5.0 + rng.random(m) * 1e-10
+    d = np.ascontiguousarray(d, dtype=np.float64)
+    # (heights out of merge order make no dendrogram, but the tail only sorts and labels: compare with the restatement)
+    rc, Z, near = _call(n, False, a, b, d)
+    want, _ = _reference(n, False, a, b, d)
+    assert rc == 0
+    assert np.array_equal(Z[:, 2], want[:, 2])
+    assert np.array_equal(Z, want)
