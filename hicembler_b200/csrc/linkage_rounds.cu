@@ -23,8 +23,13 @@
 //   kr_heavy  : new row of every merged cluster from its two old rows (pair x pair entries by a
 //               fixed "lower j first" rule so both mirror entries get bit-identical values), exact
 //               rescans of rows whose cache could not be kept; the last CTA retires the pairs.
-// The host syncs once per batch of rounds and compacts the matrix (order preserving) whenever half of
-// the columns are dead, so rows stay short in the long tail of small rounds.
+// Round 2 structure of a run (hc_linkage_rounds):
+//   initial scan (kr_light + kr_heavy, every row's candidate list)
+//   bulk rounds, while a fifth of the columns merge at once: kr_select, then ONE pass that merges and compacts
+//     (kb_rebuild3: old rows and per-chunk column lists staged by the TMA unit; kb_rebuild2 / kb_rebuild behind switches)
+//   the rest inside kr_chain, a persistent cooperative kernel (select / build + light / rescan behind grid barriers); thin
+//     rounds (1-4 pairs) take latency-optimised paths (shared-memory staged builds and rescans, eight lanes per light row)
+//   the host comes back for a compaction (order preserving) whenever a quarter of the stored columns are dead.
 #include <limits.h>
 #include <math.h>
 #include <stdlib.h>
